@@ -1,0 +1,204 @@
+"""ctypes bindings for the two oracle legs (TEST INFRASTRUCTURE ONLY).
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference``
+legs may import this module, and only as the checker / reported CPU baseline.  The product package
+(``robotic-mpc_b200``) never imports anything under ``oracle/``.
+
+Legs
+----
+``ref``   oracle/_ref/librmpc_ref.so : the UNMODIFIED acados + HPIPM + BLASFEO of the reference,
+          compiled by oracle/ref.mk, driven by oracle/ref_driver.c (needs /root/reference to BUILD,
+          not to run -- the built .so travels to the GPU box).
+``port``  oracle/_build/librmpc_oracle.so : plain-C restatement of the same algorithm
+          (oracle/rmpc_oracle.c), buildable anywhere with gcc.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+REF_SO = HERE / "_ref" / "librmpc_ref.so"
+PORT_SO = HERE / "_build" / "librmpc_oracle.so"
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int)
+
+
+class Ur10Params(C.Structure):
+    _fields_ = [("surf", C.c_double * 6), ("wcv", C.c_double * 6), ("Ts", C.c_double),
+                ("t_ee", C.c_double * 3)]
+
+
+class RmpcProblem(C.Structure):
+    _fields_ = [("N", C.c_int), ("solver_type", C.c_int), ("max_iter", C.c_int),
+                ("qp_iter_max", C.c_int), ("tol", C.c_double * 4), ("qp_tol", C.c_double),
+                ("dt", C.c_double), ("w_task", C.c_double * 5), ("w_u", C.c_double),
+                ("w_qddot", C.c_double), ("px_ref", C.c_double), ("vy_ref", C.c_double),
+                ("q_min", C.c_double * 6), ("q_max", C.c_double * 6), ("u_min", C.c_double * 6),
+                ("u_max", C.c_double * 6), ("model", Ur10Params)]
+
+
+class RmpcTrace(C.Structure):
+    _fields_ = [("z", c_dp), ("u", c_dp), ("status", c_ip), ("sqp_iter", c_ip), ("qp_iter", c_ip),
+                ("res", c_dp), ("cost", c_dp), ("time_tot", c_dp), ("xtraj", c_dp), ("utraj", c_dp),
+                ("pitraj", c_dp)]
+
+
+SQP, SQP_RTI = 0, 1
+README_Q0 = np.array([np.pi / 4, -np.pi / 3, np.pi / 4, -np.pi / 2, -np.pi / 2, 0.0])
+README_QD0 = np.array([1.0, 2.0, 1.0, 0.0, 0.0, 0.0])
+
+
+def make_problem(N=20, solver_type=SQP_RTI, dt=0.01, surf=None, wcv=200.0, w_u=0.01, w_qddot=0.02,
+                 px_ref=0.40, vy_ref=0.05, q_min=None, q_max=None, qdot_min=None, qdot_max=None,
+                 max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8) -> RmpcProblem:
+    """Problem with the reference defaults unless overridden."""
+    p = RmpcProblem()
+    p.N, p.solver_type, p.max_iter, p.qp_iter_max = int(N), int(solver_type), int(max_iter), int(qp_iter_max)
+    p.tol[:] = [tol] * 4
+    p.qp_tol = qp_tol
+    p.dt = dt
+    p.w_task[:] = [50.0] * 5
+    p.w_u, p.w_qddot, p.px_ref, p.vy_ref = w_u, w_qddot, px_ref, vy_ref
+    qdm = np.array([2.16, 2.16, np.pi, 3.20, 3.20, 3.20])
+    p.q_min[:] = list(np.full(6, -2 * np.pi) if q_min is None else np.asarray(q_min, float))
+    p.q_max[:] = list(np.full(6, 2 * np.pi) if q_max is None else np.asarray(q_max, float))
+    p.u_min[:] = list(-qdm if qdot_min is None else np.asarray(qdot_min, float))
+    p.u_max[:] = list(qdm if qdot_max is None else np.asarray(qdot_max, float))
+    s = [-0.15, 0.15, -0.01, 0.01, 0.01, 0.0] if surf is None else list(np.asarray(surf, float))
+    p.model.surf[:] = s
+    p.model.wcv[:] = list(np.broadcast_to(np.asarray(wcv, float), (6,)))
+    p.model.Ts = dt
+    p.model.t_ee[:] = [0.0, 0.0, 0.1]
+    return p
+
+
+def build(which=("port", "ref"), quiet=True) -> dict:
+    """Compile the oracle legs. The ref leg needs /root/reference; absent => uses the prebuilt .so."""
+    out = {}
+    kw = dict(stdout=subprocess.DEVNULL) if quiet else {}
+    if "port" in which:
+        subprocess.run(["make", "-s", "-C", str(HERE), "port"], check=True, **kw)
+        out["port"] = PORT_SO.exists()
+    if "ref" in which:
+        ref_root = Path(os.environ.get("RMPC_REFERENCE", "/root/reference"))
+        if (ref_root / "acados" / "acados").is_dir():
+            subprocess.run(["make", "-s", "-C", str(HERE), "-f", "ref.mk", f"REF={ref_root}",
+                            f"-j{os.cpu_count() or 4}", "ref-driver"], check=True, **kw)
+        out["ref"] = REF_SO.exists()
+    return out
+
+
+def _np(a, dtype=np.float64):
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dp)
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_ip)
+
+
+class _Leg:
+    prefix = ""
+    so = None
+
+    def __init__(self):
+        if not self.so.exists():
+            raise FileNotFoundError(f"{self.so} not built (python -c 'import oracle.pyoracle as o; o.build()')")
+        self.lib = C.CDLL(str(self.so))
+        f = getattr(self.lib, f"{self.prefix}_closed_loop")
+        f.restype = C.c_int
+        f.argtypes = [C.POINTER(RmpcProblem), c_dp, C.c_int, C.POINTER(RmpcTrace)]
+        self._closed_loop = f
+
+    def closed_loop(self, prob: RmpcProblem, z0, nsteps: int, full_traj=False) -> dict:
+        N = prob.N
+        z0 = _np(z0)
+        o = dict(z=np.zeros((nsteps + 1, 12)), u=np.zeros((nsteps, 6)),
+                 status=np.zeros(nsteps, np.int32), sqp_iter=np.zeros(nsteps, np.int32),
+                 qp_iter=np.zeros(nsteps, np.int32), res=np.zeros((nsteps, 4)), cost=np.zeros(nsteps),
+                 time_tot=np.zeros(nsteps))
+        if full_traj:
+            o.update(xtraj=np.zeros((nsteps, N + 1, 12)), utraj=np.zeros((nsteps, N, 6)),
+                     pitraj=np.zeros((nsteps, N, 12)))
+        tr = RmpcTrace()
+        for k, v in o.items():
+            setattr(tr, k, _ip(v) if v.dtype == np.int32 else _dp(v))
+        nfail = self._closed_loop(C.byref(prob), _dp(z0), int(nsteps), C.byref(tr))
+        if nfail < 0:
+            raise RuntimeError(f"{self.prefix}_closed_loop failed to create the solver")
+        o["nfail"] = nfail
+        return o
+
+
+class RefLeg(_Leg):
+    """The reference's own compiled acados/HPIPM/BLASFEO."""
+    prefix = "rmpc_ref"
+    so = REF_SO
+
+
+class PortLeg(_Leg):
+    """Plain-C restatement."""
+    prefix = "rmpc_oracle"
+    so = PORT_SO
+
+
+# ------------------------------------------------------------------ model functions (libur10 inside either .so)
+class Model:
+    def __init__(self, lib: C.CDLL):
+        self.lib = lib
+
+    def fk(self, q):
+        q = _np(q)
+        pj, aj, R, pe = np.zeros((6, 3)), np.zeros((6, 3)), np.zeros(9), np.zeros(3)
+        self.lib.ur10_fk(_dp(q), _dp(pj), _dp(aj), _dp(R), _dp(pe))
+        return pj, aj, R.reshape(3, 3), pe
+
+    def jacobian_world(self, q):
+        J = np.zeros(36)
+        self.lib.ur10_jacobian_world(_dp(_np(q)), _dp(J))
+        return J.reshape(6, 6)
+
+    def cost_y(self, P: Ur10Params, x, u):
+        y = np.zeros(18)
+        self.lib.ur10_cost_y(C.byref(P), _dp(_np(x)), _dp(_np(u)), _dp(y))
+        return y
+
+    def cost_y_jac(self, P: Ur10Params, x, u):
+        y, Jt = np.zeros(18), np.zeros(324)
+        self.lib.ur10_cost_y_jac(C.byref(P), _dp(_np(x)), _dp(_np(u)), _dp(y), _dp(Jt))
+        return y, Jt.reshape(18, 18).T.copy()  # [row v, col y]
+
+    def dyn(self, P: Ur10Params, x, u):
+        xn = np.zeros(12)
+        self.lib.ur10_dyn(C.byref(P), _dp(_np(x)), _dp(_np(u)), _dp(xn))
+        return xn
+
+    def BAbt(self, P: Ur10Params):
+        M = np.zeros(18 * 12)
+        self.lib.ur10_dyn_jac_BAbt(C.byref(P), _dp(M))
+        return M.reshape(12, 18).T.copy()  # (nu+nx) x nx
+
+    def plant_rk4(self, wcv, dt, z, u):
+        zn = np.zeros(12)
+        self.lib.ur10_plant_rk4(_dp(_np(wcv)), C.c_double(dt), _dp(_np(z)), _dp(_np(u)), _dp(zn))
+        return zn
+
+    def plant_logs(self, z):
+        pose, rpy, tw = np.zeros(12), np.zeros(3), np.zeros(6)
+        self.lib.ur10_plant_logs(_dp(_np(z)), _dp(pose), _dp(rpy), _dp(tw))
+        return pose, rpy, tw
+
+    def tracking_errors(self, P: Ur10Params, pose, twist, px_ref, vy_ref):
+        e, ptz = np.zeros(5), C.c_double(0)
+        self.lib.ur10_tracking_errors(C.byref(P), _dp(_np(pose)), _dp(_np(twist)), C.c_double(px_ref),
+                                      C.c_double(vy_ref), _dp(e), C.byref(ptz))
+        return e, ptz.value

@@ -26,6 +26,11 @@
 #include "blasfeo_d_aux.h"
 #include "blasfeo_d_aux_ext_dep.h"
 
+#include "acados/ocp_nlp/ocp_nlp_common.h"
+#include "acados/ocp_qp/ocp_qp_hpipm.h"
+#include "acados/ocp_qp/ocp_qp_xcond_solver.h"
+#include "hpipm_d_ocp_qp_ipm.h"
+
 #include "rmpc_problem.h"
 
 #define NX 12
@@ -556,4 +561,51 @@ int rmpc_ref_closed_loop(const rmpc_problem *prob, const double z0[12], int nste
     }
     rmpc_ref_destroy(c);
     return nfail;
+}
+
+/* Debug/parity hook: HPIPM's per-iteration statistics table of the LAST QP solved
+ * (H/ocp_qp/x_ocp_qp_ipm.c:2951-2960; columns: alpha_aff mu_aff sigma alpha_prim alpha_dual mu res_stat res_eq
+ * res_ineq res_comp dual_gap obj lq_fact itref_pred itref_corr lin_res x4).  Returns the iteration count. */
+int rmpc_ref_last_qp_stat(rmpc_ref *c, double *stat_out, int max_rows, int *stat_m_out)
+{
+    ocp_nlp_memory *nlp_mem = NULL;
+    ocp_nlp_get(c->solver, "nlp_mem", &nlp_mem);
+    ocp_qp_xcond_solver_memory *xm = nlp_mem->qp_solver_mem;
+    ocp_qp_hpipm_memory *hm = xm->solver_memory;
+    struct d_ocp_qp_ipm_ws *ws = hm->hpipm_workspace;
+    int stat_m = ws->stat_m, iter = ws->iter;
+    if (stat_m_out) *stat_m_out = stat_m;
+    int rows = iter + 1 < max_rows ? iter + 1 : max_rows;
+    if (stat_out) memcpy(stat_out, ws->stat, sizeof(double) * (size_t) rows * stat_m);
+    return iter;
+}
+
+/* Debug/parity hook: count, over a closed loop, how many IPM iterations fell back to the LQ factorisation
+ * (stat column 12) and the max number of corrector refinement steps (column 14). */
+int rmpc_ref_closed_loop_lq_count(const rmpc_problem *prob, const double z0[12], int nsteps, int *n_ipm_iter,
+                                  int *n_lq, int *max_itref)
+{
+    rmpc_ref *c = rmpc_ref_create(prob, z0);
+    if (!c) return -1;
+    double z[NX], zn[NX], u0[NU];
+    memcpy(z, z0, sizeof(z));
+    double *stat = malloc(sizeof(double) * 64 * 32);
+    *n_ipm_iter = 0; *n_lq = 0; *max_itref = 0;
+    for (int k = 0; k < nsteps; k++)
+    {
+        rmpc_ref_step(c, z, u0, NULL, NULL, NULL, NULL, NULL);
+        int sm = 0;
+        int it = rmpc_ref_last_qp_stat(c, stat, 64, &sm);
+        for (int i = 1; i <= it && i < 64; i++)
+        {
+            (*n_ipm_iter)++;
+            if (stat[sm * i + 12] != 0.0) (*n_lq)++;
+            if ((int) stat[sm * i + 14] > *max_itref) *max_itref = (int) stat[sm * i + 14];
+        }
+        ur10_plant_rk4(prob->model.wcv, prob->dt, z, u0, zn);
+        memcpy(z, zn, sizeof(z));
+    }
+    free(stat);
+    rmpc_ref_destroy(c);
+    return 0;
 }

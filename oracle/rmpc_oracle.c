@@ -266,7 +266,7 @@ static void qp_reduce(rmpc_oracle *s)
     const int N = s->N;
     memcpy(s->rRSQ, s->RSQ, sizeof(double) * 324 * (N + 1));
     memcpy(s->rrqz, s->rqz, sizeof(double) * NV * (N + 1));
-    memcpy(s->rb, s->b, sizeof(double) * NX * N);
+    memcpy(s->rb, s->b, sizeof(double) * NX * (size_t) N);
     for (int i = 1; i < N; i++) memcpy(s->rd + 24 * i, s->d + 36 * i, 24 * sizeof(double));
     /* stage 0: fixed x = d_lb (= x0 - x_nlp0) */
     double v[NV];
@@ -714,6 +714,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
         ipm_res(s, 1, s->res_g, s->res_b, s->res_d, s->res_m, s->dux, s->dpi, s->dlam, s->dt, s->slam, s->st, s->ig, s->ib,
                 s->id, s->im);
         ipm_res_norm(s, s->ig, s->ib, s->id, s->im, inrm);
+        if (getenv("RMPC_ORACLE_DEBUG") && kk == 0) fprintf(stderr, "port st1: res_g6 %.6e dux6 %.6e dpi1_0 %.6e dpi0_0 %.6e dlam_lb %.6e dlam_ub %.6e\n", s->res_g[NV+6], s->dux[NV+6], s->dpi[NX], s->dpi[0], s->dlam[24+6], s->dlam[24+18]);
         if ((inrm[0] == 0.0 && isnan(s->ig[0])) || any_gt(inrm, 1e-5)) s->n_lq_needed++;
         double alpha_prim, alpha_dual;
         ipm_alpha(s, &alpha, &alpha_prim, &alpha_dual);
@@ -801,7 +802,7 @@ static void qp_restore(rmpc_oracle *s)
         memcpy(s->qlam + 36 * i, s->slam + 24 * i, 24 * sizeof(double));
         memcpy(s->qt + 36 * i, s->st + 24 * i, 24 * sizeof(double));
     }
-    memcpy(s->qpi, s->spi, sizeof(double) * NX * N);
+    memcpy(s->qpi, s->spi, sizeof(double) * NX * (size_t) N);
     /* stage 0 */
     double *v = s->qux, *lam = s->qlam, *t = s->qt;
     for (int j = 0; j < NU; j++) v[j] = s->sux[j];
@@ -851,7 +852,7 @@ static int solve_qp(rmpc_oracle *s, int init_from_qp_out)
     if (init_from_qp_out)
     {
         /* initialize_next_xcond_qp_from_qp_out: d_ocp_qp_reduce_eq_dof_sol + part_cond_qp_cond_sol (copy) */
-        memcpy(s->spi, s->qpi, sizeof(double) * NX * N);
+        memcpy(s->spi, s->qpi, sizeof(double) * NX * (size_t) N);
         for (int i = 1; i <= N; i++)
         {
             memcpy(s->slam + 24 * i, s->qlam + 36 * i, 24 * sizeof(double));
@@ -953,7 +954,7 @@ static void init_qp_from_nlp(rmpc_oracle *s)
     const int N = s->N;
     memset(s->qux, 0, sizeof(double) * NV * (N + 1));
     memcpy(s->qlam, s->lam, sizeof(double) * 36 * (N + 1));
-    memcpy(s->qpi, s->pi, sizeof(double) * NX * N);
+    memcpy(s->qpi, s->pi, sizeof(double) * NX * (size_t) N);
     for (int i = 0; i <= N; i++)
         for (int j = 0; j < 2 * nb_full(s, i); j++) s->qt[36 * i + j] = -s->d[36 * i + j];
 }

@@ -1,0 +1,114 @@
+/* robotic-mpc_b200/csrc/rmpc_types.h -- plain-data structures shared by the host side of the C-ABI and the kernels.
+ *
+ * Layout of a batch in HBM ("instance-major"): every array below is [B][...] with one contiguous chunk per
+ * instance; ONE WARP owns one instance for the whole closed loop, so inside a chunk the fastest index is the one
+ * the 32 lanes sweep (component within a stage block for the Riccati sweeps, flat element index for the
+ * element-wise interior-point updates).  Stage blocks use fixed strides:
+ *     NV = 18 ([u(6); x(12)], stage N keeps the same slot layout with u unused)
+ *     NX = 12,  NB = 24 ([lower(12); upper(12)] over [u(6); q(6)], stage 0 uses only the u slots in the QP)
+ *     LS = 192 (packed lower-trapezoidal 19x18 Riccati factor: 189 doubles, padded)
+ */
+#ifndef RMPC_TYPES_H
+#define RMPC_TYPES_H
+
+#define RMPC_NX 12
+#define RMPC_NU 6
+#define RMPC_NV 18
+#define RMPC_NB 24
+#define RMPC_LS 192
+#define RMPC_NJ 60  /* 5 task rows x 12 state columns of the scaled task Jacobian */
+
+#define RMPC_SQP 0
+#define RMPC_SQP_RTI 1
+
+/* per-instance parameter block (doubles) */
+enum
+{
+    RP_SURF = 0,    /* a b c d e f                                   R/surface.py:14-30 */
+    RP_A12 = 6,     /* (1-a22)/w                                     R/prediction_model.py:87-115 */
+    RP_A22 = 12,    /* exp(-w Ts) */
+    RP_B1 = 18,     /* Ts - a12 */
+    RP_B2 = 24,     /* 1 - a22 */
+    RP_WCV = 30,    /* plant bandwidths                              R/simulation_model.py:79-83 */
+    RP_WU = 36,     /* w_u                                           R/trajectory_optimizer.py:148 */
+    RP_WQDD = 37,   /* w_qddot                                       R/trajectory_optimizer.py:150 */
+    RP_PXREF = 38,
+    RP_VYREF = 39,
+    RP_WTASK = 40,  /* 5 task weights (50 each)                      R/trajectory_optimizer.py:44-48 */
+    RP_UMIN = 45,
+    RP_UMAX = 51,
+    RP_QMIN = 57,
+    RP_QMAX = 63,
+    RP_TEE = 69,    /* task-frame offset in the EE frame             R/prediction_model.py:9 */
+    RP_COUNT = 72
+};
+
+/* per-step log record (doubles) written by the closed loop */
+enum
+{
+    RL_STATUS = 0, RL_SQP_ITER = 1, RL_QP_ITER = 2, RL_COST = 3,
+    RL_RES = 4,     /* 4: stat eq ineq comp (zeros for SQP_RTI, like the reference) */
+    RL_ALPHA = 8,   /* accepted line-search step of the last SQP iteration */
+    RL_QP_STATUS = 9,
+    RL_COUNT = 10
+};
+
+/* summary row per instance accumulated on device (R/simulator.py:347-390 metrics + solver_stats) */
+enum
+{
+    RS_SSE = 0,      /* 5: sum e_k^2 over the Nsim+1 logged samples */
+    RS_ITSE = 5,     /* 5: sum t * e_k^2 * dt */
+    RS_NFAIL = 10,   /* steps with status != 0 */
+    RS_SQP_ITERS = 11,
+    RS_QP_ITERS = 12,
+    RS_MAX_RES = 13, /* 4: max over steps of each KKT residual */
+    RS_COST_LAST = 17,
+    RS_NSAMPLES = 18,
+    RS_COUNT = 20
+};
+
+typedef struct
+{
+    double Rfix[7][9]; /* fixed rotation of joint j's origin (j = 6: ee_fixed_joint), row-major */
+    double pfix[7][3]; /* fixed translation */
+} RmpcChain;
+
+typedef struct
+{
+    int B, N;
+    int solver_type;   /* RMPC_SQP | RMPC_SQP_RTI */
+    int max_iter;      /* nlp_solver_max_iter */
+    int qp_iter_max;   /* qp_solver_iter_max */
+    double tol[4];     /* nlp tolerances stat eq ineq comp */
+    double qp_tol;     /* all four HPIPM tolerances */
+    double dt;         /* shooting interval = Ts = cost scaling */
+    double plant_dt;   /* plant RK4 step (= dt in the reference) */
+} RmpcDims;
+
+/* device pointers; all arrays [B][stride] doubles unless noted */
+typedef struct
+{
+    const double *par; /* [B][RP_COUNT] */
+    /* NLP iterate + merit weights (persist across steps) */
+    double *ux, *pi, *lam, *lamx0, *wpi, *wlam, *wlamx0;
+    double *z;         /* [B][12] plant state */
+    int *flags;        /* [B][4]: first_call, qp_warm2_pending, n_lq_needed, reserved */
+    /* linearisation / QP data */
+    double *Jc, *rqz, *b, *d, *dx0, *g0u;
+    /* IPM */
+    double *sux, *spi, *slam, *st, *qlamx0;
+    double *dux, *dpi, *dlam, *dt_;
+    double *res_g, *res_b, *res_d, *res_m, *res_m_bkp;
+    double *pvec, *Pb, *L;
+    double *ig, *ib, *id, *im, *iux, *ipi, *ilam, *it;
+    double *tux;
+    /* logs (may be null) */
+    double *zlog;      /* [B][nlog+1][12] */
+    double *ulog;      /* [B][nlog][6] */
+    double *slog;      /* [B][nlog][RL_COUNT] */
+    double *summary;   /* [B][RS_COUNT] */
+    int nlog;          /* capacity of the logs in steps */
+    int step0;         /* index of the first step of this launch */
+} RmpcWs;
+
+#endif

@@ -1,0 +1,68 @@
+/* tests/simt_emu/emu_driver.cpp -- TEST HARNESS ONLY: runs the device code of robotic-mpc_b200/csrc/rmpc_device.cuh
+ * on the host warp emulator (simt_emu.h), one emulated warp per instance, so tests/ can check the kernels' logic
+ * against the oracle without a GPU.  Not part of the product library. */
+#define RMPC_EMU 1
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "rmpc_device.cuh"
+#include "rmpc_layout.h"
+
+namespace
+{
+struct Job
+{
+    const RmpcChain *ch;
+    const RmpcDims *D;
+    const RmpcWs *W;
+    long inst;
+    int nsteps;
+    WarpSmem *sm;
+};
+void body(void *p, int)
+{
+    Job *j = (Job *) p;
+    closed_loop_warp(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
+}
+}  // namespace
+
+extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const double *z0, int nsteps, double *zlog,
+                                    double *ulog, double *slog, double *summary, int *flags_out, unsigned long long seed)
+{
+    const long B = D->B, S = D->N + 1;
+    RmpcChain ch;
+    rmpc_chain_init(&ch);
+    RmpcWs W;
+    memset(&W, 0, sizeof(W));
+    std::vector<double *> owned;
+#define X(name, n)                                                  \
+    W.name = (double *) calloc((size_t) B * (size_t) (n), sizeof(double)); \
+    owned.push_back(W.name);
+    RMPC_WS_ARRAYS(X, S)
+#undef X
+    W.par = par;
+    W.flags = (int *) calloc((size_t) B * 4, sizeof(int));
+    W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
+    W.nlog = nsteps; W.step0 = 0;
+    for (long i = 0; i < B; i++)
+    {
+        memcpy(W.z + i * NX, z0 + i * NX, NX * sizeof(double));
+        if (zlog) memcpy(zlog + i * (nsteps + 1) * NX, z0 + i * NX, NX * sizeof(double));
+        /* initial guess x_k = x0, u_k = 0 (T/c_templates_tera/acados_solver.in.c:2744-2777) */
+        for (long k = 0; k < S; k++) memcpy(W.ux + (i * S + k) * NV + 6, z0 + i * NX, NX * sizeof(double));
+        W.flags[i * 4 + 0] = 1;
+        W.flags[i * 4 + 1] = 1;
+    }
+    WarpSmem sm;
+    for (long i = 0; i < B; i++)
+    {
+        memset(&sm, 0, sizeof(sm));
+        Job j{&ch, D, &W, i, nsteps, &sm};
+        simt_emu::run_warp(body, &j, seed);
+    }
+    if (flags_out) memcpy(flags_out, W.flags, (size_t) B * 4 * sizeof(int));
+    for (double *p : owned) free(p);
+    free(W.flags);
+    return 0;
+}

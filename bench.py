@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path: MPC steps/s of the batched UR10 N=100 SQP_RTI closed loop.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--batch B] [--horizon N]
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): per GPU, 4096 problem instances
+(random quadratic surfaces, perturbed initial states; SURVEY.md 8(d) distributions, seed 42 + 2), UR10, N = 100,
+SQP_RTI + HPIPM-equivalent interior point, dt = 0.01, each instance run in closed loop from its initial state.
+One bench "step" = one closed-loop MPC step (solve + plant RK4 + metrics) of every instance of the batch = one
+launch of ``rmpc_closed_loop_kernel``; the default K = 600 is the whole closed-loop job of the config.
+The W warm-up steps run first, then the batch is reset to its initial state so that the timed region is the first K
+steps of the closed loop (transient included), not a cheaper steady-state tail.
+
+Contract: rank 0 prints ONE JSON line (see the repository instructions): ``value`` = instances * K / device time (inputs
+resident in HBM, CUDA events on the launching stream, max over ranks), ``e2e`` = the same job through the
+host-buffer C-ABI call ``rmpc_run_host`` (H2D of parameters and initial states, reset, K steps, D2H of the summaries)
+timed on the host, ``roofline`` / ``cpu_baseline`` as described in DESIGN.md.
+``--impl reference`` times the reference's own compiled acados/HPIPM/BLASFEO (oracle/_ref, built from
+/root/reference by oracle/ref.mk; falls back to the oracle port if that library did not travel) on all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "MPC steps/sec (UR10, N=100, SQP_RTI) batched; p99 per-step solve latency"
+UNIT = "mpc_steps/s"
+
+
+# ------------------------------------------------------------------------------------------------ workload
+def make_workload(B, seed):
+    """SURVEY.md 8(d) synthetic inputs: surfaces ~ N(mean, 0.01^2), q0/qd0 = README values + uniform noise."""
+    rng = np.random.default_rng(seed)
+    mean = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0])
+    surf = mean + 0.01 * rng.standard_normal((B, 6))
+    q0 = np.array([math.pi / 4, -math.pi / 3, math.pi / 4, -math.pi / 2, -math.pi / 2, 0.0])
+    qd0 = np.array([1.0, 2.0, 1.0, 0.0, 0.0, 0.0])
+    z0 = np.concatenate([q0 + rng.uniform(-0.05, 0.05, (B, 6)), qd0 + rng.uniform(-0.1, 0.1, (B, 6))], axis=1)
+    return surf, np.ascontiguousarray(z0)
+
+
+def algorithmic_bytes_per_mpc_step(N):
+    """iterate in/out + x0 in + u0 out + per-instance params."""
+    return 2 * 8 * ((N + 1) * 18 + N * 12 + 2 * 2 * (6 + 12 * (N - 1))) + 8 * (12 + 6 + 6)
+
+
+def algorithmic_flops_per_mpc_step(N, n_ipm, n_fun=2.0):
+    """dense counts of the reference algorithm (not reduced for the sparsity of A, B)."""
+    return N * 9128.0 + n_ipm * N * 17300.0 + n_fun * N * 2100.0
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,power.draw"
+
+    def __init__(self, index):
+        self.proc = None
+        self.lines = []
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 6:
+                continue
+            try:
+                sm.append(float(p[0]))
+                smax = float(p[1])
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if p[2 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+def _cpu_worker(args):
+    """One single-threaded process: closed loops of `warm + steps` MPC steps for its instances; returns the wall
+    time of the timed steps (per-step timing inside the C closed loop is acados' own time_tot for the ref leg)."""
+    kind, N, surfs, z0s, warm, steps = args
+    from oracle import pyoracle as o
+    import ctypes as C
+
+    leg = o.RefLeg() if kind == "reference" else o.PortLeg()
+    pre = "rmpc_ref" if kind == "reference" else "rmpc_oracle"
+    lib = leg.lib
+    create, step, destroy = getattr(lib, pre + "_create"), getattr(lib, pre + "_step"), getattr(lib, pre + "_destroy")
+    create.restype = C.c_void_p
+    destroy.argtypes = [C.c_void_p]
+    plant = lib.ur10_plant_rk4
+    dp = o.c_dp
+    elapsed, nsteps, lat = 0.0, 0, []
+    for surf, z0 in zip(surfs, z0s):
+        p = o.make_problem(N=N, solver_type=o.SQP_RTI, surf=surf)
+        z = np.array(z0, dtype=np.float64)
+        zn, u = np.zeros(12), np.zeros(6)
+        wcv = np.full(6, 200.0)
+        cap = C.c_void_p(create(C.byref(p), z.ctypes.data_as(dp)))
+        for k in range(warm + steps):
+            t0 = time.perf_counter()
+            if kind == "reference":
+                step(cap, z.ctypes.data_as(dp), u.ctypes.data_as(dp), None, None, None, None, None)
+            else:
+                step(cap, z.ctypes.data_as(dp), u.ctypes.data_as(dp), None, None, None, None)
+            plant(wcv.ctypes.data_as(dp), C.c_double(0.01), z.ctypes.data_as(dp), u.ctypes.data_as(dp), zn.ctypes.data_as(dp))
+            z[:] = zn
+            t1 = time.perf_counter()
+            if k >= warm:
+                elapsed += t1 - t0
+                nsteps += 1
+                lat.append(t1 - t0)
+        destroy(cap)
+    return elapsed, nsteps, lat
+
+
+def cpu_leg(N, warm, steps, inst_per_core=1, seed=44):
+    """Reference CPU path, one single-threaded process per host core."""
+    from multiprocessing import get_context
+    from oracle import pyoracle as o
+
+    kind = "reference" if o.REF_SO.exists() else "port"
+    if kind == "port" and not o.PORT_SO.exists():
+        o.build(which=("port",))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    S = cores * inst_per_core
+    surf, z0 = make_workload(S, seed)
+    jobs = [(kind, N, surf[c::cores], z0[c::cores], warm, steps) for c in range(cores)]
+    with get_context("fork").Pool(cores) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    tmax = max(r[0] for r in res)
+    tot = sum(r[1] for r in res)
+    lat = np.concatenate([np.asarray(r[2]) for r in res])
+    return {"value": tot / tmax, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{S} instances x {steps} closed-loop steps (after {warm} warm-up steps), N={N}, one "
+                      f"single-threaded process per core, slowest process {tmax:.2f} s",
+            "p50_ms": float(np.percentile(lat, 50) * 1e3), "p99_ms": float(np.percentile(lat, 99) * 1e3)}, tmax, tot
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    warm, steps = args.warmup, args.steps
+    cb, tmax, tot = cpu_leg(args.horizon, warm, steps, inst_per_core=1)
+    line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": warm, "ms_per_step": 1e3 * tmax / steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"UR10 N={args.horizon} SQP_RTI closed loop, {cb['cores']} instances "
+                                   f"(one per host core) x {steps} steps; a step = one MPC step of every instance"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def fp64_peak_tflops(torch, dev):
+    """Measured FP64 throughput of this GPU: cuBLAS DGEMM 4096^3 (library call, used only as the roofline denominator)."""
+    n = 4096
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    torch.matmul(a, b)
+    torch.cuda.synchronize(dev)
+    best = 1e9
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        e1.synchronize()
+        best = min(best, e0.elapsed_time(e1) * 1e-3)
+    return 2.0 * n ** 3 / best / 1e12
+
+
+def run_gpu(args):
+    import torch
+    import robotic_mpc_b200 as rm
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    B, N, K, Wm = args.batch, args.horizon, args.steps, args.warmup
+    surf, z0 = make_workload(B, 44 + rank)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=0, device=local)
+    par_d = torch.as_tensor(par, device=dev)
+    z0_d = torch.as_tensor(z0, device=dev)
+    eng.set_params(par_d)
+    eng.set_state(z0_d)
+    eng.reset()
+    for _ in range(Wm):
+        eng.closed_loop(1)
+    eng.set_state(z0_d)
+    eng.reset()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    launches0 = eng.launch_count
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    torch.cuda.synchronize(dev)
+    ev[0].record()
+    for k in range(K):
+        eng.closed_loop(1)
+        ev[k + 1].record()
+    torch.cuda.synchronize(dev)
+    launches = eng.launch_count - launches0
+    t_ms = ev[0].elapsed_time(ev[K])
+    per_step = np.array([ev[k].elapsed_time(ev[k + 1]) for k in range(K)])
+    if world > 1:
+        dist.barrier()
+        t = torch.tensor([t_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t_ms = float(t.item())
+    clocks = sampler.stop() if sampler else None
+    summ = eng.get("summary")
+    gather_ms = None
+    if world > 1:
+        # the only collective of the path: gather the per-instance result summaries (NCCL over NVLink)
+        out = torch.empty((world * B, summ.shape[1]), dtype=summ.dtype, device=dev)
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        dist.all_gather_into_tensor(out, summ)
+        g1.record()
+        g1.synchronize()
+        gather_ms = g0.elapsed_time(g1)
+        summ_all = out
+    else:
+        summ_all = summ
+    s = summ_all.cpu().numpy()
+    qp_iters_per_step = float(s[:, rm.RS["QP_ITERS"]].sum() / (s.shape[0] * K))
+    nfail = int(s[:, rm.RS["NFAIL"]].sum())
+    flags = eng.get("flags").cpu().numpy()
+    value = world * B * K / (t_ms * 1e-3)
+
+    # end-to-end through the host-buffer C-ABI call (every rank runs it; rank 0's time is reported at N=1,
+    # max over ranks otherwise)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    summ_h, u_h = eng.run_host(par, z0, K)
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = world * B * K / e2e_s
+    h2d = B * (rm.RP["COUNT"] + 12) * 8
+    d2h = B * (rm.RS["COUNT"] + 6) * 8
+
+    if rank == 0:
+        kernel_ms = float(per_step.mean())
+        bytes_step = algorithmic_bytes_per_mpc_step(N) * B
+        achieved_gbs = bytes_step / (kernel_ms * 1e-3) / 1e9
+        peaks = {}
+        pk = ROOT / "MEASURED_PEAKS.json"
+        if pk.exists():
+            peaks = json.loads(pk.read_text())
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        fp64_peak = fp64_peak_tflops(torch, dev)
+        flops_step = algorithmic_flops_per_mpc_step(N, qp_iters_per_step) * B
+        achieved_tf = flops_step / (kernel_ms * 1e-3) / 1e12
+        cb = None
+        if not args.no_cpu_baseline:
+            cb, _, _ = cpu_leg(N, 3, 100, inst_per_core=1)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[2]: {B} random surfaces per GPU, UR10 N={N} SQP_RTI, closed loop "
+                                   f"of {K} steps from the initial state (a step = one MPC step of all {B} instances)",
+                       "batch_per_gpu": B, "horizon": N, "solver": "SQP_RTI", "dt": 0.01,
+                       "l2": f"working set {eng.device_bytes / 2**30:.2f} GiB per GPU, far larger than the 126 MB L2 "
+                             "(inputs larger than L2, no flush needed)",
+                       "e2e_note": "h2d/d2h bytes are per job (K steps) divided by K"},
+            "latency_ms": {"p50": float(np.percentile(per_step, 50)), "p99": float(np.percentile(per_step, 99)),
+                           "max": float(per_step.max()), "what": "one batched MPC step (all instances), CUDA events"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
+                    "seconds": e2e_s},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved_gbs / hbm_peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json" if pk.exists() else "fallback",
+                         "kernel": "rmpc_closed_loop_kernel", "algorithmic_bytes_per_launch": bytes_step,
+                         "note": "the kernel is bound by FP64 issue/latency of the sequential Riccati sweeps, not by "
+                                 "HBM; see fp64"},
+            "fp64": {"achieved_tflops": achieved_tf, "peak_tflops": fp64_peak, "frac": achieved_tf / fp64_peak,
+                     "peak_source": "cuBLAS DGEMM 4096^3 measured in this run",
+                     "algorithmic_flops_per_launch": flops_step, "qp_iters_per_mpc_step": qp_iters_per_step},
+            "solver_failures": nfail, "lq_fallback_triggers": int(flags[:, 2].sum()),
+            "clocks": clocks, "cpu_baseline": cb,
+        }
+        if gather_ms is not None:
+            line["summary_gather_ms"] = gather_ms
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=600)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--horizon", type=int, default=100)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

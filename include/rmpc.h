@@ -1,0 +1,120 @@
+/* include/rmpc.h -- C ABI of librmpc.so, the batched UR10 surface-tracking MPC engine for B200 (sm_100a).
+ *
+ * Drop-in boundary.  The reference reaches its solver through ctypes into a per-instance
+ * generated shared library plus libacados:
+ *     <name>_acados_create_capsule / _create / _solve / _reset / _free      T/acados_ocp_solver.py:288-295,374-444
+ *     ocp_nlp_constraints_model_set, ocp_nlp_out_set / ocp_nlp_out_get, ocp_nlp_get, ocp_nlp_eval_cost
+ *                                                                          T/acados_ocp_solver.py:322-372
+ *     (implementations: acados/interfaces/acados_c/ocp_nlp_interface.c:516-560,637-760,1376-1425)
+ * one capsule per problem instance, one call per MPC step.  This library exposes the same operations for a BATCH of
+ * B instances that live on one GPU; each entry point names the reference call it replaces.
+ *
+ * Conventions
+ *   - plain C, no exceptions cross the boundary, never exit(): every function returns 0 on success or a negative
+ *     RMPC_E* code; rmpc_last_error() gives the message.  Per-instance solver status codes are acados' own
+ *     (0 SUCCESS, 1 NAN_DETECTED, 2 MAXITER, 3 MINSTEP, 4 QP_FAILURE, 6 UNBOUNDED; acados/utils/types.h:76-86).
+ *   - "dev" pointers are device pointers (e.g. torch tensor.data_ptr()), FP64, contiguous, instance-major
+ *     [B][n]; the callee copies, the caller keeps ownership (as acados' setters copy numpy buffers).
+ *     "host" pointers are ordinary host memory.
+ *   - all work is enqueued on the given stream (a cudaStream_t passed as void*, NULL = default stream) and is
+ *     asynchronous with respect to the host unless stated otherwise.
+ *   - a handle belongs to one device and is not re-entrant; different handles may be driven from different threads
+ *     (like acados capsules, T/c_templates_tera/acados_solver.in.c:3008-3028).
+ *   - the library needs a CUDA device: there is no host fallback, rmpc_create fails with RMPC_ENODEV without one.
+ */
+#ifndef RMPC_H
+#define RMPC_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RMPC_EINVAL (-1)  /* bad argument / unknown field */
+#define RMPC_ENODEV (-2)  /* no usable CUDA device */
+#define RMPC_ENOMEM (-3)  /* device allocation failed */
+#define RMPC_ECUDA  (-4)  /* CUDA runtime error (message in rmpc_last_error) */
+
+#define RMPC_SOLVER_SQP 0
+#define RMPC_SOLVER_SQP_RTI 1
+
+/* problem dimensions and solver options common to the batch (per-instance data goes through rmpc_set "par") */
+typedef struct
+{
+    int B;            /* number of instances */
+    int N;            /* prediction horizon (shooting intervals)             R/trajectory_optimizer.py:69 */
+    int solver_type;  /* RMPC_SOLVER_SQP | RMPC_SOLVER_SQP_RTI               R/trajectory_optimizer.py:60 */
+    int max_iter;     /* nlp_solver_max_iter (100)                           R/trajectory_optimizer.py:67 */
+    int qp_iter_max;  /* qp_solver_iter_max (50)                             T/acados_ocp_options.py:77 */
+    double tol[4];    /* nlp tol stat / eq / ineq / comp (1e-6)              T/acados_ocp_options.py:50-53 */
+    double qp_tol;    /* qp_tol (1e-8)                                       R/trajectory_optimizer.py:63 */
+    double dt;        /* shooting interval = Tf / N = model sample time      R/simulator.py:88-101 */
+    double plant_dt;  /* plant integration step (the reference uses dt)      R/simulator.py:78-86 */
+} rmpc_dims;
+
+typedef struct rmpc_handle rmpc_handle;
+
+/* Replaces <name>_acados_create_capsule + _create for B instances: allocates every workspace on `device`, zeroes the
+ * iterate.  nlog = number of closed-loop steps the on-device logs can hold (0: no per-step logs). */
+int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_handle **out);
+
+/* Replaces <name>_acados_free + _free_capsule. */
+int rmpc_destroy(rmpc_handle *h);
+
+/* Message of the last error on this handle (h may be NULL for rmpc_create failures). */
+const char *rmpc_last_error(const rmpc_handle *h);
+
+/* Bytes of device memory owned by the handle. */
+long long rmpc_device_bytes(const rmpc_handle *h);
+
+/* Setters (copy [B][n] doubles from a device pointer).  Replaces AcadosOcpSolver.set / constraints_set / cost_set
+ * (T/acados_ocp_solver.py:1743-1819).  Fields:
+ *   "par"   n = 72   per-instance parameter block (layout: RP_* in csrc/rmpc_types.h; pack with params.pack_params)
+ *   "z"     n = 12   plant state = x0 of the next solve (the reference sets lbx_0 = ubx_0 = x, R/simulator.py:210-211)
+ *   "x"     n = 12   state iterate of `stage` (0..N)        solver.set(stage, 'x', .)
+ *   "u"     n = 6    control iterate of `stage` (0..N-1)    solver.set(stage, 'u', .)
+ *   "pi"    n = 12   dynamics multipliers of `stage`        solver.set(stage, 'pi', .)
+ */
+int rmpc_set(rmpc_handle *h, const char *field, int stage, const double *dev, void *stream);
+
+/* Re-initialise every instance as a freshly created solver started at the current plant state "z":
+ * x_k = z, u_k = 0, multipliers and merit weights 0, logs and summaries cleared
+ * (T/c_templates_tera/acados_solver.in.c:2744-2777 initial guess; :2883-2932 reset). */
+int rmpc_reset(rmpc_handle *h, void *stream);
+
+/* One SQP / SQP_RTI solve for all instances with x0 = "z", without advancing the plant.
+ * Replaces solver.solve() -> <name>_acados_solve -> ocp_nlp_solve (T/acados_ocp_solver.py:468-476). */
+int rmpc_solve(rmpc_handle *h, void *stream);
+
+/* nsteps closed-loop steps for all instances entirely on the device:
+ *   x0 <- z; solve; u0; z <- RK4(z, u0); log; accumulate tracking-error sums.     R/simulator.py:199-241 */
+int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);
+
+/* Getters (copy to a device pointer).  Replaces AcadosOcpSolver.get / get_stats / get_residuals / get_cost
+ * (T/acados_ocp_solver.py:939-989,1461-1723).  Fields, with the shape written to `dev`:
+ *   "x" [B][12], "u" [B][6], "pi" [B][12], "lam" [B][24] ([lower(12); upper(12)] over [u; q]) of `stage`
+ *   "z" [B][12] plant state
+ *   "stats" [B][10]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
+ *                    alpha, qp_status (RL_* in csrc/rmpc_types.h); needs nlog > 0
+ *   "zlog" [B][nlog+1][12], "ulog" [B][nlog][6], "slog" [B][nlog][10]   closed-loop logs
+ *   "summary" [B][20]  RS_* in csrc/rmpc_types.h: sum e^2 (5), ITSE (5), failures, sqp/qp iteration totals,
+ *                      max KKT residuals (4), last cost, number of samples
+ *   "flags" [B][4] as doubles: first_call, qp_warm_pending, LQ-fallback triggers, reserved
+ */
+int rmpc_get(rmpc_handle *h, const char *field, int stage, double *dev, void *stream);
+
+/* Number of closed-loop steps taken since create / reset. */
+int rmpc_steps_done(const rmpc_handle *h);
+
+/* Host-buffer convenience used for end-to-end measurements: upload par [B][72] and z0 [B][12] from host memory,
+ * reset, run nsteps closed-loop steps, download the summary [B][20] and the last applied control [B][6] to host
+ * memory; synchronises the stream before returning.  Any output pointer may be NULL. */
+int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host, int nsteps, double *summary_host,
+                  double *u_last_host, void *stream);
+
+/* Kernels launched by this handle so far (for bench accounting). */
+long long rmpc_launch_count(const rmpc_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,7 @@
+"""robotic-mpc_b200 -- B200-native batched engine for the UR10 surface-tracking MPC hot path of lynet55/robotic-mpc.
+
+The directory name contains a hyphen (it is the repository's package name); import it through the
+``robotic_mpc_b200`` symlink at the repository root or with ``importlib.import_module("robotic-mpc_b200")``.
+"""
+from .params import RL, RP, RS, pack_params  # noqa: F401
+from .engine import SQP, SQP_RTI, Engine, RmpcError, load_library  # noqa: F401

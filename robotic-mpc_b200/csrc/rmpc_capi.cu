@@ -1,0 +1,321 @@
+/* robotic-mpc_b200/csrc/rmpc_capi.cu -- C ABI (include/rmpc.h) over the sm_100a kernels of rmpc_device.cuh.
+ *
+ * Launch geometry: one warp per instance, RMPC_WARPS_PER_CTA warps per CTA; the grid covers the batch, and CTAs are
+ * small (128 threads, ~20 KB of shared memory) so that up to 4 CTAs = 16 instances are resident per SM and the
+ * latency of the sequential Riccati sweeps of one instance is hidden by the other 15.
+ * No host fallback: every entry point needs the CUDA device the handle was created on.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rmpc.h"
+#include "rmpc_device.cuh"
+#include "rmpc_layout.h"
+
+#define RMPC_WARPS_PER_CTA 4
+
+static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layout mismatch");
+
+/* ------------------------------------------------------------------------------------------------ kernels */
+__global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, 4)
+rmpc_closed_loop_kernel(const RmpcChain ch, const RmpcDims D, const RmpcWs W, int nsteps, int advance)
+{
+    __shared__ WarpSmem smem[RMPC_WARPS_PER_CTA];
+    const int warp = threadIdx.x >> 5;
+    const long inst = (long) blockIdx.x * RMPC_WARPS_PER_CTA + warp;
+    if (inst >= D.B) return; /* whole warp exits together */
+    closed_loop_warp(ch, D, W, inst, smem[warp], nsteps, advance);
+}
+
+/* x_k = z, u_k = 0 for every stage; flags = {first_call, qp_warm_pending, 0, 0} */
+__global__ void rmpc_init_iterate_kernel(const RmpcDims D, const RmpcWs W)
+{
+    const long S = D.N + 1;
+    const long tot = (long) D.B * S * NV;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
+    {
+        const long i = k / (S * NV);
+        const int c = (int) (k % NV);
+        W.ux[k] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
+    }
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < (long) D.B * 4; k += (long) gridDim.x * blockDim.x)
+        W.flags[k] = (k % 4) < 2 ? 1 : 0;
+    if (W.zlog)
+        for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < (long) D.B * NX; k += (long) gridDim.x * blockDim.x)
+            W.zlog[(k / NX) * (W.nlog + 1) * NX + (k % NX)] = W.z[k];
+}
+
+/* dst[i][k] = src[i*stride + off + k]  (gather == 1)   or   src[i*stride + off + k] = dst[i][k]  (gather == 0) */
+__global__ void rmpc_strided_copy_kernel(double *packed, double *strided, long B, long stride, long off, int n, int gather)
+{
+    const long tot = B * n;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
+    {
+        const long i = k / n, c = k % n;
+        if (gather) packed[k] = strided[i * stride + off + c];
+        else strided[i * stride + off + c] = packed[k];
+    }
+}
+
+__global__ void rmpc_flags_to_double_kernel(const int *flags, double *out, long n)
+{
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long) gridDim.x * blockDim.x) out[k] = flags[k];
+}
+
+/* ------------------------------------------------------------------------------------------------ handle */
+struct rmpc_handle
+{
+    RmpcDims D;
+    RmpcChain ch;
+    RmpcWs W;
+    int device;
+    int nlog;
+    int steps_done;
+    long long bytes;
+    long long launches;
+    std::vector<void *> owned;
+    double *par_dev;
+    std::string err;
+};
+
+static thread_local std::string g_create_err;
+
+static int fail(rmpc_handle *h, int code, const std::string &msg)
+{
+    if (h) h->err = msg;
+    else g_create_err = msg;
+    return code;
+}
+
+#define CU(call)                                                                                     \
+    do                                                                                               \
+    {                                                                                                \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) return fail(h, RMPC_ECUDA, std::string(#call ": ") + cudaGetErrorString(e_)); \
+    } while (0)
+
+static int grid_for(long n) { long g = (n + 255) / 256; return (int) (g < 1 ? 1 : (g > 148 * 8 ? 148 * 8 : g)); }
+
+extern "C" const char *rmpc_last_error(const rmpc_handle *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+extern "C" long long rmpc_device_bytes(const rmpc_handle *h) { return h ? h->bytes : 0; }
+extern "C" int rmpc_steps_done(const rmpc_handle *h) { return h ? h->steps_done : 0; }
+extern "C" long long rmpc_launch_count(const rmpc_handle *h) { return h ? h->launches : 0; }
+
+extern "C" int rmpc_destroy(rmpc_handle *h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    for (void *p : h->owned) cudaFree(p);
+    delete h;
+    return 0;
+}
+
+extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_handle **out)
+{
+    rmpc_handle *h = nullptr;
+    if (!dims || !out) return fail(nullptr, RMPC_EINVAL, "rmpc_create: null argument");
+    if (dims->B < 1 || dims->N < 2 || dims->N > 4096 || nlog < 0)
+        return fail(nullptr, RMPC_EINVAL, "rmpc_create: need B >= 1, 2 <= N <= 4096, nlog >= 0");
+    if (dims->solver_type != RMPC_SOLVER_SQP && dims->solver_type != RMPC_SOLVER_SQP_RTI)
+        return fail(nullptr, RMPC_EINVAL, "rmpc_create: solver_type must be RMPC_SOLVER_SQP or RMPC_SOLVER_SQP_RTI");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || device < 0 || device >= ndev)
+        return fail(nullptr, RMPC_ENODEV, "rmpc_create: no usable CUDA device (this library has no host fallback)");
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, RMPC_ENODEV, "rmpc_create: cudaSetDevice failed");
+    h = new rmpc_handle();
+    memcpy(&h->D, dims, sizeof(RmpcDims));
+    rmpc_chain_init(&h->ch);
+    memset(&h->W, 0, sizeof(h->W));
+    h->device = device; h->nlog = nlog; h->steps_done = 0; h->bytes = 0; h->launches = 0;
+    const size_t B = (size_t) dims->B, S = (size_t) dims->N + 1;
+    auto dalloc = [&](size_t n_doubles, void **p) -> bool {
+        const size_t bytes = n_doubles * sizeof(double);
+        if (cudaMalloc(p, bytes) != cudaSuccess) return false;
+        cudaMemset(*p, 0, bytes);
+        h->owned.push_back(*p);
+        h->bytes += (long long) bytes;
+        return true;
+    };
+    bool ok = true;
+#define X(name, n) ok = ok && dalloc(B * (size_t) (n), (void **) &h->W.name);
+    RMPC_WS_ARRAYS(X, S)
+#undef X
+    ok = ok && dalloc(B * RP_COUNT, (void **) &h->par_dev);
+    ok = ok && dalloc(B * RS_COUNT, (void **) &h->W.summary);
+    void *fl = nullptr;
+    ok = ok && dalloc(B * 2, &fl); /* 4 ints per instance */
+    h->W.flags = (int *) fl;
+    if (nlog > 0)
+    {
+        ok = ok && dalloc(B * (size_t) (nlog + 1) * NX, (void **) &h->W.zlog);
+        ok = ok && dalloc(B * (size_t) nlog * 6, (void **) &h->W.ulog);
+        ok = ok && dalloc(B * (size_t) nlog * RL_COUNT, (void **) &h->W.slog);
+    }
+    if (!ok)
+    {
+        cudaGetLastError();
+        rmpc_destroy(h);
+        return fail(nullptr, RMPC_ENOMEM, "rmpc_create: device allocation failed");
+    }
+    h->W.par = h->par_dev;
+    h->W.nlog = nlog;
+    h->W.step0 = 0;
+    *out = h;
+    return 0;
+}
+
+static int strided(rmpc_handle *h, double *packed, double *strided_base, long stride, long off, int n, int gather, cudaStream_t s)
+{
+    rmpc_strided_copy_kernel<<<grid_for((long) h->D.B * n), 256, 0, s>>>(packed, strided_base, h->D.B, stride, off, n, gather);
+    h->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const double *dev, void *stream)
+{
+    if (!h || !field || !dev) return fail(h, RMPC_EINVAL, "rmpc_set: null argument");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const long S = h->D.N + 1;
+    const std::string f(field);
+    if (f == "par") { CU(cudaMemcpyAsync(h->par_dev, dev, sizeof(double) * h->D.B * RP_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "z") { CU(cudaMemcpyAsync(h->W.z, dev, sizeof(double) * h->D.B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "x" || f == "u" || f == "pi")
+    {
+        const int smax = (f == "x") ? h->D.N : h->D.N - 1;
+        if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_set: stage out of range for field " + f);
+        if (f == "x") return strided(h, (double *) dev, h->W.ux, S * NV, (long) stage * NV + 6, NX, 0, s);
+        if (f == "u") return strided(h, (double *) dev, h->W.ux, S * NV, (long) stage * NV, NU, 0, s);
+        return strided(h, (double *) dev, h->W.pi, S * NX, (long) stage * NX, NX, 0, s);
+    }
+    return fail(h, RMPC_EINVAL, "rmpc_set: unknown field '" + f + "'");
+}
+
+extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
+{
+    if (!h) return fail(h, RMPC_EINVAL, "rmpc_reset: null handle");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const size_t B = (size_t) h->D.B, S = (size_t) h->D.N + 1;
+    /* duals, merit weights, QP memory, summaries: back to the calloc'ed state of a new acados solver */
+    CU(cudaMemsetAsync(h->W.pi, 0, sizeof(double) * B * S * NX, s));
+    CU(cudaMemsetAsync(h->W.lam, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.lamx0, 0, sizeof(double) * B * NB, s));
+    CU(cudaMemsetAsync(h->W.wpi, 0, sizeof(double) * B * S * NX, s));
+    CU(cudaMemsetAsync(h->W.wlam, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.wlamx0, 0, sizeof(double) * B * NB, s));
+    CU(cudaMemsetAsync(h->W.spi, 0, sizeof(double) * B * S * NX, s));
+    CU(cudaMemsetAsync(h->W.slam, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.st, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.res_m, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.res_m_bkp, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.dlam, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.dt_, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.summary, 0, sizeof(double) * B * RS_COUNT, s));
+    if (h->W.slog) CU(cudaMemsetAsync(h->W.slog, 0, sizeof(double) * B * h->nlog * RL_COUNT, s));
+    if (h->W.ulog) CU(cudaMemsetAsync(h->W.ulog, 0, sizeof(double) * B * h->nlog * 6, s));
+    if (h->W.zlog) CU(cudaMemsetAsync(h->W.zlog, 0, sizeof(double) * B * (h->nlog + 1) * NX, s));
+    rmpc_init_iterate_kernel<<<grid_for((long) B * S * NV), 256, 0, s>>>(h->D, h->W);
+    h->launches++;
+    CU(cudaGetLastError());
+    h->steps_done = 0;
+    h->W.step0 = 0;
+    return 0;
+}
+
+static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
+{
+    const int grid = (h->D.B + RMPC_WARPS_PER_CTA - 1) / RMPC_WARPS_PER_CTA;
+    h->W.step0 = h->steps_done;
+    rmpc_closed_loop_kernel<<<grid, 32 * RMPC_WARPS_PER_CTA, 0, s>>>(h->ch, h->D, h->W, nsteps, advance);
+    h->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int rmpc_solve(rmpc_handle *h, void *stream)
+{
+    if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve: null handle");
+    CU(cudaSetDevice(h->device));
+    return launch_loop(h, 1, 0, (cudaStream_t) stream);
+}
+
+extern "C" int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream)
+{
+    if (!h || nsteps < 0) return fail(h, RMPC_EINVAL, "rmpc_closed_loop: bad argument");
+    CU(cudaSetDevice(h->device));
+    if (nsteps == 0) return 0;
+    int rc = launch_loop(h, nsteps, 1, (cudaStream_t) stream);
+    if (rc == 0) h->steps_done += nsteps;
+    return rc;
+}
+
+extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *dev, void *stream)
+{
+    if (!h || !field || !dev) return fail(h, RMPC_EINVAL, "rmpc_get: null argument");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const long B = h->D.B, S = h->D.N + 1;
+    const std::string f(field);
+    if (f == "x" || f == "u" || f == "pi" || f == "lam")
+    {
+        const int smax = (f == "x") ? h->D.N : h->D.N - 1;
+        if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_get: stage out of range for field " + f);
+        if (f == "x") return strided(h, dev, h->W.ux, S * NV, (long) stage * NV + 6, NX, 1, s);
+        if (f == "u") return strided(h, dev, h->W.ux, S * NV, (long) stage * NV, NU, 1, s);
+        if (f == "pi") return strided(h, dev, h->W.pi, S * NX, (long) stage * NX, NX, 1, s);
+        return strided(h, dev, h->W.lam, S * NB, (long) stage * NB, NB, 1, s);
+    }
+    if (f == "lamx0") return strided(h, dev, h->W.lamx0, NB, 0, NB, 1, s);
+    if (f == "z") { CU(cudaMemcpyAsync(dev, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "summary") { CU(cudaMemcpyAsync(dev, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "flags")
+    {
+        rmpc_flags_to_double_kernel<<<grid_for(B * 4), 256, 0, s>>>(h->W.flags, dev, B * 4);
+        h->launches++;
+        CU(cudaGetLastError());
+        return 0;
+    }
+    if (f == "stats" || f == "zlog" || f == "ulog" || f == "slog")
+    {
+        if (h->nlog <= 0) return fail(h, RMPC_EINVAL, "rmpc_get: handle was created with nlog = 0, no logs");
+        if (f == "zlog") { CU(cudaMemcpyAsync(dev, h->W.zlog, sizeof(double) * B * (h->nlog + 1) * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
+        if (f == "ulog") { CU(cudaMemcpyAsync(dev, h->W.ulog, sizeof(double) * B * h->nlog * 6, cudaMemcpyDeviceToDevice, s)); return 0; }
+        if (f == "slog") { CU(cudaMemcpyAsync(dev, h->W.slog, sizeof(double) * B * h->nlog * RL_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+        /* stats: record of the most recent step (rmpc_solve writes at index steps_done, closed loop at steps_done-1) */
+        int idx = stage >= 0 ? stage : 0;
+        if (idx >= h->nlog) return fail(h, RMPC_EINVAL, "rmpc_get: stats index beyond nlog");
+        return strided(h, dev, h->W.slog, (long) h->nlog * RL_COUNT, (long) idx * RL_COUNT, RL_COUNT, 1, s);
+    }
+    return fail(h, RMPC_EINVAL, "rmpc_get: unknown field '" + f + "'");
+}
+
+extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host, int nsteps, double *summary_host,
+                             double *u_last_host, void *stream)
+{
+    if (!h || !par_host || !z0_host || nsteps < 0) return fail(h, RMPC_EINVAL, "rmpc_run_host: bad argument");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const size_t B = (size_t) h->D.B;
+    CU(cudaMemcpyAsync(h->par_dev, par_host, sizeof(double) * B * RP_COUNT, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(h->W.z, z0_host, sizeof(double) * B * NX, cudaMemcpyHostToDevice, s));
+    int rc = rmpc_reset(h, stream);
+    if (rc) return rc;
+    rc = rmpc_closed_loop(h, nsteps, stream);
+    if (rc) return rc;
+    if (summary_host) CU(cudaMemcpyAsync(summary_host, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToHost, s));
+    if (u_last_host)
+    {
+        /* u0 of the last solve = control iterate of stage 0 */
+        CU(cudaMemcpy2DAsync(u_last_host, sizeof(double) * 6, h->W.ux, sizeof(double) * (h->D.N + 1) * NV, sizeof(double) * 6, B,
+                             cudaMemcpyDeviceToHost, s));
+    }
+    CU(cudaStreamSynchronize(s));
+    return 0;
+}

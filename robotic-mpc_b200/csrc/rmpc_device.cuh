@@ -1330,11 +1330,22 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, WarpSme
 /* ---------------------------------------------------------------------------------------------- closed loop (K5)
  * R/simulator.py:199-241: x = plant state; solver.set(0,'lbx'/'ubx',x); solve; u = solver.get(0,'u'); plant RK4.
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
-RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, WarpSmem &sm, int nsteps)
+RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, WarpSmem &sm, int nsteps,
+                         int advance = 1)
 {
     const Inst I = inst_view(W, D.N, inst);
     const int lane = rd_lane(), N = D.N;
     const double *par = I.par;
+    /* tracking errors e1..e5 are logged at every plant sample incl. the initial state (Nsim + 1 samples,
+     * R/simulation_model.py:24-38, R/simulator.py:265-344); RMSE / ITSE sums of R/simulator.py:347-390 */
+    if (W.summary && W.step0 == 0 && lane == 0 && advance)
+    {
+        double e[5], *sm_ = W.summary + inst * RS_COUNT;
+        ur10_tracking_errors(ch, par, I.z, I.z + 6, e);
+        for (int m = 0; m < 5; m++) sm_[RS_SSE + m] += e[m] * e[m];
+        sm_[RS_NSAMPLES] += 1.0;
+    }
+    rd_sync();
     for (int s = 0; s < nsteps; s++)
     {
         const int gs = W.step0 + s;
@@ -1369,7 +1380,7 @@ RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W
             (void) q2; (void) q3; (void) q4;
         }
         rd_sync();
-        if (lane < 6)
+        if (lane < 6 && advance)
         {
             I.z[lane] = zq; I.z[6 + lane] = zqd;
             if (W.ulog && gs < W.nlog) W.ulog[(inst * W.nlog + gs) * 6 + lane] = u;
@@ -1397,6 +1408,19 @@ RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W
                 for (int k = 0; k < 4; k++) sm_[RS_MAX_RES + k] = rd_fmax(sm_[RS_MAX_RES + k], o.res[k]);
                 sm_[RS_COST_LAST] = cost;
             }
+        }
+        rd_sync();
+        if (W.summary && lane == 0 && advance)
+        {
+            double e[5], *sm_ = W.summary + inst * RS_COUNT;
+            ur10_tracking_errors(ch, par, I.z, I.z + 6, e);
+            const double tk = (gs + 1) * D.plant_dt;
+            for (int m = 0; m < 5; m++)
+            {
+                sm_[RS_SSE + m] += e[m] * e[m];
+                sm_[RS_ITSE + m] += tk * (e[m] * e[m]) * D.plant_dt;
+            }
+            sm_[RS_NSAMPLES] += 1.0;
         }
         rd_sync();
     }

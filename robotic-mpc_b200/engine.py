@@ -1,0 +1,184 @@
+"""ctypes binding of ``librmpc.so`` (C ABI in ``include/rmpc.h``) -- the batched MPC engine on one B200.
+
+PyTorch is used for device memory and streams only: tensors are handed to the library as raw device pointers.
+There is NO CPU path: constructing an :class:`Engine` without the compiled library or without a CUDA device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from .params import RL, RP, RS
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "librmpc.so"
+
+SQP, SQP_RTI = 0, 1
+_SOLVER_TYPES = {"SQP": SQP, "SQP_RTI": SQP_RTI, SQP: SQP, SQP_RTI: SQP_RTI}
+
+
+class RmpcDims(C.Structure):
+    _fields_ = [("B", C.c_int), ("N", C.c_int), ("solver_type", C.c_int), ("max_iter", C.c_int),
+                ("qp_iter_max", C.c_int), ("tol", C.c_double * 4), ("qp_tol", C.c_double), ("dt", C.c_double),
+                ("plant_dt", C.c_double)]
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load librmpc.so; raises if it has not been built (``python -c 'import __graft_entry__ as g; g.build()'``)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise RuntimeError(f"{LIB_PATH} is missing: build the CUDA extension first (__graft_entry__.build()); "
+                           "robotic-mpc_b200 has no CPU fallback")
+    lib = C.CDLL(str(LIB_PATH))
+    vp, cp, dp, ip = C.c_void_p, C.c_char_p, C.c_void_p, C.c_int
+    lib.rmpc_create.argtypes = [C.POINTER(RmpcDims), ip, ip, C.POINTER(vp)]
+    lib.rmpc_destroy.argtypes = [vp]
+    lib.rmpc_last_error.argtypes = [vp]
+    lib.rmpc_last_error.restype = cp
+    lib.rmpc_device_bytes.argtypes = [vp]
+    lib.rmpc_device_bytes.restype = C.c_longlong
+    lib.rmpc_set.argtypes = [vp, cp, ip, dp, vp]
+    lib.rmpc_reset.argtypes = [vp, vp]
+    lib.rmpc_solve.argtypes = [vp, vp]
+    lib.rmpc_closed_loop.argtypes = [vp, ip, vp]
+    lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
+    lib.rmpc_steps_done.argtypes = [vp]
+    lib.rmpc_run_host.argtypes = [vp, dp, dp, ip, dp, dp, vp]
+    lib.rmpc_launch_count.argtypes = [vp]
+    lib.rmpc_launch_count.restype = C.c_longlong
+    _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
+                    "rmpc_solve", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
+                    "rmpc_launch_count"]
+
+
+class RmpcError(RuntimeError):
+    pass
+
+
+class Engine:
+    """A batch of B independent UR10 surface-tracking MPC instances resident on one GPU.
+
+    Mirrors, for a batch, what one ``AcadosOcpSolver`` + plant ``Robot`` pair does in ``R/simulator.py:199-241``.
+    """
+
+    def __init__(self, B, N, solver_type="SQP_RTI", dt=0.01, nlog=0, device=0, max_iter=100, qp_iter_max=50, tol=1e-6,
+                 qp_tol=1e-8, plant_dt=None):
+        import torch
+
+        if not torch.cuda.is_available():
+            raise RmpcError("robotic-mpc_b200 needs a CUDA device (no CPU fallback)")
+        self.torch = torch
+        self.lib = load_library()
+        self.B, self.N, self.nlog = int(B), int(N), int(nlog)
+        self.device = int(device)
+        self.dt = float(dt)
+        self.solver_type = _SOLVER_TYPES[solver_type]
+        d = RmpcDims()
+        d.B, d.N, d.solver_type, d.max_iter, d.qp_iter_max = self.B, self.N, self.solver_type, int(max_iter), int(qp_iter_max)
+        tols = [tol] * 4 if np.isscalar(tol) else list(tol)
+        d.tol[:] = [float(t) for t in tols]
+        d.qp_tol, d.dt, d.plant_dt = float(qp_tol), float(dt), float(dt if plant_dt is None else plant_dt)
+        self.dims = d
+        h = C.c_void_p()
+        rc = self.lib.rmpc_create(C.byref(d), self.device, self.nlog, C.byref(h))
+        if rc != 0:
+            raise RmpcError(f"rmpc_create failed ({rc}): {self.lib.rmpc_last_error(None).decode()}")
+        self.h = h
+        self.tdev = torch.device("cuda", self.device)
+
+    # ------------------------------------------------------------------ helpers
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RmpcError(f"{what} failed ({rc}): {self.lib.rmpc_last_error(self.h).decode()}")
+
+    def _stream(self):
+        return C.c_void_p(self.torch.cuda.current_stream(self.tdev).cuda_stream)
+
+    def _dev(self, a, shape):
+        t = self.torch.as_tensor(np.asarray(a) if not self.torch.is_tensor(a) else a, dtype=self.torch.float64)
+        t = t.to(self.tdev).contiguous()
+        if tuple(t.shape) != tuple(shape):
+            raise ValueError(f"expected shape {tuple(shape)}, got {tuple(t.shape)}")
+        return t
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.rmpc_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ setters
+    def set(self, field, value, stage=0):
+        n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12}[field]
+        t = self._dev(value, (self.B, n))
+        self._check(self.lib.rmpc_set(self.h, field.encode(), int(stage), C.c_void_p(t.data_ptr()), self._stream()),
+                    f"rmpc_set({field})")
+        self.torch.cuda.current_stream(self.tdev).synchronize()  # t may be a temporary
+
+    def set_params(self, par):
+        self.set("par", par)
+
+    def set_state(self, z):
+        self.set("z", z)
+
+    def reset(self):
+        self._check(self.lib.rmpc_reset(self.h, self._stream()), "rmpc_reset")
+
+    # ------------------------------------------------------------------ compute
+    def solve(self):
+        self._check(self.lib.rmpc_solve(self.h, self._stream()), "rmpc_solve")
+
+    def closed_loop(self, nsteps):
+        self._check(self.lib.rmpc_closed_loop(self.h, int(nsteps), self._stream()), "rmpc_closed_loop")
+
+    def run_host(self, par, z0, nsteps, want_u=True):
+        """Host buffers in, host buffers out (the end-to-end path timed by bench.py)."""
+        par = np.ascontiguousarray(par, dtype=np.float64)
+        z0 = np.ascontiguousarray(z0, dtype=np.float64)
+        assert par.shape == (self.B, RP["COUNT"]) and z0.shape == (self.B, 12)
+        summ = np.zeros((self.B, RS["COUNT"]))
+        u = np.zeros((self.B, 6))
+        self._check(self.lib.rmpc_run_host(self.h, par.ctypes.data_as(C.c_void_p), z0.ctypes.data_as(C.c_void_p),
+                                           int(nsteps), summ.ctypes.data_as(C.c_void_p),
+                                           u.ctypes.data_as(C.c_void_p) if want_u else None, self._stream()),
+                    "rmpc_run_host")
+        return summ, u
+
+    # ------------------------------------------------------------------ getters
+    def get(self, field, stage=0):
+        B, nl = self.B, self.nlog
+        shape = {"x": (B, 12), "u": (B, 6), "pi": (B, 12), "lam": (B, 24), "lamx0": (B, 24), "z": (B, 12),
+                 "stats": (B, RL["COUNT"]), "summary": (B, RS["COUNT"]), "flags": (B, 4),
+                 "zlog": (B, nl + 1, 12), "ulog": (B, nl, 6), "slog": (B, nl, RL["COUNT"])}[field]
+        out = self.torch.empty(shape, dtype=self.torch.float64, device=self.tdev)
+        self._check(self.lib.rmpc_get(self.h, field.encode(), int(stage), C.c_void_p(out.data_ptr()), self._stream()),
+                    f"rmpc_get({field})")
+        return out
+
+    @property
+    def steps_done(self):
+        return self.lib.rmpc_steps_done(self.h)
+
+    @property
+    def launch_count(self):
+        return self.lib.rmpc_launch_count(self.h)
+
+    @property
+    def device_bytes(self):
+        return self.lib.rmpc_device_bytes(self.h)

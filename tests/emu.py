@@ -1,0 +1,30 @@
+"""Python binding of tests/simt_emu/librmpc_emu.so -- the device code of robotic-mpc_b200/csrc/rmpc_device.cuh compiled
+for the host warp emulator.  TEST HARNESS ONLY (see tests/simt_emu/simt_emu.h)."""
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+SO = HERE / "simt_emu" / "librmpc_emu.so"
+
+
+class Dims(C.Structure):
+    _fields_ = [("B", C.c_int), ("N", C.c_int), ("solver_type", C.c_int), ("max_iter", C.c_int), ("qp_iter_max", C.c_int),
+                ("tol", C.c_double * 4), ("qp_tol", C.c_double), ("dt", C.c_double), ("plant_dt", C.c_double)]
+
+
+def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8):
+    lib = C.CDLL(str(SO))
+    B = par.shape[0]
+    D = Dims(B, N, solver_type, max_iter, qp_iter_max, (C.c_double * 4)(tol, tol, tol, tol), qp_tol, dt, dt)
+    par = np.ascontiguousarray(par, np.float64)
+    z0 = np.ascontiguousarray(z0, np.float64)
+    out = dict(z=np.zeros((B, nsteps + 1, 12)), u=np.zeros((B, nsteps, 6)), slog=np.zeros((B, nsteps, 10)),
+               summary=np.zeros((B, 20)), flags=np.zeros((B, 4), np.int32))
+    dp = C.POINTER(C.c_double)
+    lib.rmpc_emu_closed_loop(C.byref(D), par.ctypes.data_as(dp), z0.ctypes.data_as(dp), int(nsteps),
+                             out["z"].ctypes.data_as(dp), out["u"].ctypes.data_as(dp), out["slog"].ctypes.data_as(dp),
+                             out["summary"].ctypes.data_as(dp), out["flags"].ctypes.data_as(C.POINTER(C.c_int)),
+                             C.c_ulonglong(seed))
+    return out

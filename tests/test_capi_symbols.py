@@ -1,0 +1,61 @@
+"""The C-ABI shared library loads on a machine without a GPU, exports every symbol include/rmpc.h declares, and
+refuses to work without a CUDA device (no host fallback).  No compute calls here."""
+import ctypes as C
+import re
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_exports_match_header(built):
+    import robotic_mpc_b200.engine as eng
+
+    hdr = (ROOT / "include" / "rmpc.h").read_text()
+    declared = set(re.findall(r"\b(rmpc_[a-z_]+)\s*\(", hdr))
+    declared -= {"rmpc_handle"}
+    lib = C.CDLL(str(eng.LIB_PATH))
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"librmpc.so does not export {name}"
+    assert declared == set(eng.EXPORTED_SYMBOLS)
+
+
+def test_dims_struct_layout(built):
+    import robotic_mpc_b200.engine as eng
+    from tests import emu
+
+    assert C.sizeof(eng.RmpcDims) == C.sizeof(emu.Dims) == 5 * 4 + 4 + 7 * 8  # 5 ints (+pad) + 7 doubles
+
+
+def test_create_without_gpu_fails_loudly(built):
+    import torch
+
+    import robotic_mpc_b200.engine as eng
+
+    if torch.cuda.is_available():
+        return
+    lib = eng.load_library()
+    d = eng.RmpcDims()
+    d.B, d.N, d.solver_type, d.max_iter, d.qp_iter_max = 4, 10, 1, 100, 50
+    h = C.c_void_p()
+    rc = lib.rmpc_create(C.byref(d), 0, 0, C.byref(h))
+    assert rc == -2 and not h  # RMPC_ENODEV
+    assert b"no usable CUDA device" in lib.rmpc_last_error(None)
+    try:
+        eng.Engine(4, 10)
+    except eng.RmpcError as e:
+        assert "CUDA" in str(e)
+    else:
+        raise AssertionError("Engine() must raise without a GPU")
+
+
+def test_bad_arguments(built):
+    import robotic_mpc_b200.engine as eng
+
+    lib = eng.load_library()
+    h = C.c_void_p()
+    d = eng.RmpcDims()
+    d.B, d.N, d.solver_type = 0, 10, 1
+    assert lib.rmpc_create(C.byref(d), 0, 0, C.byref(h)) == -1
+    d.B, d.solver_type = 2, 7
+    assert lib.rmpc_create(C.byref(d), 0, 0, C.byref(h)) == -1
+    assert lib.rmpc_create(None, 0, 0, C.byref(h)) == -1

@@ -1,0 +1,71 @@
+"""CPU-side check of the DEVICE SOURCE itself: rmpc_device.cuh compiled against the host warp emulator
+(tests/simt_emu, randomised lane schedule) must reproduce the oracle.  This is a test harness for the kernels' logic
+and synchronisation -- the product has no CPU path."""
+import numpy as np
+import pytest
+
+from tests import emu
+
+
+def _inputs(o, rm, B, seed, **kw):
+    rng = np.random.default_rng(seed)
+    surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal((B, 6))
+    z0 = np.concatenate([o.README_Q0 + rng.uniform(-0.05, 0.05, (B, 6)), o.README_QD0 + rng.uniform(-0.1, 0.1, (B, 6))], 1)
+    return surf, z0, rm.pack_params(B, 0.01, surf=surf, **kw)
+
+
+@pytest.mark.parametrize("solver,N,ns,seed", [(1, 6, 25, 1), (1, 33, 8, 2), (0, 9, 8, 3), (1, 2, 10, 4)])
+def test_emulated_kernels_match_oracle(oracle, solver, N, ns, seed):
+    import robotic_mpc_b200.params as pm
+
+    o = oracle
+    B = 2
+    surf, z0, par = _inputs(o, pm, B, seed, w_u=0.003, w_qddot=0.03)
+    r = emu.closed_loop(par, z0, N, solver, ns, seed=seed)
+    port = o.PortLeg()
+    for i in range(B):
+        p = o.make_problem(N=N, solver_type=solver, surf=surf[i], w_u=0.003, w_qddot=0.03)
+        g = port.closed_loop(p, z0[i], ns)
+        assert np.abs(g["u"] - r["u"][i]).max() < 1e-10 * max(1.0, np.abs(g["u"]).max())
+        assert np.abs(g["z"] - r["z"][i]).max() < 1e-10
+        assert np.array_equal(g["status"], r["slog"][i, :, 0].astype(int))
+        assert np.array_equal(g["sqp_iter"], r["slog"][i, :, 1].astype(int))
+        assert np.array_equal(g["qp_iter"], r["slog"][i, :, 2].astype(int))
+        assert np.abs(g["cost"] - r["slog"][i, :, 3]).max() < 1e-10
+        assert np.abs(g["res"] - r["slog"][i, :, 4:8]).max() < 1e-10
+        assert r["flags"][i, 2] == 0  # LQ fall-back never needed
+
+
+def test_emulated_schedule_independence(oracle):
+    """Different lane interleavings (seeds) must give bit-identical results: no missing __syncwarp."""
+    import robotic_mpc_b200.params as pm
+
+    surf, z0, par = _inputs(oracle, pm, 1, 11)
+    a = emu.closed_loop(par, z0, 7, 1, 6, seed=0)
+    for s in (5, 9):
+        b = emu.closed_loop(par, z0, 7, 1, 6, seed=s)
+        assert np.array_equal(a["u"], b["u"]) and np.array_equal(a["slog"], b["slog"])
+
+
+def test_emulated_tracking_summary(oracle):
+    """Device-side e1..e5 sums (RS_SSE / RS_ITSE) against the oracle's post-hoc errors on the logged plant states."""
+    import ctypes as C
+
+    import robotic_mpc_b200.params as pm
+
+    o = oracle
+    surf, z0, par = _inputs(o, pm, 1, 21)
+    ns = 12
+    r = emu.closed_loop(par, z0, 5, 1, ns, seed=2)
+    m = o.Model(o.PortLeg().lib)
+    P = o.make_problem(surf=surf[0]).model
+    sse, itse = np.zeros(5), np.zeros(5)
+    for k in range(ns + 1):
+        pose, _, tw = m.plant_logs(r["z"][0, k])
+        e, _ = m.tracking_errors(P, pose, tw, 0.40, 0.05)
+        sse += e ** 2
+        itse += (k * 0.01) * e ** 2 * 0.01
+    s = r["summary"][0]
+    np.testing.assert_allclose(s[0:5], sse, rtol=1e-10)
+    np.testing.assert_allclose(s[5:10], itse, rtol=1e-10)
+    assert s[18] == ns + 1

@@ -1,0 +1,160 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (librmpc.so via robotic_mpc_b200.Engine), against
+the oracle on the same seeded inputs, against the committed golden vectors of the reference, and -- at BASELINE.json's
+full size -- through size-independent properties.  Tolerance: BASELINE.json north_star, 1e-6 relative on u / x
+trajectories and closed-loop metrics; iteration counts equal."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).resolve().parent / "golden"
+RTOL = 1e-6
+
+
+def relerr(a, b):
+    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1e-300))
+
+
+def _inputs(o, B, seed):
+    rng = np.random.default_rng(seed)
+    surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal((B, 6))
+    z0 = np.concatenate([o.README_Q0 + rng.uniform(-0.05, 0.05, (B, 6)), o.README_QD0 + rng.uniform(-0.1, 0.1, (B, 6))], 1)
+    return surf, z0
+
+
+def _run(rm, B, N, solver, par, z0, ns):
+    eng = rm.Engine(B, N, solver, dt=0.01, nlog=ns)
+    eng.set_params(par)
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    out = {k: eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog", "summary", "flags")}
+    out["x"] = np.stack([eng.get("x", s).cpu().numpy() for s in range(N + 1)], 1)
+    out["u"] = np.stack([eng.get("u", s).cpu().numpy() for s in range(N)], 1)
+    out["pi"] = np.stack([eng.get("pi", s).cpu().numpy() for s in range(N)], 1)
+    eng.close()
+    return out
+
+
+@pytest.mark.parametrize("solver,N,ns", [("SQP_RTI", 20, 60), ("SQP", 20, 25), ("SQP_RTI", 100, 20), ("SQP_RTI", 7, 40),
+                                          ("SQP", 50, 10)])
+def test_closed_loop_matches_oracle(oracle, solver, N, ns):
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B = 6
+    surf, z0 = _inputs(o, B, 100 + N)
+    par = rm.pack_params(B, 0.01, surf=surf, w_u=0.01, w_qddot=0.02)
+    r = _run(rm, B, N, solver, par, z0, ns)
+    port = o.PortLeg()
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    for i in range(B):
+        g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i], ns, full_traj=True)
+        assert relerr(r["ulog"][i], g["u"]) < RTOL
+        assert relerr(r["zlog"][i], g["z"]) < RTOL
+        assert np.array_equal(r["slog"][i, :, 0].astype(int), g["status"])
+        assert np.array_equal(r["slog"][i, :, 1].astype(int), g["sqp_iter"])
+        assert np.abs(r["slog"][i, :, 2] - g["qp_iter"]).max() <= 1  # +-1 allowed at a tolerance threshold
+        assert relerr(r["slog"][i, :, 3], g["cost"]) < RTOL
+        assert np.abs(r["slog"][i, :, 4:8] - g["res"]).max() < 1e-8
+        # final OCP iterate
+        assert relerr(r["x"][i], g["xtraj"][-1]) < RTOL
+        assert relerr(r["u"][i], g["utraj"][-1]) < RTOL
+        assert relerr(r["pi"][i], g["pitraj"][-1]) < 1e-5
+        assert r["flags"][i, 2] == 0
+
+
+@pytest.mark.parametrize("case", sorted(p.stem for p in GOLD.glob("*.npz")))
+def test_golden_vectors_of_the_reference(built, case):
+    """Device path against vectors produced by the reference's own compiled acados/HPIPM (tests/golden)."""
+    import robotic_mpc_b200 as rm
+
+    g = np.load(GOLD / f"{case}.npz")
+    N, ns = int(g["N"]), int(g["nsteps"])
+    solver = "SQP_RTI" if int(g["solver_type"]) == 1 else "SQP"
+    par = rm.pack_params(1, 0.01, surf=g["surf"][None], w_u=float(g["w_u"]), w_qddot=float(g["w_qddot"]))
+    r = _run(rm, 1, N, solver, par, g["z0"][None], ns)
+    assert relerr(r["ulog"][0], g["u"]) < RTOL
+    assert relerr(r["zlog"][0], g["z"]) < RTOL
+    assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"])
+    assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"])
+    assert np.abs(r["slog"][0, :, 2] - g["qp_iter"]).max() <= 1
+    assert relerr(r["slog"][0, :, 3], g["cost"]) < RTOL
+    assert relerr(r["x"][0], g["xtraj"][-1]) < RTOL and relerr(r["u"][0], g["utraj"][-1]) < RTOL
+
+
+def test_solver_interface_single_solve(oracle):
+    """rmpc_solve (= solver.solve() without a plant step) + setters/getters of the iterate."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N = 3, 12
+    surf, z0 = _inputs(o, B, 5)
+    eng = rm.Engine(B, N, "SQP", dt=0.01, nlog=1)
+    eng.set_params(rm.pack_params(B, 0.01, surf=surf))
+    eng.set_state(z0)
+    eng.reset()
+    eng.solve()
+    st = eng.get("stats").cpu().numpy()
+    u0 = eng.get("u", 0).cpu().numpy()
+    assert np.array_equal(eng.get("z").cpu().numpy(), z0)  # plant untouched
+    port = o.PortLeg()
+    for i in range(B):
+        g = port.closed_loop(o.make_problem(N=N, solver_type=o.SQP, surf=surf[i]), z0[i], 1)
+        assert relerr(u0[i], g["u"][0]) < RTOL
+        assert int(st[i, 0]) == g["status"][0] and int(st[i, 1]) == g["sqp_iter"][0]
+    # set/get round trip
+    x5 = np.arange(B * 12, dtype=float).reshape(B, 12)
+    eng.set("x", x5, stage=5)
+    assert np.array_equal(eng.get("x", 5).cpu().numpy(), x5)
+    with pytest.raises(rm.RmpcError):
+        eng.get("x", N + 1)
+    eng.close()
+
+
+def test_full_size_properties(built):
+    """BASELINE configs[2] shape (4096 x N=100): the oracle would take minutes, so check size-independent properties:
+    no solver failures, results independent of an instance's position in the batch (permutation equivariance) and of
+    the batch size, determinism across runs."""
+    import robotic_mpc_b200 as rm
+    from oracle import pyoracle as o
+
+    B, N, ns = 4096, 100, 4
+    surf, z0 = _inputs(o, B, 42 + 2)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    a = _run(rm, B, N, "SQP_RTI", par, z0, ns)
+    assert int(a["summary"][:, rm.RS["NFAIL"]].sum()) == 0
+    assert int(a["flags"][:, 2].sum()) == 0
+    assert np.isfinite(a["ulog"]).all()
+    perm = np.random.default_rng(0).permutation(B)
+    b = _run(rm, B, N, "SQP_RTI", par[perm], z0[perm], ns)
+    assert np.array_equal(b["ulog"], a["ulog"][perm])  # bit-identical: one warp per instance, no cross-talk
+    sub = perm[:37]  # ragged batch (not a multiple of the CTA's 4 warps)
+    c = _run(rm, len(sub), N, "SQP_RTI", par[sub], z0[sub], ns)
+    assert np.array_equal(c["ulog"], a["ulog"][sub])
+    # oracle spot check on 3 instances of the big batch
+    port = o.PortLeg()
+    for i in (0, 1234, 4095):
+        g = port.closed_loop(o.make_problem(N=N, solver_type=o.SQP_RTI, surf=surf[i]), z0[i], ns)
+        assert relerr(a["ulog"][i], g["u"]) < RTOL
+
+
+def test_tracking_summary_matches_posthoc(oracle):
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 4, 10, 50
+    surf, z0 = _inputs(o, B, 9)
+    r = _run(rm, B, N, "SQP_RTI", rm.pack_params(B, 0.01, surf=surf), z0, ns)
+    m = o.Model(o.PortLeg().lib)
+    for i in range(B):
+        P = o.make_problem(surf=surf[i]).model
+        sse, itse = np.zeros(5), np.zeros(5)
+        for k in range(ns + 1):
+            pose, _, tw = m.plant_logs(r["zlog"][i, k])
+            e, _ = m.tracking_errors(P, pose, tw, 0.40, 0.05)
+            sse += e ** 2
+            itse += (k * 0.01) * e ** 2 * 0.01
+        np.testing.assert_allclose(r["summary"][i, 0:5], sse, rtol=1e-9)
+        np.testing.assert_allclose(r["summary"][i, 5:10], itse, rtol=1e-9)

@@ -1,8 +1,8 @@
 /* robotic-mpc_b200/csrc/rmpc_capi.cu -- C ABI (include/rmpc.h) over the sm_100a kernels of rmpc_device.cuh.
  *
- * Launch geometry: one warp per instance, RMPC_WARPS_PER_CTA warps per CTA; the grid covers the batch, and CTAs are
- * small (128 threads, ~20 KB of shared memory) so that up to 4 CTAs = 16 instances are resident per SM and the
- * latency of the sequential Riccati sweeps of one instance is hidden by the other 15.
+ * Launch geometry: one group of RMPC_G lanes per instance (two instances per warp by default), RMPC_WARPS_PER_CTA
+ * warps per CTA; the grid covers the batch, and CTAs are small (128 threads) so that several are resident per SM and
+ * the latency of the sequential Riccati sweeps of one instance is hidden by the other instances on the SM.
  * No host fallback: every entry point needs the CUDA device the handle was created on.
  */
 #include <cuda_runtime.h>
@@ -18,6 +18,7 @@
 #include "rmpc_layout.h"
 
 #define RMPC_WARPS_PER_CTA 4
+#define RMPC_GROUPS_PER_CTA (RMPC_WARPS_PER_CTA * 32 / RMPC_G)
 
 static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layout mismatch");
 
@@ -25,11 +26,11 @@ static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layou
 __global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, 4)
 rmpc_closed_loop_kernel(const RmpcChain ch, const RmpcDims D, const RmpcWs W, int nsteps, int advance)
 {
-    __shared__ WarpSmem smem[RMPC_WARPS_PER_CTA];
-    const int warp = threadIdx.x >> 5;
-    const long inst = (long) blockIdx.x * RMPC_WARPS_PER_CTA + warp;
-    if (inst >= D.B) return; /* whole warp exits together */
-    closed_loop_warp(ch, D, W, inst, smem[warp], nsteps, advance);
+    __shared__ GrpSmem smem[RMPC_GROUPS_PER_CTA];
+    const int grp = threadIdx.x / RMPC_G;
+    const long inst = (long) blockIdx.x * RMPC_GROUPS_PER_CTA + grp;
+    if (inst >= D.B) return; /* a whole group exits together; the barriers of the other group carry its own mask */
+    closed_loop_group(ch, D, W, inst, smem[grp], nsteps, advance);
 }
 
 /* x_k = z, u_k = 0 for every stage; flags = {first_call, qp_warm_pending, 0, 0} */
@@ -214,7 +215,7 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
     CU(cudaMemsetAsync(h->W.slam, 0, sizeof(double) * B * S * NB, s));
     CU(cudaMemsetAsync(h->W.st, 0, sizeof(double) * B * S * NB, s));
     CU(cudaMemsetAsync(h->W.res_m, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.res_m_bkp, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.res_mc, 0, sizeof(double) * B * S * NB, s));
     CU(cudaMemsetAsync(h->W.dlam, 0, sizeof(double) * B * S * NB, s));
     CU(cudaMemsetAsync(h->W.dt_, 0, sizeof(double) * B * S * NB, s));
     CU(cudaMemsetAsync(h->W.summary, 0, sizeof(double) * B * RS_COUNT, s));
@@ -231,7 +232,7 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
 
 static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
 {
-    const int grid = (h->D.B + RMPC_WARPS_PER_CTA - 1) / RMPC_WARPS_PER_CTA;
+    const int grid = (h->D.B + RMPC_GROUPS_PER_CTA - 1) / RMPC_GROUPS_PER_CTA;
     h->W.step0 = h->steps_done;
     rmpc_closed_loop_kernel<<<grid, 32 * RMPC_WARPS_PER_CTA, 0, s>>>(h->ch, h->D, h->W, nsteps, advance);
     h->launches++;

@@ -1,82 +1,107 @@
 /* robotic-mpc_b200/csrc/rmpc_device.cuh -- device code of the batched UR10 surface-tracking MPC engine (sm_100a).
  *
- * ONE WARP owns ONE problem instance for the whole closed loop (R/simulator.py:199-241):
+ * A GROUP of GL = RMPC_G lanes (16 by default: two problem instances per warp) owns ONE problem instance for the
+ * whole closed loop (R/simulator.py:199-241):
  *     set x0 -> SQP_RTI / SQP solve -> u0 -> plant RK4 -> metrics,   nsteps times, no host round trip.
- * Inside a solve the warp alternates between two parallelisation patterns:
- *   (S) stage-parallel  : lane l handles stages l, l+32, ... (forward kinematics / Jacobian / Gauss-Newton data,
- *                         KKT and QP residuals, merit function, dual steps) with warp-shuffle reductions;
- *   (R) stage-sequential: the square-root Riccati recursion of the interior-point method; lane r owns row r of
- *                         the 19x18 stage block [[R S'],[S Q],[r' q']] + [B A b]'P[B A b], the previous stage's
- *                         factor is staged in shared memory.
+ * Inside a solve the group alternates between two parallelisation patterns:
+ *   (S) stage-parallel  : lane l handles stages l, l+GL, ... (forward kinematics / Jacobian / Gauss-Newton data,
+ *                         KKT and QP residuals, merit function, iterate updates) with shuffle reductions;
+ *   (R) stage-sequential: the Riccati sweeps of the interior-point method.  Lane l < 6 owns control row u_l and state
+ *                         row qd_l, lane 6 + j owns state row q_j of the stage block; the 12 x 12 cost-to-go matrix P
+ *                         of the next stage lives in shared memory, the 6 x 6 control block is factorised redundantly
+ *                         by every lane (no communication), and everything a later sweep needs is streamed to HBM in
+ *                         one 208-double factor block per stage (RF_* in rmpc_types.h).
+ * All shuffles / barriers carry the group's own lane mask, so the two instances of a warp may sit in different
+ * interior-point or SQP iterations (independent thread scheduling); they run in lock step while they agree.
+ *
  * Replaces, for a batch: CasADi-generated model functions, acados ocp_nlp (SQP / SQP_RTI, NLS cost, discrete
  * dynamics, BGH bounds, merit backtracking), acados ocp_qp partial condensing wrapper (x0 elimination) and the
  * HPIPM interior-point solver -- file:line citations are on each function.  R/ = reference root,
  * AC/ = acados/acados, H/ = acados/external/hpipm.
  *
+ * Numerical route of the Riccati recursion: HPIPM factorises the whole 19 x 18 stage block and carries the Cholesky
+ * factor Lxx of P (square-root form, H/ocp_qp/x_ocp_qp_kkt.c:836-1007).  Here only the 6 control columns are
+ * eliminated and P = Mxx - Lxu Lxu' is carried explicitly -- the same Schur complement the reference's Cholesky
+ * forms before factorising it -- and A = [[I, diag],[0, diag]], B = [diag; diag] are applied as the sparse row
+ * combinations they are.  Same iterates up to rounding; parity with the reference is asserted at 1e-6 relative on
+ * u / x trajectories with equal iteration counts (tests/).
+ *
  * The file compiles in two ways: with nvcc for the product, and with g++ -DRMPC_EMU against
- * tests/simt_emu/simt_emu.h (a lock-step warp emulator) for CPU-side unit tests of this very source.
+ * tests/simt_emu/simt_emu.h (a lock-step lane emulator) for CPU-side unit tests of this very source.
  */
 #pragma once
 #include "rmpc_types.h"
 
+#ifndef RMPC_G
+#define RMPC_G 16
+#endif
+#define GL RMPC_G
+
 #ifdef RMPC_EMU
 #include "simt_emu.h"
 #define RD static inline
+#define RDM inline
 RD int rd_lane() { return simt_emu::lane_id(); }
 RD void rd_sync() { simt_emu::syncwarp(); }
-RD double rd_shfl(double v, int src) { return simt_emu::shfl(v, src); }
-RD double rd_shfl_xor(double v, int m) { return simt_emu::shfl_xor(v, m); }
+RD double rd_shfl(double v, int src) { return simt_emu::shfl(v, src & (GL - 1)); }
+RD double rd_shfl_xor(double v, int m) { return simt_emu::shfl(v, (simt_emu::lane_id() ^ m) & (GL - 1)); }
 RD double rd_rsqrt(double x) { return 1.0 / sqrt(x); }
 RD void rd_sincos(double a, double *s, double *c) { *s = sin(a); *c = cos(a); }
 RD double rd_fmax(double a, double b) { return a > b ? a : b; } /* NaN-ignoring like fmax for our uses */
+RD double rd_inf() { return INFINITY; }
 #define RD_UNROLL
+struct rd_double2 { double x, y; };
 #else
 #define RD __device__ __forceinline__
-RD int rd_lane() { return threadIdx.x & 31; }
-RD void rd_sync() { __syncwarp(); }
-RD double rd_shfl(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
-RD double rd_shfl_xor(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+#define RDM __device__ __forceinline__
+RD unsigned rd_mask()
+{
+    return GL == 32 ? 0xffffffffu : (((1u << (GL & 31)) - 1u) << ((threadIdx.x & 31) & ~(GL - 1)));
+}
+RD int rd_lane() { return threadIdx.x & (GL - 1); }
+RD void rd_sync() { __syncwarp(rd_mask()); }
+RD double rd_shfl(double v, int src) { return __shfl_sync(rd_mask(), v, src, GL); }
+RD double rd_shfl_xor(double v, int m) { return __shfl_xor_sync(rd_mask(), v, m, GL); }
 RD double rd_rsqrt(double x) { return rsqrt(x); }
 RD void rd_sincos(double a, double *s, double *c) { sincos(a, s, c); }
 RD double rd_fmax(double a, double b) { return a > b ? a : b; }
+RD double rd_inf() { return __longlong_as_double(0x7ff0000000000000LL); }
 #define RD_UNROLL _Pragma("unroll")
+typedef double2 rd_double2;
 #endif
 
 #define NX RMPC_NX
 #define NU RMPC_NU
 #define NV RMPC_NV
 #define NB RMPC_NB
-#define LS RMPC_LS
+#define NJ RMPC_NJ
+#define FS RMPC_FS
 
-RD double warp_sum(double v)
+RD double grp_sum(double v)
 {
-    for (int m = 16; m; m >>= 1) v += rd_shfl_xor(v, m);
+    for (int m = GL / 2; m; m >>= 1) v += rd_shfl_xor(v, m);
     return v;
 }
-RD double warp_max(double v)
+RD double grp_max(double v)
 {
-    for (int m = 16; m; m >>= 1) { double o = rd_shfl_xor(v, m); v = o > v ? o : v; }
+    for (int m = GL / 2; m; m >>= 1) { double o = rd_shfl_xor(v, m); v = o > v ? o : v; }
     return v;
 }
-/* NaN-propagating flag OR */
-RD int warp_any(int f)
-{
-    double v = f ? 1.0 : 0.0;
-    return warp_max(v) > 0.5;
-}
 
-/* ---------------------------------------------------------------------------------------------- shared memory */
-#define SM_LXS 13 /* row stride of the staged Lxx block (odd: conflict-free row reads) */
-#define SM_ALS 18 /* row stride of AL (even: 16-byte aligned pairs) */
-struct WarpSmem
+/* ---------------------------------------------------------------------------------------------- shared memory
+ * one block per group (instance) */
+#define SM_PS 14 /* row stride of P: even (16-byte aligned pairs), 28 words -> rows 0..5 hit distinct banks */
+struct GrpSmem
 {
-    double Lx[12 * SM_LXS]; /* Lxx of stage ss+1 (lower), row-major */
-    double lx[12];          /* x part of the last row of L[ss+1] */
-    double AL[19 * SM_ALS]; /* [B A b]' Lxx' | scaled task Jacobian */
-    double col[2][20];      /* potrf column broadcast, double buffered */
-    double xv[12];          /* running state vector of the sweeps */
+    double P[12 * SM_PS]; /* cost-to-go matrix of stage ss+1, full symmetric, state order [q; qd] */
+    double pv[12];        /* cost-to-go vector p of stage ss+1 */
+    double tv[12], bv[12];
+    double Lxu[12 * 6];   /* Lxu of the current stage (for the Schur complement) */
+    double Muu[28];       /* lower 6x6 block (21) + m_u (6) */
+    double xv[12];        /* running state of the forward sweep */
     double uv[8];
-    double bv[12], wv[12], tv[18];
+    double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
+    double Jc[NJ];        /* scaled task Jacobian of the current stage */
 };
 
 /* per-instance views */
@@ -87,7 +112,7 @@ struct Inst
     int *flags;
     double *Jc, *rqz, *b, *d, *dx0, *g0u;
     double *sux, *spi, *slam, *st, *qlamx0, *dux, *dpi, *dlam, *dt_;
-    double *res_g, *res_b, *res_d, *res_m, *res_m_bkp, *pvec, *Pb, *L;
+    double *res_g, *res_b, *res_d, *res_m, *res_mc, *pvec, *F;
     double *ig, *ib, *id, *im, *iux, *ipi, *ilam, *it, *tux;
 };
 
@@ -99,27 +124,22 @@ RD Inst inst_view(const RmpcWs &w, int N, long i)
     v.ux = w.ux + i * S * NV; v.pi = w.pi + i * S * NX; v.lam = w.lam + i * S * NB; v.lamx0 = w.lamx0 + i * NB;
     v.wpi = w.wpi + i * S * NX; v.wlam = w.wlam + i * S * NB; v.wlamx0 = w.wlamx0 + i * NB;
     v.z = w.z + i * NX; v.flags = w.flags + i * 4;
-    v.Jc = w.Jc + i * S * RMPC_NJ; v.rqz = w.rqz + i * S * NV; v.b = w.b + i * S * NX; v.d = w.d + i * S * NB;
+    v.Jc = w.Jc + i * S * NJ; v.rqz = w.rqz + i * S * NV; v.b = w.b + i * S * NX; v.d = w.d + i * S * NB;
     v.dx0 = w.dx0 + i * NX; v.g0u = w.g0u + i * 8;
     v.sux = w.sux + i * S * NV; v.spi = w.spi + i * S * NX; v.slam = w.slam + i * S * NB; v.st = w.st + i * S * NB;
     v.qlamx0 = w.qlamx0 + i * NB;
     v.dux = w.dux + i * S * NV; v.dpi = w.dpi + i * S * NX; v.dlam = w.dlam + i * S * NB; v.dt_ = w.dt_ + i * S * NB;
     v.res_g = w.res_g + i * S * NV; v.res_b = w.res_b + i * S * NX; v.res_d = w.res_d + i * S * NB;
-    v.res_m = w.res_m + i * S * NB; v.res_m_bkp = w.res_m_bkp + i * S * NB;
-    v.pvec = w.pvec + i * S * NX; v.Pb = w.Pb + i * S * NX; v.L = w.L + i * S * LS;
+    v.res_m = w.res_m + i * S * NB; v.res_mc = w.res_mc + i * S * NB;
+    v.pvec = w.pvec + i * S * NX; v.F = w.F + i * S * FS;
     v.ig = w.ig + i * S * NV; v.ib = w.ib + i * S * NX; v.id = w.id + i * S * NB; v.im = w.im + i * S * NB;
     v.iux = w.iux + i * S * NV; v.ipi = w.ipi + i * S * NX; v.ilam = w.ilam + i * S * NB; v.it = w.it + i * S * NB;
     v.tux = w.tux + i * S * NV;
     return v;
 }
 
-/* offset of column c in the packed lower-trapezoidal 19x18 factor: rows c..18 stored contiguously */
-RD int lcol(int c) { return 19 * c - (c * (c - 1)) / 2; }
-#define LEL(Lp, r, c) ((Lp)[lcol(c) + (r) - (c)])
-
-/* a bound slot (stage i, slot j in [0,24)) takes part in the QP?  stage 0 keeps only the u bounds after the
- * x0 elimination (H/ocp_qp/x_ocp_qp_red.c:278-466); stage N has none */
-RD bool slot_on(int i, int j, int N) { return i < N && (i > 0 || (j % 12) < 6); }
+/* element (r, c) of a packed-lower symmetric 12 x 12 matrix */
+RD double psym(const double *P, int r, int c) { return r >= c ? P[(r * (r + 1)) / 2 + c] : P[(c * (c + 1)) / 2 + r]; }
 
 /* ---------------------------------------------------------------------------------------------- model (K1)
  * UR10 forward kinematics, WORLD-frame geometric Jacobian, task-frame outputs and their derivatives.
@@ -128,7 +148,7 @@ RD bool slot_on(int i, int j, int N) { return i < N && (i > 0 || (j % 12) < 6); 
  * Jacobian, task transform, v_task), R/surface.py:21,243-262 (S, unit normal) and
  * R/trajectory_optimizer.py:88-137 (g1..g5).  Chain constants: R/ur_description/urdf/ur10.urdf:50-222.
  *   y5 = [S(p_t) - p_tz, n . R_t[:,2], R_t[0,1], p_tx, (R_t' (v + w x t_w))_y]
- *   J  = d y5 / d x  (5 x 12; rows 0..3 depend on q only)
+ *   J  = d y5 / d x  (5 x 12; rows 0..3 depend on q only, so only 5 x 6 + 6 entries are non-zero)
  * The remaining 13 outputs (u, qddot_k, manipulability with weight 0) are affine/irrelevant and handled by the
  * callers in closed form. */
 RD void cross3(const double *a, const double *b, double *c)
@@ -139,8 +159,16 @@ RD void cross3(const double *a, const double *b, double *c)
 }
 RD double dot3(const double *a, const double *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
 
-template <bool JAC>
-RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const double *qd, double *y5, double *J /*[5][12]*/)
+struct NoEmit
+{
+    RDM void begin(const double *) {}
+    RDM void operator()(int, const double *, double) const {}
+};
+
+/* emit.begin(y5) is called once the outputs are known; emit(k, Jq[5], Jd) then receives, for joint k, column k of
+ * d y5 / d q and the entry d y5_4 / d qd_k */
+template <bool JAC, class Emit>
+RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const double *qd, double *y5, Emit &emit)
 {
     double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, p[3] = {0, 0, 0};
     double pj[6][3], aj[6][3];
@@ -214,6 +242,7 @@ RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const
     y5[3] = pt[0];
     y5[4] = dot3(r1, wv);
     if (!JAC) return;
+    emit.begin(y5);
     /* dn/dX, dn/dY */
     const double mX[3] = {2 * sa, sc, 0.0}, mY[3] = {sc, 2 * sb, 0.0};
     double nX[3], nY[3];
@@ -236,11 +265,12 @@ RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const
         cross3(aj[k], r1, dr1);
         cross3(aj[k], r2, dr2);
         cross3(aj[k], tw, dtw);
-        J[0 * 12 + k] = Sx * dpt[0] + Sy * dpt[1] - dpt[2];
+        double Jq[5];
+        Jq[0] = Sx * dpt[0] + Sy * dpt[1] - dpt[2];
         double dn[3] = {nX[0] * dpt[0] + nY[0] * dpt[1], nX[1] * dpt[0] + nY[1] * dpt[1], nX[2] * dpt[0] + nY[2] * dpt[1]};
-        J[1 * 12 + k] = dot3(dn, r2) + dot3(n, dr2);
-        J[2 * 12 + k] = dr1[0];
-        J[3 * 12 + k] = dpt[0];
+        Jq[1] = dot3(dn, r2) + dot3(n, dr2);
+        Jq[2] = dr1[0];
+        Jq[3] = dpt[0];
         double dwv[3] = {0, 0, 0};
         RD_UNROLL
         for (int j = 0; j < 6; j++)
@@ -261,11 +291,10 @@ RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const
             RD_UNROLL
             for (int r = 0; r < 3; r++) dwv[r] += qd[j] * (t1[r] + t2[r]);
         }
-        J[4 * 12 + k] = dot3(dr1, wv) + dot3(r1, dwv);
+        Jq[4] = dot3(dr1, wv) + dot3(r1, dwv);
         double e[3] = {tw[0] - pj[k][0], tw[1] - pj[k][1], tw[2] - pj[k][2]}, ce[3];
         cross3(aj[k], e, ce);
-        J[4 * 12 + 6 + k] = dot3(r1, ce);
-        J[0 * 12 + 6 + k] = 0.0; J[1 * 12 + 6 + k] = 0.0; J[2 * 12 + 6 + k] = 0.0; J[3 * 12 + 6 + k] = 0.0;
+        emit(k, Jq, dot3(r1, ce));
     }
 }
 
@@ -342,14 +371,13 @@ RD void ur10_tracking_errors(const RmpcChain &ch, const double *par, const doubl
     e[3] = par[RP_PXREF] - pt[0];
     e[4] = par[RP_VYREF] - vt1;
 }
-
 /* ---------------------------------------------------------------------------------------------- NLP level (K2, K4)
  * Per-instance constants of the Gauss-Newton Hessian that do not depend on the stage:
  *   y[5+i] = u_i (weight 2 w_u),  y[11+i] = (b2_i u_i + (a22_i - 1) qd_i) / Ts (weight w_qddot)
  * => H_uu = diag(hu), H_{qd,u} = diag(hs), H_{qd,qd} += diag(hq)        (R/trajectory_optimizer.py:121-154) */
 struct StageConst
 {
-    double hu, hs, hq, cu, cq; /* for joint (lane % 6) */
+    double hu, hs, hq, cu, cq; /* for one joint */
 };
 RD StageConst stage_const(const double *par, double dt, int i)
 {
@@ -390,32 +418,57 @@ RD void load18(const double *src, double *v)
 RD double lb_of(const double *par, int j) { return j < 6 ? par[RP_UMIN + j] : par[RP_QMIN + j - 6]; }
 RD double ub_of(const double *par, int j) { return j < 6 ? par[RP_UMAX + j] : par[RP_QMAX + j - 6]; }
 
-/* Linearisation at the current iterate, stage-parallel: ocp_nlp_approximate_qp_matrices + _vectors_sqp
- * (AC/ocp_nlp/ocp_nlp_common.c:2983-3106) with NLS cost (ocp_nlp_cost_nls.c:830-1032), discrete dynamics
- * (ocp_nlp_dynamics_disc.c:611-708) and box bounds (ocp_nlp_constraints_bgh.c:1563-1619).
- * Writes per stage: Jc = sqrt(dt W_m) * d y5_m / d x, rqz = cost gradient, b = dynamics gap, d = [lb - v; v - ub];
- * dx0 = x0 - x_nlp[0] (both bound residuals of the stage-0 state equality).  Returns the total cost. */
-RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *x0)
+struct LinEmit
 {
-    const int N = D.N, lane = rd_lane();
-    const double dt = D.dt;
-    const double *par = I.par;
-    double cost = 0.0;
-    for (int i = lane; i < N; i += 32)
+    double *Jc, *g;
+    const double *par;
+    double dt, wr[5], sw[5], gqd0[6];
+    RDM void begin(const double *y5)
     {
-        double v[NV], y5[5], J[60];
-        load18(I.ux + NV * i, v);
-        ur10_task<true>(ch, par, v + 6, v + 12, y5, J);
-        cost += stage_cost(par, dt, y5, v, v + 12);
         const double res[5] = {y5[0], y5[1] - 1.0, y5[2], y5[3] - par[RP_PXREF], y5[4] - par[RP_VYREF]};
-        double wr[5], sw[5];
         RD_UNROLL
         for (int m = 0; m < 5; m++)
         {
             wr[m] = dt * par[RP_WTASK + m] * res[m];
             sw[m] = sqrt(dt * par[RP_WTASK + m]);
         }
-        double *g = I.rqz + NV * i, *Jc = I.Jc + RMPC_NJ * i;
+    }
+    RDM void operator()(int k, const double *Jq, double Jd) const
+    {
+        double gq = 0.0, gqd = gqd0[k];
+        RD_UNROLL
+        for (int m = 0; m < 5; m++)
+        {
+            gq += Jq[m] * wr[m];
+            Jc[6 * m + k] = sw[m] * Jq[m];
+        }
+        gqd += Jd * wr[4];
+        Jc[30 + k] = sw[4] * Jd;
+        g[6 + k] = gq;
+        g[12 + k] = gqd;
+    }
+};
+
+/* Linearisation at the current iterate, stage-parallel: ocp_nlp_approximate_qp_matrices + _vectors_sqp
+ * (AC/ocp_nlp/ocp_nlp_common.c:2983-3106) with NLS cost (ocp_nlp_cost_nls.c:830-1032), discrete dynamics
+ * (ocp_nlp_dynamics_disc.c:611-708) and box bounds (ocp_nlp_constraints_bgh.c:1563-1619).
+ * Writes per stage: Jc = sqrt(dt W_m) * d y5_m / d x (non-zero entries), rqz = cost gradient, b = dynamics gap,
+ * d = [lb - v; v - ub]; dx0 = x0 - x_nlp[0] (both bound residuals of the stage-0 state equality).
+ * Returns the total cost. */
+RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *x0)
+{
+    const int N = D.N, lane = rd_lane();
+    const double dt = D.dt;
+    const double *par = I.par;
+    double cost = 0.0;
+    for (int i = lane; i < N; i += GL)
+    {
+        double v[NV], y5[5];
+        load18(I.ux + NV * i, v);
+        double *g = I.rqz + NV * i;
+        LinEmit em;
+        em.Jc = I.Jc + NJ * i;
+        em.g = g;
         const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
         RD_UNROLL
         for (int k = 0; k < 6; k++)
@@ -423,18 +476,12 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
             const double cu = par[RP_B2 + k] / dt, cq = (par[RP_A22 + k] - 1.0) / dt;
             const double a = cu * v[k] + cq * v[12 + k]; /* qddot_k */
             g[k] = dt * (wu * v[k] + wq * cu * a);
-            double gq = 0.0, gqd = dt * (wq * cq * a);
-            RD_UNROLL
-            for (int m = 0; m < 5; m++)
-            {
-                gq += J[12 * m + k] * wr[m];
-                gqd += J[12 * m + 6 + k] * wr[m];
-                Jc[12 * m + k] = sw[m] * J[12 * m + k];
-                Jc[12 * m + 6 + k] = sw[m] * J[12 * m + 6 + k];
-            }
-            g[6 + k] = gq;
-            g[12 + k] = gqd;
+            em.gqd0[k] = dt * (wq * cq * a);
         }
+        em.par = par;
+        em.dt = dt;
+        ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
+        cost += stage_cost(par, dt, y5, v, v + 12);
         /* dynamics gap b = Ad x + Bd u - x_next */
         const double *xn = I.ux + NV * (i + 1) + 6;
         double *b = I.b + NX * i, *d = I.d + NB * i;
@@ -456,9 +503,9 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
             for (int k = 0; k < NX; k++) I.dx0[k] = x0[k] - v[6 + k];
         }
     }
-    if (lane < NV) I.rqz[NV * N + lane] = 0.0; /* stage N: no cost (ny_e = 0) */
+    for (int k = lane; k < NV; k += GL) I.rqz[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
     rd_sync();
-    return warp_sum(cost);
+    return grp_sum(cost);
 }
 
 /* Merit function at the trial iterate tux, ocp_nlp_evaluate_merit_fun
@@ -469,11 +516,12 @@ RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double m = 0.0;
-    for (int i = lane; i < N; i += 32)
+    for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
         load18(tux + NV * i, v);
-        ur10_task<false>(ch, par, v + 6, v + 12, y5, nullptr);
+        NoEmit ne;
+        ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
         m += stage_cost(par, D.dt, y5, v, v + 12);
         const double *xn = tux + NV * (i + 1) + 6, *wpi = I.wpi + NX * i, *wl = I.wlam + NB * i;
         RD_UNROLL
@@ -502,7 +550,7 @@ RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const
             }
         }
     }
-    return warp_sum(m);
+    return grp_sum(m);
 }
 
 /* KKT residual inf-norms of the NLP, ocp_nlp_res_compute (AC/ocp_nlp/ocp_nlp_common.c:3641-3751); uses the
@@ -512,7 +560,7 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double rs = 0, re = 0, ri = 0, rc = 0;
-    for (int i = lane; i <= N; i += 32)
+    for (int i = lane; i <= N; i += GL)
     {
         double r[NV];
         RD_UNROLL
@@ -558,7 +606,7 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
             if (i < N || k >= 6) rs = rd_fmax(rs, fabs(r[k]));
         if (r[6] != r[6]) rs = r[6]; /* propagate NaN like the reference's isnan test */
     }
-    res[0] = warp_max(rs); res[1] = warp_max(re); res[2] = warp_max(ri); res[3] = warp_max(rc);
+    res[0] = grp_max(rs); res[1] = grp_max(re); res[2] = grp_max(ri); res[3] = grp_max(rc);
 }
 
 /* ---------------------------------------------------------------------------------------------- QP level (K3)
@@ -581,17 +629,17 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
 }
 
 /* OCP_QP_INIT_VAR (H/ocp_qp/x_ocp_qp_ipm.c:1592-1980).  warm = 2: keep pi, clip lam, t at 0.1 (:1638-1654).
- * warm = 0 (every QP but the first, see rmpc_oracle.c:solve_qp for the reference quirk): ux = 0, pi = 0,
+ * warm = 0 (every QP but the first, see oracle/rmpc_oracle.c:solve_qp for the reference quirk): ux = 0, pi = 0,
  * t = slack pushed to >= 0.1 by moving ux, lam = mu0 / t with mu0 = 1 (t0_init 2, var_init_scheme 1, :1837-1978).
  * The primal iterate is zeroed first in both cases (AC/ocp_qp/ocp_qp_hpipm.c:309-316). */
 RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
 {
     const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < (N + 1) * NV; k += 32) I.sux[k] = 0.0;
+    for (int k = lane; k < (N + 1) * NV; k += GL) I.sux[k] = 0.0;
     if (warm != 2)
-        for (int k = lane; k < N * NX; k += 32) I.spi[k] = 0.0;
+        for (int k = lane; k < N * NX; k += GL) I.spi[k] = 0.0;
     rd_sync();
-    for (int k = lane; k < N * 12; k += 32)
+    for (int k = lane; k < N * 12; k += GL)
     {
         const int i = k / 12, j = k - 12 * i;
         if (i == 0 && j >= 6) continue;
@@ -621,18 +669,45 @@ RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
     rd_sync();
 }
 
-/* QP residuals, stage-parallel.  lin = 0: OCP_QP_RES_COMPUTE (H/ocp_qp/x_ocp_qp_res.c:345-533) at (ux,pi,lam,t), m = 0;
- * lin = 1: OCP_QP_RES_COMPUTE_LIN (:535-685), residual of the linearised KKT system at the step (ux,pi,lam,t) around
- * (Lam,T) with right-hand sides (rqz,b,d,m).  Outputs the four inf-norms (OCP_QP_RES_COMPUTE_INF_NORM :689-726) in
- * nrm[0..3], nrm[4] = |res_m - tau_min|_inf, and returns sum lam*t (lin = 0).  rg[0] NaN is reported in nrm[5]. */
-RD double ipm_res(const RmpcDims &D, const Inst &I, int lin, const double *rqz, const double *b, const double *d, const double *m,
-                  const double *ux, const double *pi, const double *lam, const double *t, const double *Lam, const double *T,
-                  double *rg, double *rb, double *rd, double *rm, double *nrm)
+/* y += H_xx x for the task part of the Gauss-Newton Hessian, H_xx = Jc' Jc with the sparse Jc of one stage
+ * (rows 0..3 touch q only, row 4 touches q and qd). */
+RD void task_hess_mv(const double *Jc, const double *x, double *y)
+{
+    RD_UNROLL
+    for (int m = 0; m < 5; m++)
+    {
+        double w = 0.0;
+        RD_UNROLL
+        for (int k = 0; k < 6; k++) w += Jc[6 * m + k] * x[k];
+        if (m == 4)
+        {
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) w += Jc[30 + k] * x[6 + k];
+        }
+        RD_UNROLL
+        for (int k = 0; k < 6; k++) y[k] += Jc[6 * m + k] * w;
+        if (m == 4)
+        {
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) y[6 + k] += Jc[30 + k] * w;
+        }
+    }
+}
+
+/* QP residuals, stage-parallel.  LIN = 0: OCP_QP_RES_COMPUTE (H/ocp_qp/x_ocp_qp_res.c:345-533) at (ux,pi,lam,t), m = 0;
+ * LIN = 1: OCP_QP_RES_COMPUTE_LIN (:535-685), residual of the linearised KKT system at the step (ux,pi,lam,t) around
+ * (Lam,T) with right-hand sides (rqz,b,d,m - mshift).  Outputs the four inf-norms (OCP_QP_RES_COMPUTE_INF_NORM
+ * :689-726) in nrm[0..3], nrm[4] = |res_m - tau_min|_inf, nrm[5] = NaN flag of rg[0]; returns sum lam*t (LIN = 0).
+ * WRITE = 0 computes the norms only. */
+template <int LIN, int WRITE>
+RD double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const double *b, const double *d, const double *m,
+                  double mshift, const double *ux, const double *pi, const double *lam, const double *t, const double *Lam,
+                  const double *T, double *rg, double *rb, double *rd, double *rm, double *nrm)
 {
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double mu = 0.0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, n4 = 0, nanflag = 0;
-    for (int i = lane; i <= N; i += 32)
+    for (int i = lane; i <= N; i += GL)
     {
         double v[NV], g[NV];
         load18(ux + NV * i, v);
@@ -646,19 +721,7 @@ RD double ipm_res(const RmpcDims &D, const Inst &I, int lin, const double *rqz, 
         if (i < N)
         {
             /* H v: task part on x (stages >= 1), constant diagonal blocks */
-            if (i > 0)
-            {
-                const double *Jc = I.Jc + RMPC_NJ * i;
-                RD_UNROLL
-                for (int mm = 0; mm < 5; mm++)
-                {
-                    double w = 0.0;
-                    RD_UNROLL
-                    for (int k = 0; k < 12; k++) w += Jc[12 * mm + k] * v[6 + k];
-                    RD_UNROLL
-                    for (int k = 0; k < 12; k++) g[6 + k] += Jc[12 * mm + k] * w;
-                }
-            }
+            if (i > 0) task_hess_mv(I.Jc + NJ * i, v + 6, g + 6);
             const double *pin = pi + NX * i, *l = lam + NB * i, *tt = t + NB * i;
             const double *xn = ux + NV * (i + 1) + 6;
             RD_UNROLL
@@ -674,7 +737,7 @@ RD double ipm_res(const RmpcDims &D, const Inst &I, int lin, const double *rqz, 
                 }
                 const double r0 = b[NX * i + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
                 const double r1 = b[NX * i + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
-                rb[NX * i + k] = r0; rb[NX * i + 6 + k] = r1;
+                if (WRITE) { rb[NX * i + k] = r0; rb[NX * i + 6 + k] = r1; }
                 n1 = rd_fmax(n1, rd_fmax(fabs(r0), fabs(r1)));
             }
             RD_UNROLL
@@ -683,15 +746,15 @@ RD double ipm_res(const RmpcDims &D, const Inst &I, int lin, const double *rqz, 
                 if (i == 0 && j >= 6) continue;
                 g[j] += l[12 + j] - l[j];
                 const double dl = d[NB * i + j] + tt[j] - v[j], du = d[NB * i + 12 + j] + tt[12 + j] + v[j];
-                rd[NB * i + j] = dl; rd[NB * i + 12 + j] = du;
+                if (WRITE) { rd[NB * i + j] = dl; rd[NB * i + 12 + j] = du; }
                 double ml, mu_;
-                if (!lin) { ml = l[j] * tt[j]; mu_ = l[12 + j] * tt[12 + j]; mu += ml + mu_; }
+                if (!LIN) { ml = l[j] * tt[j]; mu_ = l[12 + j] * tt[12 + j]; mu += ml + mu_; }
                 else
                 {
-                    ml = m[NB * i + j] + Lam[NB * i + j] * tt[j] + l[j] * T[NB * i + j];
-                    mu_ = m[NB * i + 12 + j] + Lam[NB * i + 12 + j] * tt[12 + j] + l[12 + j] * T[NB * i + 12 + j];
+                    ml = (m[NB * i + j] - mshift) + Lam[NB * i + j] * tt[j] + l[j] * T[NB * i + j];
+                    mu_ = (m[NB * i + 12 + j] - mshift) + Lam[NB * i + 12 + j] * tt[12 + j] + l[12 + j] * T[NB * i + 12 + j];
                 }
-                rm[NB * i + j] = ml; rm[NB * i + 12 + j] = mu_;
+                if (WRITE) { rm[NB * i + j] = ml; rm[NB * i + 12 + j] = mu_; }
                 n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
                 n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
                 n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
@@ -705,339 +768,463 @@ RD double ipm_res(const RmpcDims &D, const Inst &I, int lin, const double *rqz, 
         RD_UNROLL
         for (int k = 0; k < NV; k++)
         {
-            rg[NV * i + k] = g[k];
+            if (WRITE) rg[NV * i + k] = g[k];
             if ((i < N || k >= 6) && (i > 0 || k < 6)) n0 = rd_fmax(n0, fabs(g[k]));
         }
         if (i == 0 && g[0] != g[0]) nanflag = 1.0;
     }
     rd_sync();
-    nrm[0] = warp_max(n0); nrm[1] = warp_max(n1); nrm[2] = warp_max(n2); nrm[3] = warp_max(n3); nrm[4] = warp_max(n4);
-    nrm[5] = warp_max(nanflag);
-    return warp_sum(mu);
+    nrm[0] = grp_max(n0); nrm[1] = grp_max(n1); nrm[2] = grp_max(n2); nrm[3] = grp_max(n3); nrm[4] = grp_max(n4);
+    nrm[5] = grp_max(nanflag);
+    return grp_sum(mu);
 }
 
-#ifdef RMPC_EMU
-struct rd_double2 { double x, y; };
-#else
-typedef double2 rd_double2;
-#endif
-
-/* Backward square-root Riccati factorisation, first half of OCP_QP_FACT_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:
- * 836-966) incl. COMPUTE_GAMMA_GAMMA_QP (H/ipm_core/x_core_qp_ipm_aux.c:38-86): for ss = N..0
- *   L_ss = chol( [RSQ + reg I + diag(Gamma_lb + Gamma_ub), (res_g + gamma_lb - gamma_ub)'] + AL AL' ),
- *   AL = [B A b]' Lxx_{ss+1}  (last row + l_{ss+1,x}),  Pb_ss = P_{ss+1} res_b_ss.
- * Lane r owns row r of the 19 x 18 block (r = 18: the right-hand-side row).  BLASFEO's dtrmm / dsyrk / dpotrf on
- * panel-major AVX2 kernels become: a sparse row combination (A, B are diagonal blocks), a rank-17 update read as
- * broadcast pairs from shared memory (12 columns of AL + the 5 scaled task-Jacobian rows, which carry the whole
- * state Hessian), and a right-looking Cholesky with one column broadcast per step. */
-RD void ipm_factor(const RmpcDims &D, const Inst &I, WarpSmem &sm)
+/* Row roles of the Riccati sweeps: lane l < 6 owns control row u_l and state row qd_l, lane 6 + j owns state row q_j.
+ * The rows of [B A]' are ca e_q + cb e_qd (B, A of the exact-ZOH model are built from diagonal blocks). */
+struct Role
 {
-    const int N = D.N, lane = rd_lane(), r = lane, jj = lane % 6;
+    int j;        /* joint */
+    int xk;       /* index of the owned state row in [q; qd] (lanes < 12) */
+    bool x, u, q; /* owns a state row / a control row / the state row is a q row */
+    double ca, cb;
+};
+RD Role make_role(const double *par)
+{
+    Role r;
+    const int l = rd_lane();
+    r.j = l % 6;
+    r.x = l < 12;
+    r.u = l < 6;
+    r.q = l >= 6 && l < 12;
+    r.xk = r.q ? r.j : 6 + r.j;
+    r.ca = r.q ? 1.0 : par[RP_A12 + r.j];
+    r.cb = r.q ? 0.0 : par[RP_A22 + r.j];
+    return r;
+}
+
+RD void smem_consts(const Inst &I, GrpSmem &sm)
+{
+    for (int k = rd_lane(); k < 24; k += GL) sm.cst[k] = I.par[RP_A12 + k]; /* a12 a22 b1 b2 are contiguous */
+    rd_sync();
+}
+#define C_A12(c) sm.cst[(c)]
+#define C_A22(c) sm.cst[6 + (c)]
+#define C_B1(c) sm.cst[12 + (c)]
+#define C_B2(c) sm.cst[18 + (c)]
+
+/* Backward Riccati factorisation, first half of OCP_QP_FACT_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:836-966) incl.
+ * COMPUTE_GAMMA_GAMMA_QP (H/ipm_core/x_core_qp_ipm_aux.c:38-86).  For ss = N-1..0, with P+, p+ of stage ss+1:
+ *   M = [[R S'],[S Q]] + reg I + diag(Gamma_lb + Gamma_ub) + [B A]' P+ [B A]
+ *   m = res_g + gamma_lb - gamma_ub + [B A]' (P+ res_b + p+)
+ *   Luu Luu' = Muu, Lxu = Mxu Luu^-T, l_u = Luu^-1 m_u, P = Mxx - Lxu Lxu', p = m_x - Lxu l_u
+ * (the reference factorises P = Lxx Lxx' as well and carries Lxx; see the header of this file).  The complementarity
+ * residual enters as res_m - tau_min (BACKUP_RES_M + COMPUTE_TAU_MIN_QP, x_core_qp_ipm_aux.c:457-475,533-553). */
+RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
+{
+    const int N = D.N, lane = rd_lane();
     const double *par = I.par;
-    const StageConst sc = stage_const(par, D.dt, jj);
-    const double reg = 1e-15;
-    double ca = 0.0, cb = 0.0; /* row r of [B;A]' = ca * e_{q_jj} + cb * e_{qd_jj} */
-    if (r < 6) { ca = par[RP_B1 + jj]; cb = par[RP_B2 + jj]; }
-    else if (r < 12) { ca = 1.0; }
-    else if (r < 18) { ca = par[RP_A12 + jj]; cb = par[RP_A22 + jj]; }
-    /* stage N: zero Hessian + reg => L_N = sqrt(reg) I, l_N = res_g_N / sqrt(reg)  (POTRF_L_MN of :871-879) */
+    const Role R = make_role(par);
+    const int j = R.j, xk = R.xk;
+    const StageConst sc = stage_const(par, D.dt, j);
+    const double reg = 1e-15, tau_min = 1e-16;
+    /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
+    if (R.x)
     {
-        const double sreg = sqrt(reg), isreg = 1.0 / sreg;
-        double *LN = I.L + (long) LS * N;
-        if (lane < 12)
-        {
-            const double lv = I.res_g[NV * N + 6 + lane] * isreg;
-            RD_UNROLL
-            for (int c = 0; c < 12; c++) sm.Lx[lane * SM_LXS + c] = (c == lane) ? sreg : 0.0;
-            sm.lx[lane] = lv;
-            for (int c = 0; c <= lane; c++) LEL(LN, 6 + lane, 6 + c) = (c == lane) ? sreg : 0.0;
-            LEL(LN, 18, 6 + lane) = lv;
-        }
+        double *FN = I.F + (long) FS * N;
+        const double pv = I.res_g[NV * N + 6 + xk];
+        RD_UNROLL
+        for (int c = 0; c < 12; c++) sm.P[xk * SM_PS + c] = (c == xk) ? reg : 0.0;
+        sm.pv[xk] = pv;
+        for (int c = 0; c <= xk; c++) FN[RF_P + (xk * (xk + 1)) / 2 + c] = (c == xk) ? reg : 0.0;
+        FN[RF_PV + xk] = pv;
     }
+    rd_sync();
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        /* (1) right-hand sides and barrier terms of this stage */
+        double *F = I.F + (long) FS * ss;
+        /* (1) barrier terms of the bound slot owned by this lane (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
         double Gam = 0.0, gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
             const double *lam = I.slam + NB * ss, *t = I.st + NB * ss, *rd = I.res_d + NB * ss, *rm = I.res_m + NB * ss;
             const double til = 1.0 / t[lane], tiu = 1.0 / t[12 + lane];
             Gam = til * lam[lane] + tiu * lam[12 + lane];
-            gam = til * (rm[lane] - lam[lane] * rd[lane]) - tiu * (rm[12 + lane] - lam[12 + lane] * rd[12 + lane]);
+            gam = til * ((rm[lane] - tau_min) - lam[lane] * rd[lane]) - tiu * ((rm[12 + lane] - tau_min) - lam[12 + lane] * rd[12 + lane]);
         }
-        if (lane < 12) sm.bv[lane] = I.res_b[NX * ss + lane];
-        if (lane < 18) sm.tv[lane] = ((s0 && lane >= 6) ? 0.0 : I.res_g[NV * ss + lane]) + gam;
-        rd_sync();
-        /* (2) w = Lxx' b ; Pb = Lxx w */
-        if (lane < 12)
-        {
-            double a = 0.0;
-            for (int k = lane; k < 12; k++) a += sm.Lx[k * SM_LXS + lane] * sm.bv[k];
-            sm.wv[lane] = a;
-        }
-        rd_sync();
-        if (lane < 12)
-        {
-            double a = 0.0;
-            for (int k = 0; k <= lane; k++) a += sm.Lx[lane * SM_LXS + k] * sm.wv[k];
-            I.Pb[NX * ss + lane] = a;
-        }
-        /* (3) own row of AL */
-        double al[18];
-        {
-            const double *La = sm.Lx + jj * SM_LXS, *Lb = sm.Lx + (6 + jj) * SM_LXS;
-            RD_UNROLL
-            for (int c = 0; c < 12; c++) al[c] = ca * La[c] + cb * Lb[c];
-            if (r == 18)
-            {
-                RD_UNROLL
-                for (int c = 0; c < 12; c++) al[c] = sm.wv[c] + sm.lx[c];
-            }
-            const bool task = (r >= 6 && r < 18 && !s0);
-            const double *Jc = I.Jc + RMPC_NJ * ss + (task ? r - 6 : 0);
-            RD_UNROLL
-            for (int mm = 0; mm < 5; mm++) al[12 + mm] = task ? Jc[12 * mm] : 0.0;
-            al[17] = 0.0;
-            if (r <= 18)
-            {
-                RD_UNROLL
-                for (int c = 0; c < 18; c++) sm.AL[r * SM_ALS + c] = al[c];
-            }
-        }
-        rd_sync();
-        /* (4) row r of  H + AL AL'  (only columns <= r are meaningful) */
-        double c[18];
-        RD_UNROLL
-        for (int cc = 0; cc < 18; cc++)
-        {
-            const rd_double2 *row = reinterpret_cast<const rd_double2 *>(sm.AL + cc * SM_ALS);
-            double a0 = 0.0, a1 = 0.0;
-            RD_UNROLL
-            for (int k = 0; k < 9; k++)
-            {
-                const rd_double2 p = row[k];
-                a0 += al[2 * k] * p.x;
-                a1 += al[2 * k + 1] * p.y;
-            }
-            double a = a0 + a1;
-            if (r == cc) a += reg + Gam + (r < 6 ? sc.hu : (r >= 12 ? sc.hq : 0.0));
-            if (r == cc + 12 && r < 18) a += sc.hs;
-            if (r == 18) a += sm.tv[cc];
-            c[cc] = a;
-        }
-        /* (5) right-looking Cholesky of the 19 x ncol block (BLASFEO dpotrf_l_mn: non-positive pivot -> zero column) */
-        const int ncol = s0 ? 6 : 18;
-        int pb = 0;
-        RD_UNROLL
-        for (int j = 0; j < 18; j++)
-        {
-            if (j < ncol)
-            {
-                const double dj = rd_shfl(c[j], j);
-                const double inv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
-                const double lj = (r == j) ? dj * inv : c[j] * inv;
-                c[j] = lj;
-                if (r >= j && r <= 18) sm.col[pb][r] = lj;
-                rd_sync();
-                RD_UNROLL
-                for (int k = j + 1; k < 18; k++) c[k] -= lj * sm.col[pb][k];
-                pb ^= 1;
-            }
-        }
-        /* (6) store the factor (packed columns: coalesced over rows) and stage Lxx, l_x for the next stage */
-        double *Ls = I.L + (long) LS * ss;
-        RD_UNROLL
-        for (int cc = 0; cc < 18; cc++)
-            if (r >= cc && r <= 18) LEL(Ls, r, cc) = (s0 && r >= 6 && r < 18) ? 0.0 : c[cc];
+        if (R.x) sm.bv[xk] = I.res_b[NX * ss + xk];
         if (!s0)
+            for (int k = lane; k < NJ; k += GL) sm.Jc[k] = I.Jc[NJ * ss + k];
+        rd_sync();
+        /* (2) tv = P+ b + p+ ; P+ b is kept for the corrector solves */
+        double Pq[12], Pd[12]; /* rows q_j and qd_j of P+ */
+        if (R.x)
         {
-            if (r >= 6 && r < 18)
+            RD_UNROLL
+            for (int c = 0; c < 12; c += 2)
+            {
+                const rd_double2 a = *reinterpret_cast<const rd_double2 *>(&sm.P[j * SM_PS + c]);
+                const rd_double2 bq = *reinterpret_cast<const rd_double2 *>(&sm.P[(6 + j) * SM_PS + c]);
+                Pq[c] = a.x; Pq[c + 1] = a.y; Pd[c] = bq.x; Pd[c + 1] = bq.y;
+            }
+            double a = 0.0;
+            RD_UNROLL
+            for (int c = 0; c < 12; c++) a += (R.q ? Pq[c] : Pd[c]) * sm.bv[c];
+            F[RF_PB + xk] = a;
+            sm.tv[xk] = a + sm.pv[xk];
+        }
+        rd_sync();
+        /* (3a) control rows: Muu row j and m_u */
+        if (R.u)
+        {
+            const double b1j = C_B1(j), b2j = C_B2(j);
+            double row[6];
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+            {
+                const double eq = b1j * Pq[c] + b2j * Pd[c], ed = b1j * Pq[6 + c] + b2j * Pd[6 + c];
+                row[c] = C_B1(c) * eq + C_B2(c) * ed;
+                if (c == j) row[c] += reg + Gam + sc.hu;
+            }
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+                if (c <= j) sm.Muu[(j * (j + 1)) / 2 + c] = row[c];
+            sm.Muu[21 + j] = I.res_g[NV * ss + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
+        }
+        rd_sync();
+        /* (3b) 6 x 6 Cholesky + forward substitution of m_u, redundantly in every lane (BLASFEO dpotrf_l: a
+         *      non-positive pivot zeroes its column) */
+        double Lu[21], lu[6], inv[6];
+        RD_UNROLL
+        for (int k = 0; k < 21; k++) Lu[k] = sm.Muu[k];
+        RD_UNROLL
+        for (int k = 0; k < 6; k++) lu[k] = sm.Muu[21 + k];
+#define LU(r, c) Lu[((r) * ((r) + 1)) / 2 + (c)]
+        RD_UNROLL
+        for (int c = 0; c < 6; c++)
+        {
+            const double dj = LU(c, c);
+            const double iv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
+            inv[c] = iv;
+            LU(c, c) = dj * iv;
+            RD_UNROLL
+            for (int r = c + 1; r < 6; r++) LU(r, c) *= iv;
+            lu[c] *= iv;
+            RD_UNROLL
+            for (int k = c + 1; k < 6; k++)
             {
                 RD_UNROLL
-                for (int cc = 6; cc < 18; cc++) sm.Lx[(r - 6) * SM_LXS + (cc - 6)] = (cc <= r) ? c[cc] : 0.0;
+                for (int r = k; r < 6; r++) LU(r, k) -= LU(r, c) * LU(k, c);
+                lu[k] -= lu[c] * LU(k, c);
             }
-            if (r == 18)
+        }
+        if (R.u)
+        {
+            double ivj = 0.0, luj = 0.0;
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+                if (c == j) { ivj = inv[c]; luj = lu[c]; }
+            F[RF_INV + j] = ivj > 0.0 ? ivj : rd_inf();
+            F[RF_LU + j] = luj;
+            RD_UNROLL
+            for (int r = 1; r < 6; r++)
+                RD_UNROLL
+                for (int c = 0; c < r; c++)
+                    if (r == j) F[RF_LUU + (r * (r - 1)) / 2 + c] = LU(r, c);
+        }
+        if (s0) { rd_sync(); continue; }
+        /* (3c) state rows: e = row of [B A]' P+, then Mxu, Lxu, p */
+        double e[12], Lx[6], pk = 0.0;
+        if (R.x)
+        {
+            RD_UNROLL
+            for (int c = 0; c < 12; c++) e[c] = R.q ? Pq[c] : (R.ca * Pq[c] + R.cb * Pd[c]);
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+            {
+                double v = C_B1(c) * e[c] + C_B2(c) * e[6 + c];
+                if (!R.q && c == j) v += sc.hs;
+                RD_UNROLL
+                for (int k = 0; k < c; k++) v -= Lx[k] * LU(c, k);
+                Lx[c] = v * inv[c];
+            }
+            pk = I.res_g[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
+            RD_UNROLL
+            for (int c = 0; c < 6; c++) pk -= Lx[c] * lu[c];
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+            {
+                sm.Lxu[xk * 6 + c] = Lx[c];
+                F[RF_LXU + xk * 6 + c] = Lx[c];
+            }
+        }
+        rd_sync();
+        /* (3d) Schur complement row: P[xk][:] = Mxx[xk][:] - Lxu[xk][:] Lxu' */
+        if (R.x)
+        {
+            double Pn[12];
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+            {
+                Pn[c] = e[c];
+                Pn[6 + c] = C_A12(c) * e[c] + C_A22(c) * e[6 + c];
+            }
+            if (R.q)
             {
                 RD_UNROLL
-                for (int cc = 6; cc < 18; cc++) sm.lx[cc - 6] = c[cc];
+                for (int c = 0; c < 6; c++)
+                {
+                    double a = 0.0;
+                    RD_UNROLL
+                    for (int m = 0; m < 5; m++) a += sm.Jc[6 * m + j] * sm.Jc[6 * m + c];
+                    Pn[c] += a;
+                    Pn[6 + c] += sm.Jc[24 + j] * sm.Jc[30 + c];
+                }
             }
+            else
+            {
+                RD_UNROLL
+                for (int c = 0; c < 6; c++)
+                {
+                    Pn[c] += sm.Jc[30 + j] * sm.Jc[24 + c];
+                    Pn[6 + c] += sm.Jc[30 + j] * sm.Jc[30 + c];
+                }
+            }
+            RD_UNROLL
+            for (int c = 0; c < 12; c++)
+                if (c == xk) Pn[c] += reg + (R.q ? Gam : sc.hq);
+            RD_UNROLL
+            for (int c = 0; c < 12; c++)
+            {
+                double a = Pn[c];
+                RD_UNROLL
+                for (int k = 0; k < 6; k += 2)
+                {
+                    const rd_double2 lc = *reinterpret_cast<const rd_double2 *>(&sm.Lxu[c * 6 + k]);
+                    a -= Lx[k] * lc.x;
+                    a -= Lx[k + 1] * lc.y;
+                }
+                Pn[c] = a;
+            }
+            RD_UNROLL
+            for (int c = 0; c < 12; c++)
+            {
+                sm.P[xk * SM_PS + c] = Pn[c];
+                if (c <= xk) F[RF_P + (xk * (xk + 1)) / 2 + c] = Pn[c];
+            }
+            sm.pv[xk] = pk;
+            F[RF_PV + xk] = pk;
         }
         rd_sync();
     }
+#undef LU
 }
 
-/* Forward substitution of the Riccati recursion (H/ocp_qp/x_ocp_qp_kkt.c:970-1005 and :1671-1721):
- *   du = -Luu^-T (src_u + Lxu' dx),  dx+ = A dx + B du + b      with src_u = l_u (row 18 of L, after the
- * factorisation) or the z_u left in dux by ipm_backward().  The multipliers dpi are computed afterwards by
- * ipm_dpi(), stage-parallel, because nothing in this recursion depends on them. */
-RD void ipm_forward(const RmpcDims &D, const Inst &I, WarpSmem &sm, const double *b, double *dux, int from_stored)
+/* Forward sweep of the Riccati recursion (H/ocp_qp/x_ocp_qp_kkt.c:970-1005 and :1671-1721) fused with everything that
+ * only depends on the step of one stage:
+ *   du = -Luu^-T (src_u + Lxu' dx),  dx+ = A dx + B du + rb,  dpi = P+ dx+ + p+,
+ *   dt = +-dv - rd, dlam = -(rm + lam dv -+ lam rd) / t        (COMPUTE_LAM_T_QP, H/ipm_core/x_core_qp_ipm_aux.c:164-189)
+ *   alpha = largest step in (0,1] keeping lam, t >= 0            (COMPUTE_ALPHA_QP, :193-263, split_step 0)
+ *   sums[0] = sum lam dt + dlam t, sums[1] = sum dlam dt          (for COMPUTE_MU_AFF_QP, :424-441, see ipm_mu_aff)
+ * STORED = 0: src_u = l_u and p+ from the factorisation (affine step); STORED = 1: src_u = z_u left in X[.][0:6] by
+ * ipm_backward() and p+ = pvec.  rm enters as rm - mshift. */
+template <int STORED>
+RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rb, const double *rd, const double *rm,
+                    double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out, double *sums)
 {
-    const int N = D.N, lane = rd_lane(), jj = lane % 6;
-    const double *par = I.par;
-    const double a12 = par[RP_A12 + jj], a22 = par[RP_A22 + jj], b1 = par[RP_B1 + jj], b2 = par[RP_B2 + jj];
-    if (lane < 12) { sm.xv[lane] = 0.0; dux[6 + lane] = 0.0; }
+    const int N = D.N, lane = rd_lane();
+    const Role R = make_role(I.par);
+    const int j = R.j, xk = R.xk;
+    const double a12 = I.par[RP_A12 + j], a22 = I.par[RP_A22 + j], b1 = I.par[RP_B1 + j], b2 = I.par[RP_B2 + j];
+    if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
     rd_sync();
+    double alpha = 1.0, sB = 0.0, sC = 0.0;
     for (int ss = 0; ss < N; ss++)
     {
-        const double *Ls = I.L + (long) LS * ss;
-        double rhs = 0.0, inv = 0.0;
-        if (lane < 6)
+        const double *F = I.F + (long) FS * ss, *Fn = F + FS;
+        /* s = src_u + Lxu' dx (lane c < 6) */
+        if (R.u)
         {
-            const double *colp = Ls + lcol(lane) - lane; /* colp[r] = L[r][lane] */
-            double t = from_stored ? dux[NV * ss + lane] : colp[18];
+            double s = STORED ? X[NV * ss + lane] : F[RF_LU + lane];
             if (ss > 0)
-                for (int rr = 6; rr < 18; rr++) t += colp[rr] * sm.xv[rr - 6];
-            rhs = -t;
-            inv = 1.0 / colp[lane];
+            {
+                RD_UNROLL
+                for (int k = 0; k < 12; k++) s += F[RF_LXU + k * 6 + lane] * sm.xv[k];
+            }
+            sm.uv[lane] = s;
         }
-        double z = 0.0;
-        for (int k = 5; k >= 0; k--)
+        rd_sync();
+        /* du = -Luu^-T s, redundantly in every lane */
+        double du[6];
         {
-            const double zk = rd_shfl(rhs * inv, k);
-            if (lane < k) rhs -= Ls[lcol(lane) + k - lane] * zk;
-            if (lane == k) z = zk;
+            double iv[6], Ls[15];
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) { du[k] = -sm.uv[k]; iv[k] = F[RF_INV + k]; }
+            RD_UNROLL
+            for (int k = 0; k < 15; k++) Ls[k] = F[RF_LUU + k];
+            RD_UNROLL
+            for (int k = 5; k >= 0; k--)
+            {
+                du[k] *= iv[k];
+                RD_UNROLL
+                for (int c = 0; c < k; c++) du[c] -= Ls[(k * (k - 1)) / 2 + c] * du[k];
+            }
         }
-        if (lane < 6) { sm.uv[lane] = z; dux[NV * ss + lane] = z; }
-        rd_sync();
+        double duj = du[0], dul = du[0];
+        RD_UNROLL
+        for (int k = 1; k < 6; k++)
+        {
+            if (k == j) duj = du[k];
+            if (k == lane) dul = du[k];
+        }
+        /* step of the variable of this lane's bound slot: u_l or q_{l-6} of THIS stage */
+        const double dv = (lane < 6) ? dul : (lane < 12 ? sm.xv[lane - 6] : 0.0);
         double xn = 0.0;
-        if (lane < 6) xn = (sm.xv[jj] + a12 * sm.xv[6 + jj]) + b1 * sm.uv[jj] + b[NX * ss + lane];
-        else if (lane < 12) xn = a22 * sm.xv[6 + jj] + b2 * sm.uv[jj] + b[NX * ss + lane];
+        if (R.x)
+        {
+            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + rb[NX * ss + j];
+            else xn = a22 * sm.xv[6 + j] + b2 * duj + rb[NX * ss + 6 + j];
+        }
+        rd_sync(); /* every lane has read xv, uv */
+        if (R.u) X[NV * ss + lane] = dul;
+        if (R.x) { sm.xv[xk] = xn; X[NV * (ss + 1) + 6 + xk] = xn; }
         rd_sync();
-        if (lane < 12) { sm.xv[lane] = xn; dux[NV * (ss + 1) + 6 + lane] = xn; }
-        rd_sync();
+        /* dpi = P+ dx+ + p+ */
+        if (R.x)
+        {
+            double a = STORED ? I.pvec[NX * (ss + 1) + xk] : Fn[RF_PV + xk];
+            RD_UNROLL
+            for (int c = 0; c < 12; c++) a += psym(Fn + RF_P, xk, c) * sm.xv[c];
+            PI[NX * ss + xk] = a;
+        }
+        /* multiplier / slack step of this lane's bound slot, step length, second-order sums */
+        if (lane < 12 && !(ss == 0 && lane >= 6))
+        {
+            const int ia = NB * ss + lane, ib = ia + 12;
+            const double la = I.slam[ia], lb = I.slam[ib], ta = I.st[ia], tb = I.st[ib];
+            const double da = rd[ia], db = rd[ib], ma = rm[ia] - mshift, mb = rm[ib] - mshift;
+            const double dla = -(ma + (la * dv) - (la * da)) / ta;
+            const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
+            const double dta = dv - da, dtb = -dv - db;
+            DL[ia] = dla; DL[ib] = dlb; DT[ia] = dta; DT[ib] = dtb;
+            if (-alpha * dla > la) alpha = -la / dla;
+            if (-alpha * dta > ta) alpha = -ta / dta;
+            if (-alpha * dlb > lb) alpha = -lb / dlb;
+            if (-alpha * dtb > tb) alpha = -tb / dtb;
+            sB += (la * dta + dla * ta) + (lb * dtb + dlb * tb);
+            sC += dla * dta + dlb * dtb;
+        }
     }
-    if (lane < 6) dux[NV * N + lane] = 0.0;
+    if (R.u) X[NV * N + lane] = 0.0;
     rd_sync();
+    *alpha_out = -grp_max(-alpha);
+    sums[0] = grp_sum(sB);
+    sums[1] = grp_sum(sC);
 }
 
 /* Backward substitution with stored factors, first half of OCP_QP_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:
- * 1543-1665) incl. COMPUTE_GAMMA_QP (x_core_qp_ipm_aux.c:133-160): leaves z_u = Luu^-1 r_u in dux[.][0:6] and the
- * Riccati vectors p_ss in pvec. */
-RD void ipm_backward(const RmpcDims &D, const Inst &I, WarpSmem &sm, const double *rqz, const double *b, const double *d,
-                     const double *m, double *dux, int use_Pb)
+ * 1543-1665) incl. COMPUTE_GAMMA_QP (x_core_qp_ipm_aux.c:133-160): leaves z_u = Luu^-1 r_u in X[.][0:6] and the
+ * Riccati vectors p_ss in pvec.  The complementarity right-hand side depends on MODE:
+ *   0  rm given (iterative refinement);
+ *   1  COMPUTE_CENTERING_CORRECTION_QP (:479-505): rm = res_m + dt_aff dlam_aff - sigma_mu, written to res_mc;
+ *   2  COMPUTE_CENTERING_QP (:509-529):            rm = res_m - sigma_mu, written to res_mc.
+ * USE_PB: P+ rb was stored by the factorisation (rb = res_b); otherwise it is recomputed from P+. */
+template <int MODE, int USE_PB>
+RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
+                     const double *rm, double sigma_mu, double *X)
 {
-    const int N = D.N, lane = rd_lane(), r = lane, jj = lane % 6;
-    const double *par = I.par;
-    double ca = 0.0, cb = 0.0;
-    if (r < 6) { ca = par[RP_B1 + jj]; cb = par[RP_B2 + jj]; }
-    else if (r < 12) { ca = 1.0; }
-    else if (r < 18) { ca = par[RP_A12 + jj]; cb = par[RP_A22 + jj]; }
-    if (lane < 12)
+    const int N = D.N, lane = rd_lane();
+    const Role R = make_role(I.par);
+    const int j = R.j, xk = R.xk;
+    const double b1 = I.par[RP_B1 + j], b2 = I.par[RP_B2 + j];
+    if (R.x)
     {
-        const double pv = rqz[NV * N + 6 + lane];
-        sm.xv[lane] = pv;
-        I.pvec[NX * N + lane] = pv;
+        const double pv = rg[NV * N + 6 + xk];
+        sm.pv[xk] = pv;
+        I.pvec[NX * N + xk] = pv;
     }
     rd_sync();
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        const double *Ls = I.L + (long) LS * ss;
-        double rr = 0.0;
-        if (r < 18 && !(s0 && r >= 6)) rr = rqz[NV * ss + r];
+        const double *F = I.F + (long) FS * ss, *Fn = F + FS;
+        if (R.x)
+        {
+            double pb;
+            if (USE_PB) pb = F[RF_PB + xk];
+            else
+            {
+                pb = 0.0;
+                RD_UNROLL
+                for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[NX * ss + c];
+            }
+            sm.tv[xk] = sm.pv[xk] + pb;
+        }
+        double gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
-            const double *lam = I.slam + NB * ss, *t = I.st + NB * ss, *dd = d + NB * ss, *mm = m + NB * ss;
-            rr += (mm[lane] - lam[lane] * dd[lane]) / t[lane] - (mm[12 + lane] - lam[12 + lane] * dd[12 + lane]) / t[12 + lane];
-        }
-        if (use_Pb)
-        {
-            if (lane < 12) sm.tv[lane] = sm.xv[lane] + I.Pb[NX * ss + lane];
-        }
-        else
-        {
-            /* P_{ss+1} b = Lxx (Lxx' b) from the stored factor of stage ss+1 */
-            const double *Ln = I.L + (long) LS * (ss + 1);
-            if (lane < 12)
+            const int ia = NB * ss + lane, ib = ia + 12;
+            const double la = I.slam[ia], lb = I.slam[ib], ta = I.st[ia], tb = I.st[ib];
+            double ma, mb;
+            if (MODE == 0) { ma = rm[ia]; mb = rm[ib]; }
+            else
             {
-                double a = 0.0;
-                for (int k = lane; k < 12; k++) a += LEL(Ln, 6 + k, 6 + lane) * b[NX * ss + k];
-                sm.wv[lane] = a;
+                if (MODE == 1)
+                {
+                    ma = I.res_m[ia] + I.dt_[ia] * I.dlam[ia] - sigma_mu;
+                    mb = I.res_m[ib] + I.dt_[ib] * I.dlam[ib] - sigma_mu;
+                }
+                else { ma = I.res_m[ia] - sigma_mu; mb = I.res_m[ib] - sigma_mu; }
+                I.res_mc[ia] = ma; I.res_mc[ib] = mb;
             }
-            rd_sync();
-            if (lane < 12)
-            {
-                double a = 0.0;
-                for (int k = 0; k <= lane; k++) a += LEL(Ln, 6 + lane, 6 + k) * sm.wv[k];
-                sm.tv[lane] = sm.xv[lane] + a;
-            }
+            gam = (ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb;
         }
         rd_sync();
-        rr += ca * sm.tv[jj] + cb * sm.tv[6 + jj];
-        /* TRSV_LNN_MN(18, 6): z_u = Luu^-1 r_u, r_x -= Lxu z_u */
-        const double inv = (lane < 6) ? 1.0 / Ls[lcol(lane)] : 0.0;
-        for (int k = 0; k < 6; k++)
+        double rx = 0.0;
+        if (R.u) sm.uv[lane] = rg[NV * ss + lane] + gam + (b1 * sm.tv[j] + b2 * sm.tv[6 + j]);
+        if (R.x && !s0) rx = rg[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
+        rd_sync();
+        /* TRSV_LNN_MN(18, 6): z_u = Luu^-1 r_u (redundantly in every lane), r_x -= Lxu z_u */
+        double z[6];
         {
-            const double zk = rd_shfl(rr * inv, k);
-            if (r > k && r < 18) rr -= Ls[lcol(k) + r - k] * zk;
-            if (r == k) rr = zk;
+            double iv[6], Ls[15];
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) { z[k] = sm.uv[k]; iv[k] = F[RF_INV + k]; }
+            RD_UNROLL
+            for (int k = 0; k < 15; k++) Ls[k] = F[RF_LUU + k];
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                z[k] *= iv[k];
+                RD_UNROLL
+                for (int r = k + 1; r < 6; r++) z[r] -= Ls[(r * (r - 1)) / 2 + k] * z[k];
+            }
         }
-        rd_sync(); /* everyone has read tv / xv */
-        if (r < 6) dux[NV * ss + r] = rr;
-        else if (r < 18 && !s0)
+        if (R.u)
         {
-            sm.xv[r - 6] = rr;
-            I.pvec[NX * ss + r - 6] = rr;
+            double zl = z[0];
+            RD_UNROLL
+            for (int k = 1; k < 6; k++)
+                if (k == lane) zl = z[k];
+            X[NV * ss + lane] = zl;
+        }
+        if (R.x && !s0)
+        {
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) rx -= F[RF_LXU + xk * 6 + k] * z[k];
+            sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
+            I.pvec[NX * ss + xk] = rx;
         }
         rd_sync();
     }
 }
 
-/* dpi_i = P_{i+1} dx_{i+1} + p_{i+1}, stage-parallel (H/ocp_qp/x_ocp_qp_kkt.c:978-984 after the factorisation:
- * p = Lxx l_x; :1683-1688 after a re-solve: p = pvec). */
-RD void ipm_dpi(const RmpcDims &D, const Inst &I, const double *dux, double *dpi, int from_stored)
-{
-    const int N = D.N, lane = rd_lane();
-    for (int i = lane; i < N; i += 32)
-    {
-        const double *Ln = I.L + (long) LS * (i + 1), *x = dux + NV * (i + 1) + 6;
-        double w[12];
-        RD_UNROLL
-        for (int c = 0; c < 12; c++)
-        {
-            double a = from_stored ? 0.0 : LEL(Ln, 18, 6 + c);
-            RD_UNROLL
-            for (int k = c; k < 12; k++) a += LEL(Ln, 6 + k, 6 + c) * x[k];
-            w[c] = a;
-        }
-        RD_UNROLL
-        for (int rr = 0; rr < 12; rr++)
-        {
-            double a = from_stored ? I.pvec[NX * (i + 1) + rr] : 0.0;
-            RD_UNROLL
-            for (int k = 0; k <= rr; k++) a += LEL(Ln, 6 + rr, 6 + k) * w[k];
-            dpi[NX * i + rr] = a;
-        }
-    }
-    rd_sync();
-}
-
-/* dt = +-dux[idxb], then COMPUTE_LAM_T_QP (H/ipm_core/x_core_qp_ipm_aux.c:164-189) */
-RD void ipm_dlam_dt(const RmpcDims &D, const Inst &I, const double *d, const double *m, const double *dux, double *dlam, double *dt)
-{
-    const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < N * 12; k += 32)
-    {
-        const int i = k / 12, j = k - 12 * i;
-        if (i == 0 && j >= 6) continue;
-        const double du = dux[NV * i + j];
-        const int a = NB * i + j, bq = a + 12;
-        const double la = I.slam[a], lb = I.slam[bq];
-        dlam[a] = -(m[a] + (la * du) - (la * d[a])) / I.st[a];
-        dlam[bq] = -(m[bq] + (lb * (-du)) - (lb * d[bq])) / I.st[bq];
-        dt[a] = du - d[a];
-        dt[bq] = -du - d[bq];
-    }
-    rd_sync();
-}
-
-/* COMPUTE_ALPHA_QP (x_core_qp_ipm_aux.c:193-263): largest step in (0,1] keeping lam, t >= 0 (single step, split_step 0) */
+/* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction) */
 RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const double *dt)
 {
     const int N = D.N, lane = rd_lane();
     double a = 1.0;
-    for (int k = lane; k < N * NB; k += 32)
+    for (int k = lane; k < N * NB; k += GL)
     {
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
@@ -1045,21 +1232,32 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
         if (-a * dl > I.slam[k]) a = -I.slam[k] / dl;
         if (-a * dtt > I.st[k]) a = -I.st[k] / dtt;
     }
-    return -warp_max(-a);
+    return -grp_max(-a);
 }
 
-/* COMPUTE_MU_AFF_QP (x_core_qp_ipm_aux.c:424-441) */
-RD double ipm_mu_aff(const RmpcDims &D, const Inst &I, double alpha, double nc_inv)
+/* COMPUTE_MU_AFF_QP (x_core_qp_ipm_aux.c:424-441): sum (lam + alpha dlam)(t + alpha dt) / nc, expanded in powers of
+ * alpha so that the sums can be accumulated by the forward sweep before alpha is known */
+RD double ipm_mu_aff(double sum_lt, const double *sums, double alpha, double nc_inv)
+{
+    return (sum_lt + alpha * sums[0] + alpha * alpha * sums[1]) * nc_inv;
+}
+
+/* UPDATE_VAR_QP (x_core_qp_ipm_aux.c:267-372): single damped step, lam / t floor */
+RD void ipm_update(const RmpcDims &D, const Inst &I, double a)
 {
     const int N = D.N, lane = rd_lane();
-    double mu = 0.0;
-    for (int k = lane; k < N * NB; k += 32)
+    const double lmin = 1e-16;
+    for (int k = lane; k < (N + 1) * NV; k += GL) I.sux[k] += a * I.dux[k];
+    for (int k = lane; k < N * NX; k += GL) I.spi[k] += a * I.dpi[k];
+    for (int k = lane; k < N * NB; k += GL)
     {
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        mu += (I.slam[k] + alpha * I.dlam[k]) * (I.st[k] + alpha * I.dt_[k]);
+        double l = I.slam[k] + a * I.dlam[k], t = I.st[k] + a * I.dt_[k];
+        I.slam[k] = l <= lmin ? lmin : l;
+        I.st[k] = t <= lmin ? lmin : t;
     }
-    return warp_sum(mu) * nc_inv;
+    rd_sync();
 }
 
 /* d_ocp_qp_ipm_solve (H/ocp_qp/x_ocp_qp_ipm.c:2626-3018) with OCP_QP_IPM_DELTA_STEP (:2155-2622) for the option set
@@ -1068,103 +1266,70 @@ RD double ipm_mu_aff(const RmpcDims &D, const Inst &I, double alpha, double nc_i
  * (0 ok, 2 max iter, 3 min step, 1 NaN).  The Householder-LQ fall-back of lq_fact = 1 is not implemented: its
  * trigger (linear-system residual > 1e-5, :2246-2276) is evaluated and counted in flags[2] so that any instance
  * that would have taken it is visible to the caller. */
-RD int ipm_solve_qp(const RmpcDims &D, const Inst &I, WarpSmem &sm, int warm, int *iters)
+RD int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters)
 {
     const int N = D.N, lane = rd_lane();
-    const double tol = D.qp_tol, alpha_min = 1e-8, tau_min = 1e-16, lmin = 1e-16;
+    const double tol = D.qp_tol, alpha_min = 1e-8, tau_min = 1e-16;
     const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12);
     ipm_init(D, I, warm);
-    double nrm[6], inrm[6], alpha = 1.0;
-    double mu = nc_inv * ipm_res(D, I, 0, I.rqz, I.b, I.d, nullptr, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g, I.res_b,
-                                 I.res_d, I.res_m, nrm);
+    double nrm[6], inrm[6], alpha = 1.0, sums[2];
+    double sum_lt = ipm_res<0, 1>(D, I, I.rqz, I.b, I.d, nullptr, 0.0, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g,
+                                  I.res_b, I.res_d, I.res_m, nrm);
+    double mu = nc_inv * sum_lt;
     int kk;
     for (kk = 0; kk < D.qp_iter_max && alpha > alpha_min && (nrm[0] > tol || nrm[1] > tol || nrm[2] > tol || nrm[4] > tol); kk++)
     {
-        /* BACKUP_RES_M, COMPUTE_TAU_MIN_QP */
-        for (int k = lane; k < N * NB; k += 32)
-        {
-            const double v = I.res_m[k];
-            I.res_m_bkp[k] = v;
-            I.res_m[k] = v - tau_min;
-        }
-        rd_sync();
         /* affine (predictor) step */
         ipm_factor(D, I, sm);
-        ipm_forward(D, I, sm, I.res_b, I.dux, 0);
-        ipm_dpi(D, I, I.dux, I.dpi, 0);
-        ipm_dlam_dt(D, I, I.res_d, I.res_m, I.dux, I.dlam, I.dt_);
-        ipm_res(D, I, 1, I.res_g, I.res_b, I.res_d, I.res_m, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, I.ig, I.ib, I.id, I.im, inrm);
-#ifdef RMPC_EMU_DEBUG
-        if (lane == 0 && kk == 0) printf("dbg st1: res_g6 %.6e dux6 %.6e dpi1_0 %.6e dpi0_0 %.6e dlam_lb %.6e dlam_ub %.6e lam %.3e %.3e t %.3e %.3e res_d %.3e %.3e res_m %.3e %.3e dt %.3e %.3e\n", I.res_g[NV+6], I.dux[NV+6], I.dpi[NX], I.dpi[0], I.dlam[NB+6], I.dlam[NB+18], I.slam[NB+6], I.slam[NB+18], I.st[NB+6], I.st[NB+18], I.res_d[NB+6], I.res_d[NB+18], I.res_m[NB+6], I.res_m[NB+18], I.dt_[NB+6], I.dt_[NB+18]);
-        if (lane == 0 && kk == 0) for (int i = 0; i <= N; i++) { printf("  ig[%d]:", i); for (int k = 0; k < NV; k++) printf(" %.2e", I.ig[NV*i+k]); printf("\n"); }
-        if (lane == 0) printf("ipm it %d: nrm %.3e %.3e %.3e %.3e | lin res after predictor %.3e %.3e %.3e %.3e\n", kk, nrm[0], nrm[1], nrm[2], nrm[4], inrm[0], inrm[1], inrm[2], inrm[3]);
-#endif
+        ipm_forward<0>(D, I, sm, I.res_b, I.res_d, I.res_m, tau_min, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
+        ipm_res<1, 0>(D, I, I.res_g, I.res_b, I.res_d, I.res_m, tau_min, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, nullptr, nullptr,
+                      nullptr, nullptr, inrm);
         if ((inrm[0] == 0.0 && inrm[5] > 0.5) || inrm[0] > 1e-5 || inrm[1] > 1e-5 || inrm[2] > 1e-5 || inrm[3] > 1e-5)
         {
             if (lane == 0) I.flags[2] += 1;
         }
-        alpha = ipm_alpha(D, I, I.dlam, I.dt_);
-        double mu_aff = ipm_mu_aff(D, I, alpha, nc_inv);
+        double mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         const double tmp = mu_aff / mu, sigma = tmp * tmp * tmp;
         double sigma_mu = sigma * mu;
         sigma_mu = sigma_mu > tau_min ? sigma_mu : tau_min;
-        /* COMPUTE_CENTERING_CORRECTION_QP */
-        for (int k = lane; k < N * NB; k += 32) I.res_m[k] = I.res_m_bkp[k] + I.dt_[k] * I.dlam[k] - sigma_mu;
-        rd_sync();
-        ipm_backward(D, I, sm, I.res_g, I.res_b, I.res_d, I.res_m, I.dux, 1);
-        ipm_forward(D, I, sm, I.res_b, I.dux, 1);
-        ipm_dpi(D, I, I.dux, I.dpi, 1);
-        ipm_dlam_dt(D, I, I.res_d, I.res_m, I.dux, I.dlam, I.dt_);
-        alpha = ipm_alpha(D, I, I.dlam, I.dt_);
+        /* corrector: centering + second-order correction */
+        ipm_backward<1, 1>(D, I, sm, I.res_g, I.res_b, I.res_d, nullptr, sigma_mu, I.dux);
+        ipm_forward<1>(D, I, sm, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
         /* conditional predictor-corrector */
         const double mu_aff0 = mu_aff;
-        mu_aff = ipm_mu_aff(D, I, alpha, nc_inv);
+        mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         if (mu_aff > 2.0 * mu_aff0)
         {
-            for (int k = lane; k < N * NB; k += 32) I.res_m[k] = I.res_m_bkp[k] - sigma_mu; /* COMPUTE_CENTERING_QP */
-            rd_sync();
-            ipm_backward(D, I, sm, I.res_g, I.res_b, I.res_d, I.res_m, I.dux, 1);
-            ipm_forward(D, I, sm, I.res_b, I.dux, 1);
-            ipm_dpi(D, I, I.dux, I.dpi, 1);
-            ipm_dlam_dt(D, I, I.res_d, I.res_m, I.dux, I.dlam, I.dt_);
-            alpha = ipm_alpha(D, I, I.dlam, I.dt_);
+            ipm_backward<2, 1>(D, I, sm, I.res_g, I.res_b, I.res_d, nullptr, sigma_mu, I.dux);
+            ipm_forward<1>(D, I, sm, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
         }
         /* iterative refinement of the corrector step, itref_corr_max = 2 */
         int refined = 0;
         for (int it = 0; it < 2; it++)
         {
-            ipm_res(D, I, 1, I.res_g, I.res_b, I.res_d, I.res_m, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, I.ig, I.ib, I.id, I.im,
-                    inrm);
+            ipm_res<1, 0>(D, I, I.res_g, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, nullptr, nullptr,
+                          nullptr, nullptr, inrm);
             if ((inrm[0] < tol || inrm[0] < 1e-3 * nrm[0]) && (inrm[1] < tol || inrm[1] < 1e-3 * nrm[1]) &&
                 (inrm[2] < tol || inrm[2] < 1e-3 * nrm[2]) && (inrm[3] < tol || inrm[3] < 1e-3 * nrm[3]))
                 break;
-            ipm_backward(D, I, sm, I.ig, I.ib, I.id, I.im, I.iux, 0);
-            ipm_forward(D, I, sm, I.ib, I.iux, 1);
-            ipm_dpi(D, I, I.iux, I.ipi, 1);
-            ipm_dlam_dt(D, I, I.id, I.im, I.iux, I.ilam, I.it);
+            ipm_res<1, 1>(D, I, I.res_g, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, I.ig, I.ib, I.id,
+                          I.im, inrm);
+            double a2, s2[2];
+            ipm_backward<0, 0>(D, I, sm, I.ig, I.ib, I.id, I.im, 0.0, I.iux);
+            ipm_forward<1>(D, I, sm, I.ib, I.id, I.im, 0.0, I.iux, I.ipi, I.ilam, I.it, &a2, s2);
             refined = 1;
-            for (int k = lane; k < (N + 1) * NV; k += 32) I.dux[k] += I.iux[k];
-            for (int k = lane; k < N * NX; k += 32) I.dpi[k] += I.ipi[k];
-            for (int k = lane; k < N * NB; k += 32) { I.dlam[k] += I.ilam[k]; I.dt_[k] += I.it[k]; }
+            for (int k = lane; k < (N + 1) * NV; k += GL) I.dux[k] += I.iux[k];
+            for (int k = lane; k < N * NX; k += GL) I.dpi[k] += I.ipi[k];
+            for (int k = lane; k < N * NB; k += GL) { I.dlam[k] += I.ilam[k]; I.dt_[k] += I.it[k]; }
             rd_sync();
         }
         if (refined) alpha = ipm_alpha(D, I, I.dlam, I.dt_);
-        /* UPDATE_VAR_QP (x_core_qp_ipm_aux.c:267-372) */
         double a = alpha;
         if (a < 1.0) a = a * ((1.0 - a) * 0.99 + a * 0.9999999);
-        for (int k = lane; k < (N + 1) * NV; k += 32) I.sux[k] += a * I.dux[k];
-        for (int k = lane; k < N * NX; k += 32) I.spi[k] += a * I.dpi[k];
-        for (int k = lane; k < N * NB; k += 32)
-        {
-            const int i = k / NB, j = k - NB * i;
-            if (i == 0 && (j % 12) >= 6) continue;
-            double l = I.slam[k] + a * I.dlam[k], t = I.st[k] + a * I.dt_[k];
-            I.slam[k] = l <= lmin ? lmin : l;
-            I.st[k] = t <= lmin ? lmin : t;
-        }
-        rd_sync();
-        mu = nc_inv * ipm_res(D, I, 0, I.rqz, I.b, I.d, nullptr, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g, I.res_b,
-                              I.res_d, I.res_m, nrm);
+        ipm_update(D, I, a);
+        sum_lt = ipm_res<0, 1>(D, I, I.rqz, I.b, I.d, nullptr, 0.0, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g, I.res_b,
+                               I.res_d, I.res_m, nrm);
+        mu = nc_inv * sum_lt;
     }
     *iters = kk;
     if (kk == D.qp_iter_max) return 2;
@@ -1188,8 +1353,11 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
         for (int mm = 0; mm < 5; mm++)
         {
             double w = 0.0;
-            for (int k = 0; k < 12; k++) w += Jc[12 * mm + k] * I.dx0[k];
-            tmp += Jc[12 * mm + lane] * w;
+            for (int k = 0; k < 6; k++) w += Jc[6 * mm + k] * I.dx0[k];
+            if (mm == 4)
+                for (int k = 0; k < 6; k++) w += Jc[30 + k] * I.dx0[6 + k];
+            if (lane < 6) tmp += Jc[6 * mm + lane] * w;
+            else if (mm == 4) tmp += Jc[30 + jj] * w;
         }
         if (lane >= 6) tmp += c.hs * I.sux[jj] + c.hq * I.dx0[lane];
         I.qlamx0[lane] = tmp >= 0.0 ? tmp : 1e-16;
@@ -1207,13 +1375,13 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
 RD int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I, int nlp_iter, double *alpha_out)
 {
     const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < N * NX; k += 32)
+    for (int k = lane; k < N * NX; k += GL)
     {
         const double t0 = fabs(I.spi[k]);
         if (nlp_iter == 0) I.wpi[k] = t0;
         else { const double t1 = 0.5 * (t0 + I.wpi[k]); I.wpi[k] = t0 > t1 ? t0 : t1; }
     }
-    for (int k = lane; k < N * NB + NB; k += 32)
+    for (int k = lane; k < N * NB + NB; k += GL)
     {
         const bool x0s = k >= N * NB;
         const int kk = x0s ? k - N * NB : k;
@@ -1229,7 +1397,7 @@ RD int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        for (int k = lane; k < (N + 1) * NV; k += 32) I.tux[k] = I.ux[k] + alpha * I.sux[k];
+        for (int k = lane; k < (N + 1) * NV; k += GL) I.tux[k] = I.ux[k] + alpha * I.sux[k];
         rd_sync();
         m1 = nlp_merit(ch, D, I, I.tux, I.z);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
@@ -1238,21 +1406,21 @@ RD int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst
     }
     *alpha_out = alpha;
     if (!accepted && ((m1 != m1) || (m1 - m1 != 0.0))) return 1;
-    for (int k = lane; k < (N + 1) * NV; k += 32) I.ux[k] = I.ux[k] + alpha * I.sux[k];
-    for (int k = lane; k < N * NX; k += 32) I.pi[k] = (1.0 - alpha) * I.pi[k] + alpha * I.spi[k];
-    for (int k = lane; k < N * NB; k += 32)
+    for (int k = lane; k < (N + 1) * NV; k += GL) I.ux[k] = I.ux[k] + alpha * I.sux[k];
+    for (int k = lane; k < N * NX; k += GL) I.pi[k] = (1.0 - alpha) * I.pi[k] + alpha * I.spi[k];
+    for (int k = lane; k < N * NB; k += GL)
     {
         if (k < NB && (k % 12) >= 6) continue;
         I.lam[k] = (1.0 - alpha) * I.lam[k] + alpha * I.slam[k];
     }
-    if (lane < NB) I.lamx0[lane] = (1.0 - alpha) * I.lamx0[lane] + alpha * I.qlamx0[lane];
+    for (int k = lane; k < NB; k += GL) I.lamx0[k] = (1.0 - alpha) * I.lamx0[k] + alpha * I.qlamx0[k];
     rd_sync();
     return 0;
 }
 
 /* ocp_qp_xcond_solve (AC/ocp_qp/ocp_qp_xcond_solver.c:518-576): reduce -> IPM -> restore.  warm start bookkeeping:
  * flags[1] != 0 until the first QP of the instance's lifetime has been solved (reference quirk, see ipm_init). */
-RD int qp_solve(const RmpcDims &D, const Inst &I, WarpSmem &sm, int init_from_nlp, int *iters)
+RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp, int *iters)
 {
     const int N = D.N, lane = rd_lane();
     const int warm = I.flags[1] ? 2 : 0;
@@ -1262,8 +1430,8 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, WarpSmem &sm, int init_from_nl
     if (init_from_nlp && warm == 2)
     {
         /* ocp_nlp_initialize_qp_from_nlp (AC/ocp_nlp/ocp_nlp_common.c:3320-3340) + ocp_qp_compute_t at ux = 0 */
-        for (int k = lane; k < N * NX; k += 32) I.spi[k] = I.pi[k];
-        for (int k = lane; k < N * NB; k += 32)
+        for (int k = lane; k < N * NX; k += GL) I.spi[k] = I.pi[k];
+        for (int k = lane; k < N * NB; k += GL)
         {
             if (k < NB && (k % 12) >= 6) continue;
             I.slam[k] = I.lam[k];
@@ -1283,7 +1451,7 @@ struct StepOut
 };
 
 /* ocp_nlp_sqp_rti, PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
-RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, WarpSmem &sm, StepOut &o)
+RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
 {
     nlp_linearise(ch, D, I, I.z);
     const int first = I.flags[0];
@@ -1301,7 +1469,7 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, WarpSme
 }
 
 /* ocp_nlp_sqp (AC/ocp_nlp/ocp_nlp_sqp.c:474-801) with check_termination (:351-443) */
-RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, WarpSmem &sm, StepOut &o)
+RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
 {
     o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0;
     for (int it = 0; it <= D.max_iter; it++)
@@ -1330,12 +1498,13 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, WarpSme
 /* ---------------------------------------------------------------------------------------------- closed loop (K5)
  * R/simulator.py:199-241: x = plant state; solver.set(0,'lbx'/'ubx',x); solve; u = solver.get(0,'u'); plant RK4.
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
-RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, WarpSmem &sm, int nsteps,
+RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, GrpSmem &sm, int nsteps,
                          int advance = 1)
 {
     const Inst I = inst_view(W, D.N, inst);
     const int lane = rd_lane(), N = D.N;
     const double *par = I.par;
+    smem_consts(I, sm);
     /* tracking errors e1..e5 are logged at every plant sample incl. the initial state (Nsim + 1 samples,
      * R/simulation_model.py:24-38, R/simulator.py:265-344); RMSE / ITSE sums of R/simulator.py:347-390 */
     if (W.summary && W.step0 == 0 && lane == 0 && advance)
@@ -1354,14 +1523,15 @@ RD void closed_loop_warp(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W
         else solve_sqp(ch, D, I, sm, o);
         /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679) */
         double cost = 0.0;
-        for (int i = lane; i < N; i += 32)
+        for (int i = lane; i < N; i += GL)
         {
             double v[NV], y5[5];
             load18(I.ux + NV * i, v);
-            ur10_task<false>(ch, par, v + 6, v + 12, y5, nullptr);
+            NoEmit ne;
+            ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
             cost += stage_cost(par, D.dt, y5, v, v + 12);
         }
-        cost = warp_sum(cost);
+        cost = grp_sum(cost);
         double zq = 0.0, zqd = 0.0, u = 0.0;
         if (lane < 6)
         {

@@ -11,7 +11,7 @@
     X(sux, (S) * RMPC_NV) X(spi, (S) * RMPC_NX) X(slam, (S) * RMPC_NB) X(st, (S) * RMPC_NB) X(qlamx0, RMPC_NB)        \
     X(dux, (S) * RMPC_NV) X(dpi, (S) * RMPC_NX) X(dlam, (S) * RMPC_NB) X(dt_, (S) * RMPC_NB)                          \
     X(res_g, (S) * RMPC_NV) X(res_b, (S) * RMPC_NX) X(res_d, (S) * RMPC_NB) X(res_m, (S) * RMPC_NB)                   \
-    X(res_m_bkp, (S) * RMPC_NB) X(pvec, (S) * RMPC_NX) X(Pb, (S) * RMPC_NX) X(L, (S) * RMPC_LS)                       \
+    X(res_mc, (S) * RMPC_NB) X(pvec, (S) * RMPC_NX) X(F, (S) * RMPC_FS)                                               \
     X(ig, (S) * RMPC_NV) X(ib, (S) * RMPC_NX) X(id, (S) * RMPC_NB) X(im, (S) * RMPC_NB)                               \
     X(iux, (S) * RMPC_NV) X(ipi, (S) * RMPC_NX) X(ilam, (S) * RMPC_NB) X(it, (S) * RMPC_NB) X(tux, (S) * RMPC_NV)
 

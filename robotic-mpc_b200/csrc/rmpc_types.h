@@ -1,12 +1,13 @@
 /* robotic-mpc_b200/csrc/rmpc_types.h -- plain-data structures shared by the host side of the C-ABI and the kernels.
  *
  * Layout of a batch in HBM ("instance-major"): every array below is [B][...] with one contiguous chunk per
- * instance; ONE WARP owns one instance for the whole closed loop, so inside a chunk the fastest index is the one
- * the 32 lanes sweep (component within a stage block for the Riccati sweeps, flat element index for the
- * element-wise interior-point updates).  Stage blocks use fixed strides:
+ * instance; a GROUP of RMPC_G lanes (half a warp by default) owns one instance for the whole closed loop, so inside
+ * a chunk the fastest index is the one the lanes sweep (component within a stage block for the Riccati sweeps,
+ * stage index for the stage-parallel passes).  Stage blocks use fixed strides:
  *     NV = 18 ([u(6); x(12)], stage N keeps the same slot layout with u unused)
  *     NX = 12,  NB = 24 ([lower(12); upper(12)] over [u(6); q(6)], stage 0 uses only the u slots in the QP)
- *     LS = 192 (packed lower-trapezoidal 19x18 Riccati factor: 189 doubles, padded)
+ *     NJ = 36 (scaled task Jacobian: 5 rows x 6 joint-angle columns + the 6 joint-velocity entries of row 5)
+ *     FS = 208 (Riccati factor block of one stage, RF_* offsets below)
  */
 #ifndef RMPC_TYPES_H
 #define RMPC_TYPES_H
@@ -15,11 +16,25 @@
 #define RMPC_NU 6
 #define RMPC_NV 18
 #define RMPC_NB 24
-#define RMPC_LS 192
-#define RMPC_NJ 60  /* 5 task rows x 12 state columns of the scaled task Jacobian */
+#define RMPC_NJ 36
+#define RMPC_FS 208
 
 #define RMPC_SQP 0
 #define RMPC_SQP_RTI 1
+
+/* Riccati factor block of one stage (doubles).  With M = [[R S'],[S Q]] + diag(Gamma) + reg I + [B A]' P+ [B A]:
+ *   Luu Luu' = Muu,  Lxu = Mxu Luu^-T,  l_u = Luu^-1 m_u,  P = Mxx - Lxu Lxu',  p = m_x - Lxu l_u            */
+enum
+{
+    RF_INV = 0,   /* 6 : 1 / diag(Luu) (+inf where the pivot was not positive, as a division by 0 would give) */
+    RF_LU = 6,    /* 6 : l_u */
+    RF_LUU = 12,  /* 15: strict lower part of Luu, row-major packed (row r at r(r-1)/2) */
+    RF_LXU = 28,  /* 72: Lxu, 12 x 6 row-major, rows in state order [q; qd] */
+    RF_P = 100,   /* 78: P, packed lower, row r at r(r+1)/2 */
+    RF_PV = 178,  /* 12: p */
+    RF_PB = 190,  /* 12: P+ b  (P of the NEXT stage times this stage's res_b) */
+    RF_END = 202
+};
 
 /* per-instance parameter block (doubles) */
 enum
@@ -95,11 +110,12 @@ typedef struct
     int *flags;        /* [B][4]: first_call, qp_warm2_pending, n_lq_needed, reserved */
     /* linearisation / QP data */
     double *Jc, *rqz, *b, *d, *dx0, *g0u;
-    /* IPM */
+    /* IPM iterate, step, residuals */
     double *sux, *spi, *slam, *st, *qlamx0;
     double *dux, *dpi, *dlam, *dt_;
-    double *res_g, *res_b, *res_d, *res_m, *res_m_bkp;
-    double *pvec, *Pb, *L;
+    double *res_g, *res_b, *res_d, *res_m, *res_mc;
+    double *pvec, *F;
+    /* iterative refinement (rare path) and line-search trial point */
     double *ig, *ib, *id, *im, *iux, *ipi, *ilam, *it;
     double *tux;
     /* logs (may be null) */

@@ -1,5 +1,5 @@
 /* tests/simt_emu/emu_driver.cpp -- TEST HARNESS ONLY: runs the device code of robotic-mpc_b200/csrc/rmpc_device.cuh
- * on the host warp emulator (simt_emu.h), one emulated warp per instance, so tests/ can check the kernels' logic
+ * on the host lane emulator (simt_emu.h), one emulated group of RMPC_G lanes per instance, so tests/ can check the kernels' logic
  * against the oracle without a GPU.  Not part of the product library. */
 #define RMPC_EMU 1
 #include <cstdlib>
@@ -18,12 +18,12 @@ struct Job
     const RmpcWs *W;
     long inst;
     int nsteps;
-    WarpSmem *sm;
+    GrpSmem *sm;
 };
 void body(void *p, int)
 {
     Job *j = (Job *) p;
-    closed_loop_warp(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
+    closed_loop_group(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
 }
 }  // namespace
 
@@ -54,12 +54,12 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
         W.flags[i * 4 + 0] = 1;
         W.flags[i * 4 + 1] = 1;
     }
-    WarpSmem sm;
+    GrpSmem sm;
     for (long i = 0; i < B; i++)
     {
         memset(&sm, 0, sizeof(sm));
         Job j{&ch, D, &W, i, nsteps, &sm};
-        simt_emu::run_warp(body, &j, seed);
+        simt_emu::run_warp(body, &j, seed, GL);
     }
     if (flags_out) memcpy(flags_out, W.flags, (size_t) B * 4 * sizeof(int));
     for (double *p : owned) free(p);

@@ -39,7 +39,7 @@ static void trampoline()
     abort(); /* never resumed */
 }
 
-void run_warp(void (*fn)(void *, int), void *arg, uint64_t seed)
+void run_warp(void (*fn)(void *, int), void *arg, uint64_t seed, int nlanes)
 {
     Warp w;
     memset(&w, 0, sizeof(w));
@@ -58,6 +58,7 @@ void run_warp(void (*fn)(void *, int), void *arg, uint64_t seed)
         for (int k = 0; k < 6; k++) *(--sp) = nullptr;
         w.lane_sp[l] = sp;
     }
+    for (int l = nlanes; l < kLanes; l++) w.done[l] = true; /* lanes beyond the group never run */
     Warp *prev = g_warp;
     g_warp = &w;
     int order[kLanes];

@@ -6,7 +6,7 @@
  * It is NOT a CPU fallback: the product library (librmpc.so) contains no host implementation of the solver and
  * fails loudly without a CUDA device; nothing outside tests/ links this file.
  *
- * Model: 32 lanes = 32 fibers of one OS thread.  A lane runs until it reaches a warp-wide primitive
+ * Model: a group of up to 32 lanes = that many fibers of one OS thread.  A lane runs until it reaches a warp-wide primitive
  * (shuffle / syncwarp), then yields to the scheduler, which resumes the lanes of each epoch in a pseudo-random
  * order (seeded) -- so code that forgets a __syncwarp between a write by one lane and a read by another fails
  * here with high probability instead of passing by luck.
@@ -60,6 +60,6 @@ inline double shfl(double v, int src)
 inline double shfl_xor(double v, int m) { return shfl(v, lane_id() ^ m); }
 inline int shfl_i(int v, int src) { return (int) shfl((double) v, src); }
 
-/* run fn(arg, lane) on 32 lock-step lanes */
-void run_warp(void (*fn)(void *, int), void *arg, uint64_t seed);
+/* run fn(arg, lane) on nlanes (<= 32) lock-step lanes */
+void run_warp(void (*fn)(void *, int), void *arg, uint64_t seed, int nlanes = kLanes);
 }  // namespace simt_emu

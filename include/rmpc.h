@@ -93,9 +93,12 @@ int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);
  * (T/acados_ocp_solver.py:939-989,1461-1723).  Fields, with the shape written to `dev`:
  *   "x" [B][12], "u" [B][6], "pi" [B][12], "lam" [B][24] ([lower(12); upper(12)] over [u; q]) of `stage`
  *   "z" [B][12] plant state
- *   "stats" [B][10]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
- *                    alpha, qp_status (RL_* in csrc/rmpc_types.h); needs nlog > 0
- *   "zlog" [B][nlog+1][12], "ulog" [B][nlog][6], "slog" [B][nlog][10]   closed-loop logs
+ *   "stats" [B][12]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
+ *                    alpha, qp_status, device time of the solve in seconds (RL_* in csrc/rmpc_types.h); needs nlog > 0
+ *   "zlog" [B][nlog+1][12], "ulog" [B][nlog][6], "slog" [B][nlog][12]   closed-loop logs
+ *   "plog" [B][nlog+1][28]  per-sample plant record computed from zlog: pose of frame ee_link (12), rpy (3), WORLD
+ *                    twist (6), tracking errors e1..e5 (5), task-frame z (RK_* in csrc/rmpc_types.h)
+ *                    -- the logs of R/simulation_model.py:60-77,85-91 and the error series of R/simulator.py:265-344
  *   "summary" [B][20]  RS_* in csrc/rmpc_types.h: sum e^2 (5), ITSE (5), failures, sqp/qp iteration totals,
  *                      max KKT residuals (4), last cost, number of samples
  *   "flags" [B][4] as doubles: first_call, qp_warm_pending, LQ-fallback triggers, reserved

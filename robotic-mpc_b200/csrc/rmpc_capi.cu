@@ -63,6 +63,22 @@ __global__ void rmpc_strided_copy_kernel(double *packed, double *strided, long B
     }
 }
 
+/* one thread per logged plant sample: pose / rpy / twist logs and tracking errors (R/simulation_model.py:60-77,
+ * R/simulator.py:265-344), out = [B][nlog+1][RK_COUNT] */
+__global__ void rmpc_plant_logs_kernel(const RmpcChain ch, const double *par, const double *zlog, double *out, long B, int nsamp)
+{
+    const long tot = B * nsamp;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
+    {
+        const long i = k / nsamp;
+        double z[NX], e[5], rec[RK_COUNT];
+        for (int c = 0; c < NX; c++) z[c] = zlog[k * NX + c];
+        rec[RK_COUNT - 1] = 0.0;
+        ur10_plant_record<true>(ch, par + i * RP_COUNT, z, z + 6, e, rec);
+        for (int c = 0; c < RK_COUNT; c++) out[k * RK_COUNT + c] = rec[c];
+    }
+}
+
 __global__ void rmpc_flags_to_double_kernel(const int *flags, double *out, long n)
 {
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long) gridDim.x * blockDim.x) out[k] = flags[k];
@@ -283,9 +299,16 @@ extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *de
         CU(cudaGetLastError());
         return 0;
     }
-    if (f == "stats" || f == "zlog" || f == "ulog" || f == "slog")
+    if (f == "stats" || f == "zlog" || f == "ulog" || f == "slog" || f == "plog")
     {
         if (h->nlog <= 0) return fail(h, RMPC_EINVAL, "rmpc_get: handle was created with nlog = 0, no logs");
+        if (f == "plog")
+        {
+            rmpc_plant_logs_kernel<<<grid_for(B * (h->nlog + 1)), 256, 0, s>>>(h->ch, h->par_dev, h->W.zlog, dev, B, h->nlog + 1);
+            h->launches++;
+            CU(cudaGetLastError());
+            return 0;
+        }
         if (f == "zlog") { CU(cudaMemcpyAsync(dev, h->W.zlog, sizeof(double) * B * (h->nlog + 1) * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
         if (f == "ulog") { CU(cudaMemcpyAsync(dev, h->W.ulog, sizeof(double) * B * h->nlog * 6, cudaMemcpyDeviceToDevice, s)); return 0; }
         if (f == "slog") { CU(cudaMemcpyAsync(dev, h->W.slog, sizeof(double) * B * h->nlog * RL_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }

@@ -49,6 +49,7 @@ RD double rd_rsqrt(double x) { return 1.0 / sqrt(x); }
 RD void rd_sincos(double a, double *s, double *c) { *s = sin(a); *c = cos(a); }
 RD double rd_fmax(double a, double b) { return a > b ? a : b; } /* NaN-ignoring like fmax for our uses */
 RD double rd_inf() { return INFINITY; }
+RD double rd_time() { return 0.0; }
 #define RD_UNROLL
 struct rd_double2 { double x, y; };
 #else
@@ -66,6 +67,12 @@ RD double rd_rsqrt(double x) { return rsqrt(x); }
 RD void rd_sincos(double a, double *s, double *c) { sincos(a, s, c); }
 RD double rd_fmax(double a, double b) { return a > b ? a : b; }
 RD double rd_inf() { return __longlong_as_double(0x7ff0000000000000LL); }
+RD double rd_time() /* seconds on the GPU's global nanosecond timer */
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return 1e-9 * (double) t;
+}
 #define RD_UNROLL _Pragma("unroll")
 typedef double2 rd_double2;
 #endif
@@ -300,8 +307,9 @@ RD void ur10_task(const RmpcChain &ch, const double *par, const double *q, const
 
 /* plant logs: pose of frame ee_link and WORLD twist J qd (R/simulation_model.py:60-77), then the post-hoc tracking
  * errors e1..e5 of R/simulator.py:301-342 -- NB e5 deliberately uses the reference's own formula
- * R_w_t (v + (w . t_w)), not the OCP's g5. */
-RD void ur10_tracking_errors(const RmpcChain &ch, const double *par, const double *q, const double *qd, double *e)
+ * R_w_t (v + (w . t_w)), not the OCP's g5.  REC = 1 also writes the per-sample record RK_* (rmpc_types.h). */
+template <bool REC>
+RD void ur10_plant_record(const RmpcChain &ch, const double *par, const double *q, const double *qd, double *e, double *rec)
 {
     double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, p[3] = {0, 0, 0};
     double tws[6] = {0, 0, 0, 0, 0, 0};
@@ -370,6 +378,25 @@ RD void ur10_tracking_errors(const RmpcChain &ch, const double *par, const doubl
     e[2] = Re[1];
     e[3] = par[RP_PXREF] - pt[0];
     e[4] = par[RP_VYREF] - vt1;
+    if (REC)
+    { /* the per-sample logs of R/simulation_model.py:60-77,85-91 and R/simulator.py:344 */
+        RD_UNROLL
+        for (int r = 0; r < 3; r++) rec[RK_POSE + r] = pe[r];
+        RD_UNROLL
+        for (int r = 0; r < 9; r++) rec[RK_POSE + 3 + r] = Re[r];
+        rec[RK_RPY] = atan2(Re[7], Re[8]);
+        rec[RK_RPY + 1] = atan2(-Re[6], sqrt(Re[0] * Re[0] + Re[3] * Re[3]));
+        rec[RK_RPY + 2] = atan2(Re[3], Re[0]);
+        RD_UNROLL
+        for (int r = 0; r < 6; r++) rec[RK_TWIST + r] = tws[r];
+        RD_UNROLL
+        for (int r = 0; r < 5; r++) rec[RK_ERR + r] = e[r];
+        rec[RK_PTZ] = pt[2];
+    }
+}
+RD void ur10_tracking_errors(const RmpcChain &ch, const double *par, const double *q, const double *qd, double *e)
+{
+    ur10_plant_record<false>(ch, par, q, qd, e, nullptr);
 }
 /* ---------------------------------------------------------------------------------------------- NLP level (K2, K4)
  * Per-instance constants of the Gauss-Newton Hessian that do not depend on the stage:
@@ -1519,8 +1546,10 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
     {
         const int gs = W.step0 + s;
         StepOut o;
+        const double t_begin = rd_time();
         if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o);
         else solve_sqp(ch, D, I, sm, o);
+        const double t_solve = rd_time() - t_begin; /* stands in for get_stats('time_tot') (R/simulator.py:220) */
         /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679) */
         double cost = 0.0;
         for (int i = lane; i < N; i += GL)
@@ -1567,7 +1596,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
                 double *sl = W.slog + (inst * W.nlog + gs) * RL_COUNT;
                 sl[RL_STATUS] = o.status; sl[RL_SQP_ITER] = o.sqp_iter; sl[RL_QP_ITER] = o.qp_iter; sl[RL_COST] = cost;
                 sl[RL_RES] = o.res[0]; sl[RL_RES + 1] = o.res[1]; sl[RL_RES + 2] = o.res[2]; sl[RL_RES + 3] = o.res[3];
-                sl[RL_ALPHA] = o.alpha; sl[RL_QP_STATUS] = o.qp_status;
+                sl[RL_ALPHA] = o.alpha; sl[RL_QP_STATUS] = o.qp_status; sl[RL_TIME] = t_solve; sl[RL_TIME + 1] = 0.0;
             }
             if (W.summary)
             {

@@ -65,7 +65,19 @@ enum
     RL_RES = 4,     /* 4: stat eq ineq comp (zeros for SQP_RTI, like the reference) */
     RL_ALPHA = 8,   /* accepted line-search step of the last SQP iteration */
     RL_QP_STATUS = 9,
-    RL_COUNT = 10
+    RL_TIME = 10,   /* seconds this instance's solve took on the device (GPU global timer), stands in for time_tot */
+    RL_COUNT = 12
+};
+
+/* per-sample plant record computed from the logged plant states (R/simulation_model.py:60-77, R/simulator.py:265-344) */
+enum
+{
+    RK_POSE = 0,    /* 12: p_ee(3), R_ee row-major(9) of frame ee_link */
+    RK_RPY = 12,    /* 3 : roll pitch yaw of R_ee */
+    RK_TWIST = 15,  /* 6 : WORLD twist J qd */
+    RK_ERR = 21,    /* 5 : tracking errors e1..e5 */
+    RK_PTZ = 26,    /* 1 : z of the task-frame origin */
+    RK_COUNT = 28
 };
 
 /* summary row per instance accumulated on device (R/simulator.py:347-390 metrics + solver_stats) */

@@ -10,7 +10,7 @@ from pathlib import Path
 
 import numpy as np
 
-from .params import RL, RP, RS
+from .params import RK, RL, RP, RS
 
 HERE = Path(__file__).resolve().parent
 LIB_PATH = HERE / "librmpc.so"
@@ -165,7 +165,8 @@ class Engine:
         B, nl = self.B, self.nlog
         shape = {"x": (B, 12), "u": (B, 6), "pi": (B, 12), "lam": (B, 24), "lamx0": (B, 24), "z": (B, 12),
                  "stats": (B, RL["COUNT"]), "summary": (B, RS["COUNT"]), "flags": (B, 4),
-                 "zlog": (B, nl + 1, 12), "ulog": (B, nl, 6), "slog": (B, nl, RL["COUNT"])}[field]
+                 "zlog": (B, nl + 1, 12), "ulog": (B, nl, 6), "slog": (B, nl, RL["COUNT"]),
+                 "plog": (B, nl + 1, RK["COUNT"])}[field]
         out = self.torch.empty(shape, dtype=self.torch.float64, device=self.tdev)
         self._check(self.lib.rmpc_get(self.h, field.encode(), int(stage), C.c_void_p(out.data_ptr()), self._stream()),
                     f"rmpc_get({field})")

@@ -12,7 +12,8 @@ import numpy as np
 
 RP = dict(SURF=0, A12=6, A22=12, B1=18, B2=24, WCV=30, WU=36, WQDD=37, PXREF=38, VYREF=39, WTASK=40, UMIN=45,
           UMAX=51, QMIN=57, QMAX=63, TEE=69, COUNT=72)
-RL = dict(STATUS=0, SQP_ITER=1, QP_ITER=2, COST=3, RES=4, ALPHA=8, QP_STATUS=9, COUNT=10)
+RL = dict(STATUS=0, SQP_ITER=1, QP_ITER=2, COST=3, RES=4, ALPHA=8, QP_STATUS=9, TIME=10, COUNT=12)
+RK = dict(POSE=0, RPY=12, TWIST=15, ERR=21, PTZ=26, COUNT=28)
 RS = dict(SSE=0, ITSE=5, NFAIL=10, SQP_ITERS=11, QP_ITERS=12, MAX_RES=13, COST_LAST=17, NSAMPLES=18, COUNT=20)
 
 DEFAULT_SURFACE = (-0.15, 0.15, -0.01, 0.01, 0.01, 0.0)

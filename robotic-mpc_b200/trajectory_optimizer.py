@@ -1,0 +1,262 @@
+"""OCP formulation and solver handles -- host-side mirror of ``R/trajectory_optimizer.py`` (class ``MPC``) and of the
+``AcadosOcpSolver`` methods the reference calls on it (``T/acados_ocp_solver.py:468-476,939-989,1461-1723,1743-1819``).
+
+``MPC`` keeps the reference's constructor signature and attributes (``w_*``, ``px_ref``, ``vy_ref``,
+``ocp.solver_options.<attr>``, ``finalize_solver()``, ``.solver``).  Nothing is code-generated: the formulation is fixed
+(UR10 surface tracking) and lives in the CUDA kernels; the objects below only carry its
+per-instance DATA to the engine's parameter block.
+
+``BatchedSolver`` is the solver interface for B instances at once (same method names, ``[B, ...]`` arrays);
+``SolverView`` is one instance's window onto it so that ``sim.mpc.solver.get(0, 'u')`` keeps working.
+There is no CPU path: creating a solver without the CUDA library / a GPU raises ``RmpcError``.
+"""
+from __future__ import annotations
+
+import uuid
+
+import numpy as np
+
+from .params import RL, pack_params
+
+_SUPPORTED_FIXED = {  # option -> the only value(s) the engine implements (the reference never uses another one)
+    "qp_solver": ("PARTIAL_CONDENSING_HPIPM",),
+    "hessian_approx": ("GAUSS_NEWTON",),
+    "integrator_type": ("DISCRETE",),
+    "globalization": ("MERIT_BACKTRACKING",),
+    "qp_solver_warm_start": (2,),
+    "nlp_solver_warm_start_first_qp": (True,),
+}
+
+
+class SolverOptions:
+    """The subset of ``AcadosOcpOptions`` the hot path reads, with the values ``MPC.__init__`` / acados resolve
+    (``R/trajectory_optimizer.py:60-70``, ``T/acados_ocp_options.py:45-165``)."""
+
+    def __init__(self, N_horizon=None, tf=None):
+        self.nlp_solver_type = "SQP"
+        self.hessian_approx = "GAUSS_NEWTON"
+        self.print_level = 0
+        self.qp_solver = "PARTIAL_CONDENSING_HPIPM"
+        self.qp_tol = 1e-8
+        self.integrator_type = "DISCRETE"
+        self.nlp_solver_warm_start_first_qp = True
+        self.qp_solver_warm_start = 2
+        self.nlp_solver_max_iter = 100
+        self.globalization = "MERIT_BACKTRACKING"
+        self.N_horizon = N_horizon
+        self.tf = tf
+        self.qp_solver_iter_max = 50
+        self.qp_solver_cond_N = None
+        self.nlp_solver_tol_stat = 1e-6
+        self.nlp_solver_tol_eq = 1e-6
+        self.nlp_solver_tol_ineq = 1e-6
+        self.nlp_solver_tol_comp = 1e-6
+
+    def validate(self):
+        if self.nlp_solver_type not in ("SQP", "SQP_RTI"):
+            raise NotImplementedError(f"nlp_solver_type {self.nlp_solver_type!r}: the engine implements SQP and SQP_RTI")
+        for key, allowed in _SUPPORTED_FIXED.items():
+            if getattr(self, key) not in allowed:
+                raise NotImplementedError(f"solver option {key}={getattr(self, key)!r} is not implemented "
+                                          f"(supported: {allowed}); see DESIGN.md 'out of scope'")
+        if self.qp_solver_cond_N not in (None, self.N_horizon):
+            raise NotImplementedError("partial condensing with qp_solver_cond_N < N is not implemented (SURVEY.md 8(f))")
+
+    def static_key(self):
+        """What must be equal for two instances to share one batched launch."""
+        return (self.nlp_solver_type, int(self.nlp_solver_max_iter), int(self.qp_solver_iter_max), float(self.qp_tol),
+                float(self.nlp_solver_tol_stat), float(self.nlp_solver_tol_eq), float(self.nlp_solver_tol_ineq),
+                float(self.nlp_solver_tol_comp))
+
+
+class _Namespace:
+    pass
+
+
+class MPC:
+    """Same constructor as ``R/trajectory_optimizer.py:13-14``.  ``surface`` needs ``coeff_vector()`` (our ``Surface``) or
+    a ``coeffs`` dict; ``model`` needs ``Ts`` and ``Wcv`` (our ``SixDofRobot`` stand-in) or may be ``None`` when ``Ts`` /
+    ``wcv`` are passed explicitly."""
+
+    def __init__(self, surface, initial_state, model, N_horizon, Tf, qmin, qmax, dq_min, dq_max, w_u, w_qddot,
+                 px_ref=0.40, vy_ref=0.01, Ts=None, wcv=None):
+        self.surface = surface
+        self.surface_pos_world = surface.get_position() if hasattr(surface, "get_position") else None
+        self.surface_rpy_world = surface.get_orientation_rpy() if hasattr(surface, "get_orientation_rpy") else None
+        self.N_horizon = int(N_horizon)
+        self.Tf = float(Tf)
+        self.px_ref, self.vy_ref = float(px_ref), float(vy_ref)
+        self._instance_id = uuid.uuid4().hex[:8]
+        # task weights (R/trajectory_optimizer.py:44-48)
+        self.w_origin_task = 50.0
+        self.w_normal_alignment_task = 50.0
+        self.w_x_alignment_task = 50.0
+        self.w_fixed_x_task = 50.0
+        self.w_fixed_vy_task = 50.0
+        self.w_u = float(w_u)
+        self.w_qddot = float(w_qddot)
+        self.nx, self.nu = 12, 6
+        self.ny = self.nx + self.nu
+        self.Ts = float(Ts if Ts is not None else getattr(model, "Ts", self.Tf / self.N_horizon))
+        self.wcv = np.asarray(wcv if wcv is not None else getattr(model, "Wcv"), dtype=float).reshape(6)
+        self.translation = np.asarray(getattr(model, "translation", (0.0, 0.0, 0.1)), dtype=float).reshape(3)
+        self.initial_state = np.asarray(initial_state, dtype=float).reshape(12)
+        self.qmin, self.qmax = np.asarray(qmin, float).reshape(6), np.asarray(qmax, float).reshape(6)
+        self.dq_min, self.dq_max = np.asarray(dq_min, float).reshape(6), np.asarray(dq_max, float).reshape(6)
+        self.ocp = _Namespace()
+        self.ocp.solver_options = SolverOptions(N_horizon=self.N_horizon, tf=self.Tf)
+        self.ocp.constraints = _Namespace()
+        self.ocp.constraints.x0 = self.initial_state
+        self.ocp.constraints.lbu, self.ocp.constraints.ubu = self.dq_min, self.dq_max
+        self.ocp.constraints.lbx, self.ocp.constraints.ubx = self.qmin, self.qmax
+        self.solver = None
+
+    def task_weights(self):
+        return np.array([self.w_origin_task, self.w_normal_alignment_task, self.w_x_alignment_task, self.w_fixed_x_task,
+                         self.w_fixed_vy_task])
+
+    def param_row(self) -> np.ndarray:
+        """This instance's row of the engine parameter block (``RP_*``)."""
+        surf = self.surface.coeff_vector() if hasattr(self.surface, "coeff_vector") else \
+            np.array([self.surface.coeffs[k] for k in "abcdef"], float)
+        return pack_params(1, self.Ts, surf=surf, wcv=self.wcv, w_u=self.w_u, w_qddot=self.w_qddot, px_ref=self.px_ref,
+                           vy_ref=self.vy_ref, w_task=self.task_weights(), q_min=self.qmin, q_max=self.qmax,
+                           qdot_min=self.dq_min, qdot_max=self.dq_max, t_ee=self.translation)[0]
+
+    def static_key(self):
+        o = self.ocp.solver_options
+        return (self.N_horizon, round(self.Tf / self.N_horizon, 15)) + o.static_key()
+
+    def finalize_solver(self, device=0):
+        """Creates the solver handle (a batch of one).  ``SimulationManager.run_all`` binds many ``MPC`` objects to one
+        shared batch instead and never calls this."""
+        self.ocp.solver_options.validate()
+        bs = BatchedSolver([self], device=device)
+        self.solver = bs.view(0)
+        return self
+
+
+class BatchedSolver:
+    """``AcadosOcpSolver`` for B instances that share (N, dt, solver options): one engine handle on one GPU.
+
+    set / get take and return ``[B, n]`` arrays (numpy or torch); ``solve()`` runs ONE SQP / SQP_RTI solve of every
+    instance (``rmpc_solve``) and returns the ``[B]`` status vector."""
+
+    def __init__(self, mpcs, device=0, nlog=1):
+        from .engine import Engine
+
+        if not mpcs:
+            raise ValueError("BatchedSolver needs at least one MPC")
+        key = mpcs[0].static_key()
+        for m in mpcs:
+            m.ocp.solver_options.validate()
+            if m.static_key() != key:
+                raise ValueError("all instances of a batch must share N, dt and the solver options")
+        self.mpcs = list(mpcs)
+        self.B = len(mpcs)
+        o = mpcs[0].ocp.solver_options
+        self.N = mpcs[0].N_horizon
+        self.dt = mpcs[0].Tf / mpcs[0].N_horizon
+        self.engine = Engine(self.B, self.N, o.nlp_solver_type, dt=self.dt, nlog=max(int(nlog), 1), device=device,
+                             max_iter=o.nlp_solver_max_iter, qp_iter_max=o.qp_solver_iter_max,
+                             tol=[o.nlp_solver_tol_stat, o.nlp_solver_tol_eq, o.nlp_solver_tol_ineq, o.nlp_solver_tol_comp],
+                             qp_tol=o.qp_tol, plant_dt=mpcs[0].Ts)
+        self.engine.set_params(np.stack([m.param_row() for m in mpcs]))
+        self.engine.set_state(np.stack([m.initial_state for m in mpcs]))
+        self.engine.reset()
+        self._stats = None
+
+    def view(self, i):
+        return SolverView(self, i)
+
+    # ---- AcadosOcpSolver.set (T/acados_ocp_solver.py:1743-1819)
+    def set(self, stage, field, value):
+        if field in ("lbx", "ubx"):
+            if stage != 0:
+                raise NotImplementedError("only the stage-0 state bounds (= the initial-state constraint) can be set")
+            self.engine.set_state(value)  # the reference always sets lbx_0 = ubx_0 = x (R/simulator.py:210-211)
+        elif field in ("x", "u", "pi"):
+            self.engine.set(field, value, stage=stage)
+        else:
+            raise NotImplementedError(f"set(..., {field!r}): per-stage {field} is part of the per-instance parameter block; "
+                                      "rebuild the batch with new MPC parameters")
+        self._stats = None
+
+    def solve(self):
+        self.engine.solve()
+        self._stats = self.engine.get("stats").cpu().numpy()
+        return self._stats[:, RL["STATUS"]].astype(int)
+
+    # ---- AcadosOcpSolver.get (T/acados_ocp_solver.py:939-989)
+    def get(self, stage, field):
+        if field not in ("x", "u", "pi", "lam"):
+            raise NotImplementedError(f"get(..., {field!r})")
+        return self.engine.get(field, stage=stage).cpu().numpy()
+
+    def _need_stats(self):
+        if self._stats is None:
+            raise RuntimeError("call solve() first")
+        return self._stats
+
+    def get_stats(self, field):
+        s = self._need_stats()
+        if field == "sqp_iter":
+            return s[:, RL["SQP_ITER"]].astype(int)
+        if field == "qp_iter":
+            return s[:, RL["QP_ITER"]].astype(int)
+        if field == "time_tot":
+            return s[:, RL["TIME"]].copy()
+        if field == "statistics":
+            return s.copy()
+        raise NotImplementedError(f"get_stats({field!r})")
+
+    def get_residuals(self):
+        return self._need_stats()[:, RL["RES"]:RL["RES"] + 4].copy()
+
+    def get_cost(self):
+        return self._need_stats()[:, RL["COST"]].copy()
+
+    def get_status(self):
+        return self._need_stats()[:, RL["STATUS"]].astype(int)
+
+
+class SolverView:
+    """One instance of a ``BatchedSolver`` behind the scalar ``AcadosOcpSolver`` method names."""
+
+    def __init__(self, batch, index):
+        self.batch, self.i = batch, int(index)
+
+    def _row_update(self, getter_field, value, stage, setter):
+        cur = self.batch.engine.get(getter_field, stage=stage).cpu().numpy()
+        cur[self.i] = np.asarray(value, dtype=float).reshape(-1)
+        setter(cur)
+
+    def set(self, stage, field, value):
+        if field in ("lbx", "ubx"):
+            if stage != 0:
+                raise NotImplementedError("only the stage-0 state bounds (= the initial-state constraint) can be set")
+            self._row_update("z", value, 0, self.batch.engine.set_state)
+        elif field in ("x", "u", "pi"):
+            self._row_update(field, value, stage, lambda a: self.batch.engine.set(field, a, stage=stage))
+        else:
+            raise NotImplementedError(f"set(..., {field!r})")
+        self.batch._stats = None
+
+    def solve(self):
+        return int(self.batch.solve()[self.i])
+
+    def get(self, stage, field):
+        return self.batch.get(stage, field)[self.i]
+
+    def get_stats(self, field):
+        v = self.batch.get_stats(field)[self.i]
+        return v if field == "statistics" else v.item()
+
+    def get_residuals(self):
+        return self.batch.get_residuals()[self.i]
+
+    def get_cost(self):
+        return float(self.batch.get_cost()[self.i])
+
+    def get_status(self):
+        return int(self.batch.get_status()[self.i])

@@ -23,7 +23,10 @@
 static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layout mismatch");
 
 /* ------------------------------------------------------------------------------------------------ kernels */
-__global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, 4)
+#ifndef RMPC_MIN_CTAS
+#define RMPC_MIN_CTAS 4
+#endif
+__global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, RMPC_MIN_CTAS)
 rmpc_closed_loop_kernel(const RmpcChain ch, const RmpcDims D, const RmpcWs W, int nsteps, int advance)
 {
     __shared__ GrpSmem smem[RMPC_GROUPS_PER_CTA];
@@ -40,9 +43,9 @@ __global__ void rmpc_init_iterate_kernel(const RmpcDims D, const RmpcWs W)
     const long tot = (long) D.B * S * NV;
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
     {
-        const long i = k / (S * NV);
+        const long i = k / (S * NV), r = k % (S * NV);
         const int c = (int) (k % NV);
-        W.ux[k] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
+        W.slab[i * W.slab_stride + W.off[RA_ux] + r] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
     }
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < (long) D.B * 4; k += (long) gridDim.x * blockDim.x)
         W.flags[k] = (k % 4) < 2 ? 1 : 0;
@@ -149,6 +152,7 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     rmpc_chain_init(&h->ch);
     memset(&h->W, 0, sizeof(h->W));
     h->device = device; h->nlog = nlog; h->steps_done = 0; h->bytes = 0; h->launches = 0;
+    h->par_dev = nullptr;
     const size_t B = (size_t) dims->B, S = (size_t) dims->N + 1;
     auto dalloc = [&](size_t n_doubles, void **p) -> bool {
         const size_t bytes = n_doubles * sizeof(double);
@@ -159,9 +163,10 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
         return true;
     };
     bool ok = true;
-#define X(name, n) ok = ok && dalloc(B * (size_t) (n), (void **) &h->W.name);
-    RMPC_WS_ARRAYS(X, S)
-#undef X
+    (void) S;
+    rmpc_ws_layout(&h->W, dims->N);
+    ok = ok && dalloc(B * (size_t) h->W.slab_stride, (void **) &h->W.slab);
+    ok = ok && dalloc(B * NX, (void **) &h->W.z);
     ok = ok && dalloc(B * RP_COUNT, (void **) &h->par_dev);
     ok = ok && dalloc(B * RS_COUNT, (void **) &h->W.summary);
     void *fl = nullptr;
@@ -207,9 +212,10 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
     {
         const int smax = (f == "x") ? h->D.N : h->D.N - 1;
         if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_set: stage out of range for field " + f);
-        if (f == "x") return strided(h, (double *) dev, h->W.ux, S * NV, (long) stage * NV + 6, NX, 0, s);
-        if (f == "u") return strided(h, (double *) dev, h->W.ux, S * NV, (long) stage * NV, NU, 0, s);
-        return strided(h, (double *) dev, h->W.pi, S * NX, (long) stage * NX, NX, 0, s);
+        const long st = h->W.slab_stride;
+        if (f == "x") return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV + 6, NX, 0, s);
+        if (f == "u") return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV, NU, 0, s);
+        return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_pi] + (long) stage * NX, NX, 0, s);
     }
     return fail(h, RMPC_EINVAL, "rmpc_set: unknown field '" + f + "'");
 }
@@ -220,20 +226,9 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
     CU(cudaSetDevice(h->device));
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B, S = (size_t) h->D.N + 1;
+    (void) S;
     /* duals, merit weights, QP memory, summaries: back to the calloc'ed state of a new acados solver */
-    CU(cudaMemsetAsync(h->W.pi, 0, sizeof(double) * B * S * NX, s));
-    CU(cudaMemsetAsync(h->W.lam, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.lamx0, 0, sizeof(double) * B * NB, s));
-    CU(cudaMemsetAsync(h->W.wpi, 0, sizeof(double) * B * S * NX, s));
-    CU(cudaMemsetAsync(h->W.wlam, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.wlamx0, 0, sizeof(double) * B * NB, s));
-    CU(cudaMemsetAsync(h->W.spi, 0, sizeof(double) * B * S * NX, s));
-    CU(cudaMemsetAsync(h->W.slam, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.st, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.res_m, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.res_mc, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.dlam, 0, sizeof(double) * B * S * NB, s));
-    CU(cudaMemsetAsync(h->W.dt_, 0, sizeof(double) * B * S * NB, s));
+    CU(cudaMemsetAsync(h->W.slab, 0, sizeof(double) * B * (size_t) h->W.slab_stride, s));
     CU(cudaMemsetAsync(h->W.summary, 0, sizeof(double) * B * RS_COUNT, s));
     if (h->W.slog) CU(cudaMemsetAsync(h->W.slog, 0, sizeof(double) * B * h->nlog * RL_COUNT, s));
     if (h->W.ulog) CU(cudaMemsetAsync(h->W.ulog, 0, sizeof(double) * B * h->nlog * 6, s));
@@ -284,12 +279,13 @@ extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *de
     {
         const int smax = (f == "x") ? h->D.N : h->D.N - 1;
         if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_get: stage out of range for field " + f);
-        if (f == "x") return strided(h, dev, h->W.ux, S * NV, (long) stage * NV + 6, NX, 1, s);
-        if (f == "u") return strided(h, dev, h->W.ux, S * NV, (long) stage * NV, NU, 1, s);
-        if (f == "pi") return strided(h, dev, h->W.pi, S * NX, (long) stage * NX, NX, 1, s);
-        return strided(h, dev, h->W.lam, S * NB, (long) stage * NB, NB, 1, s);
+        const long st = h->W.slab_stride;
+        if (f == "x") return strided(h, dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV + 6, NX, 1, s);
+        if (f == "u") return strided(h, dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV, NU, 1, s);
+        if (f == "pi") return strided(h, dev, h->W.slab, st, h->W.off[RA_pi] + (long) stage * NX, NX, 1, s);
+        return strided(h, dev, h->W.slab, st, h->W.off[RA_lam] + (long) stage * NB, NB, 1, s);
     }
-    if (f == "lamx0") return strided(h, dev, h->W.lamx0, NB, 0, NB, 1, s);
+    if (f == "lamx0") return strided(h, dev, h->W.slab, h->W.slab_stride, h->W.off[RA_lamx0], NB, 1, s);
     if (f == "z") { CU(cudaMemcpyAsync(dev, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "summary") { CU(cudaMemcpyAsync(dev, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "flags")
@@ -337,8 +333,8 @@ extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const doubl
     if (u_last_host)
     {
         /* u0 of the last solve = control iterate of stage 0 */
-        CU(cudaMemcpy2DAsync(u_last_host, sizeof(double) * 6, h->W.ux, sizeof(double) * (h->D.N + 1) * NV, sizeof(double) * 6, B,
-                             cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpy2DAsync(u_last_host, sizeof(double) * 6, h->W.slab + h->W.off[RA_ux], sizeof(double) * h->W.slab_stride,
+                             sizeof(double) * 6, B, cudaMemcpyDeviceToHost, s));
     }
     CU(cudaStreamSynchronize(s));
     return 0;

@@ -50,6 +50,7 @@ RD void rd_sincos(double a, double *s, double *c) { *s = sin(a); *c = cos(a); }
 RD double rd_fmax(double a, double b) { return a > b ? a : b; } /* NaN-ignoring like fmax for our uses */
 RD double rd_inf() { return INFINITY; }
 RD double rd_time() { return 0.0; }
+RD void rd_prefetch_l2(const void *) {}
 #define RD_UNROLL
 struct rd_double2 { double x, y; };
 #else
@@ -73,6 +74,7 @@ RD double rd_time() /* seconds on the GPU's global nanosecond timer */
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return 1e-9 * (double) t;
 }
+RD void rd_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 #define RD_UNROLL _Pragma("unroll")
 typedef double2 rd_double2;
 #endif
@@ -88,6 +90,15 @@ RD double grp_sum(double v)
 {
     for (int m = GL / 2; m; m >>= 1) v += rd_shfl_xor(v, m);
     return v;
+}
+/* group-wide: pull the 128-byte lines covering [p, p + n) doubles into L2 ahead of a sequential sweep */
+#ifndef RMPC_PF
+#define RMPC_PF 0 /* prefetch distance of the Riccati sweeps in stages (0 = off) */
+#endif
+RD void grp_prefetch(const double *p, int n)
+{
+    const char *a = (const char *) ((unsigned long long) p & ~127ULL), *e = (const char *) (p + n);
+    for (a += 128 * rd_lane(); a < e; a += 128 * GL) rd_prefetch_l2(a);
 }
 RD double grp_max(double v)
 {
@@ -126,22 +137,14 @@ struct Inst
 RD Inst inst_view(const RmpcWs &w, int N, long i)
 {
     Inst v;
-    const long S = N + 1;
+    (void) N;
+    double *slab = w.slab + i * w.slab_stride;
     v.par = w.par + i * RP_COUNT;
-    v.ux = w.ux + i * S * NV; v.pi = w.pi + i * S * NX; v.lam = w.lam + i * S * NB; v.lamx0 = w.lamx0 + i * NB;
-    v.wpi = w.wpi + i * S * NX; v.wlam = w.wlam + i * S * NB; v.wlamx0 = w.wlamx0 + i * NB;
-    v.z = w.z + i * NX; v.flags = w.flags + i * 4;
-    v.Jc = w.Jc + i * S * NJ; v.rqz = w.rqz + i * S * NV; v.b = w.b + i * S * NX; v.d = w.d + i * S * NB;
-    v.dx0 = w.dx0 + i * NX; v.g0u = w.g0u + i * 8;
-    v.sux = w.sux + i * S * NV; v.spi = w.spi + i * S * NX; v.slam = w.slam + i * S * NB; v.st = w.st + i * S * NB;
-    v.qlamx0 = w.qlamx0 + i * NB;
-    v.dux = w.dux + i * S * NV; v.dpi = w.dpi + i * S * NX; v.dlam = w.dlam + i * S * NB; v.dt_ = w.dt_ + i * S * NB;
-    v.res_g = w.res_g + i * S * NV; v.res_b = w.res_b + i * S * NX; v.res_d = w.res_d + i * S * NB;
-    v.res_m = w.res_m + i * S * NB; v.res_mc = w.res_mc + i * S * NB;
-    v.pvec = w.pvec + i * S * NX; v.F = w.F + i * S * FS;
-    v.ig = w.ig + i * S * NV; v.ib = w.ib + i * S * NX; v.id = w.id + i * S * NB; v.im = w.im + i * S * NB;
-    v.iux = w.iux + i * S * NV; v.ipi = w.ipi + i * S * NX; v.ilam = w.ilam + i * S * NB; v.it = w.it + i * S * NB;
-    v.tux = w.tux + i * S * NV;
+    v.z = w.z + i * NX;
+    v.flags = w.flags + i * 4;
+#define X(name, n) v.name = slab + w.off[RA_##name];
+    RMPC_WS_ARRAYS(X, 0)
+#undef X
     return v;
 }
 
@@ -870,6 +873,14 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
     {
         const bool s0 = (ss == 0);
         double *F = I.F + (long) FS * ss;
+        if (RMPC_PF && ss >= RMPC_PF)
+        {
+            const int pf = ss - RMPC_PF;
+            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
+            grp_prefetch(I.res_d + NB * pf, NB); grp_prefetch(I.res_m + NB * pf, NB);
+            grp_prefetch(I.res_g + NV * pf, NV); grp_prefetch(I.res_b + NX * pf, NX);
+            grp_prefetch(I.Jc + NJ * pf, NJ);
+        }
         /* (1) barrier terms of the bound slot owned by this lane (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
         double Gam = 0.0, gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
@@ -1069,6 +1080,15 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
     for (int ss = 0; ss < N; ss++)
     {
         const double *F = I.F + (long) FS * ss, *Fn = F + FS;
+        if (RMPC_PF && ss + RMPC_PF < N)
+        {
+            const int pf = ss + RMPC_PF;
+            grp_prefetch(I.F + (long) FS * (pf + 1), RF_END);
+            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
+            grp_prefetch(rd + NB * pf, NB); grp_prefetch(rm + NB * pf, NB);
+            grp_prefetch(rb + NX * pf, NX);
+            if (STORED) { grp_prefetch(X + NV * pf, 6); grp_prefetch(I.pvec + NX * (pf + 1), NX); }
+        }
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
@@ -1175,6 +1195,21 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
     {
         const bool s0 = (ss == 0);
         const double *F = I.F + (long) FS * ss, *Fn = F + FS;
+        if (RMPC_PF && ss >= RMPC_PF)
+        {
+            const int pf = ss - RMPC_PF;
+            grp_prefetch(I.F + (long) FS * pf, USE_PB ? RF_P : RF_END);
+            if (USE_PB) grp_prefetch(I.F + (long) FS * pf + RF_PB, NX);
+            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
+            grp_prefetch(rd + NB * pf, NB); grp_prefetch(rg + NV * pf, NV);
+            if (MODE == 0) grp_prefetch(rm + NB * pf, NB);
+            else
+            {
+                grp_prefetch(I.res_m + NB * pf, NB);
+                if (MODE == 1) { grp_prefetch(I.dt_ + NB * pf, NB); grp_prefetch(I.dlam + NB * pf, NB); }
+            }
+            if (!USE_PB) grp_prefetch(rb + NX * pf, NX);
+        }
         if (R.x)
         {
             double pb;

@@ -1,19 +1,8 @@
-/* robotic-mpc_b200/csrc/rmpc_layout.h -- the list of per-instance arrays of a batch (name, doubles per instance),
- * shared by the CUDA allocator in rmpc_capi.cu and by the host-side test harness.  S = N + 1 stage slots. */
+/* robotic-mpc_b200/csrc/rmpc_layout.h -- host-side constants shared by the CUDA allocator in rmpc_capi.cu and by the
+ * host-side test harness (the per-instance array list itself, RMPC_WS_ARRAYS, is in rmpc_types.h). */
 #ifndef RMPC_LAYOUT_H
 #define RMPC_LAYOUT_H
 #include "rmpc_types.h"
-
-#define RMPC_WS_ARRAYS(X, S)                                                                                          \
-    X(ux, (S) * RMPC_NV) X(pi, (S) * RMPC_NX) X(lam, (S) * RMPC_NB) X(lamx0, RMPC_NB)                                 \
-    X(wpi, (S) * RMPC_NX) X(wlam, (S) * RMPC_NB) X(wlamx0, RMPC_NB) X(z, RMPC_NX)                                     \
-    X(Jc, (S) * RMPC_NJ) X(rqz, (S) * RMPC_NV) X(b, (S) * RMPC_NX) X(d, (S) * RMPC_NB) X(dx0, RMPC_NX) X(g0u, 8)      \
-    X(sux, (S) * RMPC_NV) X(spi, (S) * RMPC_NX) X(slam, (S) * RMPC_NB) X(st, (S) * RMPC_NB) X(qlamx0, RMPC_NB)        \
-    X(dux, (S) * RMPC_NV) X(dpi, (S) * RMPC_NX) X(dlam, (S) * RMPC_NB) X(dt_, (S) * RMPC_NB)                          \
-    X(res_g, (S) * RMPC_NV) X(res_b, (S) * RMPC_NX) X(res_d, (S) * RMPC_NB) X(res_m, (S) * RMPC_NB)                   \
-    X(res_mc, (S) * RMPC_NB) X(pvec, (S) * RMPC_NX) X(F, (S) * RMPC_FS)                                               \
-    X(ig, (S) * RMPC_NV) X(ib, (S) * RMPC_NX) X(id, (S) * RMPC_NB) X(im, (S) * RMPC_NB)                               \
-    X(iux, (S) * RMPC_NV) X(ipi, (S) * RMPC_NX) X(ilam, (S) * RMPC_NB) X(it, (S) * RMPC_NB) X(tux, (S) * RMPC_NV)
 
 /* Fixed transforms of the UR10 chain: URDF joint origins (R/ur_description/urdf/ur10.urdf:50-55,78-83,106-111,
  * 134-139,162-167,190-195) and the fixed ee_fixed_joint -> frame ee_link (:218-222).  rpy -> rotation goes through a

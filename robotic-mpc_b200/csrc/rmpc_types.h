@@ -112,24 +112,37 @@ typedef struct
     double plant_dt;   /* plant RK4 step (= dt in the reference) */
 } RmpcDims;
 
-/* device pointers; all arrays [B][stride] doubles unless noted */
+/* The per-instance solver arrays (name, doubles per instance); S = N + 1 stage slots.  All arrays of ONE instance are
+ * contiguous in HBM (a "slab"): an instance touches one ~0.6 MB region instead of 40 far-apart ones (TLB / DRAM-page
+ * locality), and host getters / setters address it as slab + i * slab_stride + off[array]. */
+#define RMPC_WS_ARRAYS(X, S)                                                                                          \
+    X(ux, (S) * RMPC_NV) X(pi, (S) * RMPC_NX) X(lam, (S) * RMPC_NB) X(lamx0, RMPC_NB)                                 \
+    X(wpi, (S) * RMPC_NX) X(wlam, (S) * RMPC_NB) X(wlamx0, RMPC_NB)                                                   \
+    X(Jc, (S) * RMPC_NJ) X(rqz, (S) * RMPC_NV) X(b, (S) * RMPC_NX) X(d, (S) * RMPC_NB) X(dx0, RMPC_NX) X(g0u, 8)      \
+    X(sux, (S) * RMPC_NV) X(spi, (S) * RMPC_NX) X(slam, (S) * RMPC_NB) X(st, (S) * RMPC_NB) X(qlamx0, RMPC_NB)        \
+    X(dux, (S) * RMPC_NV) X(dpi, (S) * RMPC_NX) X(dlam, (S) * RMPC_NB) X(dt_, (S) * RMPC_NB)                          \
+    X(res_g, (S) * RMPC_NV) X(res_b, (S) * RMPC_NX) X(res_d, (S) * RMPC_NB) X(res_m, (S) * RMPC_NB)                   \
+    X(res_mc, (S) * RMPC_NB) X(pvec, (S) * RMPC_NX) X(F, (S) * RMPC_FS)                                               \
+    X(ig, (S) * RMPC_NV) X(ib, (S) * RMPC_NX) X(id, (S) * RMPC_NB) X(im, (S) * RMPC_NB)                               \
+    X(iux, (S) * RMPC_NV) X(ipi, (S) * RMPC_NX) X(ilam, (S) * RMPC_NB) X(it, (S) * RMPC_NB) X(tux, (S) * RMPC_NV)
+
+enum
+{
+#define X(name, n) RA_##name,
+    RMPC_WS_ARRAYS(X, 0)
+#undef X
+    RA_COUNT
+};
+
 typedef struct
 {
     const double *par; /* [B][RP_COUNT] */
-    /* NLP iterate + merit weights (persist across steps) */
-    double *ux, *pi, *lam, *lamx0, *wpi, *wlam, *wlamx0;
+    double *slab;      /* [B][slab_stride]: NLP iterate + merit weights (persist across steps), linearisation / QP data,
+                          IPM iterate / step / residuals / Riccati factors, refinement and line-search scratch */
+    long slab_stride;  /* doubles per instance (multiple of 16 = one 128-byte line) */
+    int off[RA_COUNT]; /* offset of each array inside a slab (multiples of 16 doubles) */
     double *z;         /* [B][12] plant state */
     int *flags;        /* [B][4]: first_call, qp_warm2_pending, n_lq_needed, reserved */
-    /* linearisation / QP data */
-    double *Jc, *rqz, *b, *d, *dx0, *g0u;
-    /* IPM iterate, step, residuals */
-    double *sux, *spi, *slam, *st, *qlamx0;
-    double *dux, *dpi, *dlam, *dt_;
-    double *res_g, *res_b, *res_d, *res_m, *res_mc;
-    double *pvec, *F;
-    /* iterative refinement (rare path) and line-search trial point */
-    double *ig, *ib, *id, *im, *iux, *ipi, *ilam, *it;
-    double *tux;
     /* logs (may be null) */
     double *zlog;      /* [B][nlog+1][12] */
     double *ulog;      /* [B][nlog][6] */
@@ -138,5 +151,18 @@ typedef struct
     int nlog;          /* capacity of the logs in steps */
     int step0;         /* index of the first step of this launch */
 } RmpcWs;
+
+/* fill off[] / slab_stride for a horizon of N intervals; returns the stride in doubles */
+static inline long rmpc_ws_layout(RmpcWs *w, int N)
+{
+    const long S = (long) N + 1;
+    long o = 0;
+    int k = 0;
+#define X(name, n) w->off[k++] = (int) o; o += (((long) (n)) + 15) / 16 * 16;
+    RMPC_WS_ARRAYS(X, S)
+#undef X
+    w->slab_stride = o;
+    return o;
+}
 
 #endif

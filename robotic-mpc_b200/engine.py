@@ -6,6 +6,7 @@ There is NO CPU path: constructing an :class:`Engine` without the compiled libra
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -13,7 +14,7 @@ import numpy as np
 from .params import RK, RL, RP, RS
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "librmpc.so"
+LIB_PATH = Path(os.environ.get("RMPC_LIB", HERE / "librmpc.so"))  # RMPC_LIB: A/B builds of the same library
 
 SQP, SQP_RTI = 0, 1
 _SOLVER_TYPES = {"SQP": SQP, "SQP_RTI": SQP_RTI, SQP: SQP, SQP_RTI: SQP_RTI}

@@ -36,11 +36,11 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
     RmpcWs W;
     memset(&W, 0, sizeof(W));
     std::vector<double *> owned;
-#define X(name, n)                                                  \
-    W.name = (double *) calloc((size_t) B * (size_t) (n), sizeof(double)); \
-    owned.push_back(W.name);
-    RMPC_WS_ARRAYS(X, S)
-#undef X
+    rmpc_ws_layout(&W, D->N);
+    W.slab = (double *) calloc((size_t) B * (size_t) W.slab_stride, sizeof(double));
+    W.z = (double *) calloc((size_t) B * NX, sizeof(double));
+    owned.push_back(W.slab);
+    owned.push_back(W.z);
     W.par = par;
     W.flags = (int *) calloc((size_t) B * 4, sizeof(int));
     W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
@@ -50,7 +50,7 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
         memcpy(W.z + i * NX, z0 + i * NX, NX * sizeof(double));
         if (zlog) memcpy(zlog + i * (nsteps + 1) * NX, z0 + i * NX, NX * sizeof(double));
         /* initial guess x_k = x0, u_k = 0 (T/c_templates_tera/acados_solver.in.c:2744-2777) */
-        for (long k = 0; k < S; k++) memcpy(W.ux + (i * S + k) * NV + 6, z0 + i * NX, NX * sizeof(double));
+        for (long k = 0; k < S; k++) memcpy(W.slab + i * W.slab_stride + W.off[RA_ux] + k * NV + 6, z0 + i * NX, NX * sizeof(double));
         W.flags[i * 4 + 0] = 1;
         W.flags[i * 4 + 1] = 1;
     }

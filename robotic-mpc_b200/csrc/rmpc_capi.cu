@@ -45,7 +45,7 @@ __global__ void rmpc_init_iterate_kernel(const RmpcDims D, const RmpcWs W)
     {
         const long i = k / (S * NV), r = k % (S * NV);
         const int c = (int) (k % NV);
-        W.slab[i * W.slab_stride + W.off[RA_ux] + r] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
+        W.slab[i * W.slab_stride + RMPC_HEAD + (long) RC_ux * W.Sp + r] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
     }
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < (long) D.B * 4; k += (long) gridDim.x * blockDim.x)
         W.flags[k] = (k % 4) < 2 ? 1 : 0;
@@ -164,7 +164,8 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     };
     bool ok = true;
     (void) S;
-    rmpc_ws_layout(&h->W, dims->N);
+    h->W.slab_stride = rmpc_slab_stride(dims->N);
+    h->W.Sp = rmpc_slab_sp(dims->N);
     ok = ok && dalloc(B * (size_t) h->W.slab_stride, (void **) &h->W.slab);
     ok = ok && dalloc(B * NX, (void **) &h->W.z);
     ok = ok && dalloc(B * RP_COUNT, (void **) &h->par_dev);
@@ -213,9 +214,9 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
         const int smax = (f == "x") ? h->D.N : h->D.N - 1;
         if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_set: stage out of range for field " + f);
         const long st = h->W.slab_stride;
-        if (f == "x") return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV + 6, NX, 0, s);
-        if (f == "u") return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV, NU, 0, s);
-        return strided(h, (double *) dev, h->W.slab, st, h->W.off[RA_pi] + (long) stage * NX, NX, 0, s);
+        if (f == "x") return strided(h, (double *) dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_ux, NV, stage) + 6, NX, 0, s);
+        if (f == "u") return strided(h, (double *) dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_ux, NV, stage), NU, 0, s);
+        return strided(h, (double *) dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_pi, NX, stage), NX, 0, s);
     }
     return fail(h, RMPC_EINVAL, "rmpc_set: unknown field '" + f + "'");
 }
@@ -280,12 +281,12 @@ extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *de
         const int smax = (f == "x") ? h->D.N : h->D.N - 1;
         if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_get: stage out of range for field " + f);
         const long st = h->W.slab_stride;
-        if (f == "x") return strided(h, dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV + 6, NX, 1, s);
-        if (f == "u") return strided(h, dev, h->W.slab, st, h->W.off[RA_ux] + (long) stage * NV, NU, 1, s);
-        if (f == "pi") return strided(h, dev, h->W.slab, st, h->W.off[RA_pi] + (long) stage * NX, NX, 1, s);
-        return strided(h, dev, h->W.slab, st, h->W.off[RA_lam] + (long) stage * NB, NB, 1, s);
+        if (f == "x") return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_ux, NV, stage) + 6, NX, 1, s);
+        if (f == "u") return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_ux, NV, stage), NU, 1, s);
+        if (f == "pi") return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_pi, NX, stage), NX, 1, s);
+        return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_lam, NB, stage), NB, 1, s);
     }
-    if (f == "lamx0") return strided(h, dev, h->W.slab, h->W.slab_stride, h->W.off[RA_lamx0], NB, 1, s);
+    if (f == "lamx0") return strided(h, dev, h->W.slab, h->W.slab_stride, H_LAMX0, NB, 1, s);
     if (f == "z") { CU(cudaMemcpyAsync(dev, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "summary") { CU(cudaMemcpyAsync(dev, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "flags")
@@ -333,7 +334,7 @@ extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const doubl
     if (u_last_host)
     {
         /* u0 of the last solve = control iterate of stage 0 */
-        CU(cudaMemcpy2DAsync(u_last_host, sizeof(double) * 6, h->W.slab + h->W.off[RA_ux], sizeof(double) * h->W.slab_stride,
+        CU(cudaMemcpy2DAsync(u_last_host, sizeof(double) * 6, h->W.slab + rmpc_slab_off(h->D.N, RC_ux, NV, 0), sizeof(double) * h->W.slab_stride,
                              sizeof(double) * 6, B, cudaMemcpyDeviceToHost, s));
     }
     CU(cudaStreamSynchronize(s));

@@ -91,15 +91,6 @@ RD double grp_sum(double v)
     for (int m = GL / 2; m; m >>= 1) v += rd_shfl_xor(v, m);
     return v;
 }
-/* group-wide: pull the 128-byte lines covering [p, p + n) doubles into L2 ahead of a sequential sweep */
-#ifndef RMPC_PF
-#define RMPC_PF 0 /* prefetch distance of the Riccati sweeps in stages (0 = off) */
-#endif
-RD void grp_prefetch(const double *p, int n)
-{
-    const char *a = (const char *) ((unsigned long long) p & ~127ULL), *e = (const char *) (p + n);
-    for (a += 128 * rd_lane(); a < e; a += 128 * GL) rd_prefetch_l2(a);
-}
 RD double grp_max(double v)
 {
     for (int m = GL / 2; m; m >>= 1) { double o = rd_shfl_xor(v, m); v = o > v ? o : v; }
@@ -122,29 +113,26 @@ struct GrpSmem
     double Jc[NJ];        /* scaled task Jacobian of the current stage */
 };
 
-/* per-instance views */
+/* per-instance view (layout: rmpc_types.h): parameter row, slab head, first array, stage slots, plant state, flags */
 struct Inst
 {
     const double *par;
-    double *ux, *pi, *lam, *lamx0, *wpi, *wlam, *wlamx0, *z;
+    double *head, *arr0, *z;
     int *flags;
-    double *Jc, *rqz, *b, *d, *dx0, *g0u;
-    double *sux, *spi, *slam, *st, *qlamx0, *dux, *dpi, *dlam, *dt_;
-    double *res_g, *res_b, *res_d, *res_m, *res_mc, *pvec, *F;
-    double *ig, *ib, *id, *im, *iux, *ipi, *ilam, *it, *tux;
+    int Sp;
 };
+#define AR(name) (I.arr0 + (long) RC_##name * I.Sp)
 
 RD Inst inst_view(const RmpcWs &w, int N, long i)
 {
     Inst v;
     (void) N;
-    double *slab = w.slab + i * w.slab_stride;
+    v.head = w.slab + i * w.slab_stride;
+    v.arr0 = v.head + RMPC_HEAD;
+    v.Sp = w.Sp;
     v.par = w.par + i * RP_COUNT;
     v.z = w.z + i * NX;
     v.flags = w.flags + i * 4;
-#define X(name, n) v.name = slab + w.off[RA_##name];
-    RMPC_WS_ARRAYS(X, 0)
-#undef X
     return v;
 }
 
@@ -494,10 +482,10 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
     for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
-        load18(I.ux + NV * i, v);
-        double *g = I.rqz + NV * i;
+        load18(AR(ux) + NV * i, v);
+        double *g = AR(rqz) + NV * i;
         LinEmit em;
-        em.Jc = I.Jc + NJ * i;
+        em.Jc = AR(Jc) + NJ * i;
         em.g = g;
         const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
         RD_UNROLL
@@ -513,8 +501,8 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
         ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
         cost += stage_cost(par, dt, y5, v, v + 12);
         /* dynamics gap b = Ad x + Bd u - x_next */
-        const double *xn = I.ux + NV * (i + 1) + 6;
-        double *b = I.b + NX * i, *d = I.d + NB * i;
+        const double *xn = AR(ux) + NV * (i + 1) + 6;
+        double *b = AR(b) + NX * i, *d = AR(d) + NB * i;
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -530,10 +518,10 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
         if (i == 0)
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) I.dx0[k] = x0[k] - v[6 + k];
+            for (int k = 0; k < NX; k++) (I.head + H_DX0)[k] = x0[k] - v[6 + k];
         }
     }
-    for (int k = lane; k < NV; k += GL) I.rqz[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
+    for (int k = lane; k < NV; k += GL) AR(rqz)[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
     rd_sync();
     return grp_sum(cost);
 }
@@ -553,7 +541,7 @@ RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const
         NoEmit ne;
         ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
         m += stage_cost(par, D.dt, y5, v, v + 12);
-        const double *xn = tux + NV * (i + 1) + 6, *wpi = I.wpi + NX * i, *wl = I.wlam + NB * i;
+        const double *xn = tux + NV * (i + 1) + 6, *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i;
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -575,8 +563,8 @@ RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const
             for (int k = 0; k < NX; k++)
             {
                 const double fl = x0[k] - v[6 + k];
-                if (fl > 0.0) m += fabs(I.wlamx0[k]) * fl;
-                if (-fl > 0.0) m += fabs(I.wlamx0[12 + k]) * (-fl);
+                if (fl > 0.0) m += fabs((I.head + H_WLAMX0)[k]) * fl;
+                if (-fl > 0.0) m += fabs((I.head + H_WLAMX0)[12 + k]) * (-fl);
             }
         }
     }
@@ -594,10 +582,10 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
     {
         double r[NV];
         RD_UNROLL
-        for (int k = 0; k < NV; k++) r[k] = I.rqz[NV * i + k];
+        for (int k = 0; k < NV; k++) r[k] = AR(rqz)[NV * i + k];
         if (i < N)
         {
-            const double *lam = I.lam + NB * i, *pi = I.pi + NX * i, *d = I.d + NB * i;
+            const double *lam = AR(lam) + NB * i, *pi = AR(pi) + NX * i, *d = AR(d) + NB * i;
             RD_UNROLL
             for (int j = 0; j < 12; j++)
             {
@@ -612,7 +600,7 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
                 r[k] += par[RP_B1 + k] * pi[k] + par[RP_B2 + k] * pi[6 + k];
                 r[6 + k] += pi[k];
                 r[12 + k] += par[RP_A12 + k] * pi[k] + par[RP_A22 + k] * pi[6 + k];
-                re = rd_fmax(re, rd_fmax(fabs(I.b[NX * i + k]), fabs(I.b[NX * i + 6 + k])));
+                re = rd_fmax(re, rd_fmax(fabs(AR(b)[NX * i + k]), fabs(AR(b)[NX * i + 6 + k])));
             }
         }
         if (i == 0)
@@ -620,7 +608,7 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
             RD_UNROLL
             for (int k = 0; k < NX; k++)
             {
-                const double ll = I.lamx0[k], lu = I.lamx0[12 + k], f = I.dx0[k];
+                const double ll = (I.head + H_LAMX0)[k], lu = (I.head + H_LAMX0)[12 + k], f = (I.head + H_DX0)[k];
                 r[6 + k] -= ll - lu;
                 ri = rd_fmax(ri, rd_fmax(f, -f));
                 rc = rd_fmax(rc, rd_fmax(fabs(ll * f), fabs(lu * f)));
@@ -629,7 +617,7 @@ RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
         else
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) r[6 + k] -= I.pi[NX * (i - 1) + k];
+            for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[NX * (i - 1) + k];
         }
         RD_UNROLL
         for (int k = 0; k < NV; k++)
@@ -649,11 +637,11 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
     if (lane < 6)
     {
         const StageConst c = stage_const(par, D.dt, lane);
-        const double g = I.rqz[lane];
-        I.g0u[lane] = g;
-        I.rqz[lane] = g + c.hs * I.dx0[6 + lane];
-        I.b[lane] += I.dx0[lane] + par[RP_A12 + lane] * I.dx0[6 + lane];
-        I.b[6 + lane] += par[RP_A22 + lane] * I.dx0[6 + lane];
+        const double g = AR(rqz)[lane];
+        (I.head + H_G0U)[lane] = g;
+        AR(rqz)[lane] = g + c.hs * (I.head + H_DX0)[6 + lane];
+        AR(b)[lane] += (I.head + H_DX0)[lane] + par[RP_A12 + lane] * (I.head + H_DX0)[6 + lane];
+        AR(b)[6 + lane] += par[RP_A22 + lane] * (I.head + H_DX0)[6 + lane];
     }
     rd_sync();
 }
@@ -665,15 +653,15 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
 RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
 {
     const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < (N + 1) * NV; k += GL) I.sux[k] = 0.0;
+    for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] = 0.0;
     if (warm != 2)
-        for (int k = lane; k < N * NX; k += GL) I.spi[k] = 0.0;
+        for (int k = lane; k < N * NX; k += GL) AR(spi)[k] = 0.0;
     rd_sync();
     for (int k = lane; k < N * 12; k += GL)
     {
         const int i = k / 12, j = k - 12 * i;
         if (i == 0 && j >= 6) continue;
-        double *lam = I.slam + NB * i, *t = I.st + NB * i;
+        double *lam = AR(slam) + NB * i, *t = AR(st) + NB * i;
         if (warm == 2)
         {
             if (lam[j] < 1e-1) lam[j] = 1e-1;
@@ -683,7 +671,7 @@ RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
         }
         else
         {
-            const double thr0 = 1e-1, dl = I.d[NB * i + j], du = I.d[NB * i + 12 + j];
+            const double thr0 = 1e-1, dl = AR(d)[NB * i + j], du = AR(d)[NB * i + 12 + j];
             double v = 0.0, tl = -dl, tu = -du;
             if (tl < thr0)
             {
@@ -691,7 +679,7 @@ RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
                 else { tl = thr0; v = dl + thr0; }
             }
             else if (tu < thr0) { tu = thr0; v = -du - thr0; }
-            I.sux[NV * i + j] = v;
+            AR(sux)[NV * i + j] = v;
             t[j] = tl; t[12 + j] = tu;
             lam[j] = 1.0 / tl; lam[12 + j] = 1.0 / tu;
         }
@@ -751,7 +739,7 @@ RD double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const dou
         if (i < N)
         {
             /* H v: task part on x (stages >= 1), constant diagonal blocks */
-            if (i > 0) task_hess_mv(I.Jc + NJ * i, v + 6, g + 6);
+            if (i > 0) task_hess_mv(AR(Jc) + NJ * i, v + 6, g + 6);
             const double *pin = pi + NX * i, *l = lam + NB * i, *tt = t + NB * i;
             const double *xn = ux + NV * (i + 1) + 6;
             RD_UNROLL
@@ -860,8 +848,8 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
     if (R.x)
     {
-        double *FN = I.F + (long) FS * N;
-        const double pv = I.res_g[NV * N + 6 + xk];
+        double *FN = AR(F) + (long) FS * N;
+        const double pv = AR(res_g)[NV * N + 6 + xk];
         RD_UNROLL
         for (int c = 0; c < 12; c++) sm.P[xk * SM_PS + c] = (c == xk) ? reg : 0.0;
         sm.pv[xk] = pv;
@@ -872,27 +860,19 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        double *F = I.F + (long) FS * ss;
-        if (RMPC_PF && ss >= RMPC_PF)
-        {
-            const int pf = ss - RMPC_PF;
-            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
-            grp_prefetch(I.res_d + NB * pf, NB); grp_prefetch(I.res_m + NB * pf, NB);
-            grp_prefetch(I.res_g + NV * pf, NV); grp_prefetch(I.res_b + NX * pf, NX);
-            grp_prefetch(I.Jc + NJ * pf, NJ);
-        }
+        double *F = AR(F) + (long) FS * ss;
         /* (1) barrier terms of the bound slot owned by this lane (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
         double Gam = 0.0, gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
-            const double *lam = I.slam + NB * ss, *t = I.st + NB * ss, *rd = I.res_d + NB * ss, *rm = I.res_m + NB * ss;
+            const double *lam = AR(slam) + NB * ss, *t = AR(st) + NB * ss, *rd = AR(res_d) + NB * ss, *rm = AR(res_m) + NB * ss;
             const double til = 1.0 / t[lane], tiu = 1.0 / t[12 + lane];
             Gam = til * lam[lane] + tiu * lam[12 + lane];
             gam = til * ((rm[lane] - tau_min) - lam[lane] * rd[lane]) - tiu * ((rm[12 + lane] - tau_min) - lam[12 + lane] * rd[12 + lane]);
         }
-        if (R.x) sm.bv[xk] = I.res_b[NX * ss + xk];
+        if (R.x) sm.bv[xk] = AR(res_b)[NX * ss + xk];
         if (!s0)
-            for (int k = lane; k < NJ; k += GL) sm.Jc[k] = I.Jc[NJ * ss + k];
+            for (int k = lane; k < NJ; k += GL) sm.Jc[k] = AR(Jc)[NJ * ss + k];
         rd_sync();
         /* (2) tv = P+ b + p+ ; P+ b is kept for the corrector solves */
         double Pq[12], Pd[12]; /* rows q_j and qd_j of P+ */
@@ -927,7 +907,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
             RD_UNROLL
             for (int c = 0; c < 6; c++)
                 if (c <= j) sm.Muu[(j * (j + 1)) / 2 + c] = row[c];
-            sm.Muu[21 + j] = I.res_g[NV * ss + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
+            sm.Muu[21 + j] = AR(res_g)[NV * ss + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
         }
         rd_sync();
         /* (3b) 6 x 6 Cholesky + forward substitution of m_u, redundantly in every lane (BLASFEO dpotrf_l: a
@@ -986,7 +966,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
                 for (int k = 0; k < c; k++) v -= Lx[k] * LU(c, k);
                 Lx[c] = v * inv[c];
             }
-            pk = I.res_g[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
+            pk = AR(res_g)[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
             RD_UNROLL
             for (int c = 0; c < 6; c++) pk -= Lx[c] * lu[c];
             RD_UNROLL
@@ -1079,16 +1059,7 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
     double alpha = 1.0, sB = 0.0, sC = 0.0;
     for (int ss = 0; ss < N; ss++)
     {
-        const double *F = I.F + (long) FS * ss, *Fn = F + FS;
-        if (RMPC_PF && ss + RMPC_PF < N)
-        {
-            const int pf = ss + RMPC_PF;
-            grp_prefetch(I.F + (long) FS * (pf + 1), RF_END);
-            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
-            grp_prefetch(rd + NB * pf, NB); grp_prefetch(rm + NB * pf, NB);
-            grp_prefetch(rb + NX * pf, NX);
-            if (STORED) { grp_prefetch(X + NV * pf, 6); grp_prefetch(I.pvec + NX * (pf + 1), NX); }
-        }
+        const double *F = AR(F) + (long) FS * ss, *Fn = F + FS;
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
@@ -1139,7 +1110,7 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
         /* dpi = P+ dx+ + p+ */
         if (R.x)
         {
-            double a = STORED ? I.pvec[NX * (ss + 1) + xk] : Fn[RF_PV + xk];
+            double a = STORED ? AR(pvec)[NX * (ss + 1) + xk] : Fn[RF_PV + xk];
             RD_UNROLL
             for (int c = 0; c < 12; c++) a += psym(Fn + RF_P, xk, c) * sm.xv[c];
             PI[NX * ss + xk] = a;
@@ -1148,7 +1119,7 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
             const int ia = NB * ss + lane, ib = ia + 12;
-            const double la = I.slam[ia], lb = I.slam[ib], ta = I.st[ia], tb = I.st[ib];
+            const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
             const double da = rd[ia], db = rd[ib], ma = rm[ia] - mshift, mb = rm[ib] - mshift;
             const double dla = -(ma + (la * dv) - (la * da)) / ta;
             const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
@@ -1188,28 +1159,13 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
     {
         const double pv = rg[NV * N + 6 + xk];
         sm.pv[xk] = pv;
-        I.pvec[NX * N + xk] = pv;
+        AR(pvec)[NX * N + xk] = pv;
     }
     rd_sync();
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        const double *F = I.F + (long) FS * ss, *Fn = F + FS;
-        if (RMPC_PF && ss >= RMPC_PF)
-        {
-            const int pf = ss - RMPC_PF;
-            grp_prefetch(I.F + (long) FS * pf, USE_PB ? RF_P : RF_END);
-            if (USE_PB) grp_prefetch(I.F + (long) FS * pf + RF_PB, NX);
-            grp_prefetch(I.slam + NB * pf, NB); grp_prefetch(I.st + NB * pf, NB);
-            grp_prefetch(rd + NB * pf, NB); grp_prefetch(rg + NV * pf, NV);
-            if (MODE == 0) grp_prefetch(rm + NB * pf, NB);
-            else
-            {
-                grp_prefetch(I.res_m + NB * pf, NB);
-                if (MODE == 1) { grp_prefetch(I.dt_ + NB * pf, NB); grp_prefetch(I.dlam + NB * pf, NB); }
-            }
-            if (!USE_PB) grp_prefetch(rb + NX * pf, NX);
-        }
+        const double *F = AR(F) + (long) FS * ss, *Fn = F + FS;
         if (R.x)
         {
             double pb;
@@ -1226,18 +1182,18 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
         if (lane < 12 && !(s0 && lane >= 6))
         {
             const int ia = NB * ss + lane, ib = ia + 12;
-            const double la = I.slam[ia], lb = I.slam[ib], ta = I.st[ia], tb = I.st[ib];
+            const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
             double ma, mb;
             if (MODE == 0) { ma = rm[ia]; mb = rm[ib]; }
             else
             {
                 if (MODE == 1)
                 {
-                    ma = I.res_m[ia] + I.dt_[ia] * I.dlam[ia] - sigma_mu;
-                    mb = I.res_m[ib] + I.dt_[ib] * I.dlam[ib] - sigma_mu;
+                    ma = AR(res_m)[ia] + AR(dt_)[ia] * AR(dlam)[ia] - sigma_mu;
+                    mb = AR(res_m)[ib] + AR(dt_)[ib] * AR(dlam)[ib] - sigma_mu;
                 }
-                else { ma = I.res_m[ia] - sigma_mu; mb = I.res_m[ib] - sigma_mu; }
-                I.res_mc[ia] = ma; I.res_mc[ib] = mb;
+                else { ma = AR(res_m)[ia] - sigma_mu; mb = AR(res_m)[ib] - sigma_mu; }
+                AR(res_mc)[ia] = ma; AR(res_mc)[ib] = mb;
             }
             gam = (ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb;
         }
@@ -1275,7 +1231,7 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
             RD_UNROLL
             for (int k = 0; k < 6; k++) rx -= F[RF_LXU + xk * 6 + k] * z[k];
             sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
-            I.pvec[NX * ss + xk] = rx;
+            AR(pvec)[NX * ss + xk] = rx;
         }
         rd_sync();
     }
@@ -1291,8 +1247,8 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
         const double dl = dlam[k], dtt = dt[k];
-        if (-a * dl > I.slam[k]) a = -I.slam[k] / dl;
-        if (-a * dtt > I.st[k]) a = -I.st[k] / dtt;
+        if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
+        if (-a * dtt > AR(st)[k]) a = -AR(st)[k] / dtt;
     }
     return -grp_max(-a);
 }
@@ -1309,15 +1265,15 @@ RD void ipm_update(const RmpcDims &D, const Inst &I, double a)
 {
     const int N = D.N, lane = rd_lane();
     const double lmin = 1e-16;
-    for (int k = lane; k < (N + 1) * NV; k += GL) I.sux[k] += a * I.dux[k];
-    for (int k = lane; k < N * NX; k += GL) I.spi[k] += a * I.dpi[k];
+    for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] += a * AR(dux)[k];
+    for (int k = lane; k < N * NX; k += GL) AR(spi)[k] += a * AR(dpi)[k];
     for (int k = lane; k < N * NB; k += GL)
     {
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        double l = I.slam[k] + a * I.dlam[k], t = I.st[k] + a * I.dt_[k];
-        I.slam[k] = l <= lmin ? lmin : l;
-        I.st[k] = t <= lmin ? lmin : t;
+        double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
+        AR(slam)[k] = l <= lmin ? lmin : l;
+        AR(st)[k] = t <= lmin ? lmin : t;
     }
     rd_sync();
 }
@@ -1335,16 +1291,16 @@ RD int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int
     const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12);
     ipm_init(D, I, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
-    double sum_lt = ipm_res<0, 1>(D, I, I.rqz, I.b, I.d, nullptr, 0.0, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g,
-                                  I.res_b, I.res_d, I.res_m, nrm);
+    double sum_lt = ipm_res<0, 1>(D, I, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g),
+                                  AR(res_b), AR(res_d), AR(res_m), nrm);
     double mu = nc_inv * sum_lt;
     int kk;
     for (kk = 0; kk < D.qp_iter_max && alpha > alpha_min && (nrm[0] > tol || nrm[1] > tol || nrm[2] > tol || nrm[4] > tol); kk++)
     {
         /* affine (predictor) step */
         ipm_factor(D, I, sm);
-        ipm_forward<0>(D, I, sm, I.res_b, I.res_d, I.res_m, tau_min, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
-        ipm_res<1, 0>(D, I, I.res_g, I.res_b, I.res_d, I.res_m, tau_min, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, nullptr, nullptr,
+        ipm_forward<0>(D, I, sm, AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
+        ipm_res<1, 0>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr, nullptr,
                       nullptr, nullptr, inrm);
         if ((inrm[0] == 0.0 && inrm[5] > 0.5) || inrm[0] > 1e-5 || inrm[1] > 1e-5 || inrm[2] > 1e-5 || inrm[3] > 1e-5)
         {
@@ -1355,42 +1311,42 @@ RD int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int
         double sigma_mu = sigma * mu;
         sigma_mu = sigma_mu > tau_min ? sigma_mu : tau_min;
         /* corrector: centering + second-order correction */
-        ipm_backward<1, 1>(D, I, sm, I.res_g, I.res_b, I.res_d, nullptr, sigma_mu, I.dux);
-        ipm_forward<1>(D, I, sm, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
+        ipm_backward<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
+        ipm_forward<1>(D, I, sm, AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
         /* conditional predictor-corrector */
         const double mu_aff0 = mu_aff;
         mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         if (mu_aff > 2.0 * mu_aff0)
         {
-            ipm_backward<2, 1>(D, I, sm, I.res_g, I.res_b, I.res_d, nullptr, sigma_mu, I.dux);
-            ipm_forward<1>(D, I, sm, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, &alpha, sums);
+            ipm_backward<2, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
+            ipm_forward<1>(D, I, sm, AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
         }
         /* iterative refinement of the corrector step, itref_corr_max = 2 */
         int refined = 0;
         for (int it = 0; it < 2; it++)
         {
-            ipm_res<1, 0>(D, I, I.res_g, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, nullptr, nullptr,
+            ipm_res<1, 0>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr, nullptr,
                           nullptr, nullptr, inrm);
             if ((inrm[0] < tol || inrm[0] < 1e-3 * nrm[0]) && (inrm[1] < tol || inrm[1] < 1e-3 * nrm[1]) &&
                 (inrm[2] < tol || inrm[2] < 1e-3 * nrm[2]) && (inrm[3] < tol || inrm[3] < 1e-3 * nrm[3]))
                 break;
-            ipm_res<1, 1>(D, I, I.res_g, I.res_b, I.res_d, I.res_mc, 0.0, I.dux, I.dpi, I.dlam, I.dt_, I.slam, I.st, I.ig, I.ib, I.id,
-                          I.im, inrm);
+            ipm_res<1, 1>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), AR(ig), AR(ib), AR(id),
+                          AR(im), inrm);
             double a2, s2[2];
-            ipm_backward<0, 0>(D, I, sm, I.ig, I.ib, I.id, I.im, 0.0, I.iux);
-            ipm_forward<1>(D, I, sm, I.ib, I.id, I.im, 0.0, I.iux, I.ipi, I.ilam, I.it, &a2, s2);
+            ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
+            ipm_forward<1>(D, I, sm, AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2);
             refined = 1;
-            for (int k = lane; k < (N + 1) * NV; k += GL) I.dux[k] += I.iux[k];
-            for (int k = lane; k < N * NX; k += GL) I.dpi[k] += I.ipi[k];
-            for (int k = lane; k < N * NB; k += GL) { I.dlam[k] += I.ilam[k]; I.dt_[k] += I.it[k]; }
+            for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
+            for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
+            for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
             rd_sync();
         }
-        if (refined) alpha = ipm_alpha(D, I, I.dlam, I.dt_);
+        if (refined) alpha = ipm_alpha(D, I, AR(dlam), AR(dt_));
         double a = alpha;
         if (a < 1.0) a = a * ((1.0 - a) * 0.99 + a * 0.9999999);
         ipm_update(D, I, a);
-        sum_lt = ipm_res<0, 1>(D, I, I.rqz, I.b, I.d, nullptr, 0.0, I.sux, I.spi, I.slam, I.st, nullptr, nullptr, I.res_g, I.res_b,
-                               I.res_d, I.res_m, nrm);
+        sum_lt = ipm_res<0, 1>(D, I, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g), AR(res_b),
+                               AR(res_d), AR(res_m), nrm);
         mu = nc_inv * sum_lt;
     }
     *iters = kk;
@@ -1408,23 +1364,23 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
     const double *par = I.par;
     if (lane < 12)
     {
-        const double *Jc = I.Jc; /* stage 0 */
+        const double *Jc = AR(Jc); /* stage 0 */
         const int jj = lane % 6;
         const StageConst c = stage_const(par, D.dt, jj);
-        double tmp = I.rqz[6 + lane] + ((lane < 6) ? I.spi[jj] : par[RP_A12 + jj] * I.spi[jj] + par[RP_A22 + jj] * I.spi[6 + jj]);
+        double tmp = AR(rqz)[6 + lane] + ((lane < 6) ? AR(spi)[jj] : par[RP_A12 + jj] * AR(spi)[jj] + par[RP_A22 + jj] * AR(spi)[6 + jj]);
         for (int mm = 0; mm < 5; mm++)
         {
             double w = 0.0;
-            for (int k = 0; k < 6; k++) w += Jc[6 * mm + k] * I.dx0[k];
+            for (int k = 0; k < 6; k++) w += Jc[6 * mm + k] * (I.head + H_DX0)[k];
             if (mm == 4)
-                for (int k = 0; k < 6; k++) w += Jc[30 + k] * I.dx0[6 + k];
+                for (int k = 0; k < 6; k++) w += Jc[30 + k] * (I.head + H_DX0)[6 + k];
             if (lane < 6) tmp += Jc[6 * mm + lane] * w;
             else if (mm == 4) tmp += Jc[30 + jj] * w;
         }
-        if (lane >= 6) tmp += c.hs * I.sux[jj] + c.hq * I.dx0[lane];
-        I.qlamx0[lane] = tmp >= 0.0 ? tmp : 1e-16;
-        I.qlamx0[12 + lane] = tmp >= 0.0 ? 1e-16 : -tmp;
-        I.sux[6 + lane] = I.dx0[lane];
+        if (lane >= 6) tmp += c.hs * AR(sux)[jj] + c.hq * (I.head + H_DX0)[lane];
+        (I.head + H_QLAMX0)[lane] = tmp >= 0.0 ? tmp : 1e-16;
+        (I.head + H_QLAMX0)[12 + lane] = tmp >= 0.0 ? 1e-16 : -tmp;
+        AR(sux)[6 + lane] = (I.head + H_DX0)[lane];
     }
     rd_sync();
 }
@@ -1439,43 +1395,43 @@ RD int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < N * NX; k += GL)
     {
-        const double t0 = fabs(I.spi[k]);
-        if (nlp_iter == 0) I.wpi[k] = t0;
-        else { const double t1 = 0.5 * (t0 + I.wpi[k]); I.wpi[k] = t0 > t1 ? t0 : t1; }
+        const double t0 = fabs(AR(spi)[k]);
+        if (nlp_iter == 0) AR(wpi)[k] = t0;
+        else { const double t1 = 0.5 * (t0 + AR(wpi)[k]); AR(wpi)[k] = t0 > t1 ? t0 : t1; }
     }
     for (int k = lane; k < N * NB + NB; k += GL)
     {
         const bool x0s = k >= N * NB;
         const int kk = x0s ? k - N * NB : k;
         if (!x0s && kk < NB && (kk % 12) >= 6) continue;
-        const double t0 = x0s ? I.qlamx0[kk] : I.slam[kk];
-        double *w = x0s ? I.wlamx0 + kk : I.wlam + kk;
+        const double t0 = x0s ? (I.head + H_QLAMX0)[kk] : AR(slam)[kk];
+        double *w = x0s ? (I.head + H_WLAMX0) + kk : AR(wlam) + kk;
         if (nlp_iter == 0) *w = t0;
         else { const double t1 = 0.5 * (t0 + *w); *w = t0 > t1 ? t0 : t1; }
     }
     rd_sync();
-    const double m0 = nlp_merit(ch, D, I, I.ux, I.z);
+    const double m0 = nlp_merit(ch, D, I, AR(ux), I.z);
     double alpha = 1.0, m1 = 0.0;
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        for (int k = lane; k < (N + 1) * NV; k += GL) I.tux[k] = I.ux[k] + alpha * I.sux[k];
+        for (int k = lane; k < (N + 1) * NV; k += GL) AR(tux)[k] = AR(ux)[k] + alpha * AR(sux)[k];
         rd_sync();
-        m1 = nlp_merit(ch, D, I, I.tux, I.z);
+        m1 = nlp_merit(ch, D, I, AR(tux), I.z);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
         if (m1 < m0 && !bad) { accepted = 1; break; }
         alpha *= 0.7;
     }
     *alpha_out = alpha;
     if (!accepted && ((m1 != m1) || (m1 - m1 != 0.0))) return 1;
-    for (int k = lane; k < (N + 1) * NV; k += GL) I.ux[k] = I.ux[k] + alpha * I.sux[k];
-    for (int k = lane; k < N * NX; k += GL) I.pi[k] = (1.0 - alpha) * I.pi[k] + alpha * I.spi[k];
+    for (int k = lane; k < (N + 1) * NV; k += GL) AR(ux)[k] = AR(ux)[k] + alpha * AR(sux)[k];
+    for (int k = lane; k < N * NX; k += GL) AR(pi)[k] = (1.0 - alpha) * AR(pi)[k] + alpha * AR(spi)[k];
     for (int k = lane; k < N * NB; k += GL)
     {
         if (k < NB && (k % 12) >= 6) continue;
-        I.lam[k] = (1.0 - alpha) * I.lam[k] + alpha * I.slam[k];
+        AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
     }
-    for (int k = lane; k < NB; k += GL) I.lamx0[k] = (1.0 - alpha) * I.lamx0[k] + alpha * I.qlamx0[k];
+    for (int k = lane; k < NB; k += GL) (I.head + H_LAMX0)[k] = (1.0 - alpha) * (I.head + H_LAMX0)[k] + alpha * (I.head + H_QLAMX0)[k];
     rd_sync();
     return 0;
 }
@@ -1492,12 +1448,12 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
     if (init_from_nlp && warm == 2)
     {
         /* ocp_nlp_initialize_qp_from_nlp (AC/ocp_nlp/ocp_nlp_common.c:3320-3340) + ocp_qp_compute_t at ux = 0 */
-        for (int k = lane; k < N * NX; k += GL) I.spi[k] = I.pi[k];
+        for (int k = lane; k < N * NX; k += GL) AR(spi)[k] = AR(pi)[k];
         for (int k = lane; k < N * NB; k += GL)
         {
             if (k < NB && (k % 12) >= 6) continue;
-            I.slam[k] = I.lam[k];
-            I.st[k] = -I.d[k];
+            AR(slam)[k] = AR(lam)[k];
+            AR(st)[k] = -AR(d)[k];
         }
         rd_sync();
     }
@@ -1590,7 +1546,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         for (int i = lane; i < N; i += GL)
         {
             double v[NV], y5[5];
-            load18(I.ux + NV * i, v);
+            load18(AR(ux) + NV * i, v);
             NoEmit ne;
             ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
             cost += stage_cost(par, D.dt, y5, v, v + 12);
@@ -1599,7 +1555,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         double zq = 0.0, zqd = 0.0, u = 0.0;
         if (lane < 6)
         {
-            u = I.ux[lane];
+            u = AR(ux)[lane];
             const double w = par[RP_WCV + lane], h = D.plant_dt;
             const double q = I.z[lane], qd = I.z[6 + lane];
             const double k1q = qd, k1d = -w * qd + w * u;

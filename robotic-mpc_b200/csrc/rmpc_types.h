@@ -112,35 +112,61 @@ typedef struct
     double plant_dt;   /* plant RK4 step (= dt in the reference) */
 } RmpcDims;
 
-/* The per-instance solver arrays (name, doubles per instance); S = N + 1 stage slots.  All arrays of ONE instance are
- * contiguous in HBM (a "slab"): an instance touches one ~0.6 MB region instead of 40 far-apart ones (TLB / DRAM-page
- * locality), and host getters / setters address it as slab + i * slab_stride + off[array]. */
-#define RMPC_WS_ARRAYS(X, S)                                                                                          \
-    X(ux, (S) * RMPC_NV) X(pi, (S) * RMPC_NX) X(lam, (S) * RMPC_NB) X(lamx0, RMPC_NB)                                 \
-    X(wpi, (S) * RMPC_NX) X(wlam, (S) * RMPC_NB) X(wlamx0, RMPC_NB)                                                   \
-    X(Jc, (S) * RMPC_NJ) X(rqz, (S) * RMPC_NV) X(b, (S) * RMPC_NX) X(d, (S) * RMPC_NB) X(dx0, RMPC_NX) X(g0u, 8)      \
-    X(sux, (S) * RMPC_NV) X(spi, (S) * RMPC_NX) X(slam, (S) * RMPC_NB) X(st, (S) * RMPC_NB) X(qlamx0, RMPC_NB)        \
-    X(dux, (S) * RMPC_NV) X(dpi, (S) * RMPC_NX) X(dlam, (S) * RMPC_NB) X(dt_, (S) * RMPC_NB)                          \
-    X(res_g, (S) * RMPC_NV) X(res_b, (S) * RMPC_NX) X(res_d, (S) * RMPC_NB) X(res_m, (S) * RMPC_NB)                   \
-    X(res_mc, (S) * RMPC_NB) X(pvec, (S) * RMPC_NX) X(F, (S) * RMPC_FS)                                               \
-    X(ig, (S) * RMPC_NV) X(ib, (S) * RMPC_NX) X(id, (S) * RMPC_NB) X(im, (S) * RMPC_NB)                               \
-    X(iux, (S) * RMPC_NV) X(ipi, (S) * RMPC_NX) X(ilam, (S) * RMPC_NB) X(it, (S) * RMPC_NB) X(tux, (S) * RMPC_NV)
+/* Per-instance "slab": all solver data of ONE instance is contiguous in HBM,
+ *     slab = [ head (RMPC_HEAD doubles) | array 0 | array 1 | ... ],   array k = [Sp stage slots][width_k doubles],
+ * Sp = number of stage slots N + 1 rounded up to even (16-byte alignment of every array).  Array k starts at
+ * RMPC_HEAD + RC_k * Sp with RC_k a COMPILE-TIME constant (the summed widths of the arrays before it), so the kernels
+ * address everything from one base pointer and the register holding Sp -- no table of 40 pointers to keep alive.
+ * Within an array the stage index is the slow one: lanes that sweep stages in parallel (stage-parallel passes) and
+ * lanes that sweep the components of one stage (Riccati sweeps) both touch neighbouring 128-byte lines. */
+#define RMPC_WS_ARRAYS(X)                                                                                             \
+    X(ux, RMPC_NV) X(pi, RMPC_NX) X(lam, RMPC_NB) X(wpi, RMPC_NX) X(wlam, RMPC_NB)                                    \
+    X(Jc, RMPC_NJ) X(rqz, RMPC_NV) X(b, RMPC_NX) X(d, RMPC_NB)                                                        \
+    X(sux, RMPC_NV) X(spi, RMPC_NX) X(slam, RMPC_NB) X(st, RMPC_NB)                                                   \
+    X(dux, RMPC_NV) X(dpi, RMPC_NX) X(dlam, RMPC_NB) X(dt_, RMPC_NB)                                                  \
+    X(res_g, RMPC_NV) X(res_b, RMPC_NX) X(res_d, RMPC_NB) X(res_m, RMPC_NB) X(res_mc, RMPC_NB) X(pvec, RMPC_NX)       \
+    X(F, RMPC_FS)                                                                                                     \
+    X(ig, RMPC_NV) X(ib, RMPC_NX) X(id, RMPC_NB) X(im, RMPC_NB) X(iux, RMPC_NV) X(ipi, RMPC_NX) X(ilam, RMPC_NB)      \
+    X(it, RMPC_NB) X(tux, RMPC_NV)
 
+/* RC_<name> = doubles per stage slot of all arrays before <name>; RC_TOTAL = doubles per stage slot of a slab */
 enum
 {
-#define X(name, n) RA_##name,
-    RMPC_WS_ARRAYS(X, 0)
+#define X(name, w) RCW_##name = (w),
+    RMPC_WS_ARRAYS(X)
 #undef X
-    RA_COUNT
+};
+struct rmpc_rc_helper_
+{
+#define X(name, w) char name[w];
+    RMPC_WS_ARRAYS(X)
+#undef X
+};
+enum
+{
+#define X(name, w) RC_##name = (int) __builtin_offsetof(struct rmpc_rc_helper_, name),
+    RMPC_WS_ARRAYS(X)
+#undef X
+    RC_TOTAL = (int) sizeof(struct rmpc_rc_helper_)
+};
+
+/* small per-instance arrays at the head of the slab */
+enum
+{
+    H_LAMX0 = 0,    /* 24: multipliers of the stage-0 state equality [lower(12); upper(12)] (NLP iterate) */
+    H_WLAMX0 = 24,  /* 24: their merit weights */
+    H_DX0 = 48,     /* 12: x0 - x_nlp[0] */
+    H_G0U = 60,     /* 8 : stage-0 control gradient before the x0 elimination */
+    H_QLAMX0 = 68,  /* 24: multipliers of the eliminated equalities recovered from the QP */
+    RMPC_HEAD = 96
 };
 
 typedef struct
 {
     const double *par; /* [B][RP_COUNT] */
-    double *slab;      /* [B][slab_stride]: NLP iterate + merit weights (persist across steps), linearisation / QP data,
-                          IPM iterate / step / residuals / Riccati factors, refinement and line-search scratch */
-    long slab_stride;  /* doubles per instance (multiple of 16 = one 128-byte line) */
-    int off[RA_COUNT]; /* offset of each array inside a slab (multiples of 16 doubles) */
+    double *slab;      /* [B][slab_stride] per-instance slabs (layout above) */
+    long slab_stride;  /* doubles per instance = RMPC_HEAD + RC_TOTAL * Sp, rounded up to a 128-byte line */
+    int Sp;            /* stage slots per array: N + 1 rounded up to even */
     double *z;         /* [B][12] plant state */
     int *flags;        /* [B][4]: first_call, qp_warm2_pending, n_lq_needed, reserved */
     /* logs (may be null) */
@@ -152,17 +178,14 @@ typedef struct
     int step0;         /* index of the first step of this launch */
 } RmpcWs;
 
-/* fill off[] / slab_stride for a horizon of N intervals; returns the stride in doubles */
-static inline long rmpc_ws_layout(RmpcWs *w, int N)
-{
-    const long S = (long) N + 1;
-    long o = 0;
-    int k = 0;
-#define X(name, n) w->off[k++] = (int) o; o += (((long) (n)) + 15) / 16 * 16;
-    RMPC_WS_ARRAYS(X, S)
-#undef X
-    w->slab_stride = o;
-    return o;
-}
+#ifdef __CUDACC__
+#define RMPC_HD __host__ __device__
+#else
+#define RMPC_HD
+#endif
+RMPC_HD static inline int rmpc_slab_sp(int N) { return (N + 2) & ~1; }
+RMPC_HD static inline long rmpc_slab_stride(int N) { return ((long) RMPC_HEAD + (long) RC_TOTAL * rmpc_slab_sp(N) + 15) / 16 * 16; }
+/* offset inside a slab of element 0 of stage s of the array whose RC_ constant is rc and width is w */
+RMPC_HD static inline long rmpc_slab_off(int N, int rc, int w, int s) { return (long) RMPC_HEAD + (long) rc * rmpc_slab_sp(N) + (long) w * s; }
 
 #endif

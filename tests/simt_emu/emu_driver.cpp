@@ -36,7 +36,8 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
     RmpcWs W;
     memset(&W, 0, sizeof(W));
     std::vector<double *> owned;
-    rmpc_ws_layout(&W, D->N);
+    W.slab_stride = rmpc_slab_stride(D->N);
+    W.Sp = rmpc_slab_sp(D->N);
     W.slab = (double *) calloc((size_t) B * (size_t) W.slab_stride, sizeof(double));
     W.z = (double *) calloc((size_t) B * NX, sizeof(double));
     owned.push_back(W.slab);
@@ -50,7 +51,7 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
         memcpy(W.z + i * NX, z0 + i * NX, NX * sizeof(double));
         if (zlog) memcpy(zlog + i * (nsteps + 1) * NX, z0 + i * NX, NX * sizeof(double));
         /* initial guess x_k = x0, u_k = 0 (T/c_templates_tera/acados_solver.in.c:2744-2777) */
-        for (long k = 0; k < S; k++) memcpy(W.slab + i * W.slab_stride + W.off[RA_ux] + k * NV + 6, z0 + i * NX, NX * sizeof(double));
+        for (long k = 0; k < S; k++) memcpy(W.slab + i * W.slab_stride + rmpc_slab_off(D->N, RC_ux, NV, (int) k) + 6, z0 + i * NX, NX * sizeof(double));
         W.flags[i * 4 + 0] = 1;
         W.flags[i * 4 + 1] = 1;
     }

@@ -29,7 +29,7 @@ static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layou
 __global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, RMPC_MIN_CTAS)
 rmpc_closed_loop_kernel(const RmpcChain ch, const RmpcDims D, const RmpcWs W, int nsteps, int advance)
 {
-    __shared__ GrpSmem smem[RMPC_GROUPS_PER_CTA];
+    __shared__ __align__(16) GrpSmem smem[RMPC_GROUPS_PER_CTA];
     const int grp = threadIdx.x / RMPC_G;
     const long inst = (long) blockIdx.x * RMPC_GROUPS_PER_CTA + grp;
     if (inst >= D.B) return; /* a whole group exits together; the barriers of the other group carry its own mask */

@@ -51,6 +51,10 @@ RD double rd_fmax(double a, double b) { return a > b ? a : b; } /* NaN-ignoring 
 RD double rd_inf() { return INFINITY; }
 RD double rd_time() { return 0.0; }
 RD void rd_prefetch_l2(const void *) {}
+RD void rd_cp_async16(double *dst_smem, const double *src) { dst_smem[0] = src[0]; dst_smem[1] = src[1]; }
+RD void rd_cp_commit() {}
+RD void rd_cp_wait1() {}
+RD void rd_cp_wait0() {}
 #define RD_UNROLL
 struct rd_double2 { double x, y; };
 #else
@@ -75,6 +79,15 @@ RD double rd_time() /* seconds on the GPU's global nanosecond timer */
     return 1e-9 * (double) t;
 }
 RD void rd_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+/* asynchronous 16-byte global -> shared copy (LDGSTS, bypasses L1 and the register file); completion is tracked per
+ * thread in commit groups; data of OTHER lanes is visible after wait + rd_sync() */
+RD void rd_cp_async16(double *dst_smem, const double *src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+RD void rd_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+RD void rd_cp_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+RD void rd_cp_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 #define RD_UNROLL _Pragma("unroll")
 typedef double2 rd_double2;
 #endif
@@ -98,20 +111,36 @@ RD double grp_max(double v)
 }
 
 /* ---------------------------------------------------------------------------------------------- shared memory
- * one block per group (instance) */
+ * one block per group (instance).  `buf` is carved per sweep:
+ *   factorisation : P+ (12 x SM_PS) | Lxu (72) | Muu in (28) | L out (34) | two staging buffers of FS_STGN doubles
+ *   forward / backward substitution : two staging buffers of SW_STGN doubles
+ * The staging buffers are filled one stage AHEAD by cp.async (LDGSTS), so that inside a stage every operand comes from
+ * shared memory and the HBM / L2 latency of the streamed factors and residuals is off the critical path. */
 #define SM_PS 14 /* row stride of P: even (16-byte aligned pairs), 28 words -> rows 0..5 hit distinct banks */
+#define SM_BUF 640
 struct GrpSmem
 {
-    double P[12 * SM_PS]; /* cost-to-go matrix of stage ss+1, full symmetric, state order [q; qd] */
-    double pv[12];        /* cost-to-go vector p of stage ss+1 */
-    double tv[12], bv[12];
-    double Lxu[12 * 6];   /* Lxu of the current stage (for the Schur complement) */
-    double Muu[28];       /* lower 6x6 block (21) + m_u (6) */
+    double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
     double xv[12];        /* running state of the forward sweep */
     double uv[8];
-    double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
-    double Jc[NJ];        /* scaled task Jacobian of the current stage */
+    double tv[12];
+    double pv[12];        /* cost-to-go vector p of stage ss+1 */
+    double buf[SM_BUF];
 };
+#define FS_P(sm) ((sm).buf)         /* cost-to-go matrix of stage ss+1, full symmetric, state order [q; qd] */
+#define FS_LXU(sm) ((sm).buf + 168) /* Lxu of the current stage (for the Schur complement) */
+#define FS_MIN(sm) ((sm).buf + 240) /* lower 6x6 block Muu (21) + m_u (6) */
+#define FS_LOUT(sm) ((sm).buf + 268) /* L (21, packed with diagonal) + l_u (6) + 1/diag (6) */
+#define FS_STGN 164
+#define FS_STG(sm, k) ((sm).buf + 304 + (k) * FS_STGN)
+#define SW_STGN 320
+#define SW_STG(sm, k) ((sm).buf + (k) * SW_STGN)
+
+/* group-wide asynchronous copy of n doubles (n even, both sides 16-byte aligned) global -> shared */
+RD void stage_cp(double *dst, const double *src, const int n)
+{
+    for (int c = rd_lane(); c < n / 2; c += GL) rd_cp_async16(dst + 2 * c, src + 2 * c);
+}
 
 /* per-instance view (layout: rmpc_types.h): parameter row, slab head, first array, stage slots, plant state, flags */
 struct Inst
@@ -837,6 +866,19 @@ RD void smem_consts(const Inst &I, GrpSmem &sm)
  *   Luu Luu' = Muu, Lxu = Mxu Luu^-T, l_u = Luu^-1 m_u, P = Mxx - Lxu Lxu', p = m_x - Lxu l_u
  * (the reference factorises P = Lxx Lxx' as well and carries Lxx; see the header of this file).  The complementarity
  * residual enters as res_m - tau_min (BACKUP_RES_M + COMPUTE_TAU_MIN_QP, x_core_qp_ipm_aux.c:457-475,533-553). */
+/* staging layout of one stage for the factorisation */
+enum { FG_LAM = 0, FG_T = 24, FG_RD = 48, FG_RM = 72, FG_RG = 96, FG_RB = 114, FG_JC = 126 };
+RD void fac_stage_in(const Inst &I, double *dst, int ss)
+{
+    stage_cp(dst + FG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + FG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + FG_RD, AR(res_d) + NB * ss, NB);
+    stage_cp(dst + FG_RM, AR(res_m) + NB * ss, NB);
+    stage_cp(dst + FG_RG, AR(res_g) + NV * ss, NV);
+    stage_cp(dst + FG_RB, AR(res_b) + NX * ss, NX);
+    if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
+}
+
 RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
 {
     const int N = D.N, lane = rd_lane();
@@ -845,49 +887,49 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
     const int j = R.j, xk = R.xk;
     const StageConst sc = stage_const(par, D.dt, j);
     const double reg = 1e-15, tau_min = 1e-16;
+    double *P = FS_P(sm), *Lxu = FS_LXU(sm), *Min = FS_MIN(sm), *Lo = FS_LOUT(sm);
+    fac_stage_in(I, FS_STG(sm, (N - 1) & 1), N - 1);
+    rd_cp_commit();
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
     if (R.x)
     {
         double *FN = AR(F) + (long) FS * N;
         const double pv = AR(res_g)[NV * N + 6 + xk];
         RD_UNROLL
-        for (int c = 0; c < 12; c++) sm.P[xk * SM_PS + c] = (c == xk) ? reg : 0.0;
+        for (int c = 0; c < 12; c++) P[xk * SM_PS + c] = (c == xk) ? reg : 0.0;
         sm.pv[xk] = pv;
         for (int c = 0; c <= xk; c++) FN[RF_P + (xk * (xk + 1)) / 2 + c] = (c == xk) ? reg : 0.0;
         FN[RF_PV + xk] = pv;
     }
-    rd_sync();
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
         double *F = AR(F) + (long) FS * ss;
+        const double *G = FS_STG(sm, ss & 1);
+        if (ss > 0) fac_stage_in(I, FS_STG(sm, (ss - 1) & 1), ss - 1);
+        rd_cp_commit();
+        rd_cp_wait1();
+        rd_sync();
         /* (1) barrier terms of the bound slot owned by this lane (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
         double Gam = 0.0, gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
-            const double *lam = AR(slam) + NB * ss, *t = AR(st) + NB * ss, *rd = AR(res_d) + NB * ss, *rm = AR(res_m) + NB * ss;
+            const double *lam = G + FG_LAM, *t = G + FG_T, *rd = G + FG_RD, *rm = G + FG_RM;
             const double til = 1.0 / t[lane], tiu = 1.0 / t[12 + lane];
             Gam = til * lam[lane] + tiu * lam[12 + lane];
             gam = til * ((rm[lane] - tau_min) - lam[lane] * rd[lane]) - tiu * ((rm[12 + lane] - tau_min) - lam[12 + lane] * rd[12 + lane]);
         }
-        if (R.x) sm.bv[xk] = AR(res_b)[NX * ss + xk];
-        if (!s0)
-            for (int k = lane; k < NJ; k += GL) sm.Jc[k] = AR(Jc)[NJ * ss + k];
-        rd_sync();
         /* (2) tv = P+ b + p+ ; P+ b is kept for the corrector solves */
-        double Pq[12], Pd[12]; /* rows q_j and qd_j of P+ */
         if (R.x)
         {
+            double a = 0.0;
             RD_UNROLL
             for (int c = 0; c < 12; c += 2)
             {
-                const rd_double2 a = *reinterpret_cast<const rd_double2 *>(&sm.P[j * SM_PS + c]);
-                const rd_double2 bq = *reinterpret_cast<const rd_double2 *>(&sm.P[(6 + j) * SM_PS + c]);
-                Pq[c] = a.x; Pq[c + 1] = a.y; Pd[c] = bq.x; Pd[c + 1] = bq.y;
+                const rd_double2 pr = *reinterpret_cast<const rd_double2 *>(&P[xk * SM_PS + c]);
+                a += pr.x * G[FG_RB + c];
+                a += pr.y * G[FG_RB + c + 1];
             }
-            double a = 0.0;
-            RD_UNROLL
-            for (int c = 0; c < 12; c++) a += (R.q ? Pq[c] : Pd[c]) * sm.bv[c];
             F[RF_PB + xk] = a;
             sm.tv[xk] = a + sm.pv[xk];
         }
@@ -896,83 +938,92 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
         if (R.u)
         {
             const double b1j = C_B1(j), b2j = C_B2(j);
-            double row[6];
             RD_UNROLL
             for (int c = 0; c < 6; c++)
             {
-                const double eq = b1j * Pq[c] + b2j * Pd[c], ed = b1j * Pq[6 + c] + b2j * Pd[6 + c];
-                row[c] = C_B1(c) * eq + C_B2(c) * ed;
-                if (c == j) row[c] += reg + Gam + sc.hu;
+                const double eq = b1j * P[j * SM_PS + c] + b2j * P[(6 + j) * SM_PS + c];
+                const double ed = b1j * P[j * SM_PS + 6 + c] + b2j * P[(6 + j) * SM_PS + 6 + c];
+                double row = C_B1(c) * eq + C_B2(c) * ed;
+                if (c == j) row += reg + Gam + sc.hu;
+                if (c <= j) Min[(j * (j + 1)) / 2 + c] = row;
             }
-            RD_UNROLL
-            for (int c = 0; c < 6; c++)
-                if (c <= j) sm.Muu[(j * (j + 1)) / 2 + c] = row[c];
-            sm.Muu[21 + j] = AR(res_g)[NV * ss + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
+            Min[21 + j] = G[FG_RG + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
         }
         rd_sync();
         /* (3b) 6 x 6 Cholesky + forward substitution of m_u, redundantly in every lane (BLASFEO dpotrf_l: a
-         *      non-positive pivot zeroes its column) */
-        double Lu[21], lu[6], inv[6];
-        RD_UNROLL
-        for (int k = 0; k < 21; k++) Lu[k] = sm.Muu[k];
-        RD_UNROLL
-        for (int k = 0; k < 6; k++) lu[k] = sm.Muu[21 + k];
+         *      non-positive pivot zeroes its column); lane j < 6 publishes row j */
+        {
+            double Lu[21], lu[6], inv[6];
+            RD_UNROLL
+            for (int k = 0; k < 21; k++) Lu[k] = Min[k];
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) lu[k] = Min[21 + k];
 #define LU(r, c) Lu[((r) * ((r) + 1)) / 2 + (c)]
-        RD_UNROLL
-        for (int c = 0; c < 6; c++)
-        {
-            const double dj = LU(c, c);
-            const double iv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
-            inv[c] = iv;
-            LU(c, c) = dj * iv;
-            RD_UNROLL
-            for (int r = c + 1; r < 6; r++) LU(r, c) *= iv;
-            lu[c] *= iv;
-            RD_UNROLL
-            for (int k = c + 1; k < 6; k++)
-            {
-                RD_UNROLL
-                for (int r = k; r < 6; r++) LU(r, k) -= LU(r, c) * LU(k, c);
-                lu[k] -= lu[c] * LU(k, c);
-            }
-        }
-        if (R.u)
-        {
-            double ivj = 0.0, luj = 0.0;
             RD_UNROLL
             for (int c = 0; c < 6; c++)
-                if (c == j) { ivj = inv[c]; luj = lu[c]; }
-            F[RF_INV + j] = ivj > 0.0 ? ivj : rd_inf();
-            F[RF_LU + j] = luj;
-            RD_UNROLL
-            for (int r = 1; r < 6; r++)
+            {
+                const double dj = LU(c, c);
+                const double iv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
+                inv[c] = iv;
+                LU(c, c) = dj * iv;
                 RD_UNROLL
-                for (int c = 0; c < r; c++)
-                    if (r == j) F[RF_LUU + (r * (r - 1)) / 2 + c] = LU(r, c);
+                for (int r = c + 1; r < 6; r++) LU(r, c) *= iv;
+                lu[c] *= iv;
+                RD_UNROLL
+                for (int k = c + 1; k < 6; k++)
+                {
+                    RD_UNROLL
+                    for (int r = k; r < 6; r++) LU(r, k) -= LU(r, c) * LU(k, c);
+                    lu[k] -= lu[c] * LU(k, c);
+                }
+            }
+            if (R.u)
+            {
+                double ivj = 0.0, luj = 0.0;
+                RD_UNROLL
+                for (int c = 0; c < 6; c++)
+                    if (c == j) { ivj = inv[c]; luj = lu[c]; }
+                F[RF_INV + j] = ivj > 0.0 ? ivj : rd_inf();
+                F[RF_LU + j] = luj;
+                Lo[21 + j] = luj;
+                Lo[27 + j] = ivj;
+                RD_UNROLL
+                for (int r = 0; r < 6; r++)
+                    RD_UNROLL
+                    for (int c = 0; c <= r; c++)
+                        if (r == j)
+                        {
+                            Lo[(r * (r + 1)) / 2 + c] = LU(r, c);
+                            if (c < r) F[RF_LUU + (r * (r - 1)) / 2 + c] = LU(r, c);
+                        }
+            }
+#undef LU
         }
-        if (s0) { rd_sync(); continue; }
+        rd_sync();
+        if (s0) continue;
         /* (3c) state rows: e = row of [B A]' P+, then Mxu, Lxu, p */
         double e[12], Lx[6], pk = 0.0;
         if (R.x)
         {
             RD_UNROLL
-            for (int c = 0; c < 12; c++) e[c] = R.q ? Pq[c] : (R.ca * Pq[c] + R.cb * Pd[c]);
+            for (int c = 0; c < 12; c++)
+                e[c] = R.q ? P[j * SM_PS + c] : (R.ca * P[j * SM_PS + c] + R.cb * P[(6 + j) * SM_PS + c]);
             RD_UNROLL
             for (int c = 0; c < 6; c++)
             {
                 double v = C_B1(c) * e[c] + C_B2(c) * e[6 + c];
                 if (!R.q && c == j) v += sc.hs;
                 RD_UNROLL
-                for (int k = 0; k < c; k++) v -= Lx[k] * LU(c, k);
-                Lx[c] = v * inv[c];
+                for (int k = 0; k < c; k++) v -= Lx[k] * Lo[(c * (c + 1)) / 2 + k];
+                Lx[c] = v * Lo[27 + c];
             }
-            pk = AR(res_g)[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
+            pk = G[FG_RG + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
             RD_UNROLL
-            for (int c = 0; c < 6; c++) pk -= Lx[c] * lu[c];
+            for (int c = 0; c < 6; c++) pk -= Lx[c] * Lo[21 + c];
             RD_UNROLL
             for (int c = 0; c < 6; c++)
             {
-                sm.Lxu[xk * 6 + c] = Lx[c];
+                Lxu[xk * 6 + c] = Lx[c];
                 F[RF_LXU + xk * 6 + c] = Lx[c];
             }
         }
@@ -980,6 +1031,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
         /* (3d) Schur complement row: P[xk][:] = Mxx[xk][:] - Lxu[xk][:] Lxu' */
         if (R.x)
         {
+            const double *Jc = G + FG_JC;
             double Pn[12];
             RD_UNROLL
             for (int c = 0; c < 6; c++)
@@ -994,9 +1046,9 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
                 {
                     double a = 0.0;
                     RD_UNROLL
-                    for (int m = 0; m < 5; m++) a += sm.Jc[6 * m + j] * sm.Jc[6 * m + c];
+                    for (int m = 0; m < 5; m++) a += Jc[6 * m + j] * Jc[6 * m + c];
                     Pn[c] += a;
-                    Pn[6 + c] += sm.Jc[24 + j] * sm.Jc[30 + c];
+                    Pn[6 + c] += Jc[24 + j] * Jc[30 + c];
                 }
             }
             else
@@ -1004,8 +1056,8 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
                 RD_UNROLL
                 for (int c = 0; c < 6; c++)
                 {
-                    Pn[c] += sm.Jc[30 + j] * sm.Jc[24 + c];
-                    Pn[6 + c] += sm.Jc[30 + j] * sm.Jc[30 + c];
+                    Pn[c] += Jc[30 + j] * Jc[24 + c];
+                    Pn[6 + c] += Jc[30 + j] * Jc[30 + c];
                 }
             }
             RD_UNROLL
@@ -1018,7 +1070,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
                 RD_UNROLL
                 for (int k = 0; k < 6; k += 2)
                 {
-                    const rd_double2 lc = *reinterpret_cast<const rd_double2 *>(&sm.Lxu[c * 6 + k]);
+                    const rd_double2 lc = *reinterpret_cast<const rd_double2 *>(&Lxu[c * 6 + k]);
                     a -= Lx[k] * lc.x;
                     a -= Lx[k + 1] * lc.y;
                 }
@@ -1027,7 +1079,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
             RD_UNROLL
             for (int c = 0; c < 12; c++)
             {
-                sm.P[xk * SM_PS + c] = Pn[c];
+                P[xk * SM_PS + c] = Pn[c];
                 if (c <= xk) F[RF_P + (xk * (xk + 1)) / 2 + c] = Pn[c];
             }
             sm.pv[xk] = pk;
@@ -1035,7 +1087,7 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
         }
         rd_sync();
     }
-#undef LU
+    rd_cp_wait0();
 }
 
 /* Forward sweep of the Riccati recursion (H/ocp_qp/x_ocp_qp_kkt.c:970-1005 and :1671-1721) fused with everything that
@@ -1046,6 +1098,27 @@ RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
  *   sums[0] = sum lam dt + dlam t, sums[1] = sum dlam dt          (for COMPUTE_MU_AFF_QP, :424-441, see ipm_mu_aff)
  * STORED = 0: src_u = l_u and p+ from the factorisation (affine step); STORED = 1: src_u = z_u left in X[.][0:6] by
  * ipm_backward() and p+ = pvec.  rm enters as rm - mshift. */
+/* staging layout of one stage for the forward sweep: [0,100) = F[ss] (1/diag, l_u, Luu, Lxu), [100,190) = P, p of
+ * F[ss+1] at their RF_* offsets, then the bound-slot data, res_b and (STORED) z_u, p of the corrector */
+enum { WG_LAM = 190, WG_T = 214, WG_RD = 238, WG_RM = 262, WG_RB = 286, WG_ZU = 298, WG_PVEC = 304 };
+template <int STORED>
+RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rb, const double *rd, const double *rm, const double *X)
+{
+    const double *F = AR(F) + (long) FS * ss;
+    stage_cp(dst, F, RF_P);
+    stage_cp(dst + RF_P, F + FS + RF_P, STORED ? RF_PV - RF_P : RF_PB - RF_P);
+    stage_cp(dst + WG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + WG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + WG_RD, rd + NB * ss, NB);
+    stage_cp(dst + WG_RM, rm + NB * ss, NB);
+    stage_cp(dst + WG_RB, rb + NX * ss, NX);
+    if (STORED)
+    {
+        stage_cp(dst + WG_ZU, X + NV * ss, 6);
+        stage_cp(dst + WG_PVEC, AR(pvec) + NX * (ss + 1), NX);
+    }
+}
+
 template <int STORED>
 RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rb, const double *rd, const double *rm,
                     double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out, double *sums)
@@ -1053,40 +1126,40 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
-    const double a12 = I.par[RP_A12 + j], a22 = I.par[RP_A22 + j], b1 = I.par[RP_B1 + j], b2 = I.par[RP_B2 + j];
+    const double a12 = C_A12(j), a22 = C_A22(j), b1 = C_B1(j), b2 = C_B2(j);
+    fwd_stage_in<STORED>(I, SW_STG(sm, 0), 0, rb, rd, rm, X);
+    rd_cp_commit();
     if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
-    rd_sync();
     double alpha = 1.0, sB = 0.0, sC = 0.0;
     for (int ss = 0; ss < N; ss++)
     {
-        const double *F = AR(F) + (long) FS * ss, *Fn = F + FS;
+        const double *G = SW_STG(sm, ss & 1);
+        if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rb, rd, rm, X);
+        rd_cp_commit();
+        rd_cp_wait1();
+        rd_sync();
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
-            double s = STORED ? X[NV * ss + lane] : F[RF_LU + lane];
+            double s = STORED ? G[WG_ZU + lane] : G[RF_LU + lane];
             if (ss > 0)
             {
                 RD_UNROLL
-                for (int k = 0; k < 12; k++) s += F[RF_LXU + k * 6 + lane] * sm.xv[k];
+                for (int k = 0; k < 12; k++) s += G[RF_LXU + k * 6 + lane] * sm.xv[k];
             }
             sm.uv[lane] = s;
         }
         rd_sync();
         /* du = -Luu^-T s, redundantly in every lane */
         double du[6];
+        RD_UNROLL
+        for (int k = 0; k < 6; k++) du[k] = -sm.uv[k];
+        RD_UNROLL
+        for (int k = 5; k >= 0; k--)
         {
-            double iv[6], Ls[15];
+            du[k] *= G[RF_INV + k];
             RD_UNROLL
-            for (int k = 0; k < 6; k++) { du[k] = -sm.uv[k]; iv[k] = F[RF_INV + k]; }
-            RD_UNROLL
-            for (int k = 0; k < 15; k++) Ls[k] = F[RF_LUU + k];
-            RD_UNROLL
-            for (int k = 5; k >= 0; k--)
-            {
-                du[k] *= iv[k];
-                RD_UNROLL
-                for (int c = 0; c < k; c++) du[c] -= Ls[(k * (k - 1)) / 2 + c] * du[k];
-            }
+            for (int c = 0; c < k; c++) du[c] -= G[RF_LUU + (k * (k - 1)) / 2 + c] * du[k];
         }
         double duj = du[0], dul = du[0];
         RD_UNROLL
@@ -1100,8 +1173,8 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
         double xn = 0.0;
         if (R.x)
         {
-            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + rb[NX * ss + j];
-            else xn = a22 * sm.xv[6 + j] + b2 * duj + rb[NX * ss + 6 + j];
+            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[WG_RB + j];
+            else xn = a22 * sm.xv[6 + j] + b2 * duj + G[WG_RB + 6 + j];
         }
         rd_sync(); /* every lane has read xv, uv */
         if (R.u) X[NV * ss + lane] = dul;
@@ -1110,17 +1183,17 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
         /* dpi = P+ dx+ + p+ */
         if (R.x)
         {
-            double a = STORED ? AR(pvec)[NX * (ss + 1) + xk] : Fn[RF_PV + xk];
+            double a = STORED ? G[WG_PVEC + xk] : G[RF_PV + xk];
             RD_UNROLL
-            for (int c = 0; c < 12; c++) a += psym(Fn + RF_P, xk, c) * sm.xv[c];
+            for (int c = 0; c < 12; c++) a += psym(G + RF_P, xk, c) * sm.xv[c];
             PI[NX * ss + xk] = a;
         }
         /* multiplier / slack step of this lane's bound slot, step length, second-order sums */
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
             const int ia = NB * ss + lane, ib = ia + 12;
-            const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
-            const double da = rd[ia], db = rd[ib], ma = rm[ia] - mshift, mb = rm[ib] - mshift;
+            const double la = G[WG_LAM + lane], lb = G[WG_LAM + 12 + lane], ta = G[WG_T + lane], tb = G[WG_T + 12 + lane];
+            const double da = G[WG_RD + lane], db = G[WG_RD + 12 + lane], ma = G[WG_RM + lane] - mshift, mb = G[WG_RM + 12 + lane] - mshift;
             const double dla = -(ma + (la * dv) - (la * da)) / ta;
             const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
             const double dta = dv - da, dtb = -dv - db;
@@ -1132,7 +1205,9 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
             sB += (la * dta + dla * ta) + (lb * dtb + dlb * tb);
             sC += dla * dta + dlb * dtb;
         }
+        rd_sync(); /* the staging buffer of this stage is refilled by the next iteration */
     }
+    rd_cp_wait0();
     if (R.u) X[NV * N + lane] = 0.0;
     rd_sync();
     *alpha_out = -grp_max(-alpha);
@@ -1147,6 +1222,31 @@ RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double 
  *   1  COMPUTE_CENTERING_CORRECTION_QP (:479-505): rm = res_m + dt_aff dlam_aff - sigma_mu, written to res_mc;
  *   2  COMPUTE_CENTERING_QP (:509-529):            rm = res_m - sigma_mu, written to res_mc.
  * USE_PB: P+ rb was stored by the factorisation (rb = res_b); otherwise it is recomputed from P+. */
+/* staging layout of one stage for the backward substitution: [0,100) = F[ss] (1/diag, -, Luu, Lxu), then P+ b, res_g,
+ * lam, t, res_d and the complementarity data of the MODE */
+enum { BG_PB = 100, BG_RG = 112, BG_LAM = 130, BG_T = 154, BG_RD = 178, BG_RM = 202, BG_DT = 226, BG_DLAM = 250 };
+template <int MODE, int USE_PB>
+RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rd, const double *rm)
+{
+    const double *F = AR(F) + (long) FS * ss;
+    stage_cp(dst, F, RF_P);
+    if (USE_PB) stage_cp(dst + BG_PB, F + RF_PB, NX);
+    stage_cp(dst + BG_RG, rg + NV * ss, NV);
+    stage_cp(dst + BG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + BG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + BG_RD, rd + NB * ss, NB);
+    if (MODE == 0) stage_cp(dst + BG_RM, rm + NB * ss, NB);
+    else
+    {
+        stage_cp(dst + BG_RM, AR(res_m) + NB * ss, NB);
+        if (MODE == 1)
+        {
+            stage_cp(dst + BG_DT, AR(dt_) + NB * ss, NB);
+            stage_cp(dst + BG_DLAM, AR(dlam) + NB * ss, NB);
+        }
+    }
+}
+
 template <int MODE, int USE_PB>
 RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                      const double *rm, double sigma_mu, double *X)
@@ -1154,24 +1254,30 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
-    const double b1 = I.par[RP_B1 + j], b2 = I.par[RP_B2 + j];
+    const double b1 = C_B1(j), b2 = C_B2(j);
+    bwd_stage_in<MODE, USE_PB>(I, SW_STG(sm, (N - 1) & 1), N - 1, rg, rd, rm);
+    rd_cp_commit();
     if (R.x)
     {
         const double pv = rg[NV * N + 6 + xk];
         sm.pv[xk] = pv;
         AR(pvec)[NX * N + xk] = pv;
     }
-    rd_sync();
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        const double *F = AR(F) + (long) FS * ss, *Fn = F + FS;
+        const double *G = SW_STG(sm, ss & 1);
+        if (ss > 0) bwd_stage_in<MODE, USE_PB>(I, SW_STG(sm, (ss - 1) & 1), ss - 1, rg, rd, rm);
+        rd_cp_commit();
+        rd_cp_wait1();
+        rd_sync();
         if (R.x)
         {
             double pb;
-            if (USE_PB) pb = F[RF_PB + xk];
+            if (USE_PB) pb = G[BG_PB + xk];
             else
             {
+                const double *Fn = AR(F) + (long) FS * (ss + 1);
                 pb = 0.0;
                 RD_UNROLL
                 for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[NX * ss + c];
@@ -1182,41 +1288,36 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
         if (lane < 12 && !(s0 && lane >= 6))
         {
             const int ia = NB * ss + lane, ib = ia + 12;
-            const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
+            const double la = G[BG_LAM + lane], lb = G[BG_LAM + 12 + lane], ta = G[BG_T + lane], tb = G[BG_T + 12 + lane];
             double ma, mb;
-            if (MODE == 0) { ma = rm[ia]; mb = rm[ib]; }
+            if (MODE == 0) { ma = G[BG_RM + lane]; mb = G[BG_RM + 12 + lane]; }
             else
             {
                 if (MODE == 1)
                 {
-                    ma = AR(res_m)[ia] + AR(dt_)[ia] * AR(dlam)[ia] - sigma_mu;
-                    mb = AR(res_m)[ib] + AR(dt_)[ib] * AR(dlam)[ib] - sigma_mu;
+                    ma = G[BG_RM + lane] + G[BG_DT + lane] * G[BG_DLAM + lane] - sigma_mu;
+                    mb = G[BG_RM + 12 + lane] + G[BG_DT + 12 + lane] * G[BG_DLAM + 12 + lane] - sigma_mu;
                 }
-                else { ma = AR(res_m)[ia] - sigma_mu; mb = AR(res_m)[ib] - sigma_mu; }
+                else { ma = G[BG_RM + lane] - sigma_mu; mb = G[BG_RM + 12 + lane] - sigma_mu; }
                 AR(res_mc)[ia] = ma; AR(res_mc)[ib] = mb;
             }
-            gam = (ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb;
+            gam = (ma - la * G[BG_RD + lane]) / ta - (mb - lb * G[BG_RD + 12 + lane]) / tb;
         }
         rd_sync();
         double rx = 0.0;
-        if (R.u) sm.uv[lane] = rg[NV * ss + lane] + gam + (b1 * sm.tv[j] + b2 * sm.tv[6 + j]);
-        if (R.x && !s0) rx = rg[NV * ss + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
+        if (R.u) sm.uv[lane] = G[BG_RG + lane] + gam + (b1 * sm.tv[j] + b2 * sm.tv[6 + j]);
+        if (R.x && !s0) rx = G[BG_RG + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
         rd_sync();
         /* TRSV_LNN_MN(18, 6): z_u = Luu^-1 r_u (redundantly in every lane), r_x -= Lxu z_u */
         double z[6];
+        RD_UNROLL
+        for (int k = 0; k < 6; k++) z[k] = sm.uv[k];
+        RD_UNROLL
+        for (int k = 0; k < 6; k++)
         {
-            double iv[6], Ls[15];
+            z[k] *= G[RF_INV + k];
             RD_UNROLL
-            for (int k = 0; k < 6; k++) { z[k] = sm.uv[k]; iv[k] = F[RF_INV + k]; }
-            RD_UNROLL
-            for (int k = 0; k < 15; k++) Ls[k] = F[RF_LUU + k];
-            RD_UNROLL
-            for (int k = 0; k < 6; k++)
-            {
-                z[k] *= iv[k];
-                RD_UNROLL
-                for (int r = k + 1; r < 6; r++) z[r] -= Ls[(r * (r - 1)) / 2 + k] * z[k];
-            }
+            for (int r = k + 1; r < 6; r++) z[r] -= G[RF_LUU + (r * (r - 1)) / 2 + k] * z[k];
         }
         if (R.u)
         {
@@ -1229,12 +1330,13 @@ RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
         if (R.x && !s0)
         {
             RD_UNROLL
-            for (int k = 0; k < 6; k++) rx -= F[RF_LXU + xk * 6 + k] * z[k];
+            for (int k = 0; k < 6; k++) rx -= G[RF_LXU + xk * 6 + k] * z[k];
             sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
             AR(pvec)[NX * ss + xk] = rx;
         }
         rd_sync();
     }
+    rd_cp_wait0();
 }
 
 /* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction) */

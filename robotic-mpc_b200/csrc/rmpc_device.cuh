@@ -40,9 +40,12 @@
 #ifdef RMPC_EMU
 #include "simt_emu.h"
 #define RD static inline
+#define RDN static
 #define RDM inline
 RD int rd_lane() { return simt_emu::lane_id(); }
 RD void rd_sync() { simt_emu::syncwarp(); }
+RD void rd_sync_mask(unsigned) { simt_emu::syncwarp(); }
+RD unsigned rd_mask() { return 0; }
 RD double rd_shfl(double v, int src) { return simt_emu::shfl(v, src & (GL - 1)); }
 RD double rd_shfl_xor(double v, int m) { return simt_emu::shfl(v, (simt_emu::lane_id() ^ m) & (GL - 1)); }
 RD double rd_rsqrt(double x) { return 1.0 / sqrt(x); }
@@ -59,6 +62,9 @@ RD void rd_cp_wait0() {}
 struct rd_double2 { double x, y; };
 #else
 #define RD __device__ __forceinline__
+/* the large phases are real functions: one copy each (the SQP and SQP_RTI drivers, the predictor and corrector solves
+ * share them), which keeps the kernel's code inside the instruction caches */
+#define RDN __device__ __noinline__
 #define RDM __device__ __forceinline__
 RD unsigned rd_mask()
 {
@@ -66,6 +72,7 @@ RD unsigned rd_mask()
 }
 RD int rd_lane() { return threadIdx.x & (GL - 1); }
 RD void rd_sync() { __syncwarp(rd_mask()); }
+RD void rd_sync_mask(unsigned m) { __syncwarp(m); }
 RD double rd_shfl(double v, int src) { return __shfl_sync(rd_mask(), v, src, GL); }
 RD double rd_shfl_xor(double v, int m) { return __shfl_xor_sync(rd_mask(), v, m, GL); }
 RD double rd_rsqrt(double x) { return rsqrt(x); }
@@ -149,7 +156,12 @@ struct Inst
     double *head, *arr0, *z;
     int *flags;
     int Sp;
+    unsigned pair; /* lane mask of all groups of this warp that run an instance (re-convergence points) */
 };
+/* Re-convergence point for the groups that share a warp.  They run independent instances and may drift apart inside
+ * the interior-point loop (different iteration counts); once apart, the warp issues every instruction twice at half
+ * width.  At places that every group passes exactly once per step they wait for each other and run in lock step again. */
+#define PAIR_SYNC() rd_sync_mask(I.pair)
 #define AR(name) (I.arr0 + (long) RC_##name * I.Sp)
 
 RD Inst inst_view(const RmpcWs &w, int N, long i)
@@ -162,6 +174,7 @@ RD Inst inst_view(const RmpcWs &w, int N, long i)
     v.par = w.par + i * RP_COUNT;
     v.z = w.z + i * NX;
     v.flags = w.flags + i * 4;
+    v.pair = rd_mask();
     return v;
 }
 
@@ -502,7 +515,7 @@ struct LinEmit
  * Writes per stage: Jc = sqrt(dt W_m) * d y5_m / d x (non-zero entries), rqz = cost gradient, b = dynamics gap,
  * d = [lb - v; v - ub]; dx0 = x0 - x_nlp[0] (both bound residuals of the stage-0 state equality).
  * Returns the total cost. */
-RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *x0)
+RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *x0)
 {
     const int N = D.N, lane = rd_lane();
     const double dt = D.dt;
@@ -558,7 +571,7 @@ RD double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, c
 /* Merit function at the trial iterate tux, ocp_nlp_evaluate_merit_fun
  * (AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:606-702):
  *   M = cost + sum |w_pi| |dyn gap| + sum |w_lam| max(0, bound violation)   (incl. the stage-0 x0 equality) */
-RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *tux, const double *x0)
+RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *tux, const double *x0)
 {
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
@@ -602,7 +615,7 @@ RD double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const
 
 /* KKT residual inf-norms of the NLP, ocp_nlp_res_compute (AC/ocp_nlp/ocp_nlp_common.c:3641-3751); uses the
  * linearisation (rqz, b, d, dx0) of the current iterate.  res = [stat, eq, ineq, comp]. */
-RD void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
+RDN void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
 {
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
@@ -679,7 +692,7 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
  * warm = 0 (every QP but the first, see oracle/rmpc_oracle.c:solve_qp for the reference quirk): ux = 0, pi = 0,
  * t = slack pushed to >= 0.1 by moving ux, lam = mu0 / t with mu0 = 1 (t0_init 2, var_init_scheme 1, :1837-1978).
  * The primal iterate is zeroed first in both cases (AC/ocp_qp/ocp_qp_hpipm.c:309-316). */
-RD void ipm_init(const RmpcDims &D, const Inst &I, int warm)
+RDN void ipm_init(const RmpcDims &D, const Inst &I, int warm)
 {
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] = 0.0;
@@ -747,7 +760,7 @@ RD void task_hess_mv(const double *Jc, const double *x, double *y)
  * :689-726) in nrm[0..3], nrm[4] = |res_m - tau_min|_inf, nrm[5] = NaN flag of rg[0]; returns sum lam*t (LIN = 0).
  * WRITE = 0 computes the norms only. */
 template <int LIN, int WRITE>
-RD double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const double *b, const double *d, const double *m,
+RDN double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const double *b, const double *d, const double *m,
                   double mshift, const double *ux, const double *pi, const double *lam, const double *t, const double *Lam,
                   const double *T, double *rg, double *rb, double *rd, double *rm, double *nrm)
 {
@@ -879,7 +892,7 @@ RD void fac_stage_in(const Inst &I, double *dst, int ss)
     if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
 }
 
-RD void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
+RDN void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
 {
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
@@ -1120,7 +1133,7 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rb, const
 }
 
 template <int STORED>
-RD void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rb, const double *rd, const double *rm,
+RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rb, const double *rd, const double *rm,
                     double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out, double *sums)
 {
     const int N = D.N, lane = rd_lane();
@@ -1248,7 +1261,7 @@ RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
 }
 
 template <int MODE, int USE_PB>
-RD void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
+RDN void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                      const double *rm, double sigma_mu, double *X)
 {
     const int N = D.N, lane = rd_lane();
@@ -1363,7 +1376,7 @@ RD double ipm_mu_aff(double sum_lt, const double *sums, double alpha, double nc_
 }
 
 /* UPDATE_VAR_QP (x_core_qp_ipm_aux.c:267-372): single damped step, lam / t floor */
-RD void ipm_update(const RmpcDims &D, const Inst &I, double a)
+RDN void ipm_update(const RmpcDims &D, const Inst &I, double a)
 {
     const int N = D.N, lane = rd_lane();
     const double lmin = 1e-16;
@@ -1386,7 +1399,7 @@ RD void ipm_update(const RmpcDims &D, const Inst &I, double a)
  * (0 ok, 2 max iter, 3 min step, 1 NaN).  The Householder-LQ fall-back of lq_fact = 1 is not implemented: its
  * trigger (linear-system residual > 1e-5, :2246-2276) is evaluated and counted in flags[2] so that any instance
  * that would have taken it is visible to the caller. */
-RD int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters)
+RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters)
 {
     const int N = D.N, lane = rd_lane();
     const double tol = D.qp_tol, alpha_min = 1e-8, tau_min = 1e-16;
@@ -1492,7 +1505,7 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
  * AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:705-755), ocp_nlp_line_search (:290-408, alpha = 1, 0.7, ...
  * while alpha*0.7 > 0.05; the last alpha is taken untested), ocp_nlp_update_variables_sqp
  * (AC/ocp_nlp/ocp_nlp_common.c:3259-3318, full_step_dual = 0).  Returns 1 on a NaN/inf merit value. */
-RD int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I, int nlp_iter, double *alpha_out)
+RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I, int nlp_iter, double *alpha_out)
 {
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < N * NX; k += GL)
@@ -1578,6 +1591,7 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
     rd_sync();
     int it = 0;
     const int qs = qp_solve(D, I, sm, first, &it);
+    PAIR_SYNC();
     o.sqp_iter = 1; o.qp_iter = it; o.qp_status = qs;
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0; /* rti_log_residuals = 0: the reference reports zeros */
     o.alpha = 0.0;
@@ -1619,9 +1633,11 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
  * R/simulator.py:199-241: x = plant state; solver.set(0,'lbx'/'ubx',x); solve; u = solver.get(0,'u'); plant RK4.
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
 RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, GrpSmem &sm, int nsteps,
-                         int advance = 1)
+                         int advance = 1, unsigned pairmask = 0)
 {
-    const Inst I = inst_view(W, D.N, inst);
+    Inst I_ = inst_view(W, D.N, inst);
+    if (pairmask) I_.pair = pairmask;
+    const Inst I = I_;
     const int lane = rd_lane(), N = D.N;
     const double *par = I.par;
     smem_consts(I, sm);
@@ -1639,6 +1655,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
     {
         const int gs = W.step0 + s;
         StepOut o;
+        PAIR_SYNC();
         const double t_begin = rd_time();
         if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o);
         else solve_sqp(ch, D, I, sm, o);

@@ -71,7 +71,7 @@ try:
     path = os.path.join(os.path.dirname(__file__), "..", "..", "robotic-mpc_b200", "csrc", "rmpc_device.cuh")
     name = "?"
     for i, ln in enumerate(open(path), 1):
-        m = re.match(r"^(?:template.*\n)?RDM? .*?(\w+)\(", ln)
+        m = re.match(r"^(?:template.*\n)?RD[MN]? .*?(\w+)\(", ln)
         if m and not ln.startswith(" "):
             name = m.group(1)
         func_of[i] = name

@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, RMPC_MIN_CTAS)
 rmpc_closed_loop_kernel(const __grid_constant__ RmpcChain ch, const __grid_constant__ RmpcDims D, const __grid_constant__ RmpcWs W, int nsteps,
                         int advance)
 {
-    __shared__ __align__(16) GrpSmem smem[RMPC_GROUPS_PER_CTA];
+    extern __shared__ __align__(16) unsigned char smem_raw[]; /* > 48 KB per CTA: dynamic, opted in at rmpc_create */
+    GrpSmem *smem = reinterpret_cast<GrpSmem *>(smem_raw);
     const int grp = threadIdx.x / RMPC_G;
     const long inst = (long) blockIdx.x * RMPC_GROUPS_PER_CTA + grp;
     if (inst >= D.B) return; /* a whole group exits together; the barriers of the other group carry its own mask */
@@ -153,6 +154,9 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || device < 0 || device >= ndev)
         return fail(nullptr, RMPC_ENODEV, "rmpc_create: no usable CUDA device (this library has no host fallback)");
     if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, RMPC_ENODEV, "rmpc_create: cudaSetDevice failed");
+    if (cudaFuncSetAttribute(rmpc_closed_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int) (sizeof(GrpSmem) * RMPC_GROUPS_PER_CTA)) != cudaSuccess)
+        return fail(nullptr, RMPC_ECUDA, "rmpc_create: cannot reserve the shared memory the closed-loop kernel needs");
     h = new rmpc_handle();
     memcpy(&h->D, dims, sizeof(RmpcDims));
     rmpc_chain_init(&h->ch);
@@ -252,7 +256,7 @@ static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
 {
     const int grid = (h->D.B + RMPC_GROUPS_PER_CTA - 1) / RMPC_GROUPS_PER_CTA;
     h->W.step0 = h->steps_done;
-    rmpc_closed_loop_kernel<<<grid, 32 * RMPC_WARPS_PER_CTA, 0, s>>>(h->ch, h->D, h->W, nsteps, advance);
+    rmpc_closed_loop_kernel<<<grid, 32 * RMPC_WARPS_PER_CTA, sizeof(GrpSmem) * RMPC_GROUPS_PER_CTA, s>>>(h->ch, h->D, h->W, nsteps, advance);
     h->launches++;
     CU(cudaGetLastError());
     return 0;

@@ -124,29 +124,90 @@ RD double grp_max(double v)
  * The staging buffers are filled one stage AHEAD by cp.async (LDGSTS), so that inside a stage every operand comes from
  * shared memory and the HBM / L2 latency of the streamed factors and residuals is off the critical path. */
 #define SM_PS 14 /* row stride of P: even (16-byte aligned pairs), 28 words -> rows 0..5 hit distinct banks */
-#define SM_BUF 640
+#define SM_BUF 752
 struct GrpSmem
 {
     double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
+    double hc[18];        /* hu(6) hs(6) hq(6): constant diagonal blocks of the Gauss-Newton Hessian (StageConst) */
     double xv[12];        /* running state of the forward sweep */
     double uv[8];
     double tv[12];
     double pv[12];        /* cost-to-go vector p of stage ss+1 */
+    double dp[12];        /* multiplier step of the current stage (forward sweep, residual check) */
+    double wv[6];         /* Jc dx of the current stage (forward sweep, residual check) */
     double buf[SM_BUF];
 };
+#define C_A12(c) sm.cst[(c)]
+#define C_A22(c) sm.cst[6 + (c)]
+#define C_B1(c) sm.cst[12 + (c)]
+#define C_B2(c) sm.cst[18 + (c)]
 #define FS_P(sm) ((sm).buf)         /* cost-to-go matrix of stage ss+1, full symmetric, state order [q; qd] */
 #define FS_LXU(sm) ((sm).buf + 168) /* Lxu of the current stage (for the Schur complement) */
 #define FS_MIN(sm) ((sm).buf + 240) /* lower 6x6 block Muu (21) + m_u (6) */
 #define FS_LOUT(sm) ((sm).buf + 268) /* L (21, packed with diagonal) + l_u (6) + 1/diag (6) */
 #define FS_STGN 164
 #define FS_STG(sm, k) ((sm).buf + 304 + (k) * FS_STGN)
-#define SW_STGN 320
+#define SW_STGN 376
 #define SW_STG(sm, k) ((sm).buf + (k) * SW_STGN)
 
 /* group-wide asynchronous copy of n doubles (n even, both sides 16-byte aligned) global -> shared */
 RD void stage_cp(double *dst, const double *src, const int n)
 {
     for (int c = rd_lane(); c < n / 2; c += GL) rd_cp_async16(dst + 2 * c, src + 2 * c);
+}
+
+/* Flat group-wide vector updates with the loads of four strides issued before the first use (memory-level
+ * parallelism: these passes are pure streaming and otherwise wait for one load round trip per element). */
+#ifdef RMPC_EMU
+#define RD_RESTRICT
+#else
+#define RD_RESTRICT __restrict__
+#endif
+RD void grp_axpy(double *RD_RESTRICT y, const double *RD_RESTRICT x, double a, int n) /* y += a x */
+{
+    int k = rd_lane();
+    for (; k + 3 * GL < n; k += 4 * GL)
+    {
+        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
+        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
+        y[k] = y0 + a * x0; y[k + GL] = y1 + a * x1; y[k + 2 * GL] = y2 + a * x2; y[k + 3 * GL] = y3 + a * x3;
+    }
+    for (; k < n; k += GL) y[k] += a * x[k];
+}
+RD void grp_xpay_to(double *RD_RESTRICT z, const double *RD_RESTRICT x, const double *RD_RESTRICT y, double a, int n) /* z = x + a y */
+{
+    int k = rd_lane();
+    for (; k + 3 * GL < n; k += 4 * GL)
+    {
+        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
+        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
+        z[k] = x0 + a * y0; z[k + GL] = x1 + a * y1; z[k + 2 * GL] = x2 + a * y2; z[k + 3 * GL] = x3 + a * y3;
+    }
+    for (; k < n; k += GL) z[k] = x[k] + a * y[k];
+}
+RD void grp_lerp(double *RD_RESTRICT y, const double *RD_RESTRICT x, double al, int k0, int n) /* y = (1-al) y + al x on [k0, n) */
+{
+    int k = k0 + rd_lane();
+    for (; k + 3 * GL < n; k += 4 * GL)
+    {
+        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
+        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
+        y[k] = (1.0 - al) * y0 + al * x0; y[k + GL] = (1.0 - al) * y1 + al * x1;
+        y[k + 2 * GL] = (1.0 - al) * y2 + al * x2; y[k + 3 * GL] = (1.0 - al) * y3 + al * x3;
+    }
+    for (; k < n; k += GL) y[k] = (1.0 - al) * y[k] + al * x[k];
+}
+/* y = max(y + a x, lo) on [k0, n)   (UPDATE_VAR_QP for lam / t) */
+RD void grp_axpy_floor(double *RD_RESTRICT y, const double *RD_RESTRICT x, double a, double lo, int k0, int n)
+{
+    int k = k0 + rd_lane();
+    for (; k + 3 * GL < n; k += 4 * GL)
+    {
+        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
+        const double y0 = y[k] + a * x0, y1 = y[k + GL] + a * x1, y2 = y[k + 2 * GL] + a * x2, y3 = y[k + 3 * GL] + a * x3;
+        y[k] = y0 <= lo ? lo : y0; y[k + GL] = y1 <= lo ? lo : y1; y[k + 2 * GL] = y2 <= lo ? lo : y2; y[k + 3 * GL] = y3 <= lo ? lo : y3;
+    }
+    for (; k < n; k += GL) { const double v = y[k] + a * x[k]; y[k] = v <= lo ? lo : v; }
 }
 
 /* per-instance view (layout: rmpc_types.h): parameter row, slab head, first array, stage slots, plant state, flags */
@@ -760,7 +821,7 @@ RD void task_hess_mv(const double *Jc, const double *x, double *y)
  * :689-726) in nrm[0..3], nrm[4] = |res_m - tau_min|_inf, nrm[5] = NaN flag of rg[0]; returns sum lam*t (LIN = 0).
  * WRITE = 0 computes the norms only. */
 template <int LIN, int WRITE>
-RDN double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const double *b, const double *d, const double *m,
+RDN double ipm_res(const RmpcDims &D, const Inst &I, const GrpSmem &sm, const double *rqz, const double *b, const double *d, const double *m,
                   double mshift, const double *ux, const double *pi, const double *lam, const double *t, const double *Lam,
                   const double *T, double *rg, double *rb, double *rd, double *rm, double *nrm)
 {
@@ -787,13 +848,13 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I, const double *rqz, const do
             RD_UNROLL
             for (int k = 0; k < 6; k++)
             {
-                const StageConst c = stage_const(par, D.dt, k);
-                const double a12 = par[RP_A12 + k], a22 = par[RP_A22 + k], b1 = par[RP_B1 + k], b2 = par[RP_B2 + k];
-                g[k] += c.hu * v[k] + c.hs * v[12 + k] + b1 * pin[k] + b2 * pin[6 + k];
+                const double hu = sm.hc[k], hs = sm.hc[6 + k], hq = sm.hc[12 + k];
+                const double a12 = C_A12(k), a22 = C_A22(k), b1 = C_B1(k), b2 = C_B2(k);
+                g[k] += hu * v[k] + hs * v[12 + k] + b1 * pin[k] + b2 * pin[6 + k];
                 if (i > 0)
                 {
                     g[6 + k] += pin[k];
-                    g[12 + k] += c.hs * v[k] + c.hq * v[12 + k] + a12 * pin[k] + a22 * pin[6 + k];
+                    g[12 + k] += hs * v[k] + hq * v[12 + k] + a12 * pin[k] + a22 * pin[6 + k];
                 }
                 const double r0 = b[NX * i + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
                 const double r1 = b[NX * i + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
@@ -862,15 +923,16 @@ RD Role make_role(const double *par)
     return r;
 }
 
-RD void smem_consts(const Inst &I, GrpSmem &sm)
+RD void smem_consts(const Inst &I, GrpSmem &sm, double dt)
 {
     for (int k = rd_lane(); k < 24; k += GL) sm.cst[k] = I.par[RP_A12 + k]; /* a12 a22 b1 b2 are contiguous */
+    if (rd_lane() < 6)
+    {
+        const StageConst c = stage_const(I.par, dt, rd_lane());
+        sm.hc[rd_lane()] = c.hu; sm.hc[6 + rd_lane()] = c.hs; sm.hc[12 + rd_lane()] = c.hq;
+    }
     rd_sync();
 }
-#define C_A12(c) sm.cst[(c)]
-#define C_A22(c) sm.cst[6 + (c)]
-#define C_B1(c) sm.cst[12 + (c)]
-#define C_B2(c) sm.cst[18 + (c)]
 
 /* Backward Riccati factorisation, first half of OCP_QP_FACT_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:836-966) incl.
  * COMPUTE_GAMMA_GAMMA_QP (H/ipm_core/x_core_qp_ipm_aux.c:38-86).  For ss = N-1..0, with P+, p+ of stage ss+1:
@@ -1113,10 +1175,13 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
  * ipm_backward() and p+ = pvec.  rm enters as rm - mshift. */
 /* staging layout of one stage for the forward sweep: [0,100) = F[ss] (1/diag, l_u, Luu, Lxu), [100,190) = P, p of
  * F[ss+1] at their RF_* offsets, then the bound-slot data, res_b and (STORED) z_u, p of the corrector */
-enum { WG_LAM = 190, WG_T = 214, WG_RD = 238, WG_RM = 262, WG_RB = 286, WG_ZU = 298, WG_PVEC = 304 };
+enum { WG_LAM = 190, WG_T = 214, WG_RD = 238, WG_RM = 262, WG_RB = 286, WG_ZU = 298, WG_PVEC = 304, WG_RG = 316, WG_JC = 334 };
 template <int STORED>
-RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rb, const double *rd, const double *rm, const double *X)
+RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rb, const double *rd, const double *rm,
+                     const double *X)
 {
+    stage_cp(dst + WG_RG, rg + NV * ss, NV);
+    if (ss > 0) stage_cp(dst + WG_JC, AR(Jc) + NJ * ss, NJ);
     const double *F = AR(F) + (long) FS * ss;
     stage_cp(dst, F, RF_P);
     stage_cp(dst + RF_P, F + FS + RF_P, STORED ? RF_PV - RF_P : RF_PB - RF_P);
@@ -1132,22 +1197,31 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rb, const
     }
 }
 
+/* The sweep also evaluates, at no extra pass over the data, the stationarity residual of the LINEAR system it solves,
+ *   r = rg + H dv + [B A]' dpi - [0; dpi-] + dlam_ub - dlam_lb          (OCP_QP_RES_COMPUTE_LIN, H/ocp_qp/x_ocp_qp_res.c:535-685)
+ * whose inf-norm drives the LQ-fallback trigger and the iterative refinement (x_ocp_qp_ipm.c:2228-2276,2493-2594):
+ * lin[0] = |r|_inf, lin[1] = NaN flag of r_u[0] at stage 0.  The other three residuals of that system (dynamics,
+ * bounds, complementarity) are zero up to rounding BY CONSTRUCTION of dx+, dt and dlam in this sweep and are not
+ * re-evaluated. */
 template <int STORED>
-RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rb, const double *rd, const double *rm,
-                    double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out, double *sums)
+RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
+                    const double *rm, double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out,
+                    double *sums, double *lin)
 {
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
     const double a12 = C_A12(j), a22 = C_A22(j), b1 = C_B1(j), b2 = C_B2(j);
-    fwd_stage_in<STORED>(I, SW_STG(sm, 0), 0, rb, rd, rm, X);
+    const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
+    fwd_stage_in<STORED>(I, SW_STG(sm, 0), 0, rg, rb, rd, rm, X);
     rd_cp_commit();
     if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
     double alpha = 1.0, sB = 0.0, sC = 0.0;
+    double n0 = 0.0, nanflag = 0.0, dp_prev = 0.0;
     for (int ss = 0; ss < N; ss++)
     {
         const double *G = SW_STG(sm, ss & 1);
-        if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rb, rd, rm, X);
+        if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
         rd_cp_commit();
         rd_cp_wait1();
         rd_sync();
@@ -1161,6 +1235,18 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
                 for (int k = 0; k < 12; k++) s += G[RF_LXU + k * 6 + lane] * sm.xv[k];
             }
             sm.uv[lane] = s;
+        }
+        /* w = Jc dx of this stage (lane m < 5), for the residual check */
+        double wm = 0.0;
+        if (ss > 0 && lane < 5)
+        {
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) wm += G[WG_JC + 6 * lane + k] * sm.xv[k];
+            if (lane == 4)
+            {
+                RD_UNROLL
+                for (int k = 0; k < 6; k++) wm += G[WG_JC + 30 + k] * sm.xv[6 + k];
+            }
         }
         rd_sync();
         /* du = -Luu^-T s, redundantly in every lane */
@@ -1183,6 +1269,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
         }
         /* step of the variable of this lane's bound slot: u_l or q_{l-6} of THIS stage */
         const double dv = (lane < 6) ? dul : (lane < 12 ? sm.xv[lane - 6] : 0.0);
+        const double xo = R.x ? sm.xv[xk] : 0.0; /* own state row of THIS stage */
         double xn = 0.0;
         if (R.x)
         {
@@ -1192,16 +1279,21 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
         rd_sync(); /* every lane has read xv, uv */
         if (R.u) X[NV * ss + lane] = dul;
         if (R.x) { sm.xv[xk] = xn; X[NV * (ss + 1) + 6 + xk] = xn; }
+        if (lane < 5) sm.wv[lane] = wm;
         rd_sync();
         /* dpi = P+ dx+ + p+ */
+        double dpo = 0.0;
         if (R.x)
         {
             double a = STORED ? G[WG_PVEC + xk] : G[RF_PV + xk];
             RD_UNROLL
             for (int c = 0; c < 12; c++) a += psym(G + RF_P, xk, c) * sm.xv[c];
             PI[NX * ss + xk] = a;
+            sm.dp[xk] = a;
+            dpo = a;
         }
         /* multiplier / slack step of this lane's bound slot, step length, second-order sums */
+        double dlm = 0.0; /* dlam_ub - dlam_lb of the own slot */
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
             const int ia = NB * ss + lane, ib = ia + 12;
@@ -1217,15 +1309,51 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
             if (-alpha * dtb > tb) alpha = -tb / dtb;
             sB += (la * dta + dla * ta) + (lb * dtb + dlb * tb);
             sC += dla * dta + dlb * dtb;
+            dlm = dlb - dla;
         }
-        rd_sync(); /* the staging buffer of this stage is refilled by the next iteration */
+        /* operands of the residual rows that live in the staging buffer (refilled after the barrier) */
+        double rgu = 0.0, rgx = 0.0, jq[5] = {0, 0, 0, 0, 0}, jd = 0.0;
+        if (R.u) rgu = G[WG_RG + lane];
+        if (R.x && ss > 0)
+        {
+            rgx = G[WG_RG + 6 + xk];
+            if (R.q)
+            {
+                RD_UNROLL
+                for (int m = 0; m < 5; m++) jq[m] = G[WG_JC + 6 * m + j];
+            }
+            else jd = G[WG_JC + 30 + j];
+        }
+        rd_sync(); /* dp, wv published; the staging buffer of this stage is refilled by the next iteration */
+        if (R.u)
+        {
+            const double r = rgu + hu * dul + hs * xo + b1 * sm.dp[j] + b2 * sm.dp[6 + j] + dlm;
+            n0 = rd_fmax(n0, fabs(r));
+            if (ss == 0 && lane == 0 && r != r) nanflag = 1.0;
+        }
+        if (R.x && ss > 0)
+        {
+            double r;
+            if (R.q)
+            {
+                r = rgx + dlm + sm.dp[j] - dp_prev;
+                RD_UNROLL
+                for (int m = 0; m < 5; m++) r += jq[m] * sm.wv[m];
+            }
+            else r = rgx + jd * sm.wv[4] + hs * dul + hq * xo + a12 * sm.dp[j] + a22 * sm.dp[6 + j] - dp_prev;
+            n0 = rd_fmax(n0, fabs(r));
+        }
+        dp_prev = dpo;
     }
     rd_cp_wait0();
     if (R.u) X[NV * N + lane] = 0.0;
+    if (R.x) n0 = rd_fmax(n0, fabs(rg[NV * N + 6 + xk] - dp_prev)); /* stage N: no cost, no bounds */
     rd_sync();
     *alpha_out = -grp_max(-alpha);
     sums[0] = grp_sum(sB);
     sums[1] = grp_sum(sC);
+    lin[0] = grp_max(n0);
+    lin[1] = grp_max(nanflag);
 }
 
 /* Backward substitution with stored factors, first half of OCP_QP_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:
@@ -1380,16 +1508,18 @@ RDN void ipm_update(const RmpcDims &D, const Inst &I, double a)
 {
     const int N = D.N, lane = rd_lane();
     const double lmin = 1e-16;
-    for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] += a * AR(dux)[k];
-    for (int k = lane; k < N * NX; k += GL) AR(spi)[k] += a * AR(dpi)[k];
-    for (int k = lane; k < N * NB; k += GL)
+    grp_axpy(AR(sux), AR(dux), a, (N + 1) * NV);
+    grp_axpy(AR(spi), AR(dpi), a, N * NX);
+    /* stage 0 has bounds on u only: slots 0..5 and 12..17 */
+    if (lane < 12)
     {
-        const int i = k / NB, j = k - NB * i;
-        if (i == 0 && (j % 12) >= 6) continue;
-        double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
+        const int k = lane < 6 ? lane : lane + 6;
+        const double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
         AR(slam)[k] = l <= lmin ? lmin : l;
         AR(st)[k] = t <= lmin ? lmin : t;
     }
+    grp_axpy_floor(AR(slam), AR(dlam), a, lmin, NB, N * NB);
+    grp_axpy_floor(AR(st), AR(dt_), a, lmin, NB, N * NB);
     rd_sync();
 }
 
@@ -1406,7 +1536,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
     const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12);
     ipm_init(D, I, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
-    double sum_lt = ipm_res<0, 1>(D, I, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g),
+    double sum_lt = ipm_res<0, 1>(D, I, sm, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g),
                                   AR(res_b), AR(res_d), AR(res_m), nrm);
     double mu = nc_inv * sum_lt;
     int kk;
@@ -1414,10 +1544,9 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
     {
         /* affine (predictor) step */
         ipm_factor(D, I, sm);
-        ipm_forward<0>(D, I, sm, AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
-        ipm_res<1, 0>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr, nullptr,
-                      nullptr, nullptr, inrm);
-        if ((inrm[0] == 0.0 && inrm[5] > 0.5) || inrm[0] > 1e-5 || inrm[1] > 1e-5 || inrm[2] > 1e-5 || inrm[3] > 1e-5)
+        double lin[2];
+        ipm_forward<0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);
+        if ((lin[0] == 0.0 && lin[1] > 0.5) || lin[0] > 1e-5)
         {
             if (lane == 0) I.flags[2] += 1;
         }
@@ -1427,29 +1556,33 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         sigma_mu = sigma_mu > tau_min ? sigma_mu : tau_min;
         /* corrector: centering + second-order correction */
         ipm_backward<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
-        ipm_forward<1>(D, I, sm, AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
+        double clin[2];
+        ipm_forward<1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, clin);
         /* conditional predictor-corrector */
         const double mu_aff0 = mu_aff;
         mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         if (mu_aff > 2.0 * mu_aff0)
         {
             ipm_backward<2, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
-            ipm_forward<1>(D, I, sm, AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums);
+            ipm_forward<1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, clin);
         }
         /* iterative refinement of the corrector step, itref_corr_max = 2 */
         int refined = 0;
         for (int it = 0; it < 2; it++)
         {
-            ipm_res<1, 0>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr, nullptr,
-                          nullptr, nullptr, inrm);
+            /* first check: residual evaluated by the corrector's forward sweep itself; after a refinement: full pass */
+            if (it == 0) { inrm[0] = clin[0]; inrm[1] = inrm[2] = inrm[3] = 0.0; }
+            else
+                ipm_res<1, 0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr,
+                              nullptr, nullptr, nullptr, inrm);
             if ((inrm[0] < tol || inrm[0] < 1e-3 * nrm[0]) && (inrm[1] < tol || inrm[1] < 1e-3 * nrm[1]) &&
                 (inrm[2] < tol || inrm[2] < 1e-3 * nrm[2]) && (inrm[3] < tol || inrm[3] < 1e-3 * nrm[3]))
                 break;
-            ipm_res<1, 1>(D, I, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), AR(ig), AR(ib), AR(id),
+            ipm_res<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), AR(ig), AR(ib), AR(id),
                           AR(im), inrm);
-            double a2, s2[2];
+            double a2, s2[2], l2[2];
             ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-            ipm_forward<1>(D, I, sm, AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2);
+            ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
             refined = 1;
             for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
             for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
@@ -1460,7 +1593,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         double a = alpha;
         if (a < 1.0) a = a * ((1.0 - a) * 0.99 + a * 0.9999999);
         ipm_update(D, I, a);
-        sum_lt = ipm_res<0, 1>(D, I, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g), AR(res_b),
+        sum_lt = ipm_res<0, 1>(D, I, sm, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g), AR(res_b),
                                AR(res_d), AR(res_m), nrm);
         mu = nc_inv * sum_lt;
     }
@@ -1530,7 +1663,7 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        for (int k = lane; k < (N + 1) * NV; k += GL) AR(tux)[k] = AR(ux)[k] + alpha * AR(sux)[k];
+        grp_xpay_to(AR(tux), AR(ux), AR(sux), alpha, (N + 1) * NV);
         rd_sync();
         m1 = nlp_merit(ch, D, I, AR(tux), I.z);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
@@ -1539,13 +1672,14 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     }
     *alpha_out = alpha;
     if (!accepted && ((m1 != m1) || (m1 - m1 != 0.0))) return 1;
-    for (int k = lane; k < (N + 1) * NV; k += GL) AR(ux)[k] = AR(ux)[k] + alpha * AR(sux)[k];
-    for (int k = lane; k < N * NX; k += GL) AR(pi)[k] = (1.0 - alpha) * AR(pi)[k] + alpha * AR(spi)[k];
-    for (int k = lane; k < N * NB; k += GL)
+    grp_axpy(AR(ux), AR(sux), alpha, (N + 1) * NV);
+    grp_lerp(AR(pi), AR(spi), alpha, 0, N * NX);
+    if (lane < 12)
     {
-        if (k < NB && (k % 12) >= 6) continue;
+        const int k = lane < 6 ? lane : lane + 6;
         AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
     }
+    grp_lerp(AR(lam), AR(slam), alpha, NB, N * NB);
     for (int k = lane; k < NB; k += GL) (I.head + H_LAMX0)[k] = (1.0 - alpha) * (I.head + H_LAMX0)[k] + alpha * (I.head + H_QLAMX0)[k];
     rd_sync();
     return 0;
@@ -1640,7 +1774,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
     const Inst I = I_;
     const int lane = rd_lane(), N = D.N;
     const double *par = I.par;
-    smem_consts(I, sm);
+    smem_consts(I, sm, D.dt);
     /* tracking errors e1..e5 are logged at every plant sample incl. the initial state (Nsim + 1 samples,
      * R/simulation_model.py:24-38, R/simulator.py:265-344); RMSE / ITSE sums of R/simulator.py:347-390 */
     if (W.summary && W.step0 == 0 && lane == 0 && advance)

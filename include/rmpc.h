@@ -73,6 +73,14 @@ long long rmpc_device_bytes(const rmpc_handle *h);
  *   "x"     n = 12   state iterate of `stage` (0..N)        solver.set(stage, 'x', .)
  *   "u"     n = 6    control iterate of `stage` (0..N-1)    solver.set(stage, 'u', .)
  *   "pi"    n = 12   dynamics multipliers of `stage`        solver.set(stage, 'pi', .)
+ * Terminal ellipsoid lh_e <= x_N' P_e x_N <= alpha_e at stage N (BASELINE config 4; P_e, alpha_e from
+ * R/_terminal_constraint.py:96-116 terminal_ellipsoid_from_lqr; the acados equivalent is constraints.lh_e / uh_e with
+ * con_h_expr_e, i.e. ocp_nlp_constraints_model_set(.., N, "lh" / "uh", ..), acados_solver.in.c:2109-2116).  The first of
+ * these calls switches the row on for the handle; set all three (or "term") before the first solve:
+ *   "P_e"     n = 144  symmetric 12 x 12, row-major, state order [q; qd]
+ *   "alpha_e" n = 1    upper bound uh_e
+ *   "lh_e"    n = 1    lower bound (keep it finite and negative, e.g. -alpha_e: the row is two-sided like acados')
+ *   "term"    n = 146  [P_e(144), lh_e, alpha_e] in one call
  */
 int rmpc_set(rmpc_handle *h, const char *field, int stage, const double *dev, void *stream);
 
@@ -91,7 +99,8 @@ int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);
 
 /* Getters (copy to a device pointer).  Replaces AcadosOcpSolver.get / get_stats / get_residuals / get_cost
  * (T/acados_ocp_solver.py:939-989,1461-1723).  Fields, with the shape written to `dev`:
- *   "x" [B][12], "u" [B][6], "pi" [B][12], "lam" [B][24] ([lower(12); upper(12)] over [u; q]) of `stage`
+ *   "x" [B][12], "u" [B][6], "pi" [B][12], "lam" [B][24] ([lower(12); upper(12)] over [u; q]) of `stage`;
+ *       with a terminal row, "lam" of stage N holds its multipliers in entries 0 (lower) and 12 (upper)
  *   "z" [B][12] plant state
  *   "stats" [B][12]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
  *                    alpha, qp_status, device time of the solve in seconds (RL_* in csrc/rmpc_types.h); needs nlog > 0

@@ -43,9 +43,10 @@ typedef struct
     external_function_generic base; /* must be first: acados calls base.evaluate(self, ...) */
     const ur10_params *P;
     int kind;
+    const double *term_P; /* K_TERM_*: 12 x 12 symmetric, row-major */
 } ur10_ext_fun;
 
-enum { K_DYN_FUN, K_DYN_FUN_JAC, K_COST_FUN, K_COST_FUN_JAC };
+enum { K_DYN_FUN, K_DYN_FUN_JAC, K_COST_FUN, K_COST_FUN_JAC, K_TERM_FUN, K_TERM_FUN_JAC };
 
 static void read_vec(ext_fun_arg_t t, void *a, int n, double *out)
 {
@@ -122,6 +123,21 @@ static void ur10_ext_evaluate(void *self_, ext_fun_arg_t *tin, void **in, ext_fu
     ur10_ext_fun *self = self_;
     double x[NX], u[NU];
     read_vec(tin[0], in[0], NX, x);
+    if (self->kind == K_TERM_FUN || self->kind == K_TERM_FUN_JAC)
+    { /* h_e(x) = x' P x and its gradient 2 P x at stage N (nu = 0): the *_constr_h_e_fun[_jac_uxt_zt] pair of
+       * T/casadi_function_generation.py for con_h_expr_e = x' P x */
+        double h = 0.0, g[NX];
+        for (int r = 0; r < NX; r++)
+        {
+            double a = 0.0;
+            for (int k = 0; k < NX; k++) a += self->term_P[NX * r + k] * x[k];
+            g[r] = 2.0 * a;
+            h += x[r] * a;
+        }
+        write_vec(tout[0], out[0], 1, &h);
+        if (self->kind == K_TERM_FUN_JAC) write_mat(tout[1], out[1], NX, 1, g);
+        return;
+    }
     read_vec(tin[1], in[1], NU, u);
     switch (self->kind)
     {
@@ -182,7 +198,7 @@ typedef struct
     ocp_nlp_in *in;
     ocp_nlp_out *out;
     ocp_nlp_solver *solver;
-    ur10_ext_fun dyn_fun, dyn_fun_jac, cost_fun, cost_fun_jac;
+    ur10_ext_fun dyn_fun, dyn_fun_jac, cost_fun, cost_fun_jac, term_fun, term_fun_jac;
 } rmpc_ref;
 
 void rmpc_ref_destroy(rmpc_ref *c)
@@ -256,7 +272,8 @@ rmpc_ref *rmpc_ref_create(const rmpc_problem *prob, const double x0[12])
         for (int i = 0; i < N; i++) ocp_nlp_dims_set_cost(c->config, c->dims, i, "ny", &ny);
         for (int i = 0; i <= N; i++)
         {
-            ocp_nlp_dims_set_constraints(c->config, c->dims, i, "nh", &zero);
+            int nh = (i == N && p->term) ? 1 : 0; /* nh_e = 1: terminal ellipsoid */
+            ocp_nlp_dims_set_constraints(c->config, c->dims, i, "nh", &nh);
             ocp_nlp_dims_set_constraints(c->config, c->dims, i, "nsh", &zero);
         }
         ocp_nlp_dims_set_cost(c->config, c->dims, N, "ny", &zero);
@@ -453,6 +470,19 @@ rmpc_ref *rmpc_ref_create(const rmpc_problem *prob, const double x0[12])
             ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, i, "lbx", lbx);
             ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, i, "ubx", ubx);
         }
+    }
+
+    if (p->term)
+    { /* acados_solver.in.c:2109-2116 */
+        ur10_ext_init(&c->term_fun, &c->prob.model, K_TERM_FUN);
+        ur10_ext_init(&c->term_fun_jac, &c->prob.model, K_TERM_FUN_JAC);
+        c->term_fun.term_P = c->prob.term_P;
+        c->term_fun_jac.term_P = c->prob.term_P;
+        double lh = p->term_lh, uh = p->term_uh;
+        ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, N, "nl_constr_h_fun_jac", &c->term_fun_jac);
+        ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, N, "nl_constr_h_fun", &c->term_fun);
+        ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, N, "lh", &lh);
+        ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, N, "uh", &uh);
     }
 
     /* 7) solver, 8) precompute */

@@ -39,6 +39,7 @@ typedef struct
     double Wd[NY], yref[NY];
     double BAbt[NV * NX]; /* (nu+nx) x nx, column-major ld 18, identical for all stages (LTI) */
     double x0[NX];        /* lbx_0 = ubx_0 */
+    double term_c[NX];    /* gradient 2 P x_N of the terminal row h_e = x_N' P x_N at the current iterate (DCt of stage N) */
 
     /* NLP iterate (ocp_nlp_out): ux[i] = [u;x] (stage N: x at offset 0), pi[i], lam[i] = [lower; upper] */
     double *ux, *pi, *lam;
@@ -75,6 +76,23 @@ static int nb_full(const rmpc_oracle *s, int i) { return i == 0 ? 18 : (i < s->N
 static int rnu(const rmpc_oracle *s, int i) { return i < s->N ? NU : 0; }
 static int rnx(const rmpc_oracle *s, int i) { (void) s; return i == 0 ? 0 : NX; }
 static int rnb(const rmpc_oracle *s, int i) { return i == 0 ? 6 : (i < s->N ? 12 : 0); }
+/* general rows of the QP: the linearised terminal ellipsoid (nh_e = 1 -> ng = 1 at stage N); per-stage constraint vectors
+ * are laid out [lb(nb), lg(ng); ub(nb), ug(ng)] like acados / HPIPM do */
+static int ng_of(const rmpc_oracle *s, int i) { return (i == s->N && s->prob.term) ? 1 : 0; }
+static int nc_full(const rmpc_oracle *s, int i) { return nb_full(s, i) + ng_of(s, i); }
+static int rnc(const rmpc_oracle *s, int i) { return rnb(s, i) + ng_of(s, i); }
+static double term_h(const rmpc_oracle *s, const double *x, double *grad)
+{
+    double h = 0.0;
+    for (int r = 0; r < NX; r++)
+    {
+        double a = 0.0;
+        for (int k = 0; k < NX; k++) a += s->prob.term_P[NX * r + k] * x[k];
+        if (grad) grad[r] = 2.0 * a;
+        h += x[r] * a;
+    }
+    return h;
+}
 
 void rmpc_oracle_destroy(rmpc_oracle *s)
 {
@@ -219,6 +237,12 @@ static void linearise(rmpc_oracle *s)
     s->cost_fun[N] = 0.0;
     memset(s->rqz + NV * N, 0, NV * sizeof(double));
     memset(s->RSQ + 324 * N, 0, 324 * sizeof(double));
+    if (s->prob.term)
+    { /* BGH nh_e = 1 (AC/ocp_nlp/ocp_nlp_constraints_bgh.c:1219-1445,1563-1619): fun = [lh - h; h - uh], DCt = grad h */
+        const double h = term_h(s, s->ux + NV * N, s->term_c);
+        s->d[36 * N] = s->prob.term_lh - h;
+        s->d[36 * N + 1] = h - s->prob.term_uh;
+    }
 }
 
 /* KKT residuals of the NLP, ocp_nlp_res_compute (AC/ocp_nlp/ocp_nlp_common.c:3641-3751):
@@ -235,6 +259,8 @@ static void nlp_residuals(rmpc_oracle *s)
         double r[NV];
         for (int k = 0; k < nv; k++) r[k] = s->rqz[NV * i + k];
         for (int k = 0; k < nb; k++) r[k] -= lam[k] - lam[nb + k];
+        if (ng_of(s, i))
+            for (int k = 0; k < NX; k++) r[k] -= s->term_c[k] * (lam[0] - lam[1]); /* adj += DCt (lam_l - lam_u) */
         if (i < N)
             for (int k = 0; k < nv; k++)
             {
@@ -247,7 +273,7 @@ static void nlp_residuals(rmpc_oracle *s)
         for (int k = 0; k < nv; k++) if (fabs(r[k]) > rs) rs = fabs(r[k]);
         if (i < N)
             for (int j = 0; j < NX; j++) if (fabs(s->b[NX * i + j]) > re) re = fabs(s->b[NX * i + j]);
-        for (int k = 0; k < 2 * nb; k++)
+        for (int k = 0; k < 2 * nc_full(s, i); k++)
         {
             double f = s->d[36 * i + k];
             if (f > ri) ri = f;
@@ -267,7 +293,7 @@ static void qp_reduce(rmpc_oracle *s)
     memcpy(s->rRSQ, s->RSQ, sizeof(double) * 324 * (N + 1));
     memcpy(s->rrqz, s->rqz, sizeof(double) * NV * (N + 1));
     memcpy(s->rb, s->b, sizeof(double) * NX * (size_t) N);
-    for (int i = 1; i < N; i++) memcpy(s->rd + 24 * i, s->d + 36 * i, 24 * sizeof(double));
+    for (int i = 1; i <= N; i++) memcpy(s->rd + 24 * i, s->d + 36 * i, 24 * sizeof(double));
     /* stage 0: fixed x = d_lb (= x0 - x_nlp0) */
     double v[NV];
     memset(v, 0, sizeof(v));
@@ -316,6 +342,14 @@ static double ipm_res(const rmpc_oracle *s, int lin, const double *rqz, const do
             rd[24 * i + j] = d[24 * i + j] + tt[j] - v[j];
             rd[24 * i + nb + j] = d[24 * i + nb + j] + tt[nb + j] + v[j];
         }
+        if (ng_of(s, i))
+        { /* general row C x of stage N (nb = 0): res_g += C' (lam_ug - lam_lg), res_d = d + t -+ C x */
+            double cx = 0.0;
+            for (int k = 0; k < NX; k++) cx += s->term_c[k] * v[k];
+            for (int k = 0; k < NX; k++) g[k] += s->term_c[k] * (l[1] - l[0]);
+            rd[24 * i] = d[24 * i] + tt[0] - cx;
+            rd[24 * i + 1] = d[24 * i + 1] + tt[1] + cx;
+        }
         if (i < N)
         {
             const double *x1 = ux + NV * (i + 1) + rnu(s, i + 1);
@@ -332,7 +366,7 @@ static double ipm_res(const rmpc_oracle *s, int lin, const double *rqz, const do
                 g[k] += a;
             }
         }
-        for (int j = 0; j < 2 * nb; j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             if (!lin)
             {
@@ -353,7 +387,7 @@ static void ipm_res_norm(const rmpc_oracle *s, const double *rg, const double *r
     nrm[0] = nrm[1] = nrm[2] = nrm[3] = 0.0;
     for (int i = 0; i <= N; i++)
     {
-        const int nv = rnu(s, i) + rnx(s, i), nb = rnb(s, i);
+        const int nv = rnu(s, i) + rnx(s, i), nb = rnc(s, i);
         for (int k = 0; k < nv; k++) if (fabs(rg[NV * i + k]) > nrm[0]) nrm[0] = fabs(rg[NV * i + k]);
         if (i < N)
             for (int k = 0; k < NX; k++) if (fabs(rbb[NX * i + k]) > nrm[1]) nrm[1] = fabs(rbb[NX * i + k]);
@@ -441,7 +475,14 @@ static void ipm_dt_dlam(rmpc_oracle *s, const double *res_d, const double *res_m
             dt[24 * i + j] = dux[NV * i + j];
             dt[24 * i + nb + j] = -dux[NV * i + j];
         }
-        for (int j = 0; j < 2 * nb; j++)
+        if (ng_of(s, i))
+        {
+            double cx = 0.0;
+            for (int k = 0; k < NX; k++) cx += s->term_c[k] * dux[NV * i + k];
+            dt[24 * i] = cx;
+            dt[24 * i + 1] = -cx;
+        }
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             const int k = 24 * i + j;
             double lam0 = s->slam[k];
@@ -459,7 +500,7 @@ static void ipm_fact_solve(rmpc_oracle *s)
     const double reg = 1e-15;
     /* COMPUTE_GAMMA_GAMMA_QP, t_lam_min = 2 branch (x_core_qp_ipm_aux.c:38-86) */
     for (int i = 0; i <= N; i++)
-        for (int j = 0; j < 2 * rnb(s, i); j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             const int k = 24 * i + j;
             s->tinv[k] = 1.0 / s->st[k];
@@ -482,6 +523,15 @@ static void ipm_fact_solve(rmpc_oracle *s)
         {
             L[j + LD * j] += s->Gamma[24 * ss + nb + j] + s->Gamma[24 * ss + j];
             L[nv + LD * j] += -s->gamma[24 * ss + nb + j] + s->gamma[24 * ss + j];
+        }
+        if (ng_of(s, ss))
+        { /* general rows (x_ocp_qp_kkt.c:859-868): AL = [DCt diag(Gamma); gamma'], L += AL DCt' (lower part) */
+            const double Ga = s->Gamma[24 * ss + 1] + s->Gamma[24 * ss], ga = -s->gamma[24 * ss + 1] + s->gamma[24 * ss];
+            for (int c = 0; c < nv; c++)
+            {
+                for (int r = c; r < nv; r++) L[r + LD * c] += (s->term_c[r] * Ga) * s->term_c[c];
+                L[nv + LD * c] += ga * s->term_c[c];
+            }
         }
         if (ss < N)
         {
@@ -560,7 +610,7 @@ static void ipm_solve(rmpc_oracle *s, const double *rqz, const double *b, const 
 {
     const int N = s->N;
     for (int i = 0; i <= N; i++) /* COMPUTE_GAMMA_QP */
-        for (int j = 0; j < 2 * rnb(s, i); j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             const int k = 24 * i + j;
             s->gamma[k] = s->tinv[k] * (m[k] - s->slam[k] * d[k]);
@@ -572,6 +622,8 @@ static void ipm_solve(rmpc_oracle *s, const double *rqz, const double *b, const 
         double *dv = dux + NV * ss;
         for (int k = 0; k < nv; k++) dv[k] = rqz[NV * ss + k];
         for (int j = 0; j < nb; j++) dv[j] += -s->gamma[24 * ss + nb + j] + s->gamma[24 * ss + j];
+        if (ng_of(s, ss))
+            for (int k = 0; k < NX; k++) dv[k] += s->term_c[k] * (-s->gamma[24 * ss + 1] + s->gamma[24 * ss]);
         if (ss < N)
         {
             const int nu1 = rnu(s, ss + 1);
@@ -614,12 +666,132 @@ static void ipm_solve(rmpc_oracle *s, const double *rqz, const double *b, const 
     ipm_dt_dlam(s, d, m, dux, dlam, dt);
 }
 
+/* OCP_QP_FACT_LQ_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:1201-1541): the fall-back of lq_fact = 1 when the Cholesky step
+ * left a linear-system residual above 1e-5 (x_ocp_qp_ipm.c:2246-2276).  The stage factor L_ss (lower, L L' = the
+ * Riccati matrix M_ss) is obtained WITHOUT forming M: it is the triangular factor of the Householder LQ decomposition
+ * of   [ Lh | diag(sqrt(Gamma_b)) | DCt sqrt(Gamma_g) | BAbt L_{ss+1,xx} ],   Lh Lh' = RSQ + reg I   (:1263-1320),
+ * with the diagonal made positive.  The vectors then follow the stored-factor solve (ipm_solve, = :1322,1469-1512).
+ * BLASFEO's GELQF_PD_LLA is a blocked, structure-exploiting Householder LQ; this is the textbook unblocked one --
+ * same factor up to rounding. */
+#define LQ_KMAX (2 * NV + 1 + NX)
+static void lq_lower(int m, int K, double *A /* m x K row-major, ld LQ_KMAX */, double *L /* ld LD, col-major */)
+{
+    for (int i = 0; i < m; i++)
+    {
+        double *v = A + (size_t) LQ_KMAX * i + i;
+        const int n = K - i;
+        double sigma = 0.0;
+        for (int k = 1; k < n; k++) sigma += v[k] * v[k];
+        double diag = v[0];
+        if (sigma > 0.0)
+        {
+            const double mu = sqrt(v[0] * v[0] + sigma);
+            const double v0 = v[0] <= 0.0 ? v[0] - mu : -sigma / (v[0] + mu);
+            const double beta = 2.0 * v0 * v0 / (sigma + v0 * v0);
+            for (int k = 1; k < n; k++) v[k] /= v0;
+            v[0] = 1.0;
+            for (int j = i + 1; j < m; j++)
+            {
+                double *r = A + (size_t) LQ_KMAX * j + i, w = 0.0;
+                for (int k = 0; k < n; k++) w += r[k] * v[k];
+                w *= beta;
+                for (int k = 0; k < n; k++) r[k] -= w * v[k];
+            }
+            diag = mu;
+        }
+        v[0] = diag;
+    }
+    for (int c = 0; c < m; c++)
+    {
+        const double sg = A[(size_t) LQ_KMAX * c + c] < 0.0 ? -1.0 : 1.0;
+        for (int r = c; r < m; r++) L[r + LD * c] = sg * A[(size_t) LQ_KMAX * r + c];
+    }
+}
+
+static void ipm_fact_lq_solve(rmpc_oracle *s)
+{
+    const int N = s->N;
+    const double reg = 1e-15;
+    for (int i = 0; i <= N; i++) /* COMPUTE_GAMMA_GAMMA_QP */
+        for (int j = 0; j < 2 * rnc(s, i); j++)
+        {
+            const int k = 24 * i + j;
+            s->tinv[k] = 1.0 / s->st[k];
+            s->Gamma[k] = s->tinv[k] * s->slam[k];
+            s->gamma[k] = s->tinv[k] * (s->res_m[k] - s->slam[k] * s->res_d[k]);
+        }
+    for (int ss = N; ss >= 0; ss--)
+    {
+        const int nu = rnu(s, ss), nx = rnx(s, ss), nv = nu + nx, nb = rnb(s, ss), ng = ng_of(s, ss);
+        double *L = s->L + LD * NV * ss;
+        const double *H = s->rRSQ + 324 * ss;
+        double A[NV * LQ_KMAX], Lh[LD * NV];
+        memset(A, 0, sizeof(A));
+        memset(Lh, 0, sizeof(Lh));
+        for (int c = 0; c < nv; c++)
+        {
+            for (int r = c; r < nv; r++) Lh[r + LD * c] = H[r + NV * c];
+            Lh[c + LD * c] += reg;
+        }
+        potrf_mn(nv, nv, Lh); /* POTRF_L of RSQ + reg I (use_hess_fact) */
+        int K = 0;
+        for (int c = 0; c < nv; c++)
+            for (int r = c; r < nv; r++) A[(size_t) LQ_KMAX * r + c] = Lh[r + LD * c];
+        K = nv;
+        for (int j = 0; j < nb; j++)
+        { /* box rows: idxb = 0..nb-1 */
+            double t = s->Gamma[24 * ss + j] + s->Gamma[24 * ss + nb + ng + j];
+            t = t >= 0.0 ? t : 0.0;
+            t = sqrt(t);
+            A[(size_t) LQ_KMAX * j + K + j] = t > 0.0 ? t : 0.0;
+        }
+        K += nv;
+        if (ng)
+        {
+            double t = s->Gamma[24 * ss] + s->Gamma[24 * ss + 1];
+            t = t >= 0.0 ? t : 0.0;
+            t = sqrt(t);
+            for (int r = 0; r < nv; r++) A[(size_t) LQ_KMAX * r + K] = s->term_c[r] * t;
+            K += 1;
+        }
+        if (ss < N)
+        {
+            const int nu1 = rnu(s, ss + 1);
+            const double *Ln = s->L + LD * NV * (ss + 1);
+            for (int r = 0; r < nv; r++) /* TRMM_RLNN: BAbt * Lxx */
+                for (int c = 0; c < NX; c++)
+                {
+                    double a = 0.0;
+                    for (int k = c; k < NX; k++) a += s->BAbt[r + NV * k] * Ln[(nu1 + k) + LD * (nu1 + c)];
+                    A[(size_t) LQ_KMAX * r + K + c] = a;
+                }
+            K += NX;
+            double tmp[NX]; /* Pb = Lxx (Lxx' res_b) */
+            for (int c = 0; c < NX; c++)
+            {
+                double a = 0.0;
+                for (int k = c; k < NX; k++) a += Ln[(nu1 + k) + LD * (nu1 + c)] * s->res_b[NX * ss + k];
+                tmp[c] = a;
+            }
+            for (int r = 0; r < NX; r++)
+            {
+                double a = 0.0;
+                for (int k = 0; k <= r; k++) a += Ln[(nu1 + r) + LD * (nu1 + k)] * tmp[k];
+                s->Pb[NX * ss + r] = a;
+            }
+        }
+        memset(L, 0, sizeof(double) * LD * NV);
+        lq_lower(nv, K, A, L);
+    }
+    ipm_solve(s, s->res_g, s->res_b, s->res_d, s->res_m, s->dux, s->dpi, s->dlam, s->dt, 1);
+}
+
 /* COMPUTE_ALPHA_QP (x_core_qp_ipm_aux.c:193-263) */
 static void ipm_alpha(const rmpc_oracle *s, double *alpha, double *alpha_prim, double *alpha_dual)
 {
     double ap = -1.0, ad = -1.0;
     for (int i = 0; i <= s->N; i++)
-        for (int j = 0; j < 2 * rnb(s, i); j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             const int k = 24 * i + j;
             if (ad * s->dlam[k] > s->slam[k]) ad = s->slam[k] / s->dlam[k];
@@ -633,7 +805,7 @@ static double ipm_mu_aff(const rmpc_oracle *s, double alpha, double nc_inv)
 {
     double mu = 0.0;
     for (int i = 0; i <= s->N; i++)
-        for (int j = 0; j < 2 * rnb(s, i); j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
         {
             const int k = 24 * i + j;
             mu += (s->slam[k] + alpha * s->dlam[k]) * (s->st[k] + alpha * s->dt[k]);
@@ -647,13 +819,13 @@ static int any_gt(const double n[4], double thr) { return n[0] > thr || n[1] > t
  * argument set acados resolves: warm_start 2, pred_corr, cond_pred_corr, itref_pred_max 0,
  * itref_corr_max 2, lq_fact 1, split_step 0, t_lam_min 2, abs_form 0.  Returns the HPIPM status
  * (0 SUCCESS, 1 MAX_ITER, 2 MIN_STEP, 3 NAN_SOL).  The LQ (Householder) fall-back factorisation of lq_fact = 1 is
- * NOT restated: when its trigger fires the event is counted in n_lq_needed and the Cholesky step is kept. */
+ * ipm_fact_lq_solve(); every time its trigger fires the event is also counted in n_lq_needed. */
 static int ipm_solve_qp(rmpc_oracle *s, int warm)
 {
     const int N = s->N, iter_max = s->prob.qp_iter_max;
     const double tol = s->prob.qp_tol, alpha_min = 1e-8, tau_min = 1e-16, lam_min = 1e-16, t_min = 1e-16;
     int nc = 0;
-    for (int i = 0; i <= N; i++) nc += 2 * rnb(s, i);
+    for (int i = 0; i <= N; i++) nc += 2 * rnc(s, i);
     const double nc_inv = 1.0 / nc;
     const size_t nc_pad = 24 * (size_t) (N + 1);
 
@@ -661,7 +833,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
     {
         /* OCP_QP_INIT_VAR, warm_start == 2 (:1638-1654): keep ux (zeroed by acados), pi; clip lam, t */
         for (int i = 0; i <= N; i++)
-            for (int j = 0; j < 2 * rnb(s, i); j++)
+            for (int j = 0; j < 2 * rnc(s, i); j++)
             {
                 const int k = 24 * i + j;
                 if (s->slam[k] < 1e-1) s->slam[k] = 1e-1;
@@ -692,6 +864,18 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
                 else if (tu[j] < thr0) { tu[j] = thr0; v[j] = -du[j] - thr0; }
             }
             for (int j = 0; j < 2 * nb; j++) s->slam[24 * i + j] = mu0 / tl[j];
+            if (ng_of(s, i))
+            { /* general rows (:1780-1817): t = +-C ux - d clipped at thr0 (ux is not moved), lam = mu0 / t */
+                double cx = 0.0;
+                for (int k = 0; k < NX; k++) cx += s->term_c[k] * v[k];
+                tl[0] = cx - dl[0];
+                tl[1] = -cx - dl[1];
+                for (int j = 0; j < 2; j++)
+                {
+                    tl[j] = thr0 > tl[j] ? thr0 : tl[j];
+                    s->slam[24 * i + j] = mu0 / tl[j];
+                }
+            }
         }
     }
     double alpha = 1.0, nrm[4], mu, res_m_tau;
@@ -700,7 +884,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
     ipm_res_norm(s, s->res_g, s->res_b, s->res_d, s->res_m, nrm);
     res_m_tau = 0.0;
     for (int i = 0; i <= N; i++)
-        for (int j = 0; j < 2 * rnb(s, i); j++)
+        for (int j = 0; j < 2 * rnc(s, i); j++)
             if (fabs(s->res_m[24 * i + j] - tau_min) > res_m_tau) res_m_tau = fabs(s->res_m[24 * i + j] - tau_min);
     int kk;
     for (kk = 0; kk < iter_max && alpha > alpha_min &&
@@ -715,7 +899,18 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
                 s->id, s->im);
         ipm_res_norm(s, s->ig, s->ib, s->id, s->im, inrm);
         if (getenv("RMPC_ORACLE_DEBUG") && kk == 0) fprintf(stderr, "port st1: res_g6 %.6e dux6 %.6e dpi1_0 %.6e dpi0_0 %.6e dlam_lb %.6e dlam_ub %.6e\n", s->res_g[NV+6], s->dux[NV+6], s->dpi[NX], s->dpi[0], s->dlam[24+6], s->dlam[24+18]);
-        if ((inrm[0] == 0.0 && isnan(s->ig[0])) || any_gt(inrm, 1e-5)) s->n_lq_needed++;
+        /* HPIPM's own NaN test looks at the first residual entry only (its norms skip NaNs).  A numerically singular
+         * stage-N block (rank-one terminal row + reg) can make the dense Cholesky produce NaNs elsewhere, depending on
+         * rounding noise that differs between BLASFEO's blocked kernels and this scalar code; any NaN in the step
+         * therefore also takes the LQ route here. */
+        int step_nan = 0;
+        for (size_t k = 0; k < (size_t) NV * (N + 1) && !step_nan; k++) step_nan = isnan(s->dux[k]) || isinf(s->dux[k]);
+        for (size_t k = 0; k < (size_t) NX * N && !step_nan; k++) step_nan = isnan(s->dpi[k]) || isinf(s->dpi[k]);
+        if ((inrm[0] == 0.0 && isnan(s->ig[0])) || any_gt(inrm, 1e-5) || step_nan)
+        { /* inaccurate factorisation: refactorise this iteration with LQ (:2246-2276) */
+            s->n_lq_needed++;
+            ipm_fact_lq_solve(s);
+        }
         double alpha_prim, alpha_dual;
         ipm_alpha(s, &alpha, &alpha_prim, &alpha_dual);
         double alpha_aff = alpha;
@@ -760,7 +955,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
         for (size_t k = 0; k < (size_t) NV * (N + 1); k++) s->sux[k] += a * s->dux[k];
         for (size_t k = 0; k < (size_t) NX * N; k++) s->spi[k] += a * s->dpi[k];
         for (int i = 0; i <= N; i++)
-            for (int j = 0; j < 2 * rnb(s, i); j++)
+            for (int j = 0; j < 2 * rnc(s, i); j++)
             {
                 const int k = 24 * i + j;
                 s->slam[k] += a * s->dlam[k];
@@ -774,7 +969,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
         ipm_res_norm(s, s->res_g, s->res_b, s->res_d, s->res_m, nrm);
         res_m_tau = 0.0;
         for (int i = 0; i <= N; i++)
-            for (int j = 0; j < 2 * rnb(s, i); j++)
+            for (int j = 0; j < 2 * rnc(s, i); j++)
                 if (fabs(s->res_m[24 * i + j] - tau_min) > res_m_tau) res_m_tau = fabs(s->res_m[24 * i + j] - tau_min);
         if (kk < 63)
         {
@@ -899,6 +1094,13 @@ static double merit_fun(rmpc_oracle *s)
         for (int j = 0; j < 2 * nb; j++)
             if (fun[j] > 0.0) con += fabs(s->wlam[36 * i + j]) * fun[j];
     }
+    if (s->prob.term)
+    {
+        const double h = term_h(s, s->tux + NV * N, NULL);
+        const double fl = s->prob.term_lh - h, fu = h - s->prob.term_uh;
+        if (fl > 0.0) con += fabs(s->wlam[36 * N]) * fl;
+        if (fu > 0.0) con += fabs(s->wlam[36 * N + 1]) * fu;
+    }
     return cost + dyn + con;
 }
 
@@ -922,7 +1124,7 @@ static int line_search_and_update(rmpc_oracle *s, int nlp_iter)
             s->wpi[k] = t0 > t1 ? t0 : t1;
         }
         for (int i = 0; i <= N; i++)
-            for (int j = 0; j < 2 * nb_full(s, i); j++)
+            for (int j = 0; j < 2 * nc_full(s, i); j++)
             {
                 double t0 = s->qlam[36 * i + j], t1 = 0.5 * (t0 + s->wlam[36 * i + j]);
                 s->wlam[36 * i + j] = t0 > t1 ? t0 : t1;
@@ -956,7 +1158,7 @@ static void init_qp_from_nlp(rmpc_oracle *s)
     memcpy(s->qlam, s->lam, sizeof(double) * 36 * (N + 1));
     memcpy(s->qpi, s->pi, sizeof(double) * NX * (size_t) N);
     for (int i = 0; i <= N; i++)
-        for (int j = 0; j < 2 * nb_full(s, i); j++) s->qt[36 * i + j] = -s->d[36 * i + j];
+        for (int j = 0; j < 2 * nc_full(s, i); j++) s->qt[36 * i + j] = -s->d[36 * i + j];
 }
 
 /* ocp_nlp_sqp_rti, rti_phase = PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
@@ -1034,6 +1236,15 @@ void rmpc_oracle_get_iterate(const rmpc_oracle *s, double *xtraj, double *utraj,
 }
 
 int rmpc_oracle_n_lq_needed(const rmpc_oracle *s) { return s->n_lq_needed; }
+/* Debug/parity hook: per-iteration table of the LAST QP (8 columns: alpha_aff mu_aff sigma alpha mu res_stat res_eq
+ * res_ineq; row k+1 = iteration k); returns the iteration count. */
+int rmpc_oracle_last_qp_stat(const rmpc_oracle *s, double *out, int max_rows)
+{
+    int rows = s->qp_iter_last + 1 < max_rows ? s->qp_iter_last + 1 : max_rows;
+    if (rows > 64) rows = 64;
+    memcpy(out, s->stat, sizeof(double) * 8 * (size_t) rows);
+    return s->qp_iter_last;
+}
 
 /* Whole closed loop, R/simulator.py:199-241 without sleeps / visualisation. Returns #failed steps. */
 int rmpc_oracle_closed_loop(const rmpc_problem *prob, const double z0[12], int nsteps, rmpc_trace *tr)
@@ -1066,7 +1277,7 @@ int rmpc_oracle_closed_loop(const rmpc_problem *prob, const double z0[12], int n
                                     tr->utraj ? tr->utraj + (size_t) k * N * NU : NULL,
                                     tr->pitraj ? tr->pitraj + (size_t) k * N * NX : NULL);
     }
-    if (s->n_lq_needed) fprintf(stderr, "rmpc_oracle: LQ fall-back would have triggered %d times\n", s->n_lq_needed);
+    if (s->n_lq_needed) fprintf(stderr, "rmpc_oracle: LQ fall-back factorisation used %d times\n", s->n_lq_needed);
     rmpc_oracle_destroy(s);
     return nfail;
 }

@@ -32,6 +32,13 @@ typedef struct
     double q_min[6], q_max[6]; /* lbx/ubx on q, stages 1..N-1       R/trajectory_optimizer.py:169-171 */
     double u_min[6], u_max[6]; /* lbu/ubu, stages 0..N-1            R/trajectory_optimizer.py:164-166 */
     ur10_params model;
+    /* terminal ellipsoid h_e(x_N) = x_N' P x_N, lh_e <= h_e <= uh_e = alpha at stage N (BASELINE config 4).  P, alpha come
+     * from R/_terminal_constraint.py:96-116 (terminal_ellipsoid_from_lqr); the reference MPC never wires them into its
+     * OCP, so the wiring is the standard acados one: BGH constraint module with nh_e = 1
+     * (T/acados_ocp_constraints.py lh_e/uh_e, AC/ocp_nlp/ocp_nlp_constraints_bgh.c:1219-1445). */
+    int term;          /* 0: no terminal constraint (the reference MPC as shipped) */
+    double term_P[144]; /* symmetric 12 x 12, row-major, state order [q; qd] */
+    double term_lh, term_uh;
 } rmpc_problem;
 
 /* Fill every field except model.surf / model.wcv / N / dt / solver_type with the reference defaults. */
@@ -64,6 +71,10 @@ static inline void rmpc_problem_defaults(rmpc_problem *p)
     p->model.t_ee[0] = 0.0;
     p->model.t_ee[1] = 0.0;
     p->model.t_ee[2] = 0.1;
+    p->term = 0;
+    for (int i = 0; i < 144; i++) p->term_P[i] = 0.0;
+    p->term_lh = 0.0;
+    p->term_uh = 0.0;
 }
 
 /* Closed-loop trace written by both legs (any pointer may be NULL). Layouts are row-major.

@@ -10,3 +10,4 @@ from .prediction_model import SixDofRobot  # noqa: F401,E402
 from .simulation_model import Robot  # noqa: F401,E402
 from .trajectory_optimizer import MPC, BatchedSolver, SolverOptions, SolverView  # noqa: F401,E402
 from .simulator import SimulationManager, Simulator, run_batch, summary_from_row  # noqa: F401,E402
+from . import terminal_constraint  # noqa: F401,E402

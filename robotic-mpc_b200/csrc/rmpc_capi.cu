@@ -107,6 +107,7 @@ struct rmpc_handle
     long long launches;
     std::vector<void *> owned;
     double *par_dev;
+    double *pe_dev; /* [B][RE_COUNT] terminal-set blocks, allocated by the first "P_e" / "alpha_e" / "lh_e" / "term" set */
     std::string err;
 };
 
@@ -163,6 +164,7 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     memset(&h->W, 0, sizeof(h->W));
     h->device = device; h->nlog = nlog; h->steps_done = 0; h->bytes = 0; h->launches = 0;
     h->par_dev = nullptr;
+    h->pe_dev = nullptr;
     const size_t B = (size_t) dims->B, S = (size_t) dims->N + 1;
     auto dalloc = [&](size_t n_doubles, void **p) -> bool {
         const size_t bytes = n_doubles * sizeof(double);
@@ -219,6 +221,25 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
     const std::string f(field);
     if (f == "par") { CU(cudaMemcpyAsync(h->par_dev, dev, sizeof(double) * h->D.B * RP_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "z") { CU(cudaMemcpyAsync(h->W.z, dev, sizeof(double) * h->D.B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "P_e" || f == "alpha_e" || f == "lh_e" || f == "term")
+    {
+        /* terminal ellipsoid row of stage N; the first call switches the row on (all-zero block until everything is set) */
+        if (!h->pe_dev)
+        {
+            const size_t bytes = sizeof(double) * (size_t) h->D.B * RE_COUNT;
+            void *p = nullptr;
+            if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set: device allocation failed"); }
+            CU(cudaMemsetAsync(p, 0, bytes, s));
+            h->owned.push_back(p);
+            h->bytes += (long long) bytes;
+            h->pe_dev = (double *) p;
+            h->W.pe = h->pe_dev;
+        }
+        if (f == "term") { CU(cudaMemcpyAsync(h->pe_dev, dev, sizeof(double) * h->D.B * RE_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+        if (f == "P_e") return strided(h, (double *) dev, h->pe_dev, RE_COUNT, RE_P, 144, 0, s);
+        if (f == "alpha_e") return strided(h, (double *) dev, h->pe_dev, RE_COUNT, RE_UH, 1, 0, s);
+        return strided(h, (double *) dev, h->pe_dev, RE_COUNT, RE_LH, 1, 0, s);
+    }
     if (f == "x" || f == "u" || f == "pi")
     {
         const int smax = (f == "x") ? h->D.N : h->D.N - 1;
@@ -300,7 +321,8 @@ extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *de
     const std::string f(field);
     if (f == "x" || f == "u" || f == "pi" || f == "lam")
     {
-        const int smax = (f == "x") ? h->D.N : h->D.N - 1;
+        /* "lam" of stage N exists with a terminal row only: entry 0 = lower side, entry 12 = upper side */
+        const int smax = (f == "x" || (f == "lam" && h->pe_dev)) ? h->D.N : h->D.N - 1;
         if (stage < 0 || stage > smax) return fail(h, RMPC_EINVAL, "rmpc_get: stage out of range for field " + f);
         const long st = h->W.slab_stride;
         if (f == "x") return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_ux, NV, stage) + 6, NX, 1, s);

@@ -214,6 +214,7 @@ RD void grp_axpy_floor(double *RD_RESTRICT y, const double *RD_RESTRICT x, doubl
 struct Inst
 {
     const double *par;
+    const double *pe; /* terminal-set block (RE_*), null without a terminal constraint */
     double *head, *arr0, *z;
     int *flags;
     int Sp;
@@ -233,6 +234,7 @@ RD Inst inst_view(const RmpcWs &w, int N, long i)
     v.arr0 = v.head + RMPC_HEAD;
     v.Sp = w.Sp;
     v.par = w.par + i * RP_COUNT;
+    v.pe = w.pe ? w.pe + i * RE_COUNT : nullptr;
     v.z = w.z + i * NX;
     v.flags = w.flags + i * 4;
     v.pair = rd_mask();
@@ -241,6 +243,26 @@ RD Inst inst_view(const RmpcWs &w, int N, long i)
 
 /* element (r, c) of a packed-lower symmetric 12 x 12 matrix */
 RD double psym(const double *P, int r, int c) { return r >= c ? P[(r * (r + 1)) / 2 + c] : P[(c * (c + 1)) / 2 + r]; }
+
+/* Terminal ellipsoid row h_e(x) = x' P x of stage N, group-wide: lane k < 12 forms row k of P x; returns h_e on every
+ * lane and, with `grad`, writes the gradient 2 P x (the stage-N row of DCt).  Replaces the CasADi-generated
+ * *_constr_h_e_fun[_jac_uxt_zt] pair that acados' BGH module would call (AC/ocp_nlp/ocp_nlp_constraints_bgh.c:
+ * 1219-1445,1563-1619) for con_h_expr_e = x' P x with P from R/_terminal_constraint.py:96-116. */
+#define TERM_LO(N) (NB * (N))      /* slot of the lower side lh - h_e in the NB-wide per-stage arrays */
+#define TERM_UP(N) (NB * (N) + 12) /* slot of the upper side h_e - uh */
+RD double term_eval(const double *pe, const double *x, double *grad)
+{
+    const int l = rd_lane();
+    double px = 0.0, hx = 0.0;
+    if (l < NX)
+    {
+        RD_UNROLL
+        for (int k = 0; k < NX; k++) px += pe[RE_P + NX * l + k] * x[k];
+        hx = x[l] * px;
+        if (grad) grad[l] = 2.0 * px;
+    }
+    return grp_sum(hx);
+}
 
 /* ---------------------------------------------------------------------------------------------- model (K1)
  * UR10 forward kinematics, WORLD-frame geometric Jacobian, task-frame outputs and their derivatives.
@@ -625,6 +647,15 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, 
         }
     }
     for (int k = lane; k < NV; k += GL) AR(rqz)[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
+    if (I.pe)
+    { /* terminal row: fun = [lh - h_e; h_e - uh], DCt = grad h_e (kept in Jc[N][0..11]) */
+        const double h = term_eval(I.pe, AR(ux) + NV * N + 6, AR(Jc) + NJ * N);
+        if (lane == 0)
+        {
+            AR(d)[TERM_LO(N)] = I.pe[RE_LH] - h;
+            AR(d)[TERM_UP(N)] = h - I.pe[RE_UH];
+        }
+    }
     rd_sync();
     return grp_sum(cost);
 }
@@ -669,6 +700,16 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, cons
                 if (fl > 0.0) m += fabs((I.head + H_WLAMX0)[k]) * fl;
                 if (-fl > 0.0) m += fabs((I.head + H_WLAMX0)[12 + k]) * (-fl);
             }
+        }
+    }
+    if (I.pe)
+    {
+        const double h = term_eval(I.pe, tux + NV * N + 6, nullptr);
+        const double fl = I.pe[RE_LH] - h, fu = h - I.pe[RE_UH];
+        if (lane == 0)
+        {
+            if (fl > 0.0) m += fabs(AR(wlam)[TERM_LO(N)]) * fl;
+            if (fu > 0.0) m += fabs(AR(wlam)[TERM_UP(N)]) * fu;
         }
     }
     return grp_sum(m);
@@ -721,6 +762,14 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
         {
             RD_UNROLL
             for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[NX * (i - 1) + k];
+        }
+        if (i == N && I.pe)
+        { /* terminal row: adj += DCt (lam_l - lam_u) */
+            const double ll = AR(lam)[TERM_LO(N)], lu = AR(lam)[TERM_UP(N)], fl = AR(d)[TERM_LO(N)], fu = AR(d)[TERM_UP(N)];
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) r[6 + k] -= (AR(Jc) + NJ * N)[k] * (ll - lu);
+            ri = rd_fmax(ri, rd_fmax(fl, fu));
+            rc = rd_fmax(rc, rd_fmax(fabs(ll * fl), fabs(lu * fu)));
         }
         RD_UNROLL
         for (int k = 0; k < NV; k++)
@@ -785,6 +834,22 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I, int warm)
             AR(sux)[NV * i + j] = v;
             t[j] = tl; t[12 + j] = tu;
             lam[j] = 1.0 / tl; lam[12 + j] = 1.0 / tu;
+        }
+    }
+    if (I.pe && lane < 2)
+    { /* general row of stage N (x_ocp_qp_ipm.c:1780-1817): t = +-C ux - d at ux = 0, clipped at 0.1; lam = mu0 / t */
+        const int k = lane ? TERM_UP(N) : TERM_LO(N);
+        if (warm == 2)
+        {
+            if (AR(slam)[k] < 1e-1) AR(slam)[k] = 1e-1;
+            if (AR(st)[k] < 1e-1) AR(st)[k] = 1e-1;
+        }
+        else
+        {
+            double t = -AR(d)[k];
+            t = 1e-1 > t ? 1e-1 : t;
+            AR(st)[k] = t;
+            AR(slam)[k] = 1.0 / t;
         }
     }
     rd_sync();
@@ -886,6 +951,29 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I, const GrpSmem &sm, const do
             RD_UNROLL
             for (int k = 0; k < NX; k++) g[6 + k] -= pi[NX * (i - 1) + k];
         }
+        if (i == N && I.pe)
+        { /* general row C x of stage N: res_g += C' (lam_u - lam_l), res_d = d + t -+ C x, res_m */
+            const double *c = AR(Jc) + NJ * N;
+            const int ka = TERM_LO(N), kb = TERM_UP(N);
+            double cx = 0.0;
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) cx += c[k] * v[6 + k];
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) g[6 + k] += c[k] * (lam[kb] - lam[ka]);
+            const double dl = d[ka] + t[ka] - cx, du = d[kb] + t[kb] + cx;
+            if (WRITE) { rd[ka] = dl; rd[kb] = du; }
+            double ml, mu_;
+            if (!LIN) { ml = lam[ka] * t[ka]; mu_ = lam[kb] * t[kb]; mu += ml + mu_; }
+            else
+            {
+                ml = (m[ka] - mshift) + Lam[ka] * t[ka] + lam[ka] * T[ka];
+                mu_ = (m[kb] - mshift) + Lam[kb] * t[kb] + lam[kb] * T[kb];
+            }
+            if (WRITE) { rm[ka] = ml; rm[kb] = mu_; }
+            n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
+            n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
+            n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
+        }
         RD_UNROLL
         for (int k = 0; k < NV; k++)
         {
@@ -969,11 +1057,29 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
     if (R.x)
     {
         double *FN = AR(F) + (long) FS * N;
-        const double pv = AR(res_g)[NV * N + 6 + xk];
+        double pv = AR(res_g)[NV * N + 6 + xk];
+        double Prow[12];
         RD_UNROLL
-        for (int c = 0; c < 12; c++) P[xk * SM_PS + c] = (c == xk) ? reg : 0.0;
+        for (int c = 0; c < 12; c++) Prow[c] = (c == xk) ? reg : 0.0;
+        if (I.pe)
+        { /* general row of stage N (x_ocp_qp_kkt.c:859-868): P_N += C' Gamma C, p_N += C' gamma */
+            const double *cv = AR(Jc) + NJ * N;
+            const int ka = TERM_LO(N), kb = TERM_UP(N);
+            const double til = 1.0 / AR(st)[ka], tiu = 1.0 / AR(st)[kb];
+            const double la = AR(slam)[ka], lb = AR(slam)[kb];
+            const double Ga = tiu * lb + til * la;
+            const double ga = til * ((AR(res_m)[ka] - tau_min) - la * AR(res_d)[ka]) - tiu * ((AR(res_m)[kb] - tau_min) - lb * AR(res_d)[kb]);
+            const double cg = cv[xk] * Ga;
+            RD_UNROLL
+            for (int c = 0; c < 12; c++) Prow[c] += cg * cv[c];
+            pv += ga * cv[xk];
+        }
+        RD_UNROLL
+        for (int c = 0; c < 12; c++) P[xk * SM_PS + c] = Prow[c];
         sm.pv[xk] = pv;
-        for (int c = 0; c <= xk; c++) FN[RF_P + (xk * (xk + 1)) / 2 + c] = (c == xk) ? reg : 0.0;
+        RD_UNROLL
+        for (int c = 0; c < 12; c++)
+            if (c <= xk) FN[RF_P + (xk * (xk + 1)) / 2 + c] = Prow[c];
         FN[RF_PV + xk] = pv;
     }
     for (int ss = N - 1; ss >= 0; ss--)
@@ -1347,7 +1453,30 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double
     }
     rd_cp_wait0();
     if (R.u) X[NV * N + lane] = 0.0;
-    if (R.x) n0 = rd_fmax(n0, fabs(rg[NV * N + 6 + xk] - dp_prev)); /* stage N: no cost, no bounds */
+    double dlmN = 0.0;
+    if (I.pe)
+    { /* general row of stage N: dv = C dx_N, then the same multiplier / slack step, step length and sums */
+        const double *cv = AR(Jc) + NJ * N;
+        const double dv = grp_sum(R.x ? cv[xk] * sm.xv[xk] : 0.0);
+        const int ia = TERM_LO(N), ib = TERM_UP(N);
+        const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
+        const double da = rd[ia], db = rd[ib], ma = rm[ia] - mshift, mb = rm[ib] - mshift;
+        const double dla = -(ma + (la * dv) - (la * da)) / ta;
+        const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
+        const double dta = dv - da, dtb = -dv - db;
+        if (-alpha * dla > la) alpha = -la / dla;
+        if (-alpha * dta > ta) alpha = -ta / dta;
+        if (-alpha * dlb > lb) alpha = -lb / dlb;
+        if (-alpha * dtb > tb) alpha = -tb / dtb;
+        if (lane == 0)
+        {
+            DL[ia] = dla; DL[ib] = dlb; DT[ia] = dta; DT[ib] = dtb;
+            sB += (la * dta + dla * ta) + (lb * dtb + dlb * tb);
+            sC += dla * dta + dlb * dtb;
+        }
+        if (R.x) dlmN = cv[xk] * (dlb - dla);
+    }
+    if (R.x) n0 = rd_fmax(n0, fabs(rg[NV * N + 6 + xk] + dlmN - dp_prev)); /* stage N: no cost, no box bounds */
     rd_sync();
     *alpha_out = -grp_max(-alpha);
     sums[0] = grp_sum(sB);
@@ -1400,7 +1529,25 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const doubl
     rd_cp_commit();
     if (R.x)
     {
-        const double pv = rg[NV * N + 6 + xk];
+        double pv = rg[NV * N + 6 + xk];
+        if (I.pe)
+        { /* general row of stage N: p_N += C' gamma with the complementarity right-hand side of the MODE */
+            const int ia = TERM_LO(N), ib = TERM_UP(N);
+            const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
+            double ma, mb;
+            if (MODE == 0) { ma = rm[ia]; mb = rm[ib]; }
+            else
+            {
+                if (MODE == 1)
+                {
+                    ma = AR(res_m)[ia] + AR(dt_)[ia] * AR(dlam)[ia] - sigma_mu;
+                    mb = AR(res_m)[ib] + AR(dt_)[ib] * AR(dlam)[ib] - sigma_mu;
+                }
+                else { ma = AR(res_m)[ia] - sigma_mu; mb = AR(res_m)[ib] - sigma_mu; }
+                if (xk == 0) { AR(res_mc)[ia] = ma; AR(res_mc)[ib] = mb; }
+            }
+            pv += (AR(Jc) + NJ * N)[xk] * ((ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb);
+        }
         sm.pv[xk] = pv;
         AR(pvec)[NX * N + xk] = pv;
     }
@@ -1493,6 +1640,13 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
         if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
         if (-a * dtt > AR(st)[k]) a = -AR(st)[k] / dtt;
     }
+    if (I.pe && lane < 2)
+    {
+        const int k = lane ? TERM_UP(N) : TERM_LO(N);
+        const double dl = dlam[k], dtt = dt[k];
+        if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
+        if (-a * dtt > AR(st)[k]) a = -AR(st)[k] / dtt;
+    }
     return -grp_max(-a);
 }
 
@@ -1520,6 +1674,13 @@ RDN void ipm_update(const RmpcDims &D, const Inst &I, double a)
     }
     grp_axpy_floor(AR(slam), AR(dlam), a, lmin, NB, N * NB);
     grp_axpy_floor(AR(st), AR(dt_), a, lmin, NB, N * NB);
+    if (I.pe && lane >= 12 && lane < 14)
+    {
+        const int k = lane == 12 ? TERM_LO(N) : TERM_UP(N);
+        const double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
+        AR(slam)[k] = l <= lmin ? lmin : l;
+        AR(st)[k] = t <= lmin ? lmin : t;
+    }
     rd_sync();
 }
 
@@ -1533,7 +1694,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
 {
     const int N = D.N, lane = rd_lane();
     const double tol = D.qp_tol, alpha_min = 1e-8, tau_min = 1e-16;
-    const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12);
+    const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12 + (I.pe ? 2 : 0));
     ipm_init(D, I, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
     double sum_lt = ipm_res<0, 1>(D, I, sm, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g),
@@ -1587,6 +1748,11 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
             for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
             for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
             for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
+            if (I.pe && lane < 2)
+            {
+                const int k = lane ? TERM_UP(N) : TERM_LO(N);
+                AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k];
+            }
             rd_sync();
         }
         if (refined) alpha = ipm_alpha(D, I, AR(dlam), AR(dt_));
@@ -1657,6 +1823,13 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
         if (nlp_iter == 0) *w = t0;
         else { const double t1 = 0.5 * (t0 + *w); *w = t0 > t1 ? t0 : t1; }
     }
+    if (I.pe && lane < 2)
+    {
+        const int k = lane ? TERM_UP(N) : TERM_LO(N);
+        const double t0 = AR(slam)[k];
+        if (nlp_iter == 0) AR(wlam)[k] = t0;
+        else { const double t1 = 0.5 * (t0 + AR(wlam)[k]); AR(wlam)[k] = t0 > t1 ? t0 : t1; }
+    }
     rd_sync();
     const double m0 = nlp_merit(ch, D, I, AR(ux), I.z);
     double alpha = 1.0, m1 = 0.0;
@@ -1680,6 +1853,11 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
         AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
     }
     grp_lerp(AR(lam), AR(slam), alpha, NB, N * NB);
+    if (I.pe && lane >= 12 && lane < 14)
+    {
+        const int k = lane == 12 ? TERM_LO(N) : TERM_UP(N);
+        AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
+    }
     for (int k = lane; k < NB; k += GL) (I.head + H_LAMX0)[k] = (1.0 - alpha) * (I.head + H_LAMX0)[k] + alpha * (I.head + H_QLAMX0)[k];
     rd_sync();
     return 0;
@@ -1701,6 +1879,12 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
         for (int k = lane; k < N * NB; k += GL)
         {
             if (k < NB && (k % 12) >= 6) continue;
+            AR(slam)[k] = AR(lam)[k];
+            AR(st)[k] = -AR(d)[k];
+        }
+        if (I.pe && lane < 2)
+        {
+            const int k = lane ? TERM_UP(N) : TERM_LO(N);
             AR(slam)[k] = AR(lam)[k];
             AR(st)[k] = -AR(d)[k];
         }

@@ -94,6 +94,18 @@ enum
     RS_COUNT = 20
 };
 
+/* per-instance terminal-set block (doubles), optional: h_e(x_N) = x_N' P x_N with lh <= h_e <= uh at stage N
+ * (R/_terminal_constraint.py:96-116 gives P, alpha = uh; acados BGH nh_e = 1).  In the per-stage solver arrays the row
+ * uses slot 0 (lower side) and slot 12 (upper side) of stage N -- free there, stage N has no box bounds -- and its
+ * gradient 2 P x_N (the row of DCt) is kept in Jc[N][0..11]. */
+enum
+{
+    RE_P = 0,     /* 144: P, symmetric, row-major, state order [q; qd] */
+    RE_LH = 144,
+    RE_UH = 145,
+    RE_COUNT = 146
+};
+
 typedef struct
 {
     double Rfix[7][9]; /* fixed rotation of joint j's origin (j = 6: ee_fixed_joint), row-major */
@@ -176,6 +188,7 @@ typedef struct
     double *summary;   /* [B][RS_COUNT] */
     int nlog;          /* capacity of the logs in steps */
     int step0;         /* index of the first step of this launch */
+    const double *pe;  /* [B][RE_COUNT] terminal-set blocks, null: no terminal constraint (the reference MPC as shipped) */
 } RmpcWs;
 
 #ifdef __CUDACC__

@@ -126,7 +126,7 @@ class Engine:
 
     # ------------------------------------------------------------------ setters
     def set(self, field, value, stage=0):
-        n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12}[field]
+        n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12, "P_e": 144, "alpha_e": 1, "lh_e": 1, "term": 146}[field]
         t = self._dev(value, (self.B, n))
         self._check(self.lib.rmpc_set(self.h, field.encode(), int(stage), C.c_void_p(t.data_ptr()), self._stream()),
                     f"rmpc_set({field})")
@@ -137,6 +137,16 @@ class Engine:
 
     def set_state(self, z):
         self.set("z", z)
+
+    def set_terminal(self, P, alpha, lh=None):
+        """Terminal ellipsoid ``lh <= x_N' P x_N <= alpha`` at stage N (R/_terminal_constraint.py:96-116 gives P, alpha).
+        P: [12,12] or [B,12,12]; alpha, lh: scalars or [B]; lh defaults to -alpha (never active, keeps the row two-sided)."""
+        P = np.broadcast_to(np.asarray(P, float), (self.B, 12, 12))
+        P = 0.5 * (P + np.swapaxes(P, 1, 2))
+        alpha = np.broadcast_to(np.asarray(alpha, float), (self.B,))
+        lh = -alpha if lh is None else np.broadcast_to(np.asarray(lh, float), (self.B,))
+        blk = np.concatenate([P.reshape(self.B, 144), lh[:, None], alpha[:, None]], axis=1)
+        self.set("term", blk)
 
     def reset(self):
         self._check(self.lib.rmpc_reset(self.h, self._stream()), "rmpc_reset")

@@ -26,7 +26,7 @@ from .params import RK, RL, RS
 from .prediction_model import SixDofRobot
 from .simulation_model import Robot
 from .surface import Surface
-from .trajectory_optimizer import MPC
+from .trajectory_optimizer import MPC, bind_terminal
 
 SUMMARY_KEYS = ("rmse_e1", "rmse_e2", "rmse_e3", "rmse_e4", "rmse_e5", "itse_e1", "itse_e2", "itse_e3", "itse_e4",
                 "itse_e5", "weighted_rmse", "total_sqp_iterations", "avg_sqp_iterations", "num_failures",
@@ -48,7 +48,7 @@ def _solver_options_dict(opts):
 class Simulator:
     def __init__(self, robot_name, dt, simulation_time, prediction_horizon, q_0, qdot_0, wcv, q_min, q_max, qdot_min, qdot_max,
                  surface_limits=None, surface_origin=None, surface_orientation_rpy=None, w_qddot=0.02, surface_coeffs=None,
-                 solver_options=None, w_u=0.01, px_ref=0.40, vy_ref=0.05, scene=True):
+                 solver_options=None, w_u=0.01, px_ref=0.40, vy_ref=0.05, scene=True, terminal_constraint=None):
         self.name = robot_name
         self.robot_name = robot_name
         self.dt = dt
@@ -81,7 +81,7 @@ class Simulator:
         self.mpc = MPC(surface=self.surface, initial_state=self.initial_state, model=self.prediction_model,
                        N_horizon=self.prediction_horizon, Tf=self.dt * self.prediction_horizon, qmin=self.q_min,
                        qmax=self.q_max, dq_min=self.qdot_min, dq_max=self.qdot_max, w_u=self.w_u, w_qddot=self.w_qddot,
-                       px_ref=self.px_ref, vy_ref=self.vy_ref)
+                       px_ref=self.px_ref, vy_ref=self.vy_ref, terminal_constraint=terminal_constraint)
         so = _solver_options_dict(solver_options)
         if so:
             self._apply_solver_options(so)
@@ -255,6 +255,7 @@ def run_batch(sims, device=0, keep_logs=True):
     try:
         par = np.stack([s.mpc.param_row() for s in sims])
         z0 = np.stack([s.initial_state for s in sims])
+        bind_terminal(eng, [s.mpc for s in sims])
         if keep_logs:
             eng.set_params(par)
             eng.set_state(z0)

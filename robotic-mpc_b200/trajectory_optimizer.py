@@ -79,7 +79,7 @@ class MPC:
     ``wcv`` are passed explicitly."""
 
     def __init__(self, surface, initial_state, model, N_horizon, Tf, qmin, qmax, dq_min, dq_max, w_u, w_qddot,
-                 px_ref=0.40, vy_ref=0.01, Ts=None, wcv=None):
+                 px_ref=0.40, vy_ref=0.01, Ts=None, wcv=None, terminal_constraint=None):
         self.surface = surface
         self.surface_pos_world = surface.get_position() if hasattr(surface, "get_position") else None
         self.surface_rpy_world = surface.get_orientation_rpy() if hasattr(surface, "get_orientation_rpy") else None
@@ -110,6 +110,28 @@ class MPC:
         self.ocp.constraints.lbu, self.ocp.constraints.ubu = self.dq_min, self.dq_max
         self.ocp.constraints.lbx, self.ocp.constraints.ubx = self.qmin, self.qmax
         self.solver = None
+        self.terminal = None
+        if terminal_constraint is not None:
+            self.set_terminal_constraint(terminal_constraint)
+
+    def set_terminal_constraint(self, spec):
+        """Terminal ellipsoid ``lh_e <= x_N' P x_N <= alpha`` at stage N.  The reference computes (P, alpha)
+        in ``R/_terminal_constraint.py`` but never wires them into its OCP; this is the acados wiring one would add
+        (``ocp.model.con_h_expr_e = x.T @ P @ x``, ``ocp.constraints.lh_e / uh_e``).  ``spec``: a dict with ``P`` (12x12) and
+        ``alpha`` (and optionally ``lh``, default ``-alpha``), or a dict with ``rho`` (and optionally ``Q_diag``,
+        ``safety``) from which ``terminal_ellipsoid_from_lqr`` builds them for this instance's (Ad, Bd) and boxes."""
+        from . import terminal_constraint as tc
+
+        spec = dict(spec)
+        if "P" in spec:
+            P, alpha = np.asarray(spec["P"], float).reshape(12, 12), float(spec["alpha"])
+        else:
+            P, alpha = tc.default_terminal_set(wcv=self.wcv, Ts=self.Ts, rho=float(spec["rho"]), q_min=self.qmin, q_max=self.qmax,
+                                               qdot_min=self.dq_min, qdot_max=self.dq_max, Q_diag=spec.get("Q_diag"),
+                                               safety=float(spec.get("safety", 0.98)))
+        lh = float(spec.get("lh", -alpha))
+        self.terminal = {"P": 0.5 * (P + P.T), "alpha": alpha, "lh": lh}
+        self.ocp.constraints.lh_e, self.ocp.constraints.uh_e = np.array([lh]), np.array([alpha])
 
     def task_weights(self):
         return np.array([self.w_origin_task, self.w_normal_alignment_task, self.w_x_alignment_task, self.w_fixed_x_task,
@@ -125,7 +147,7 @@ class MPC:
 
     def static_key(self):
         o = self.ocp.solver_options
-        return (self.N_horizon, round(self.Tf / self.N_horizon, 15)) + o.static_key()
+        return (self.N_horizon, round(self.Tf / self.N_horizon, 15), self.terminal is not None) + o.static_key()
 
     def finalize_solver(self, device=0):
         """Creates the solver handle (a batch of one).  ``SimulationManager.run_all`` binds many ``MPC`` objects to one
@@ -134,6 +156,14 @@ class MPC:
         bs = BatchedSolver([self], device=device)
         self.solver = bs.view(0)
         return self
+
+
+def bind_terminal(engine, mpcs):
+    """Hand the terminal sets of a batch to the engine (all instances of a batch have one, or none has)."""
+    if mpcs[0].terminal is None:
+        return
+    engine.set_terminal(np.stack([m.terminal["P"] for m in mpcs]), np.array([m.terminal["alpha"] for m in mpcs]),
+                        np.array([m.terminal["lh"] for m in mpcs]))
 
 
 class BatchedSolver:
@@ -162,6 +192,7 @@ class BatchedSolver:
                              tol=[o.nlp_solver_tol_stat, o.nlp_solver_tol_eq, o.nlp_solver_tol_ineq, o.nlp_solver_tol_comp],
                              qp_tol=o.qp_tol, plant_dt=mpcs[0].Ts)
         self.engine.set_params(np.stack([m.param_row() for m in mpcs]))
+        bind_terminal(self.engine, mpcs)
         self.engine.set_state(np.stack([m.initial_state for m in mpcs]))
         self.engine.reset()
         self._stats = None

@@ -14,7 +14,9 @@ class Dims(C.Structure):
                 ("tol", C.c_double * 4), ("qp_tol", C.c_double), ("dt", C.c_double), ("plant_dt", C.c_double)]
 
 
-def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8):
+def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8,
+                term=None):
+    """term: optional [B][146] terminal-set blocks [P(144), lh, uh] (RE_* in csrc/rmpc_types.h)."""
     lib = C.CDLL(str(SO))
     B = par.shape[0]
     D = Dims(B, N, solver_type, max_iter, qp_iter_max, (C.c_double * 4)(tol, tol, tol, tol), qp_tol, dt, dt)
@@ -23,7 +25,12 @@ def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, 
     out = dict(z=np.zeros((B, nsteps + 1, 12)), u=np.zeros((B, nsteps, 6)), slog=np.zeros((B, nsteps, 12)),
                summary=np.zeros((B, 20)), flags=np.zeros((B, 4), np.int32))
     dp = C.POINTER(C.c_double)
-    lib.rmpc_emu_closed_loop(C.byref(D), par.ctypes.data_as(dp), z0.ctypes.data_as(dp), int(nsteps),
+    pe = None
+    if term is not None:
+        term = np.ascontiguousarray(term, np.float64)
+        assert term.shape == (B, 146)
+        pe = term.ctypes.data_as(dp)
+    lib.rmpc_emu_closed_loop_term(C.byref(D), par.ctypes.data_as(dp), pe, z0.ctypes.data_as(dp), int(nsteps),
                              out["z"].ctypes.data_as(dp), out["u"].ctypes.data_as(dp), out["slog"].ctypes.data_as(dp),
                              out["summary"].ctypes.data_as(dp), out["flags"].ctypes.data_as(C.POINTER(C.c_int)),
                              C.c_ulonglong(seed))

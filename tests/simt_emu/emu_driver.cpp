@@ -27,8 +27,20 @@ void body(void *p, int)
 }
 }  // namespace
 
+extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, const double *pe, const double *z0, int nsteps,
+                                         double *zlog, double *ulog, double *slog, double *summary, int *flags_out,
+                                         unsigned long long seed);
+
 extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const double *z0, int nsteps, double *zlog,
                                     double *ulog, double *slog, double *summary, int *flags_out, unsigned long long seed)
+{
+    return rmpc_emu_closed_loop_term(D, par, nullptr, z0, nsteps, zlog, ulog, slog, summary, flags_out, seed);
+}
+
+/* pe: [B][RE_COUNT] terminal-set blocks or null */
+extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, const double *pe, const double *z0, int nsteps,
+                                         double *zlog, double *ulog, double *slog, double *summary, int *flags_out,
+                                         unsigned long long seed)
 {
     const long B = D->B, S = D->N + 1;
     RmpcChain ch;
@@ -43,6 +55,7 @@ extern "C" int rmpc_emu_closed_loop(const RmpcDims *D, const double *par, const 
     owned.push_back(W.slab);
     owned.push_back(W.z);
     W.par = par;
+    W.pe = pe;
     W.flags = (int *) calloc((size_t) B * 4, sizeof(int));
     W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
     W.nlog = nsteps; W.step0 = 0;

@@ -36,6 +36,28 @@ def test_emulated_kernels_match_oracle(oracle, solver, N, ns, seed):
         assert r["flags"][i, 2] == 0  # LQ fall-back never needed
 
 
+@pytest.mark.parametrize("case", ["term_rti_n20_inactive", "term_rti_n20_active", "term_sqp_n10_active", "term_sqp_n12_inactive"])
+def test_emulated_kernels_terminal_row_against_reference_golden(built, case):
+    """Terminal ellipsoid row: the device source, emulated, against the vectors of the compiled
+    reference (acados BGH nh_e = 1 + HPIPM, incl. its LQ fall-back in the active cases)."""
+    from pathlib import Path
+
+    import robotic_mpc_b200.params as pm
+
+    g = np.load(Path(__file__).resolve().parent / "golden" / f"{case}.npz")
+    N, ns, st = int(g["N"]), min(int(g["nsteps"]), 30), int(g["solver_type"])
+    par = pm.pack_params(1, 0.01, surf=g["surf"][None], w_u=float(g["w_u"]), w_qddot=float(g["w_qddot"]))
+    term = np.concatenate([g["term_P"].ravel(), [float(g["term_lh"])], [float(g["term_alpha"])]])[None]
+    r = emu.closed_loop(par, g["z0"][None], N, st, ns, seed=3, term=term)
+    tol = 1e-6 if case.endswith("_active") else 1e-10
+    assert np.abs(r["u"][0] - g["u"][:ns]).max() < tol * np.abs(g["u"]).max()
+    assert np.abs(r["z"][0] - g["z"][:ns + 1]).max() < tol * np.abs(g["z"]).max()
+    assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"][:ns])
+    assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"][:ns])
+    assert np.abs(r["slog"][0, :, 2] - g["qp_iter"][:ns]).max() <= 1
+    assert np.abs(r["slog"][0, :, 3] - g["cost"][:ns]).max() < tol * np.abs(g["cost"]).max()
+
+
 def test_emulated_schedule_independence(oracle):
     """Different lane interleavings (seeds) must give bit-identical results: no missing __syncwarp."""
     import robotic_mpc_b200.params as pm

@@ -23,9 +23,11 @@ def _inputs(o, B, seed):
     return surf, z0
 
 
-def _run(rm, B, N, solver, par, z0, ns):
+def _run(rm, B, N, solver, par, z0, ns, term=None):
     eng = rm.Engine(B, N, solver, dt=0.01, nlog=ns)
     eng.set_params(par)
+    if term is not None:
+        eng.set_terminal(*term)
     eng.set_state(z0)
     eng.reset()
     eng.closed_loop(ns)
@@ -74,7 +76,8 @@ def test_golden_vectors_of_the_reference(built, case):
     N, ns = int(g["N"]), int(g["nsteps"])
     solver = "SQP_RTI" if int(g["solver_type"]) == 1 else "SQP"
     par = rm.pack_params(1, 0.01, surf=g["surf"][None], w_u=float(g["w_u"]), w_qddot=float(g["w_qddot"]))
-    r = _run(rm, 1, N, solver, par, g["z0"][None], ns)
+    term = (g["term_P"], float(g["term_alpha"]), float(g["term_lh"])) if "term_P" in g.files else None
+    r = _run(rm, 1, N, solver, par, g["z0"][None], ns, term=term)
     assert relerr(r["ulog"][0], g["u"]) < RTOL
     assert relerr(r["zlog"][0], g["z"]) < RTOL
     assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"])
@@ -158,3 +161,33 @@ def test_tracking_summary_matches_posthoc(oracle):
             itse += (k * 0.01) * e ** 2 * 0.01
         np.testing.assert_allclose(r["summary"][i, 0:5], sse, rtol=1e-9)
         np.testing.assert_allclose(r["summary"][i, 5:10], itse, rtol=1e-9)
+
+
+@pytest.mark.parametrize("solver,N,ns", [("SQP_RTI", 15, 30), ("SQP", 10, 8)])
+def test_terminal_row_batch_matches_oracle(oracle, solver, N, ns):
+    """Terminal ellipsoid x_N' P x_N <= alpha on a batch whose instances differ in how tight the set
+    is: inactive (alpha from the LQR construction) down to strongly active (alpha = 0.7 x0' P x0)."""
+    import robotic_mpc_b200 as rm
+    import robotic_mpc_b200.terminal_constraint as tc
+
+    o = oracle
+    B = 6
+    surf, z0 = _inputs(o, B, 300 + N)
+    P, alpha0 = tc.default_terminal_set(rho=100.0)
+    scale = [None, 0.95, 0.9, 0.8, 0.7, None]
+    alpha = np.array([alpha0 if s is None else s * float(z @ P @ z) for s, z in zip(scale, z0)])
+    par = rm.pack_params(B, 0.01, surf=surf)
+    r = _run(rm, B, N, solver, par, z0, ns, term=(P, alpha, -alpha))
+    port = o.PortLeg()
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    for i in range(B):
+        g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i], term_P=P, term_alpha=alpha[i]), z0[i], ns,
+                             full_traj=True)
+        assert relerr(r["ulog"][i], g["u"]) < RTOL
+        assert relerr(r["zlog"][i], g["z"]) < RTOL
+        assert np.array_equal(r["slog"][i, :, 0].astype(int), g["status"])
+        assert relerr(r["x"][i], g["xtraj"][-1]) < RTOL
+        # the row really binds where it was made tight: h_e(x_N) = alpha at the solution
+        if scale[i] is not None and g["status"][-1] == 0:
+            xN = r["x"][i, -1]
+            assert float(xN @ P @ xN) <= alpha[i] * (1 + 1e-6)

@@ -17,7 +17,9 @@
 #include "rmpc_device.cuh"
 #include "rmpc_layout.h"
 
+#ifndef RMPC_WARPS_PER_CTA
 #define RMPC_WARPS_PER_CTA 4
+#endif
 #define RMPC_GROUPS_PER_CTA (RMPC_WARPS_PER_CTA * 32 / RMPC_G)
 
 static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layout mismatch");

@@ -1650,6 +1650,28 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
     return -grp_max(-a);
 }
 
+/* the two sums of ipm_mu_aff as a separate pass (only needed after a refinement of the predictor step) */
+RD void ipm_mu_sums(const RmpcDims &D, const Inst &I, const double *dlam, const double *dt, double *sums)
+{
+    const int N = D.N, lane = rd_lane();
+    double sB = 0.0, sC = 0.0;
+    for (int k = lane; k < N * NB; k += GL)
+    {
+        const int i = k / NB, j = k - NB * i;
+        if (i == 0 && (j % 12) >= 6) continue;
+        sB += AR(slam)[k] * dt[k] + dlam[k] * AR(st)[k];
+        sC += dlam[k] * dt[k];
+    }
+    if (I.pe && lane < 2)
+    {
+        const int k = lane ? TERM_UP(N) : TERM_LO(N);
+        sB += AR(slam)[k] * dt[k] + dlam[k] * AR(st)[k];
+        sC += dlam[k] * dt[k];
+    }
+    sums[0] = grp_sum(sB);
+    sums[1] = grp_sum(sC);
+}
+
 /* COMPUTE_MU_AFF_QP (x_core_qp_ipm_aux.c:424-441): sum (lam + alpha dlam)(t + alpha dt) / nc, expanded in powers of
  * alpha so that the sums can be accumulated by the forward sweep before alpha is known */
 RD double ipm_mu_aff(double sum_lt, const double *sums, double alpha, double nc_inv)
@@ -1709,7 +1731,31 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         ipm_forward<0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);
         if ((lin[0] == 0.0 && lin[1] > 0.5) || lin[0] > 1e-5)
         {
+            /* Inaccurate factorisation (x_ocp_qp_ipm.c:2246-2276).  HPIPM re-factorises this iteration with Householder
+             * LQ; here the SAME linear system is brought to the same accuracy by iterative refinement of the predictor
+             * step with the factors at hand (residual of the linear system -> correction solve -> add), at most twice.
+             * The event is counted in flags[2]. */
             if (lane == 0) I.flags[2] += 1;
+            for (int it = 0; it < 2; it++)
+            {
+                double pn[6], a2, s2[2], l2[2];
+                ipm_res<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), AR(ig),
+                              AR(ib), AR(id), AR(im), pn);
+                if (pn[0] < 1e-5 && pn[1] < 1e-5 && pn[2] < 1e-5 && pn[3] < 1e-5 && !(pn[5] > 0.5)) break;
+                ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
+                ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
+                for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
+                for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
+                for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
+                if (I.pe && lane < 2)
+                {
+                    const int k = lane ? TERM_UP(N) : TERM_LO(N);
+                    AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k];
+                }
+                rd_sync();
+            }
+            alpha = ipm_alpha(D, I, AR(dlam), AR(dt_));
+            ipm_mu_sums(D, I, AR(dlam), AR(dt_), sums);
         }
         double mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         const double tmp = mu_aff / mu, sigma = tmp * tmp * tmp;

@@ -178,15 +178,17 @@ def test_terminal_row_batch_matches_oracle(oracle, solver, N, ns):
     alpha = np.array([alpha0 if s is None else s * float(z @ P @ z) for s, z in zip(scale, z0)])
     par = rm.pack_params(B, 0.01, surf=surf)
     r = _run(rm, B, N, solver, par, z0, ns, term=(P, alpha, -alpha))
-    port = o.PortLeg()
+    # An active row drives HPIPM into its LQ fall-back at noise-picked iterations; the port (own noise) then agrees with the
+    # reference to a few 1e-7 only.  The compiled reference travels with the repo (oracle/_ref): use it when it is there.
+    leg, tol = (o.RefLeg(), RTOL) if o.REF_SO.exists() else (o.PortLeg(), 5 * RTOL)
     st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
     for i in range(B):
-        g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i], term_P=P, term_alpha=alpha[i]), z0[i], ns,
-                             full_traj=True)
-        assert relerr(r["ulog"][i], g["u"]) < RTOL
-        assert relerr(r["zlog"][i], g["z"]) < RTOL
+        g = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i], term_P=P, term_alpha=alpha[i]), z0[i], ns,
+                            full_traj=True)
+        assert relerr(r["ulog"][i], g["u"]) < tol
+        assert relerr(r["zlog"][i], g["z"]) < tol
         assert np.array_equal(r["slog"][i, :, 0].astype(int), g["status"])
-        assert relerr(r["x"][i], g["xtraj"][-1]) < RTOL
+        assert relerr(r["x"][i], g["xtraj"][-1]) < tol
         # the row really binds where it was made tight: h_e(x_N) = alpha at the solution
         if scale[i] is not None and g["status"][-1] == 0:
             xN = r["x"][i, -1]

@@ -3,8 +3,8 @@
 
   config2   README grid search, 24 option tuples x 256 random surfaces = 6144 instances, 600 closed-loop steps, through
             SimulationManager.grid_search / run_all (one batched run per (N, solver) group), summaries only
-  config4   full SQP, N = 200, terminal ellipsoid, B instances: one rmpc_solve of every instance from the initial guess;
-            solves/s and the per-solve device latency distribution (RL_TIME of each instance)
+  config4   full SQP, N = 200, terminal ellipsoid, B instances: K closed-loop steps, each one full SQP solve of every
+            instance; per step: solves/s and the per-solve device latency distribution (RL_TIME of each instance)
   config5   horizon sweep N in {10, 50, 100, 200, 300}, SQP_RTI, 600 steps: this GPU's 1/8 share of the 65536 instances
             (8192 instances, 1638/1639 per horizon) unless --batch says otherwise
 
@@ -60,7 +60,7 @@ def config2(args):
     S = mgr.last_summaries
     K = int(base["simulation_time"] / 0.01)
     print(json.dumps({"config": "configs[1] README grid search", "instances": n, "closed_loop_steps": K,
-                      "groups": len(mgr.last_run_info["groups"]) if mgr.last_run_info else None,
+                      "run_info": mgr.last_run_info,
                       "wall_s": dt, "mpc_steps_per_s_incl_host_setup": n * K / dt,
                       "failures": int(S[:, rm.RS["NFAIL"]].sum()), "sqp_iters_total": int(S[:, rm.RS["SQP_ITERS"]].sum()),
                       "qp_iters_total": int(S[:, rm.RS["QP_ITERS"]].sum())}))
@@ -71,38 +71,42 @@ def config4(args):
     import robotic_mpc_b200 as rm
     import robotic_mpc_b200.terminal_constraint as tc
 
-    B, N = args.batch or 16384, args.horizon or 200
+    B, N, K = args.batch or 16384, args.horizon or 200, args.steps or 5
     surf, z0 = workload(B, 42 + 3)
     P, alpha = tc.default_terminal_set(wcv=200.0, Ts=0.01, rho=args.rho)
-    eng = rm.Engine(B, N, "SQP", dt=0.01, nlog=1)
+    eng = rm.Engine(B, N, "SQP", dt=0.01, nlog=K)
     eng.set_params(rm.pack_params(B, 0.01, surf=surf))
     eng.set_terminal(P, alpha)
     eng.set_state(z0)
-    out = []
-    for rep in range(args.reps):
-        eng.reset()
-        torch.cuda.synchronize()
+    eng.reset()
+    torch.cuda.synchronize()
+    ms = []
+    for k in range(K):  # every closed-loop step is one full SQP solve of every instance (<= 100 iterations, tol 1e-6)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        eng.solve()
+        eng.closed_loop(1)
         e1.record()
         e1.synchronize()
-        ms = e0.elapsed_time(e1)
-        st = eng.get("stats").cpu().numpy()
-        lat = st[:, rm.RL["TIME"]] * 1e3
-        xN = eng.get("x", N).cpu().numpy()
-        h = np.einsum("bi,ij,bj->b", xN, P, xN)
-        out.append({"config": "configs[3] full SQP N=%d + terminal ellipsoid (rho=%g, alpha=%.4g)" % (N, args.rho, alpha),
-                    "instances": B, "batch_ms": ms, "solves_per_s": B / (ms * 1e-3),
-                    "per_solve_latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
-                                             "max": float(lat.max()), "what": "device time of each instance's own solve"},
-                    "status_hist": {int(k): int(v) for k, v in zip(*np.unique(st[:, 0].astype(int), return_counts=True))},
-                    "sqp_iter_mean": float(st[:, rm.RL["SQP_ITER"]].mean()), "qp_iter_mean": float(st[:, rm.RL["QP_ITER"]].mean()),
-                    "terminal_row_max_h_over_alpha": float(h.max() / alpha),
-                    "lq_triggers": int(eng.get("flags").cpu().numpy()[:, 2].sum()), "device_GiB": eng.device_bytes / 2 ** 30})
+        ms.append(e0.elapsed_time(e1))
+    sl = eng.get("slog").cpu().numpy()
+    xN = eng.get("x", N).cpu().numpy()
+    h = np.einsum("bi,ij,bj->b", xN, P, xN)
+    for k in range(K):
+        lat = sl[:, k, rm.RL["TIME"]] * 1e3
+        print(json.dumps({
+            "config": "configs[3] full SQP N=%d + terminal ellipsoid (rho=%g, alpha=%.4g), closed-loop step %d" % (N, args.rho, alpha, k),
+            "note": "step 0 starts from the flat initial guess: its first QP fails in the reference too (status 4, 1 SQP / 3 QP "
+                    "iterations, checked against the compiled acados) and the solve proper happens at step 1" if k == 0 else "",
+            "instances": B, "batch_ms": ms[k], "solves_per_s": B / (ms[k] * 1e-3),
+            "per_solve_latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
+                                     "max": float(lat.max()), "what": "device time of each instance's own solve (RL_TIME)"},
+            "status_hist": {int(a): int(b) for a, b in zip(*np.unique(sl[:, k, 0].astype(int), return_counts=True))},
+            "sqp_iter_mean": float(sl[:, k, rm.RL["SQP_ITER"]].mean()), "sqp_iter_max": int(sl[:, k, rm.RL["SQP_ITER"]].max()),
+            "qp_iter_mean": float(sl[:, k, rm.RL["QP_ITER"]].mean()),
+            "max_kkt_res": [float(v) for v in sl[:, k, rm.RL["RES"]:rm.RL["RES"] + 4].max(axis=0)]}))
+    print(json.dumps({"config": "configs[3] summary", "terminal_row_max_h_over_alpha": float(h.max() / alpha),
+                      "lq_triggers": int(eng.get("flags").cpu().numpy()[:, 2].sum()), "device_GiB": eng.device_bytes / 2 ** 30}))
     eng.close()
-    for o in out:
-        print(json.dumps(o))
 
 
 def config5(args):

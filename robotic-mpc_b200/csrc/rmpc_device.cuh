@@ -1706,6 +1706,201 @@ RDN void ipm_update(const RmpcDims &D, const Inst &I, double a)
     rd_sync();
 }
 
+/* UPDATE_VAR_QP + OCP_QP_RES_COMPUTE in ONE stage-by-stage pass with staged operands (the hot pair of every interior-point
+ * iteration; ipm_update + ipm_res<0, 1> are the same two steps as separate passes and stay for the rare paths).
+ * UPD = 1: the iterate is first moved, (ux, pi) += a (dux, dpi), (lam, t) = max((lam, t) + a (dlam, dt), 1e-16), written
+ * back, and the residuals are evaluated at the new point; UPD = 0: residuals at the current point (first call of a QP).
+ * The 16 lanes of the group work on ONE stage at a time with the row roles of the Riccati sweeps (lane l < 6: rows u_l
+ * and qd_l, lane 6 + j: row q_j; lane l < 12 also owns bound slot l), all operands of the stage are fetched one stage
+ * ahead by cp.async into shared memory -- coalesced 16-byte copies instead of 16 lanes striding through 16 different
+ * stages -- and the multiplier of the previous stage is carried in a register.  Returns sum lam t; norms as ipm_res. */
+enum { QG_UX = 0, QG_DUX = 18, QG_XN = 36, QG_DXN = 48, QG_RQZ = 60, QG_PI = 78, QG_DPI = 90, QG_LAM = 102, QG_DLAM = 126,
+       QG_T = 150, QG_DT = 174, QG_B = 198, QG_D = 210, QG_JC = 234, QG_END = 270 };
+template <int UPD>
+RD void res_stage_in(const Inst &I, double *dst, int i, int N)
+{
+    const bool cons = (i < N) || I.pe; /* stage N carries constraint slots only with a terminal row */
+    stage_cp(dst + QG_UX, AR(sux) + NV * i, NV);
+    stage_cp(dst + QG_RQZ, AR(rqz) + NV * i, NV);
+    if (UPD) stage_cp(dst + QG_DUX, AR(dux) + NV * i, NV);
+    if (i < N)
+    {
+        stage_cp(dst + QG_XN, AR(sux) + NV * (i + 1) + 6, NX);
+        stage_cp(dst + QG_PI, AR(spi) + NX * i, NX);
+        stage_cp(dst + QG_B, AR(b) + NX * i, NX);
+        if (UPD)
+        {
+            stage_cp(dst + QG_DXN, AR(dux) + NV * (i + 1) + 6, NX);
+            stage_cp(dst + QG_DPI, AR(dpi) + NX * i, NX);
+        }
+    }
+    if (cons)
+    {
+        stage_cp(dst + QG_LAM, AR(slam) + NB * i, NB);
+        stage_cp(dst + QG_T, AR(st) + NB * i, NB);
+        stage_cp(dst + QG_D, AR(d) + NB * i, NB);
+        if (UPD)
+        {
+            stage_cp(dst + QG_DLAM, AR(dlam) + NB * i, NB);
+            stage_cp(dst + QG_DT, AR(dt_) + NB * i, NB);
+        }
+        if (i > 0) stage_cp(dst + QG_JC, AR(Jc) + NJ * i, NJ);
+    }
+}
+
+template <int UPD>
+RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double a, double *nrm)
+{
+    const int N = D.N, lane = rd_lane();
+    const Role R = make_role(I.par);
+    const int j = R.j, xk = R.xk;
+    const double a12 = C_A12(j), a22 = C_A22(j), b1 = C_B1(j), b2 = C_B2(j);
+    const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
+    const double lmin = 1e-16;
+    double mu = 0.0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, n4 = 0, nanflag = 0, pprev = 0.0;
+    res_stage_in<UPD>(I, SW_STG(sm, 0), 0, N);
+    rd_cp_commit();
+#define QV(off, doff, c) (UPD ? G[(off) + (c)] + a * G[(doff) + (c)] : G[(off) + (c)])
+#define QF(off, doff, c, out)                                                                 \
+    do                                                                                        \
+    {                                                                                         \
+        double q_ = G[(off) + (c)];                                                           \
+        if (UPD) { q_ = q_ + a * G[(doff) + (c)]; q_ = q_ <= lmin ? lmin : q_; }              \
+        (out) = q_;                                                                           \
+    } while (0)
+    for (int i = 0; i <= N; i++)
+    {
+        const double *G = SW_STG(sm, i & 1);
+        if (i < N) res_stage_in<UPD>(I, SW_STG(sm, (i + 1) & 1), i + 1, N);
+        rd_cp_commit();
+        rd_cp_wait1();
+        rd_sync();
+        const bool mid = i < N, x_on = i > 0;
+        /* new values of this lane's joint: u_j, q_j, qd_j (the state is fixed at stage 0 of the reduced QP) */
+        const double uj = mid ? QV(QG_UX, QG_DUX, j) : 0.0;
+        const double qj = x_on ? QV(QG_UX, QG_DUX, 6 + j) : 0.0;
+        const double dj = x_on ? QV(QG_UX, QG_DUX, 12 + j) : 0.0;
+        double pq = 0.0, pd = 0.0;
+        if (mid) { pq = QV(QG_PI, QG_DPI, j); pd = QV(QG_PI, QG_DPI, 6 + j); }
+        /* bound slot of this lane */
+        double dlm = 0.0;
+        if (mid && lane < 12 && !(i == 0 && lane >= 6))
+        {
+            const double vl = lane < 6 ? uj : qj;
+            double la, lb, ta, tb;
+            QF(QG_LAM, QG_DLAM, lane, la); QF(QG_LAM, QG_DLAM, 12 + lane, lb);
+            QF(QG_T, QG_DT, lane, ta); QF(QG_T, QG_DT, 12 + lane, tb);
+            const int ia = NB * i + lane, ib = ia + 12;
+            if (UPD) { AR(slam)[ia] = la; AR(slam)[ib] = lb; AR(st)[ia] = ta; AR(st)[ib] = tb; }
+            const double dl = G[QG_D + lane] + ta - vl, du = G[QG_D + 12 + lane] + tb + vl;
+            const double ml = la * ta, mu_ = lb * tb;
+            mu += ml + mu_;
+            AR(res_d)[ia] = dl; AR(res_d)[ib] = du; AR(res_m)[ia] = ml; AR(res_m)[ib] = mu_;
+            n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
+            n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
+            n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
+            dlm = lb - la;
+        }
+        /* control row u_j */
+        if (R.u && mid)
+        {
+            double g = G[QG_RQZ + lane];
+            g += hu * uj + hs * dj + b1 * pq + b2 * pd;
+            g += dlm;
+            AR(res_g)[NV * i + lane] = g;
+            n0 = rd_fmax(n0, fabs(g));
+            if (i == 0 && lane == 0 && g != g) nanflag = 1.0;
+        }
+        /* state row (q_j on lanes 6..11, qd_j on lanes 0..5), dynamics residual of the same row */
+        if (R.x)
+        {
+            if (x_on)
+            {
+                double g = G[QG_RQZ + 6 + xk];
+                if (mid)
+                {
+                    if (R.q)
+                    {
+                        RD_UNROLL
+                        for (int m = 0; m < 5; m++)
+                        {
+                            double w = 0.0;
+                            RD_UNROLL
+                            for (int k = 0; k < 6; k++) w += G[QG_JC + 6 * m + k] * QV(QG_UX, QG_DUX, 6 + k);
+                            if (m == 4)
+                            {
+                                RD_UNROLL
+                                for (int k = 0; k < 6; k++) w += G[QG_JC + 30 + k] * QV(QG_UX, QG_DUX, 12 + k);
+                            }
+                            g += G[QG_JC + 6 * m + j] * w;
+                        }
+                        g += pq;
+                        g += dlm;
+                    }
+                    else
+                    {
+                        double w = 0.0;
+                        RD_UNROLL
+                        for (int k = 0; k < 6; k++) w += G[QG_JC + 24 + k] * QV(QG_UX, QG_DUX, 6 + k);
+                        RD_UNROLL
+                        for (int k = 0; k < 6; k++) w += G[QG_JC + 30 + k] * QV(QG_UX, QG_DUX, 12 + k);
+                        g += G[QG_JC + 30 + j] * w;
+                        g += hs * uj + hq * dj + a12 * pq + a22 * pd;
+                    }
+                }
+                g -= pprev;
+                if (!mid && I.pe)
+                { /* general row of stage N: res_g += C' (lam_u - lam_l) */
+                    double la, lb;
+                    QF(QG_LAM, QG_DLAM, 0, la); QF(QG_LAM, QG_DLAM, 12, lb);
+                    g += G[QG_JC + xk] * (lb - la);
+                }
+                AR(res_g)[NV * i + 6 + xk] = g;
+                n0 = rd_fmax(n0, fabs(g));
+            }
+            if (mid)
+            {
+                const double xn = QV(QG_XN, QG_DXN, xk);
+                double r;
+                if (R.q) r = G[QG_B + j] - xn + (qj + a12 * dj) + b1 * uj;
+                else r = G[QG_B + 6 + j] - xn + a22 * dj + b2 * uj;
+                AR(res_b)[NX * i + xk] = r;
+                n1 = rd_fmax(n1, fabs(r));
+                pprev = R.q ? pq : pd;
+            }
+        }
+        if (!mid && I.pe && lane == 12)
+        { /* general row of stage N: res_d = d + t -+ C x, res_m; its two slots are moved here as well */
+            double cx = 0.0, la, lb, ta, tb;
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) cx += G[QG_JC + k] * QV(QG_UX, QG_DUX, 6 + k);
+            QF(QG_LAM, QG_DLAM, 0, la); QF(QG_LAM, QG_DLAM, 12, lb);
+            QF(QG_T, QG_DT, 0, ta); QF(QG_T, QG_DT, 12, tb);
+            const int ia = TERM_LO(N), ib = TERM_UP(N);
+            if (UPD) { AR(slam)[ia] = la; AR(slam)[ib] = lb; AR(st)[ia] = ta; AR(st)[ib] = tb; }
+            const double dl = G[QG_D] + ta - cx, du = G[QG_D + 12] + tb + cx;
+            const double ml = la * ta, mu_ = lb * tb;
+            mu += ml + mu_;
+            AR(res_d)[ia] = dl; AR(res_d)[ib] = du; AR(res_m)[ia] = ml; AR(res_m)[ib] = mu_;
+            n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
+            n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
+            n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
+        }
+        if (UPD)
+        { /* write the moved primal iterate and multipliers of this stage back */
+            for (int c = lane; c < NV; c += GL) AR(sux)[NV * i + c] = G[QG_UX + c] + a * G[QG_DUX + c];
+            if (mid && lane < NX) AR(spi)[NX * i + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
+        }
+        rd_sync(); /* the buffer of this stage is refilled by the next iteration */
+    }
+#undef QV
+#undef QF
+    rd_cp_wait0();
+    nrm[0] = grp_max(n0); nrm[1] = grp_max(n1); nrm[2] = grp_max(n2); nrm[3] = grp_max(n3); nrm[4] = grp_max(n4);
+    nrm[5] = grp_max(nanflag);
+    return grp_sum(mu);
+}
+
 /* d_ocp_qp_ipm_solve (H/ocp_qp/x_ocp_qp_ipm.c:2626-3018) with OCP_QP_IPM_DELTA_STEP (:2155-2622) for the option set
  * acados resolves: Mehrotra predictor-corrector, conditional second centering solve, up to two
  * refinement steps on the corrector, single damped step, lam/t floor 1e-16.  Returns the acados QP status
@@ -1719,8 +1914,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
     const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12 + (I.pe ? 2 : 0));
     ipm_init(D, I, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
-    double sum_lt = ipm_res<0, 1>(D, I, sm, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g),
-                                  AR(res_b), AR(res_d), AR(res_m), nrm);
+    double sum_lt = ipm_res_sweep<0>(D, I, sm, 0.0, nrm);
     double mu = nc_inv * sum_lt;
     int kk;
     for (kk = 0; kk < D.qp_iter_max && alpha > alpha_min && (nrm[0] > tol || nrm[1] > tol || nrm[2] > tol || nrm[4] > tol); kk++)
@@ -1804,9 +1998,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         if (refined) alpha = ipm_alpha(D, I, AR(dlam), AR(dt_));
         double a = alpha;
         if (a < 1.0) a = a * ((1.0 - a) * 0.99 + a * 0.9999999);
-        ipm_update(D, I, a);
-        sum_lt = ipm_res<0, 1>(D, I, sm, AR(rqz), AR(b), AR(d), nullptr, 0.0, AR(sux), AR(spi), AR(slam), AR(st), nullptr, nullptr, AR(res_g), AR(res_b),
-                               AR(res_d), AR(res_m), nrm);
+        sum_lt = ipm_res_sweep<1>(D, I, sm, a, nrm); /* UPDATE_VAR_QP + OCP_QP_RES_COMPUTE */
         mu = nc_inv * sum_lt;
     }
     *iters = kk;

@@ -598,8 +598,9 @@ struct LinEmit
  * Writes per stage: Jc = sqrt(dt W_m) * d y5_m / d x (non-zero entries), rqz = cost gradient, b = dynamics gap,
  * d = [lb - v; v - ub]; dx0 = x0 - x_nlp[0] (both bound residuals of the stage-0 state equality).
  * Returns the total cost. */
-RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *x0)
+RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, const double *x0)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double dt = D.dt;
     const double *par = I.par;
@@ -663,8 +664,9 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I, 
 /* Merit function at the trial iterate tux, ocp_nlp_evaluate_merit_fun
  * (AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:606-702):
  *   M = cost + sum |w_pi| |dyn gap| + sum |w_lam| max(0, bound violation)   (incl. the stage-0 x0 equality) */
-RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, const double *tux, const double *x0)
+RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, const double *tux, const double *x0)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double m = 0.0;
@@ -717,8 +719,9 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I, cons
 
 /* KKT residual inf-norms of the NLP, ocp_nlp_res_compute (AC/ocp_nlp/ocp_nlp_common.c:3641-3751); uses the
  * linearisation (rqz, b, d, dx0) of the current iterate.  res = [stat, eq, ineq, comp]. */
-RDN void nlp_residuals(const RmpcDims &D, const Inst &I, double *res)
+RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double rs = 0, re = 0, ri = 0, rc = 0;
@@ -802,8 +805,9 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
  * warm = 0 (every QP but the first, see oracle/rmpc_oracle.c:solve_qp for the reference quirk): ux = 0, pi = 0,
  * t = slack pushed to >= 0.1 by moving ux, lam = mu0 / t with mu0 = 1 (t0_init 2, var_init_scheme 1, :1837-1978).
  * The primal iterate is zeroed first in both cases (AC/ocp_qp/ocp_qp_hpipm.c:309-316). */
-RDN void ipm_init(const RmpcDims &D, const Inst &I, int warm)
+RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] = 0.0;
     if (warm != 2)
@@ -886,10 +890,11 @@ RD void task_hess_mv(const double *Jc, const double *x, double *y)
  * :689-726) in nrm[0..3], nrm[4] = |res_m - tau_min|_inf, nrm[5] = NaN flag of rg[0]; returns sum lam*t (LIN = 0).
  * WRITE = 0 computes the norms only. */
 template <int LIN, int WRITE>
-RDN double ipm_res(const RmpcDims &D, const Inst &I, const GrpSmem &sm, const double *rqz, const double *b, const double *d, const double *m,
+RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const double *rqz, const double *b, const double *d, const double *m,
                   double mshift, const double *ux, const double *pi, const double *lam, const double *t, const double *Lam,
                   const double *T, double *rg, double *rb, double *rd, double *rm, double *nrm)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     double mu = 0.0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, n4 = 0, nanflag = 0;
@@ -1042,8 +1047,9 @@ RD void fac_stage_in(const Inst &I, double *dst, int ss)
     if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
 }
 
-RDN void ipm_factor(const RmpcDims &D, const Inst &I, GrpSmem &sm)
+RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
     const Role R = make_role(par);
@@ -1310,10 +1316,11 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
  * bounds, complementarity) are zero up to rounding BY CONSTRUCTION of dx+, dt and dlam in this sweep and are not
  * re-evaluated. */
 template <int STORED>
-RDN void ipm_forward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
+RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                     const double *rm, double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out,
                     double *sums, double *lin)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
@@ -1518,9 +1525,10 @@ RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
 }
 
 template <int MODE, int USE_PB>
-RDN void ipm_backward(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
+RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                      const double *rm, double sigma_mu, double *X)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
@@ -1749,8 +1757,9 @@ RD void res_stage_in(const Inst &I, double *dst, int i, int N)
 }
 
 template <int UPD>
-RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I, GrpSmem &sm, const double a, double *nrm)
+RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const double a, double *nrm)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
@@ -2042,8 +2051,9 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
  * AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:705-755), ocp_nlp_line_search (:290-408, alpha = 1, 0.7, ...
  * while alpha*0.7 > 0.05; the last alpha is taken untested), ocp_nlp_update_variables_sqp
  * (AC/ocp_nlp/ocp_nlp_common.c:3259-3318, full_step_dual = 0).  Returns 1 on a NaN/inf merit value. */
-RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I, int nlp_iter, double *alpha_out)
+RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, int nlp_iter, double *alpha_out)
 {
+    const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < N * NX; k += GL)
     {

@@ -338,11 +338,13 @@ def run_gpu(args):
                          "frac": achieved_gbs / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": "MEASURED_PEAKS.json" if pk.exists() else "fallback",
                          "kernel": "rmpc_closed_loop_kernel", "algorithmic_bytes_per_launch": bytes_step,
+                         "traffic_over_launch_time_GBs": (traffic / (kernel_ms * 1e-3) / 1e9) if traffic else None,
+                         "traffic_frac_of_peak": (traffic / (kernel_ms * 1e-3) / 1e9 / hbm_peak) if traffic else None,
                          "note": "achieved = ALGORITHMIC bytes (iterate in/out, x0, u0, parameters) / launch time.  The "
-                                 "measured DRAM traffic per launch (`traffic`, ncu) is ~50x that: the interior-point work "
-                                 "arrays of 4096 instances (2.6 GB) do not fit in L2 and every Riccati sweep streams them; "
-                                 "traffic / launch time is ~45 % of the HBM peak, the rest of the time is dependent-issue "
-                                 "latency of the stage recursion (see fp64 and DESIGN.md 4)"},
+                                 "measured DRAM traffic per launch (`traffic`, ncu capture of the same workload) is ~45x "
+                                 "that: the interior-point work arrays of 4096 instances (2.6 GB) do not fit in L2 and "
+                                 "every Riccati sweep streams them; traffic / launch time is the fraction of the HBM peak "
+                                 "the kernel really draws (traffic_frac_of_peak), see DESIGN.md 4"},
             "fp64": {"achieved_tflops": achieved_tf, "peak_tflops": fp64_peak, "frac": achieved_tf / fp64_peak,
                      "peak_source": "cuBLAS DGEMM 4096^3 measured in this run",
                      "algorithmic_flops_per_launch": flops_step, "qp_iters_per_mpc_step": qp_iters_per_step},

@@ -625,7 +625,9 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         em.par = par;
         em.dt = dt;
         ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
-        cost += stage_cost(par, dt, y5, v, v + 12);
+        const double ci = stage_cost(par, dt, y5, v, v + 12);
+        cost += ci;
+        AR(tux)[NV * i] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
         /* dynamics gap b = Ad x + Bd u - x_next */
         const double *xn = AR(ux) + NV * (i + 1) + 6;
         double *b = AR(b) + NX * i, *d = AR(d) + NB * i;
@@ -664,8 +666,9 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
 /* Merit function at the trial iterate tux, ocp_nlp_evaluate_merit_fun
  * (AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:606-702):
  *   M = cost + sum |w_pi| |dyn gap| + sum |w_lam| max(0, bound violation)   (incl. the stage-0 x0 equality) */
-RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, const double *tux, const double *x0)
+RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, const double *tux, const double *x0, double *cost_out)
 {
+    double csum = 0.0;
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     const double *par = I.par;
@@ -676,7 +679,9 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
         load18(tux + NV * i, v);
         NoEmit ne;
         ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
-        m += stage_cost(par, D.dt, y5, v, v + 12);
+        const double ci = stage_cost(par, D.dt, y5, v, v + 12);
+        m += ci;
+        csum += ci; /* the cost alone, summed like solver.get_cost() does (closed_loop_group) */
         const double *xn = tux + NV * (i + 1) + 6, *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i;
         RD_UNROLL
         for (int k = 0; k < 6; k++)
@@ -713,6 +718,65 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
             if (fl > 0.0) m += fabs(AR(wlam)[TERM_LO(N)]) * fl;
             if (fu > 0.0) m += fabs(AR(wlam)[TERM_UP(N)]) * fu;
         }
+    }
+    if (cost_out) *cost_out = grp_sum(csum);
+    return grp_sum(m);
+}
+
+/* The same merit value at the CURRENT iterate, without a kinematics pass: every ingredient was produced by the
+ * linearisation of this iterate -- stage costs (kept in tux[.][0]), dynamics gaps b, bound residuals d, dx0 -- and is
+ * accumulated in the order nlp_merit uses.  Stage 0's gap is re-formed from the iterate (qp_reduce folded dx0 into b_0). */
+RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
+{
+    const Inst I = I_;
+    const int N = D.N, lane = rd_lane();
+    const double *par = I.par;
+    double m = 0.0;
+    for (int i = lane; i < N; i += GL)
+    {
+        m += AR(tux)[NV * i];
+        const double *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i, *d = AR(d) + NB * i;
+        if (i == 0)
+        {
+            const double *v = AR(ux), *xn = AR(ux) + NV + 6;
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                const double g0 = (v[6 + k] + par[RP_A12 + k] * v[12 + k]) + par[RP_B1 + k] * v[k] - xn[k];
+                const double g1 = par[RP_A22 + k] * v[12 + k] + par[RP_B2 + k] * v[k] - xn[6 + k];
+                m += fabs(wpi[k]) * fabs(g0) + fabs(wpi[6 + k]) * fabs(g1);
+            }
+        }
+        else
+        {
+            const double *b = AR(b) + NX * i;
+            RD_UNROLL
+            for (int k = 0; k < 6; k++) m += fabs(wpi[k]) * fabs(b[k]) + fabs(wpi[6 + k]) * fabs(b[6 + k]);
+        }
+        RD_UNROLL
+        for (int j = 0; j < 12; j++)
+        {
+            if (i == 0 && j >= 6) continue;
+            const double fl = d[j], fu = d[12 + j];
+            if (fl > 0.0) m += fabs(wl[j]) * fl;
+            if (fu > 0.0) m += fabs(wl[12 + j]) * fu;
+        }
+        if (i == 0)
+        {
+            RD_UNROLL
+            for (int k = 0; k < NX; k++)
+            {
+                const double fl = x0[k] - AR(ux)[6 + k];
+                if (fl > 0.0) m += fabs((I.head + H_WLAMX0)[k]) * fl;
+                if (-fl > 0.0) m += fabs((I.head + H_WLAMX0)[12 + k]) * (-fl);
+            }
+        }
+    }
+    if (I.pe && lane == 0)
+    {
+        const double fl = AR(d)[TERM_LO(N)], fu = AR(d)[TERM_UP(N)];
+        if (fl > 0.0) m += fabs(AR(wlam)[TERM_LO(N)]) * fl;
+        if (fu > 0.0) m += fabs(AR(wlam)[TERM_UP(N)]) * fu;
     }
     return grp_sum(m);
 }
@@ -2051,8 +2115,10 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
  * AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:705-755), ocp_nlp_line_search (:290-408, alpha = 1, 0.7, ...
  * while alpha*0.7 > 0.05; the last alpha is taken untested), ocp_nlp_update_variables_sqp
  * (AC/ocp_nlp/ocp_nlp_common.c:3259-3318, full_step_dual = 0).  Returns 1 on a NaN/inf merit value. */
-RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, int nlp_iter, double *alpha_out)
+RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, int nlp_iter, double *alpha_out,
+                               double *cost_new, int *cost_valid)
 {
+    *cost_valid = 0; /* set when the accepted trial point's cost is known from its merit evaluation */
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
     for (int k = lane; k < N * NX; k += GL)
@@ -2079,16 +2145,16 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
         else { const double t1 = 0.5 * (t0 + AR(wlam)[k]); AR(wlam)[k] = t0 > t1 ? t0 : t1; }
     }
     rd_sync();
-    const double m0 = nlp_merit(ch, D, I, AR(ux), I.z);
-    double alpha = 1.0, m1 = 0.0;
+    const double m0 = nlp_merit_lin(D, I, I.z);
+    double alpha = 1.0, m1 = 0.0, c1 = 0.0;
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
         grp_xpay_to(AR(tux), AR(ux), AR(sux), alpha, (N + 1) * NV);
         rd_sync();
-        m1 = nlp_merit(ch, D, I, AR(tux), I.z);
+        m1 = nlp_merit(ch, D, I, AR(tux), I.z, &c1);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
-        if (m1 < m0 && !bad) { accepted = 1; break; }
+        if (m1 < m0 && !bad) { accepted = 1; *cost_new = c1; *cost_valid = 1; break; }
         alpha *= 0.7;
     }
     *alpha_out = alpha;
@@ -2146,13 +2212,15 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
 struct StepOut
 {
     int status, sqp_iter, qp_iter, qp_status;
-    double res[4], alpha;
+    int cost_valid; /* cost holds the NLS cost at the returned iterate (else closed_loop_group evaluates it) */
+    double res[4], alpha, cost;
 };
 
 /* ocp_nlp_sqp_rti, PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
 RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
 {
-    nlp_linearise(ch, D, I, I.z);
+    o.cost = nlp_linearise(ch, D, I, I.z);
+    o.cost_valid = 1; /* cost at the iterate the step starts from; replaced below once the iterate moves */
     const int first = I.flags[0];
     rd_sync();
     int it = 0;
@@ -2162,7 +2230,8 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0; /* rti_log_residuals = 0: the reference reports zeros */
     o.alpha = 0.0;
     if (qs != 0 && qs != 2) { o.status = 4; return; } /* ACADOS_QP_FAILURE, iterate untouched (:609-622) */
-    nlp_line_search_update(ch, D, I, 1, &o.alpha);    /* globalisation status ignored (:627-635) */
+    /* globalisation status ignored (:627-635); a NaN merit leaves the iterate where it was */
+    if (nlp_line_search_update(ch, D, I, 1, &o.alpha, &o.cost, &o.cost_valid)) o.cost_valid = 1;
     if (rd_lane() == 0) I.flags[0] = 0;
     rd_sync();
     o.status = 0;
@@ -2171,7 +2240,7 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
 /* ocp_nlp_sqp (AC/ocp_nlp/ocp_nlp_sqp.c:474-801) with check_termination (:351-443) */
 RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
 {
-    o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0;
+    o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0; o.cost = 0.0; o.cost_valid = 0;
     for (int it = 0; it <= D.max_iter; it++)
     {
         o.sqp_iter = it;
@@ -2179,6 +2248,7 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
         if (it != D.max_iter)
         {
             cost = nlp_linearise(ch, D, I, I.z);
+            o.cost = cost; o.cost_valid = 1; /* every exit before the next update returns this iterate */
             nlp_residuals(D, I, o.res);
         }
         const double *r = o.res;
@@ -2190,7 +2260,7 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
         const int qs = qp_solve(D, I, sm, 0, &qi);
         o.qp_iter += qi; o.qp_status = qs;
         if (qs != 0 && qs != 2) { o.sqp_iter = it + 1; o.status = 4; return; }
-        if (nlp_line_search_update(ch, D, I, it, &o.alpha)) { o.status = 1; return; }
+        if (nlp_line_search_update(ch, D, I, it, &o.alpha, &o.cost, &o.cost_valid)) { o.cost = cost; o.cost_valid = 1; o.status = 1; return; }
     }
     o.status = 2;
 }
@@ -2226,17 +2296,22 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o);
         else solve_sqp(ch, D, I, sm, o);
         const double t_solve = rd_time() - t_begin; /* stands in for get_stats('time_tot') (R/simulator.py:220) */
-        /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679) */
-        double cost = 0.0;
-        for (int i = lane; i < N; i += GL)
+        /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679).  The solve usually knows it
+         * already (linearisation of an iterate it did not move, or the merit evaluation of the accepted trial point). */
+        double cost = o.cost;
+        if (!o.cost_valid)
         {
-            double v[NV], y5[5];
-            load18(AR(ux) + NV * i, v);
-            NoEmit ne;
-            ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
-            cost += stage_cost(par, D.dt, y5, v, v + 12);
+            cost = 0.0;
+            for (int i = lane; i < N; i += GL)
+            {
+                double v[NV], y5[5];
+                load18(AR(ux) + NV * i, v);
+                NoEmit ne;
+                ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
+                cost += stage_cost(par, D.dt, y5, v, v + 12);
+            }
+            cost = grp_sum(cost);
         }
-        cost = grp_sum(cost);
         double zq = 0.0, zqd = 0.0, u = 0.0;
         if (lane < 6)
         {

@@ -193,3 +193,44 @@ def test_terminal_row_batch_matches_oracle(oracle, solver, N, ns):
         if scale[i] is not None and g["status"][-1] == 0:
             xN = r["x"][i, -1]
             assert float(xN @ P @ xN) <= alpha[i] * (1 + 1e-6)
+
+
+@pytest.mark.parametrize("solver,N,ns", [("SQP_RTI", 300, 6), ("SQP_RTI", 200, 8), ("SQP", 200, 2)])
+def test_long_horizons_match_oracle(oracle, solver, N, ns):
+    """The longest horizons of BASELINE configs[3] / configs[4] (N = 200, 300) on a ragged batch of 5."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B = 5
+    surf, z0 = _inputs(o, B, 700 + N)
+    r = _run(rm, B, N, solver, rm.pack_params(B, 0.01, surf=surf), z0, ns)
+    port = o.PortLeg()
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    for i in range(B):
+        g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i], ns, full_traj=True)
+        assert relerr(r["ulog"][i], g["u"]) < RTOL
+        assert np.array_equal(r["slog"][i, :, 0].astype(int), g["status"])
+        assert np.array_equal(r["slog"][i, :, 1].astype(int), g["sqp_iter"])
+        assert np.abs(r["slog"][i, :, 2] - g["qp_iter"]).max() <= 1
+        assert relerr(r["x"][i], g["xtraj"][-1]) < RTOL
+        assert relerr(r["slog"][i, :, 3], g["cost"]) < RTOL
+
+
+def test_active_box_bounds_match_oracle(oracle):
+    """Tight velocity bounds: the u box is active over long stretches of the horizon (degenerate QPs, many IPM iterations)."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 4, 15, 60
+    surf, z0 = _inputs(o, B, 91)
+    qd = np.array([1.2, 2.1, 1.1, 0.3, 0.3, 0.3])
+    r = _run(rm, B, N, "SQP_RTI", rm.pack_params(B, 0.01, surf=surf, qdot_min=-qd, qdot_max=qd), z0, ns)
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    hit = 0.0
+    for i in range(B):
+        g = leg.closed_loop(o.make_problem(N=N, solver_type=o.SQP_RTI, surf=surf[i], qdot_min=-qd, qdot_max=qd), z0[i], ns)
+        assert relerr(r["ulog"][i], g["u"]) < RTOL
+        assert np.array_equal(r["slog"][i, :, 0].astype(int), g["status"])
+        assert np.abs(r["slog"][i, :, 2] - g["qp_iter"]).max() <= 1
+        hit = max(hit, float(np.abs(g["u"] / qd).max()))
+    assert hit > 0.999  # the bounds really are hit

@@ -120,6 +120,8 @@ def test_shard_bounds():
     assert rdist.shard_bounds(2, 4) == [(0, 1), (1, 2), (2, 2), (2, 2)]
     assert rdist.shard_bounds(4096, 8)[-1] == (3584, 4096)
     assert rdist.world() == (0, 1)
+    st = rdist.reduce_group_stats([1.0, 3.0, 10.0], [0, 0, 1], 2)  # single process: local reduction
+    assert list(st["count"]) == [2, 1] and np.allclose(st["mean"], [2.0, 10.0]) and np.allclose(st["var"], [1.0, 0.0])
 
 
 def _gloo_worker(rank, ws, port, q):
@@ -139,6 +141,13 @@ def _gloo_worker(rank, ws, port, q):
         m.sweep("surface_coeffs.a", [0.01 * k for k in range(5)])
         plan = m.plan_groups(m.build_simulators(), ws)
         ok = ok and plan[0]["rank_chunks"] == [[0, 1, 2], [3, 4]]
+        # per-group statistics over all ranks (tracking-error stats per horizon of the horizon sweep)
+        vals, grp = np.arange(n, dtype=float) ** 2, np.array([0, 1, 0, 1, 0, 1, 3])
+        st = rdist.reduce_group_stats(vals[b:e], grp[b:e], 4)
+        ok = ok and list(st["count"]) == [3, 3, 0, 1]
+        ok = ok and np.allclose(st["mean"][[0, 1, 3]], [vals[grp == 0].mean(), vals[grp == 1].mean(), 36.0])
+        ok = ok and np.allclose(st["var"][[0, 1]], [vals[grp == 0].var(), vals[grp == 1].var()])
+        ok = ok and st["min"][1] == 1.0 and st["max"][0] == 16.0 and np.isnan(st["mean"][2])
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()

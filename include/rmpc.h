@@ -93,6 +93,15 @@ int rmpc_reset(rmpc_handle *h, void *stream);
  * Replaces solver.solve() -> <name>_acados_solve -> ocp_nlp_solve (T/acados_ocp_solver.py:468-476). */
 int rmpc_solve(rmpc_handle *h, void *stream);
 
+/* SQP_RTI only: the solve split in the two phases of acados' real-time iteration (opts 'rti_phase',
+ * AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175; T/acados_ocp_solver.py options_set('rti_phase', .)):
+ *   phase 1 PREPARATION  everything that does not depend on x0 (model functions, Gauss-Newton data, gaps, bound residuals)
+ *   phase 2 FEEDBACK     x0-dependent right-hand side from the current "z", QP solve, globalisation, iterate update
+ *   phase 0              both (= rmpc_solve)
+ * Phase 1 followed by phase 2 gives bit-identical results to phase 0 for the same "z" (in acados: equal within the QP tolerance,
+ * tests/test_oracle_port.py); set "z" between the two calls. */
+int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream);
+
 /* nsteps closed-loop steps for all instances entirely on the device:
  *   x0 <- z; solve; u0; z <- RK4(z, u0); log; accumulate tracking-error sums.     R/simulator.py:199-241 */
 int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);

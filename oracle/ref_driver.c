@@ -540,6 +540,22 @@ int rmpc_ref_step(rmpc_ref *c, const double x[12], double u0[6], int *sqp_iter, 
     return status;
 }
 
+/* opts 'rti_phase' (0 preparation + feedback, 1 preparation, 2 feedback; AC/ocp_nlp/ocp_nlp_sqp_rti.c:1140-1170), as
+ * AcadosOcpSolver.options_set('rti_phase', .) does (T/acados_ocp_solver.py:2326-2340). */
+void rmpc_ref_set_rti_phase(rmpc_ref *c, int phase)
+{
+    ocp_nlp_solver_opts_set(c->config, c->opts, "rti_phase", &phase);
+}
+
+/* Preparation phase only: the solve call without touching the stage-0 bounds. */
+int rmpc_ref_prepare(rmpc_ref *c)
+{
+    rmpc_ref_set_rti_phase(c, 1);
+    int status = ocp_nlp_solve(c->solver, c->in, c->out);
+    rmpc_ref_set_rti_phase(c, 0);
+    return status;
+}
+
 void rmpc_ref_get_iterate(rmpc_ref *c, double *xtraj, double *utraj, double *pitraj)
 {
     const int N = c->prob.N;

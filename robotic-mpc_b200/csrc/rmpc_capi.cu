@@ -292,7 +292,20 @@ extern "C" int rmpc_solve(rmpc_handle *h, void *stream)
 {
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve: null handle");
     CU(cudaSetDevice(h->device));
+    h->W.rti_phase = 0;
     return launch_loop(h, 1, 0, (cudaStream_t) stream);
+}
+
+extern "C" int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream)
+{
+    if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: null handle");
+    if (h->D.solver_type != RMPC_SOLVER_SQP_RTI) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: rti_phase is only supported for SQP_RTI");
+    if (phase < 0 || phase > 2) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: phase must be 0, 1 or 2");
+    CU(cudaSetDevice(h->device));
+    h->W.rti_phase = phase;
+    int rc = launch_loop(h, 1, 0, (cudaStream_t) stream);
+    h->W.rti_phase = 0;
+    return rc;
 }
 
 extern "C" int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream)

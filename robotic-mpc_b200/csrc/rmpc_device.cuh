@@ -2217,10 +2217,29 @@ struct StepOut
 };
 
 /* ocp_nlp_sqp_rti, PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
-RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
+/* phase (opts->rti_phase, :1140-1170): 0 = both, 1 = PREPARATION only -- everything that does not depend on x0: model
+ * functions, Gauss-Newton data, dynamics gaps, bound residuals (ocp_nlp_approximate_qp_matrices) --, 2 = FEEDBACK only:
+ * the x0-dependent right-hand side (here: dx0 of the stage-0 equality), QP solve, globalisation and iterate update.
+ * Preparation followed by feedback gives bit-identical results to the combined call for the same x0. */
+RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o, int phase)
 {
-    o.cost = nlp_linearise(ch, D, I, I.z);
+    o.sqp_iter = 0; o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0; o.status = 0;
+    o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0;
+    if (phase != 2)
+    {
+        o.cost = nlp_linearise(ch, D, I, I.z);
+        if (rd_lane() == 0) (I.head + H_LINCOST)[0] = o.cost;
+    }
+    else
+    {
+        /* ocp_nlp_approximate_qp_vectors_sqp: only the stage-0 state equality depends on x0 */
+        const int l = rd_lane();
+        if (l < NX) (I.head + H_DX0)[l] = I.z[l] - AR(ux)[6 + l];
+        rd_sync();
+        o.cost = (I.head + H_LINCOST)[0];
+    }
     o.cost_valid = 1; /* cost at the iterate the step starts from; replaced below once the iterate moves */
+    if (phase == 1) return;
     const int first = I.flags[0];
     rd_sync();
     int it = 0;
@@ -2293,7 +2312,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         StepOut o;
         PAIR_SYNC();
         const double t_begin = rd_time();
-        if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o);
+        if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o, advance ? 0 : W.rti_phase);
         else solve_sqp(ch, D, I, sm, o);
         const double t_solve = rd_time() - t_begin; /* stands in for get_stats('time_tot') (R/simulator.py:220) */
         /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679).  The solve usually knows it

@@ -170,6 +170,7 @@ enum
     H_DX0 = 48,     /* 12: x0 - x_nlp[0] */
     H_G0U = 60,     /* 8 : stage-0 control gradient before the x0 elimination */
     H_QLAMX0 = 68,  /* 24: multipliers of the eliminated equalities recovered from the QP */
+    H_LINCOST = 92, /* 1 : cost at the linearisation point, carried from an RTI preparation phase to its feedback phase */
     RMPC_HEAD = 96
 };
 
@@ -189,6 +190,7 @@ typedef struct
     int nlog;          /* capacity of the logs in steps */
     int step0;         /* index of the first step of this launch */
     const double *pe;  /* [B][RE_COUNT] terminal-set blocks, null: no terminal constraint (the reference MPC as shipped) */
+    int rti_phase;     /* SQP_RTI only: 0 preparation + feedback in one solve, 1 preparation, 2 feedback (acados rti_phase) */
 } RmpcWs;
 
 #ifdef __CUDACC__

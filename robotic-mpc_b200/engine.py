@@ -48,6 +48,7 @@ def load_library() -> C.CDLL:
     lib.rmpc_set.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_reset.argtypes = [vp, vp]
     lib.rmpc_solve.argtypes = [vp, vp]
+    lib.rmpc_solve_rti_phase.argtypes = [vp, ip, vp]
     lib.rmpc_closed_loop.argtypes = [vp, ip, vp]
     lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_steps_done.argtypes = [vp]
@@ -59,7 +60,7 @@ def load_library() -> C.CDLL:
 
 
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
-                    "rmpc_solve", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
+                    "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
                     "rmpc_launch_count"]
 
 
@@ -152,8 +153,12 @@ class Engine:
         self._check(self.lib.rmpc_reset(self.h, self._stream()), "rmpc_reset")
 
     # ------------------------------------------------------------------ compute
-    def solve(self):
-        self._check(self.lib.rmpc_solve(self.h, self._stream()), "rmpc_solve")
+    def solve(self, rti_phase=0):
+        """One solve of every instance; rti_phase 1 / 2 = preparation / feedback only (SQP_RTI, acados 'rti_phase')."""
+        if rti_phase:
+            self._check(self.lib.rmpc_solve_rti_phase(self.h, int(rti_phase), self._stream()), "rmpc_solve_rti_phase")
+        else:
+            self._check(self.lib.rmpc_solve(self.h, self._stream()), "rmpc_solve")
 
     def closed_loop(self, nsteps):
         self._check(self.lib.rmpc_closed_loop(self.h, int(nsteps), self._stream()), "rmpc_closed_loop")

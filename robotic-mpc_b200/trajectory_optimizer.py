@@ -196,6 +196,18 @@ class BatchedSolver:
         self.engine.set_state(np.stack([m.initial_state for m in mpcs]))
         self.engine.reset()
         self._stats = None
+        self.rti_phase = 0
+
+    def options_set(self, field, value):
+        """``AcadosOcpSolver.options_set`` (T/acados_ocp_solver.py:2220-2340) for the one runtime option the hot path has:
+        ``rti_phase`` (0 preparation + feedback, 1 preparation, 2 feedback; SQP_RTI only, like acados)."""
+        if field != "rti_phase":
+            raise NotImplementedError(f"options_set({field!r}): only 'rti_phase' can be changed after creation")
+        if value not in (0, 1, 2):
+            raise ValueError("AcadosOcpSolver.options_set(): argument 'rti_phase' can take only values 0, 1, 2")
+        if value and self.mpcs[0].ocp.solver_options.nlp_solver_type != "SQP_RTI":
+            raise ValueError("AcadosOcpSolver.options_set(): argument 'rti_phase' can take only value 0 for SQP-type solvers")
+        self.rti_phase = int(value)
 
     def view(self, i):
         return SolverView(self, i)
@@ -214,7 +226,7 @@ class BatchedSolver:
         self._stats = None
 
     def solve(self):
-        self.engine.solve()
+        self.engine.solve(rti_phase=self.rti_phase)
         self._stats = self.engine.get("stats").cpu().numpy()
         return self._stats[:, RL["STATUS"]].astype(int)
 
@@ -272,6 +284,9 @@ class SolverView:
         else:
             raise NotImplementedError(f"set(..., {field!r})")
         self.batch._stats = None
+
+    def options_set(self, field, value):
+        self.batch.options_set(field, value)
 
     def solve(self):
         return int(self.batch.solve()[self.i])

@@ -234,3 +234,49 @@ def test_active_box_bounds_match_oracle(oracle):
         assert np.abs(r["slog"][i, :, 2] - g["qp_iter"]).max() <= 1
         hit = max(hit, float(np.abs(g["u"] / qd).max()))
     assert hit > 0.999  # the bounds really are hit
+
+
+def test_rti_phase_split_equals_combined(oracle):
+    """rmpc_solve_rti_phase: preparation (stale x0) + feedback (new x0) == the combined solve, bit for bit; the feedback
+    phase alone is the shorter one (no kinematics / linearisation in it)."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N = 64, 40
+    surf, z0 = _inputs(o, B, 77)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    engs = []
+    for _ in range(2):
+        e = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=1)
+        e.set_params(par)
+        e.set_state(z0)
+        e.reset()
+        engs.append(e)
+    a, b = engs
+    rng = np.random.default_rng(3)
+    z = z0.copy()
+    t_fb, t_all = [], []
+    for k in range(5):
+        b.solve(rti_phase=1)                  # preparation with the previous x0 still in place
+        a.set_state(z)
+        b.set_state(z)
+        a.solve()
+        t_all.append(a.get("stats").cpu().numpy()[:, rm.RL["TIME"]].mean())
+        b.solve(rti_phase=2)
+        sb = b.get("stats").cpu().numpy()
+        t_fb.append(sb[:, rm.RL["TIME"]].mean())
+        sa = a.get("stats").cpu().numpy()
+        assert np.array_equal(sa[:, :4], sb[:, :4])  # status, sqp_iter, qp_iter, cost
+        for s in (0, 1, N // 2, N - 1):
+            assert np.array_equal(a.get("u", s).cpu().numpy(), b.get("u", s).cpu().numpy())
+            assert np.array_equal(a.get("x", s + 1).cpu().numpy(), b.get("x", s + 1).cpu().numpy())
+            assert np.array_equal(a.get("pi", s).cpu().numpy(), b.get("pi", s).cpu().numpy())
+        z = z + 0.01 * rng.standard_normal(z.shape)
+    assert np.mean(t_fb) < np.mean(t_all)
+    with pytest.raises(rm.RmpcError):
+        b.solve(rti_phase=3)
+    e = rm.Engine(2, 5, "SQP", dt=0.01, nlog=1)
+    with pytest.raises(rm.RmpcError):
+        e.solve(rti_phase=1)
+    for e_ in (a, b, e):
+        e_.close()

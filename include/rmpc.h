@@ -57,6 +57,17 @@ typedef struct rmpc_handle rmpc_handle;
  * iterate.  nlog = number of closed-loop steps the on-device logs can hold (0: no per-step logs). */
 int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_handle **out);
 
+/* Kinematic chain of the arm, shared by all instances of the handle (default: the UR10 of R/ur_description/urdf/ur10.urdf,
+ * frame ee_link).  Replaces the pinocchio model the reference builds from a URDF and bakes into the generated functions
+ * (R/loader.py:24-36, R/prediction_model.py:22-31: robot_name 'ur5' -> frame tool0, 'ur10' -> frame ee_link).
+ *   xyzR  HOST pointer, [8][12] doubles = {xyz(3), rotation row-major(9)} of: row 0 the fixed transform between the base
+ *         link and the parent of joint 1, rows 1..6 the <origin> of the six revolute joints, row 7 joint 6 -> end-effector
+ *         frame (fixed joints folded)
+ *   axis  HOST pointer, [6] ints: joint axis 0 = +x, 1 = +y, 2 = +z
+ * Either pointer NULL restores the built-in UR10.  Call it before the first solve; no device work is done here (the table
+ * travels as a kernel argument). */
+int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
+
 /* Replaces <name>_acados_free + _free_capsule. */
 int rmpc_destroy(rmpc_handle *h);
 

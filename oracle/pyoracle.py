@@ -128,6 +128,15 @@ class _Leg:
         f.argtypes = [C.POINTER(RmpcProblem), c_dp, C.c_int, C.POINTER(RmpcTrace)]
         self._closed_loop = f
 
+    def set_chain(self, xyzR=None, axis=None):
+        """Kinematic chain used by this leg's model functions (process-global inside the .so); None restores the UR10.
+        Same table as rmpc_set_chain (include/rmpc.h)."""
+        if xyzR is None:
+            self.lib.ur10_model_set_chain(None, None)
+            return
+        t, a = _np(np.asarray(xyzR).reshape(8, 12)), _np(axis, np.int32)
+        self.lib.ur10_model_set_chain(_dp(t), _ip(a))
+
     def closed_loop(self, prob: RmpcProblem, z0, nsteps: int, full_traj=False) -> dict:
         N = prob.N
         z0 = _np(z0)

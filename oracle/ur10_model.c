@@ -61,35 +61,60 @@ static const int UR10_AXIS[6] = {2, 1, 1, 1, 2, 1}; /* z y y y z y */
 static const double UR10_EE_XYZ[3] = {0.0, 0.0922, 0.0};
 static const double UR10_EE_RPY[3] = {-1.5707963267948966, 0.0, 0.0};
 
+/* Another serial 6R chain (e.g. the reference's UR5 with frame tool0, R/prediction_model.py:28-31,
+ * R/ur_description/urdf/ur5.urdf) as a table of rigid transforms [xyz(3); R row-major(9)]: row 0 = root (fixed joints
+ * between the base link and joint 1's parent), rows 1..6 = joint origins, row 7 = joint 6 -> end-effector frame (fixed
+ * joints folded), plus the joint axes (0 x, 1 y, 2 z).  Process-global: the oracle is test infrastructure and a test
+ * uses one robot at a time.  NULL restores the built-in UR10. */
+static int g_custom = 0;
+static double g_chain[8][12];
+static int g_axis[6];
+void ur10_model_set_chain(const double *xyzR /* [8][12] or NULL */, const int *axis /* [6] */)
+{
+    g_custom = xyzR != NULL;
+    if (!g_custom) return;
+    memcpy(g_chain, xyzR, sizeof(g_chain));
+    memcpy(g_axis, axis, sizeof(g_axis));
+}
+
 /* pinocchio forwardKinematics + updateFramePlacements (R/prediction_model.py:126-132). */
 void ur10_fk(const double q[6], double p_joint[6][3], double a_joint[6][3], double R_ee[9],
              double p_ee[3])
 {
     double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; /* parent orientation */
     double p[3] = {0, 0, 0};                   /* parent origin */
+    if (g_custom)
+    {
+        memcpy(p, g_chain[0], sizeof(p));
+        memcpy(R, g_chain[0] + 3, sizeof(R));
+    }
     for (int j = 0; j < 6; j++)
     {
         double Ro[9], Rj[9], t[3], Rq[9], Rn[9];
-        rpy_to_rot(UR10_RPY[j][0], UR10_RPY[j][1], UR10_RPY[j][2], Ro);
+        if (g_custom) memcpy(Ro, g_chain[1 + j] + 3, sizeof(Ro));
+        else rpy_to_rot(UR10_RPY[j][0], UR10_RPY[j][1], UR10_RPY[j][2], Ro);
         mat3_mul(R, Ro, Rj);         /* joint frame orientation before its own rotation */
-        mat3_vec(R, UR10_XYZ[j], t); /* joint origin */
+        mat3_vec(R, g_custom ? g_chain[1 + j] : UR10_XYZ[j], t); /* joint origin */
         for (int k = 0; k < 3; k++) p[k] += t[k];
         for (int k = 0; k < 3; k++) p_joint[j][k] = p[k];
-        int ax = UR10_AXIS[j];
+        int ax = g_custom ? g_axis[j] : UR10_AXIS[j];
         for (int k = 0; k < 3; k++) a_joint[j][k] = Rj[3 * k + ax]; /* Rj * e_ax */
         double c = cos(q[j]), s = sin(q[j]);
         if (ax == 2) { /* Rz */
             Rq[0] = c; Rq[1] = -s; Rq[2] = 0; Rq[3] = s; Rq[4] = c; Rq[5] = 0; Rq[6] = 0; Rq[7] = 0; Rq[8] = 1;
-        } else { /* Ry */
+        } else if (ax == 1) { /* Ry */
             Rq[0] = c; Rq[1] = 0; Rq[2] = s; Rq[3] = 0; Rq[4] = 1; Rq[5] = 0; Rq[6] = -s; Rq[7] = 0; Rq[8] = c;
+        } else { /* Rx */
+            Rq[0] = 1; Rq[1] = 0; Rq[2] = 0; Rq[3] = 0; Rq[4] = c; Rq[5] = -s; Rq[6] = 0; Rq[7] = s; Rq[8] = c;
         }
         mat3_mul(Rj, Rq, Rn);
         memcpy(R, Rn, sizeof(Rn));
     }
     double Re[9], t[3];
-    rpy_to_rot(UR10_EE_RPY[0], UR10_EE_RPY[1], UR10_EE_RPY[2], Re);
+    if (g_custom) memcpy(Re, g_chain[7] + 3, sizeof(Re));
+    else rpy_to_rot(UR10_EE_RPY[0], UR10_EE_RPY[1], UR10_EE_RPY[2], Re);
     mat3_mul(R, Re, R_ee);
-    mat3_vec(R, UR10_EE_XYZ, t);
+    mat3_vec(R, g_custom ? g_chain[7] : UR10_EE_XYZ, t);
     for (int k = 0; k < 3; k++) p_ee[k] = p[k] + t[k];
 }
 

@@ -45,6 +45,10 @@ typedef struct
 void ur10_fk(const double q[6], double p_joint[6][3], double a_joint[6][3], double R_ee[9],
              double p_ee[3]);
 
+/* Replace the built-in UR10 chain by a table of rigid transforms [xyz(3); R row-major(9)] x 8 (root, joints 1..6, joint 6 ->
+ * end-effector frame) and joint axes (0 x, 1 y, 2 z); NULL restores UR10.  Process-global (test infrastructure). */
+void ur10_model_set_chain(const double *xyzR, const int *axis);
+
 /* pinocchio computeFrameJacobian(..., ee_link, WORLD): J (row-major 6x6), column j = [p_j x a_j ; a_j]. */
 void ur10_jacobian_world(const double q[6], double J[36]);
 

@@ -6,8 +6,8 @@ The directory name contains a hyphen (it is the repository's package name); impo
 from .params import RK, RL, RP, RS, pack_params  # noqa: F401
 from .engine import SQP, SQP_RTI, Engine, RmpcError, load_library  # noqa: F401
 from .surface import Surface  # noqa: F401,E402
-from .prediction_model import SixDofRobot  # noqa: F401,E402
+from .prediction_model import SixDofRobot, UrdfLoader  # noqa: F401,E402
 from .simulation_model import Robot  # noqa: F401,E402
 from .trajectory_optimizer import MPC, BatchedSolver, SolverOptions, SolverView  # noqa: F401,E402
 from .simulator import SimulationManager, Simulator, run_batch, summary_from_row  # noqa: F401,E402
-from . import terminal_constraint  # noqa: F401,E402
+from . import robots, terminal_constraint  # noqa: F401,E402

@@ -209,6 +209,18 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     return 0;
 }
 
+extern "C" int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis)
+{
+    if (!h) return fail(h, RMPC_EINVAL, "rmpc_set_chain: null handle");
+    if (!xyzR || !axis) { rmpc_chain_init(&h->ch); return 0; } /* back to the built-in UR10 */
+    for (int k = 0; k < 8 * 12; k++)
+        if (!std::isfinite(xyzR[k])) return fail(h, RMPC_EINVAL, "rmpc_set_chain: non-finite entry in the chain table");
+    RmpcChain ch;
+    if (rmpc_chain_from_table(&ch, xyzR, axis) != 0) return fail(h, RMPC_EINVAL, "rmpc_set_chain: joint axes must be 0 (x), 1 (y) or 2 (z)");
+    h->ch = ch;
+    return 0;
+}
+
 static int strided(rmpc_handle *h, double *packed, double *strided_base, long stride, long off, int n, int gather, cudaStream_t s)
 {
     rmpc_strided_copy_kernel<<<grid_for((long) h->D.B * n), 256, 0, s>>>(packed, strided_base, h->D.B, stride, off, n, gather);

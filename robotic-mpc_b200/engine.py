@@ -49,6 +49,7 @@ def load_library() -> C.CDLL:
     lib.rmpc_reset.argtypes = [vp, vp]
     lib.rmpc_solve.argtypes = [vp, vp]
     lib.rmpc_solve_rti_phase.argtypes = [vp, ip, vp]
+    lib.rmpc_set_chain.argtypes = [vp, dp, dp]
     lib.rmpc_closed_loop.argtypes = [vp, ip, vp]
     lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_steps_done.argtypes = [vp]
@@ -61,7 +62,7 @@ def load_library() -> C.CDLL:
 
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
                     "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
-                    "rmpc_launch_count"]
+                    "rmpc_launch_count", "rmpc_set_chain"]
 
 
 class RmpcError(RuntimeError):
@@ -148,6 +149,19 @@ class Engine:
         lh = -alpha if lh is None else np.broadcast_to(np.asarray(lh, float), (self.B,))
         blk = np.concatenate([P.reshape(self.B, 144), lh[:, None], alpha[:, None]], axis=1)
         self.set("term", blk)
+
+    def set_chain(self, xyzR=None, axis=None):
+        """Kinematic chain of the arm for every instance: a ``robots.chain_table`` / ``robots.chain_from_urdf`` pair, or a
+        robot name ('ur10', 'ur5'); None restores the built-in UR10 (R/loader.py:24-36, R/prediction_model.py:22-31)."""
+        if isinstance(xyzR, str):
+            from .robots import chain_table
+            xyzR, axis = chain_table(xyzR)
+        if xyzR is None or axis is None:
+            self._check(self.lib.rmpc_set_chain(self.h, None, None), "rmpc_set_chain")
+            return
+        t = np.ascontiguousarray(np.asarray(xyzR, dtype=np.float64).reshape(8, 12))
+        a = np.ascontiguousarray(np.asarray(axis, dtype=np.int32).reshape(6))
+        self._check(self.lib.rmpc_set_chain(self.h, t.ctypes.data_as(C.c_void_p), a.ctypes.data_as(C.c_void_p)), "rmpc_set_chain")
 
     def reset(self):
         self._check(self.lib.rmpc_reset(self.h, self._stream()), "rmpc_reset")

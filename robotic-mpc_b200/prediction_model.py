@@ -1,19 +1,41 @@
 """Prediction-model constants -- host-side mirror of the data ``R/prediction_model.py`` (class ``SixDofRobot``) hands to
 the OCP: sample time, joint bandwidths, the exact-ZOH matrices ``Ad, Bd`` (``R/prediction_model.py:87-115``) and the
 task-frame offset (``:9``).  The symbolic FK / Jacobian / output functions of the reference are hand-written device
-code (``csrc/rmpc_device.cuh: ur10_task``); only ``robot_name == 'ur10'`` (frame ``ee_link``) is built in."""
+code (``csrc/rmpc_device.cuh: ur10_task``) over a constant chain table: 'ur10' (frame ``ee_link``) and 'ur5' (frame ``tool0``)
+are built in (``R/prediction_model.py:28-31``), any other serial 6R arm comes in through ``UrdfLoader`` / ``robots.chain_from_urdf``."""
 from __future__ import annotations
 
 import math
 
 import numpy as np
 
+from . import robots
+
+
+class UrdfLoader:
+    """Mirror of ``R/loader.py:5-36`` without pinocchio: resolves the chain table of a robot.  ``UrdfLoader('ur5')`` /
+    ``('ur10')`` use the built-in tables; ``UrdfLoader(name, urdf_path=..., ee_frame=...)`` reads a serial 6R chain from a URDF
+    file (axes along +x / +y / +z).  Meshes, collision and visual models are presentation and are not loaded."""
+
+    def __init__(self, robot_name, urdf_path=None, ee_frame=None, base_link=None):
+        self.name = robot_name
+        if urdf_path is None:
+            self.chain = robots.chain_table(robot_name)
+            self.ee_frame = {"ur5": "tool0", "ur10": "ee_link"}[str(robot_name).lower()]
+        else:
+            if ee_frame is None:
+                raise ValueError("UrdfLoader: ee_frame is needed with urdf_path")
+            self.chain = robots.chain_from_urdf(urdf_path, ee_frame, base_link=base_link)
+            self.ee_frame = ee_frame
+
 
 class SixDofRobot:
     def __init__(self, urdf_loader=None, Ts=0.01, Wcv=None, translation_ee_t=(0.0, 0.0, 0.1), robot_name="ur10"):
-        name = getattr(urdf_loader, "name", robot_name) if urdf_loader is not None else robot_name
-        if str(name).lower() != "ur10":
-            raise NotImplementedError(f"robot {name!r}: only the UR10 chain is compiled into the kernels (SURVEY.md 8(f) #4)")
+        if urdf_loader is None:
+            urdf_loader = UrdfLoader(robot_name)  # ValueError for a name without a built-in table
+        self.robot_name = urdf_loader.name
+        xyzR, axis = urdf_loader.chain
+        self.chain = (np.ascontiguousarray(xyzR, dtype=float).reshape(8, 12), np.ascontiguousarray(axis, dtype=np.int32).reshape(6))
         self.n_dof = 6
         self.Ts = float(Ts)
         self.Wcv = np.full(6, 200.0) if Wcv is None else np.asarray(Wcv, dtype=float).reshape(6)
@@ -27,3 +49,11 @@ class SixDofRobot:
         I, Z = np.eye(6), np.zeros((6, 6))
         self.Ad = np.block([[I, np.diag(a12)], [Z, np.diag(a22)]])
         self.Bd = np.vstack([Ts * I - np.diag(a12), np.diag(1.0 - a22)])
+
+    def chain_key(self):
+        """Hashable identity of the kinematic chain (instances of one batched launch share it)."""
+        return (self.chain[0].tobytes(), self.chain[1].tobytes())
+
+    def forward_kinematics(self, q):
+        """(p, R) of the end-effector frame at joint angles q -- host-side check of the table (R/prediction_model.py:126-132)."""
+        return robots.forward_kinematics(self.chain[0], self.chain[1], np.asarray(q, float))

@@ -26,7 +26,7 @@ from .params import RK, RL, RS
 from .prediction_model import SixDofRobot
 from .simulation_model import Robot
 from .surface import Surface
-from .trajectory_optimizer import MPC, bind_terminal
+from .trajectory_optimizer import MPC, bind_chain, bind_terminal
 
 SUMMARY_KEYS = ("rmse_e1", "rmse_e2", "rmse_e3", "rmse_e4", "rmse_e5", "itse_e1", "itse_e2", "itse_e3", "itse_e4",
                 "itse_e5", "weighted_rmse", "total_sqp_iterations", "avg_sqp_iterations", "num_failures",
@@ -255,6 +255,7 @@ def run_batch(sims, device=0, keep_logs=True):
     try:
         par = np.stack([s.mpc.param_row() for s in sims])
         z0 = np.stack([s.initial_state for s in sims])
+        bind_chain(eng, [s.mpc for s in sims])
         bind_terminal(eng, [s.mpc for s in sims])
         if keep_logs:
             eng.set_params(par)

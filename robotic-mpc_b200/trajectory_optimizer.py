@@ -81,6 +81,7 @@ class MPC:
     def __init__(self, surface, initial_state, model, N_horizon, Tf, qmin, qmax, dq_min, dq_max, w_u, w_qddot,
                  px_ref=0.40, vy_ref=0.01, Ts=None, wcv=None, terminal_constraint=None):
         self.surface = surface
+        self.model = model
         self.surface_pos_world = surface.get_position() if hasattr(surface, "get_position") else None
         self.surface_rpy_world = surface.get_orientation_rpy() if hasattr(surface, "get_orientation_rpy") else None
         self.N_horizon = int(N_horizon)
@@ -147,7 +148,8 @@ class MPC:
 
     def static_key(self):
         o = self.ocp.solver_options
-        return (self.N_horizon, round(self.Tf / self.N_horizon, 15), self.terminal is not None) + o.static_key()
+        chain = self.model.chain_key() if hasattr(self.model, "chain_key") else None
+        return (self.N_horizon, round(self.Tf / self.N_horizon, 15), self.terminal is not None, chain) + o.static_key()
 
     def finalize_solver(self, device=0):
         """Creates the solver handle (a batch of one).  ``SimulationManager.run_all`` binds many ``MPC`` objects to one
@@ -156,6 +158,13 @@ class MPC:
         bs = BatchedSolver([self], device=device)
         self.solver = bs.view(0)
         return self
+
+
+def bind_chain(engine, mpcs):
+    """Hand the kinematic chain of a batch to the engine (part of the static key: one chain per batch)."""
+    chain = getattr(mpcs[0].model, "chain", None)
+    if chain is not None:
+        engine.set_chain(*chain)
 
 
 def bind_terminal(engine, mpcs):
@@ -192,6 +201,7 @@ class BatchedSolver:
                              tol=[o.nlp_solver_tol_stat, o.nlp_solver_tol_eq, o.nlp_solver_tol_ineq, o.nlp_solver_tol_comp],
                              qp_tol=o.qp_tol, plant_dt=mpcs[0].Ts)
         self.engine.set_params(np.stack([m.param_row() for m in mpcs]))
+        bind_chain(self.engine, mpcs)
         bind_terminal(self.engine, mpcs)
         self.engine.set_state(np.stack([m.initial_state for m in mpcs]))
         self.engine.reset()

@@ -35,3 +35,24 @@ def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, 
                              out["summary"].ctypes.data_as(dp), out["flags"].ctypes.data_as(C.POINTER(C.c_int)),
                              C.c_ulonglong(seed))
     return out
+
+
+def set_chain(xyzR=None, axis=None):
+    """Process-global chain of the emulated device code (same table as rmpc_set_chain); None restores the UR10."""
+    lib = C.CDLL(str(SO))
+    if xyzR is None:
+        lib.rmpc_emu_set_chain(None, None)
+        return
+    t = np.ascontiguousarray(np.asarray(xyzR, np.float64).reshape(8, 12))
+    a = np.ascontiguousarray(axis, np.int32)
+    assert lib.rmpc_emu_set_chain(t.ctypes.data_as(C.POINTER(C.c_double)), a.ctypes.data_as(C.POINTER(C.c_int))) == 0
+
+
+def plant_record(par, z):
+    """(rec [28] = RK_* record, y5 [5] task outputs) of one state through the emulated device FK."""
+    lib = C.CDLL(str(SO))
+    par, z = np.ascontiguousarray(par, np.float64), np.ascontiguousarray(z, np.float64)
+    rec, y5 = np.zeros(28), np.zeros(5)
+    dp = C.POINTER(C.c_double)
+    lib.rmpc_emu_plant_record(par.ctypes.data_as(dp), z.ctypes.data_as(dp), rec.ctypes.data_as(dp), y5.ctypes.data_as(dp))
+    return rec, y5

@@ -25,7 +25,38 @@ void body(void *p, int)
     Job *j = (Job *) p;
     closed_loop_group(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
 }
+bool g_custom_chain = false;
+RmpcChain g_chain;
+void current_chain(RmpcChain *ch)
+{
+    if (g_custom_chain) *ch = g_chain;
+    else rmpc_chain_init(ch);
+}
 }  // namespace
+
+/* same table as rmpc_set_chain (include/rmpc.h), process-global here; null restores the UR10 */
+extern "C" int rmpc_emu_set_chain(const double *xyzR, const int *axis)
+{
+    if (!xyzR || !axis) { g_custom_chain = false; return 0; }
+    if (rmpc_chain_from_table(&g_chain, xyzR, axis) != 0) return -1;
+    g_custom_chain = true;
+    return 0;
+}
+
+/* the per-sample plant record (RK_*, 28 doubles) and the task outputs y5 of one state, with the current chain */
+extern "C" int rmpc_emu_plant_record(const double *par, const double *z, double *rec, double *y5)
+{
+    RmpcChain ch;
+    current_chain(&ch);
+    double e[5];
+    ur10_plant_record<true>(ch, par, z, z + 6, e, rec);
+    if (y5)
+    {
+        NoEmit ne;
+        ur10_task<false>(ch, par, z, z + 6, y5, ne);
+    }
+    return 0;
+}
 
 extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, const double *pe, const double *z0, int nsteps,
                                          double *zlog, double *ulog, double *slog, double *summary, int *flags_out,
@@ -44,7 +75,7 @@ extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, c
 {
     const long B = D->B, S = D->N + 1;
     RmpcChain ch;
-    rmpc_chain_init(&ch);
+    current_chain(&ch);
     RmpcWs W;
     memset(&W, 0, sizeof(W));
     std::vector<double *> owned;

@@ -23,15 +23,17 @@ def _inputs(o, B, seed):
     return surf, z0
 
 
-def _run(rm, B, N, solver, par, z0, ns, term=None):
+def _run(rm, B, N, solver, par, z0, ns, term=None, chain=None):
     eng = rm.Engine(B, N, solver, dt=0.01, nlog=ns)
     eng.set_params(par)
+    if chain is not None:
+        eng.set_chain(*chain)
     if term is not None:
         eng.set_terminal(*term)
     eng.set_state(z0)
     eng.reset()
     eng.closed_loop(ns)
-    out = {k: eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog", "summary", "flags")}
+    out = {k: eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog", "summary", "flags", "plog")}
     out["x"] = np.stack([eng.get("x", s).cpu().numpy() for s in range(N + 1)], 1)
     out["u"] = np.stack([eng.get("u", s).cpu().numpy() for s in range(N)], 1)
     out["pi"] = np.stack([eng.get("pi", s).cpu().numpy() for s in range(N)], 1)
@@ -280,3 +282,77 @@ def test_rti_phase_split_equals_combined(oracle):
         e.solve(rti_phase=1)
     for e_ in (a, b, e):
         e_.close()
+
+
+ROBOT_GOLD = GOLD / "robots"
+
+
+@pytest.mark.parametrize("case", sorted(p.stem for p in ROBOT_GOLD.glob("*.npz")))
+def test_ur5_chain_golden_and_batch(oracle, case):
+    """rmpc_set_chain: the UR5 of R/ur_description/urdf/ur5.urdf (frame tool0) through the C ABI against
+    the vectors of the compiled acados reference, inside a batch whose other instances (perturbed) are checked against
+    the oracle run on the same chain; the plant log reports the pose of tool0."""
+    import robotic_mpc_b200 as rm
+    import robotic_mpc_b200.robots as rb
+
+    o = oracle
+    g = np.load(ROBOT_GOLD / f"{case}.npz")
+    N, ns, st = int(g["N"]), int(g["nsteps"]), int(g["solver_type"])
+    solver = "SQP_RTI" if st == o.SQP_RTI else "SQP"
+    B = 5
+    rng = np.random.default_rng(7)
+    surf = np.tile(g["surf"], (B, 1))
+    surf[1:] += 0.005 * rng.standard_normal((B - 1, 6))
+    z0 = np.tile(g["z0"], (B, 1))
+    z0[1:] += rng.uniform(-0.03, 0.03, (B - 1, 12))
+    term, tkw = None, {}
+    if "term_P" in g.files:
+        term = (g["term_P"], float(g["term_alpha"]), float(g["term_lh"]))
+        tkw = dict(term_P=g["term_P"], term_alpha=term[1], term_lh=term[2])
+    chain = rb.chain_table("ur5")
+    par = rm.pack_params(B, 0.01, surf=surf)
+    r = _run(rm, B, N, solver, par, z0, ns, term=term, chain=chain)
+    assert relerr(r["ulog"][0], g["u"]) < RTOL and relerr(r["zlog"][0], g["z"]) < RTOL
+    assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"])
+    assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"])
+    assert relerr(r["slog"][0, :, 3], g["cost"]) < RTOL
+    assert relerr(r["x"][0], g["xtraj"][-1]) < RTOL and relerr(r["u"][0], g["utraj"][-1]) < RTOL
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    leg.set_chain(*chain)
+    try:
+        for i in range(1, B):
+            ref = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i], **tkw), z0[i], ns)
+            assert relerr(r["ulog"][i], ref["u"]) < RTOL and relerr(r["zlog"][i], ref["z"]) < RTOL
+            assert np.array_equal(r["slog"][i, :, 1].astype(int), ref["sqp_iter"])
+    finally:
+        leg.set_chain(None)
+    for i in (0, B - 1):
+        for k in (0, ns):
+            p, R = rb.forward_kinematics(chain[0], chain[1], r["zlog"][i, k, :6])
+            assert np.abs(r["plog"][i, k, rm.RK["POSE"]:rm.RK["POSE"] + 3] - p).max() < 1e-12
+            assert np.abs(r["plog"][i, k, rm.RK["POSE"] + 3:rm.RK["POSE"] + 12].reshape(3, 3) - R).max() < 1e-12
+
+
+def test_set_chain_default_is_ur10_and_resets(oracle):
+    """rmpc_set_chain with the UR10 table of robots.py reproduces the built-in chain (to rounding of the table); NULL restores
+    the built-in one bit for bit."""
+    import robotic_mpc_b200 as rm
+    import robotic_mpc_b200.robots as rb
+
+    B, N, ns = 4, 10, 15
+    surf, z0 = _inputs(oracle, B, 9)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    a = _run(rm, B, N, "SQP_RTI", par, z0, ns)
+    b = _run(rm, B, N, "SQP_RTI", par, z0, ns, chain=rb.chain_table("ur10"))
+    assert np.abs(a["ulog"] - b["ulog"]).max() < 1e-10 and np.abs(a["zlog"] - b["zlog"]).max() < 1e-10
+    eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=ns)
+    eng.set_chain("ur5")
+    eng.set_chain(None)
+    eng.set_params(par)
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    assert np.array_equal(eng.get("ulog").cpu().numpy(), a["ulog"])
+    with pytest.raises(rm.RmpcError):
+        eng.set_chain(rb.chain_table("ur5")[0], [0, 1, 2, 3, 0, 0])
+    eng.close()

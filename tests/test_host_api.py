@@ -74,8 +74,10 @@ def test_solver_options_handling(capsys):
     assert "Unknown solver option 'bogus_option'" in capsys.readouterr().out  # R/simulator.py:129-135
     with pytest.raises(NotImplementedError):
         rm.Simulator(**{**BASE, "solver_options": {"qp_solver": "FULL_CONDENSING_QPOASES"}})
-    with pytest.raises(NotImplementedError):
-        rm.Simulator(**{**BASE, "robot_name": "ur5"})
+    with pytest.raises(ValueError):
+        rm.Simulator(**{**BASE, "robot_name": "ur3"})  # no built-in chain table
+    s5 = rm.Simulator(**{**BASE, "robot_name": "ur5"})
+    assert s5.static_key() != s.static_key()  # another chain = another batched launch
 
 
 def test_plan_groups_by_static_shape_and_rank():

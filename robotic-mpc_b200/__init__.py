@@ -9,5 +9,5 @@ from .surface import Surface  # noqa: F401,E402
 from .prediction_model import SixDofRobot, UrdfLoader  # noqa: F401,E402
 from .simulation_model import Robot  # noqa: F401,E402
 from .trajectory_optimizer import MPC, BatchedSolver, SolverOptions, SolverView  # noqa: F401,E402
-from .simulator import SimulationManager, Simulator, run_batch, summary_from_row  # noqa: F401,E402
+from .simulator import SimulationManager, Simulator, run_batch, save_result_npz, summary_from_row  # noqa: F401,E402
 from . import robots, terminal_constraint  # noqa: F401,E402

@@ -217,6 +217,29 @@ class Simulator:
         return out
 
 
+def _flatten_arrays(prefix, d, out):
+    """Numeric leaves of a (nested) result dict as a flat {name: ndarray} for numpy.savez."""
+    for k, v in d.items():
+        key = f"{prefix}{k}"
+        if isinstance(v, dict):
+            _flatten_arrays(key + ".", v, out)
+        elif v is not None:
+            a = np.asarray(v)
+            if a.dtype.kind in "fiub":
+                out[key] = a
+
+
+def save_result_npz(path, result):
+    """One simulation's ``get_data()`` / ``get_analysis()`` / ``get_summary()`` arrays (the inputs of the reference's plot
+    pipeline, R/main.py:84-342) as one ``.npz``: keys ``data.<k>``, ``analysis.<k>`` (nested dicts dotted), ``summary.<k>``."""
+    out = {}
+    for part in ("data", "analysis", "summary"):
+        if result.get(part) is not None:
+            _flatten_arrays(part + ".", result[part], out)
+    np.savez_compressed(path, name=np.array(result.get("name", "")), **out)
+    return sorted(out)
+
+
 def summary_from_row(row, w_task, nsteps=None):
     """get_summary() keys from a device summary row (RS_*): RMSE = sqrt(SSE / samples), ITSE as accumulated."""
     row = np.asarray(row, float)
@@ -337,6 +360,48 @@ class SimulationManager:
 
     def clear(self):
         self.simulations = []
+
+    # ------------------------------------------------------------------ results surface
+    def summary_table(self, results):
+        """One row per simulation: ``name``, the scalar entries of its queued config (nested ``solver_options`` /
+        ``surface_coeffs`` dotted) and the 20 ``get_summary()`` scalars (R/simulator.py:509-547) as a pandas DataFrame --
+        the table the comparison plots of R/main.py are drawn from."""
+        import pandas as pd
+
+        rows = []
+        for spec, res in zip(self.simulations, results):
+            row = {"name": res["name"]}
+            for k, v in spec["config"].items():
+                if isinstance(v, (list, tuple)) and len(v) == 1 and isinstance(v[0], dict):
+                    v = v[0]
+                if isinstance(v, dict):
+                    row.update({f"{k}.{kk}": vv for kk, vv in v.items() if np.isscalar(vv)})
+                elif np.isscalar(v):
+                    row[k] = v
+            row.update(res["summary"])
+            rows.append(row)
+        return pd.DataFrame(rows)
+
+    def export(self, directory, results, arrays=True):
+        """Write ``summaries.parquet`` (+ ``summaries.csv``) and, with ``arrays``, one ``<index>_<name>.npz`` per simulation
+        whose logs are on this rank (``save_result_npz``).  Returns the list of files written."""
+        from pathlib import Path
+
+        d = Path(directory)
+        d.mkdir(parents=True, exist_ok=True)
+        table = self.summary_table(results)
+        files = [d / "summaries.parquet", d / "summaries.csv"]
+        table.to_parquet(files[0], index=False)
+        table.to_csv(files[1], index=False)
+        if arrays:
+            for i, res in enumerate(results):
+                if res.get("data") is None:
+                    continue
+                safe = "".join(c if (c.isalnum() or c in "-_.=") else "_" for c in str(res["name"]))[:80]
+                f = d / f"{i:05d}_{safe}.npz"
+                save_result_npz(f, res)
+                files.append(f)
+        return files
 
     # ------------------------------------------------------------------ planning (pure host logic)
     def build_simulators(self):

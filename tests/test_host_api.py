@@ -171,3 +171,43 @@ def test_two_rank_gather_on_gloo():
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_results_export_table_and_arrays(tmp_path):
+    """summary table (parquet / csv) and per-simulation arrays (.npz) of a run_all() result list, built
+    here from synthetic device logs (no GPU): keys are those of R/simulator.py:450-547."""
+    import pandas as pd
+
+    m = rm.SimulationManager(BASE)
+    m.grid_search({"prediction_horizon": [20, 30], "solver_options.nlp_solver_type": ["SQP", "SQP_RTI"]},
+                  surface_coeff_sets=[{"a": -0.1, "b": 0.1, "c": 0.0, "d": 0.0, "e": 0.0, "f": 0.0}])
+    sims = m.build_simulators()
+    rng = np.random.default_rng(0)
+    results = []
+    for i, s in enumerate(sims):
+        ns = s.Nsim
+        row = np.abs(rng.standard_normal(rm.RS["COUNT"]))
+        row[rm.RS["NSAMPLES"]] = ns + 1
+        if i % 2 == 0:  # logs on this rank
+            slog = np.abs(rng.standard_normal((ns, rm.RL["COUNT"])))
+            slog[:, 0] = 0
+            s._load_logs(rng.standard_normal((ns + 1, 12)), rng.standard_normal((ns, 6)), slog,
+                         rng.standard_normal((ns + 1, rm.RK["COUNT"])), row)
+            results.append({"name": s.name, "simulator": s, "data": s.get_data(), "analysis": s.get_analysis(), "summary": s.get_summary()})
+        else:           # solved by another rank: summary only
+            results.append({"name": s.name, "simulator": None, "data": None, "analysis": None,
+                            "summary": rm.summary_from_row(row, s.mpc.task_weights(), ns)})
+    table = m.summary_table(results)
+    assert len(table) == 4 and {"name", "prediction_horizon", "solver_options.nlp_solver_type", "surface_coeffs.a", "rmse_e1",
+                                "weighted_rmse", "num_failures", "total_computation_time"} <= set(table.columns)
+    assert list(table["prediction_horizon"]) == [20, 20, 30, 30]
+    files = m.export(tmp_path / "out", results)
+    assert [f.name for f in files[:2]] == ["summaries.parquet", "summaries.csv"] and len(files) == 4
+    back = pd.read_parquet(files[0])
+    assert np.allclose(back["rmse_e3"], table["rmse_e3"]) and list(back["name"]) == [r["name"] for r in results]
+    z = np.load(files[2])
+    d = results[0]["data"]
+    assert np.array_equal(z["data.q"], d["q"]) and np.array_equal(z["data.ee_pose"], d["ee_pose"]) and z["data.N"] == 20
+    assert np.array_equal(z["analysis.e1"], results[0]["analysis"]["e1"])
+    assert np.isclose(z["analysis.rmse.e2"], results[0]["analysis"]["rmse"]["e2"])
+    assert np.isclose(z["summary.weighted_rmse"], results[0]["summary"]["weighted_rmse"])

@@ -111,9 +111,11 @@ RD double grp_sum(double v)
     for (int m = GL / 2; m; m >>= 1) v += rd_shfl_xor(v, m);
     return v;
 }
+/* NaN-propagating, so that every lane of the group ends with the same value whatever the data (a comparison-only butterfly
+ * leaves lanes disagreeing once a NaN is involved, and the callers branch on the result assuming it is uniform) */
 RD double grp_max(double v)
 {
-    for (int m = GL / 2; m; m >>= 1) { double o = rd_shfl_xor(v, m); v = o > v ? o : v; }
+    for (int m = GL / 2; m; m >>= 1) { double o = rd_shfl_xor(v, m); v = (o > v || o != o) ? o : v; }
     return v;
 }
 

@@ -28,13 +28,13 @@ _G = {}
 def _worker(job):
     from oracle import pyoracle as o
 
-    idx, N, st, ns, chain = job
+    idx, N, st, ns, chain, term = job
     leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
     if chain is not None:
         leg.set_chain(*chain)
     out = []
     for i in idx:
-        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i]), _G["z0"][i], ns)
+        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i], **term), _G["z0"][i], ns)
         out.append((i, r["u"], r["z"], r["status"], r["sqp_iter"], r["qp_iter"]))
     return out
 
@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--solver", default="SQP_RTI")
     ap.add_argument("--robot", default="ur10")
     ap.add_argument("--seed", type=int, default=44)
+    ap.add_argument("--term-rho", type=float, default=0.0, help="> 0: terminal ellipsoid of the LQR with R = rho I (BASELINE configs[3])")
     a = ap.parse_args()
     B, N, K = a.batch, a.horizon, a.steps
     surf, z0 = workload(B, a.seed)
@@ -62,17 +63,27 @@ def main():
     eng = rm.Engine(B, N, a.solver, dt=0.01, nlog=K)
     if chain is not None:
         eng.set_chain(*chain)
+    term = {}
+    if a.term_rho > 0:
+        P, alpha = rm.terminal_constraint.default_terminal_set(wcv=200.0, Ts=0.01, rho=a.term_rho)
+        term = dict(term_P=P, term_alpha=alpha, term_lh=-alpha)
+        eng.set_terminal(P, alpha)
     eng.set_params(rm.pack_params(B, 0.01, surf=surf))
     eng.set_state(z0)
     eng.reset()
-    eng.closed_loop(K)
     torch.cuda.synchronize()
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    g0.record()
+    eng.closed_loop(K)
+    g1.record()
+    torch.cuda.synchronize()
+    gpu_s = g0.elapsed_time(g1) * 1e-3
     ulog, zlog, slog = (eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog"))
     eng.close()
     _G["surf"], _G["z0"] = surf, z0
     cores = os.cpu_count() or 1
     st = o.SQP_RTI if a.solver == "SQP_RTI" else o.SQP
-    jobs = [(list(range(c, B, cores * 4)), N, st, K, chain) for c in range(cores * 4)]
+    jobs = [(list(range(c, B, cores * 4)), N, st, K, chain, term) for c in range(cores * 4)]
     from multiprocessing import get_context
 
     t0 = time.time()
@@ -92,13 +103,13 @@ def main():
         qp_pm1 += int(d.max() <= 1)
     print(json.dumps({
         "what": "CUDA path vs compiled reference, closed loop, every instance", "oracle": "reference" if o.REF_SO.exists() else "port",
-        "robot": a.robot, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
+        "robot": a.robot, "terminal_rho": a.term_rho, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
         "u_relerr": {"max": float(eu.max()), "p99": float(np.percentile(eu, 99)), "median": float(np.median(eu))},
         "z_relerr": {"max": float(ez.max()), "p99": float(np.percentile(ez, 99)), "median": float(np.median(ez))},
         "instances_over_1e-6": int((np.maximum(eu, ez) > 1e-6).sum()),
         "status_sequences_equal": same_status, "sqp_iter_sequences_equal": same_sqp, "qp_iter_sequences_equal": same_qp,
         "qp_iter_sequences_within_1": qp_pm1, "failures_gpu": int((slog[:, :, 0] != 0).sum()),
-        "cpu_cores": cores, "cpu_seconds": cpu_s}))
+        "cpu_cores": cores, "cpu_seconds": cpu_s, "gpu_seconds": gpu_s}))
 
 
 if __name__ == "__main__":

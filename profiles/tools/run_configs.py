@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Side measurements of the BASELINE.json configs that are NOT the bench line (bench.py = configs[2]):
 
+  config1   B = 1, N = 20, SQP_RTI, flat surface: single-instance step latency on the device beside one host core
   config2   README grid search, 24 option tuples x 256 random surfaces = 6144 instances, 600 closed-loop steps, through
             SimulationManager.grid_search / run_all (one batched run per (N, solver) group), summaries only
   config4   full SQP, N = 200, terminal ellipsoid, B instances: K closed-loop steps, each one full SQP solve of every
@@ -8,7 +9,7 @@
   config5   horizon sweep N in {10, 50, 100, 200, 300}, SQP_RTI, 600 steps: this GPU's 1/8 share of the 65536 instances
             (8192 instances, 1638/1639 per horizon) unless --batch says otherwise
 
-    python profiles/tools/run_configs.py config2|config4|config5 [--batch B] [--steps K]
+    python profiles/tools/run_configs.py config1|config2|config4|config5 [--batch B] [--steps K]
 
 Prints one JSON line per measurement.  Needs a GPU.
 """
@@ -33,6 +34,50 @@ def workload(B, seed):
     qd0 = np.array([1.0, 2.0, 1.0, 0.0, 0.0, 0.0])
     z0 = np.concatenate([q0 + rng.uniform(-0.05, 0.05, (B, 6)), qd0 + rng.uniform(-0.1, 0.1, (B, 6))], axis=1)
     return surf, np.ascontiguousarray(z0)
+
+
+def config1(args):
+    """B = 1, N = 20, SQP_RTI, flat surface, README initial state, 600 steps: per-step latency of ONE instance on the device
+    (a group of 16 lanes on one SM; everything else idle) beside the compiled reference on one host core."""
+    import torch
+    import robotic_mpc_b200 as rm
+    from oracle import pyoracle as o
+
+    K = args.steps or 600
+    z0 = np.concatenate([o.README_Q0, o.README_QD0])[None]
+    par = rm.pack_params(1, 0.01, surf=np.zeros((1, 6)))
+    eng = rm.Engine(1, 20, "SQP_RTI", dt=0.01, nlog=K)
+    eng.set_params(par)
+    out = {}
+    for mode in ("one_launch_per_step", "one_call"):
+        eng.set_state(z0)
+        eng.reset()
+        torch.cuda.synchronize()
+        ms = []
+        t0 = time.perf_counter()
+        if mode == "one_call":
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); eng.closed_loop(K); e1.record(); e1.synchronize()
+            ms = [e0.elapsed_time(e1) / K]
+        else:
+            for _ in range(K):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); eng.closed_loop(1); e1.record(); e1.synchronize()
+                ms.append(e0.elapsed_time(e1))
+        wall = time.perf_counter() - t0
+        sl = eng.get("slog").cpu().numpy()[0]
+        out[mode] = {"ms_per_step_mean": float(np.mean(ms)), "p50": float(np.percentile(ms, 50)), "p99": float(np.percentile(ms, 99)),
+                     "wall_s": wall, "device_solve_ms_mean": float(sl[:, rm.RL["TIME"]].mean() * 1e3)}
+    s = eng.get("summary").cpu().numpy()[0]
+    eng.close()
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    t0 = time.perf_counter()
+    r = leg.closed_loop(o.make_problem(N=20, solver_type=o.SQP_RTI, surf=np.zeros(6)), z0[0], K)
+    cpu_wall = time.perf_counter() - t0
+    print(json.dumps({"config": "configs[0] single run B=1 N=20 SQP_RTI flat surface, %d steps" % K, "gpu": out,
+                      "gpu_failures": int(s[rm.RS["NFAIL"]]), "gpu_rmse_e1": float(np.sqrt(s[0] / s[rm.RS["NSAMPLES"]])),
+                      "cpu_reference_one_core": {"kind": "reference" if o.REF_SO.exists() else "port", "ms_per_step_wall": cpu_wall / K * 1e3,
+                                                 "ms_per_step_acados_timer": float(r["time_tot"].mean() * 1e3), "failures": int(r["nfail"])}}))
 
 
 def config2(args):
@@ -143,11 +188,11 @@ def config5(args):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("which", choices=["config2", "config4", "config5"])
+    ap.add_argument("which", choices=["config1", "config2", "config4", "config5"])
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--steps", type=int, default=0)
     ap.add_argument("--horizon", type=int, default=0)
     ap.add_argument("--rho", type=float, default=100.0)
     ap.add_argument("--reps", type=int, default=2)
     a = ap.parse_args()
-    {"config2": config2, "config4": config4, "config5": config5}[a.which](a)
+    {"config1": config1, "config2": config2, "config4": config4, "config5": config5}[a.which](a)

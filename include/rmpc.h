@@ -68,6 +68,14 @@ int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_handle **out);
  * travels as a kernel argument). */
 int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
 
+/* Runtime options of the handle (ocp_nlp_solver_opts_set-style, by name).  Options:
+ *   "shift"  0 | 1   closed loop only: after every step shift the primal iterate by one stage before the next solve --
+ *                    x_k <- x_{k+1}, u_k <- u_{k+1} for k < N-1, x_{N-1} <- x_N; multipliers and merit weights stay -- i.e. the
+ *                    loop `for i < N-1: solver.set(i,'x',solver.get(i+1,'x')); solver.set(i,'u',solver.get(i+1,'u'));
+ *                    solver.set(N-1,'x',solver.get(N,'x'))` an acados MPC runs between two solves.  Default 0: the reference's
+ *                    loop keeps the unshifted iterate (R/simulator.py:199-241). */
+int rmpc_set_option(rmpc_handle *h, const char *name, double value);
+
 /* Replaces <name>_acados_free + _free_capsule. */
 int rmpc_destroy(rmpc_handle *h);
 

@@ -41,7 +41,8 @@ class RmpcProblem(C.Structure):
                 ("w_qddot", C.c_double), ("px_ref", C.c_double), ("vy_ref", C.c_double),
                 ("q_min", C.c_double * 6), ("q_max", C.c_double * 6), ("u_min", C.c_double * 6),
                 ("u_max", C.c_double * 6), ("model", Ur10Params),
-                ("term", C.c_int), ("term_P", C.c_double * 144), ("term_lh", C.c_double), ("term_uh", C.c_double)]
+                ("term", C.c_int), ("term_P", C.c_double * 144), ("term_lh", C.c_double), ("term_uh", C.c_double),
+                ("shift", C.c_int)]
 
 
 class RmpcTrace(C.Structure):
@@ -58,7 +59,7 @@ README_QD0 = np.array([1.0, 2.0, 1.0, 0.0, 0.0, 0.0])
 def make_problem(N=20, solver_type=SQP_RTI, dt=0.01, surf=None, wcv=200.0, w_u=0.01, w_qddot=0.02,
                  px_ref=0.40, vy_ref=0.05, q_min=None, q_max=None, qdot_min=None, qdot_max=None,
                  max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8, term_P=None, term_alpha=None,
-                 term_lh=None) -> RmpcProblem:
+                 term_lh=None, shift=False) -> RmpcProblem:
     """Problem with the reference defaults unless overridden."""
     p = RmpcProblem()
     p.N, p.solver_type, p.max_iter, p.qp_iter_max = int(N), int(solver_type), int(max_iter), int(qp_iter_max)
@@ -77,6 +78,7 @@ def make_problem(N=20, solver_type=SQP_RTI, dt=0.01, surf=None, wcv=200.0, w_u=0
     p.model.wcv[:] = list(np.broadcast_to(np.asarray(wcv, float), (6,)))
     p.model.Ts = dt
     p.model.t_ee[:] = [0.0, 0.0, 0.1]
+    p.shift = int(bool(shift))
     if term_P is not None:
         # terminal ellipsoid x_N' P x_N <= alpha (R/_terminal_constraint.py:96-116); lower side -alpha unless given
         P = np.asarray(term_P, float).reshape(12, 12)

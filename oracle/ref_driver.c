@@ -574,6 +574,23 @@ void rmpc_ref_get_lam(rmpc_ref *c, int stage, double *lam)
     ocp_nlp_out_get(c->config, c->dims, c->out, stage, "lam", lam);
 }
 
+/* Primal shift of the initial guess through the solver's own get / set (what an acados MPC loop does between two solves:
+ * for i < N-1: set(i, 'x', get(i+1, 'x')), set(i, 'u', get(i+1, 'u')); set(N-1, 'x', get(N, 'x'))). */
+void rmpc_ref_shift(rmpc_ref *c)
+{
+    const int N = c->prob.N;
+    double v[NX];
+    for (int i = 0; i + 1 < N; i++)
+    {
+        ocp_nlp_out_get(c->config, c->dims, c->out, i + 1, "x", v);
+        ocp_nlp_out_set(c->config, c->dims, c->out, c->in, i, "x", v);
+        ocp_nlp_out_get(c->config, c->dims, c->out, i + 1, "u", v);
+        ocp_nlp_out_set(c->config, c->dims, c->out, c->in, i, "u", v);
+    }
+    ocp_nlp_out_get(c->config, c->dims, c->out, N, "x", v);
+    ocp_nlp_out_set(c->config, c->dims, c->out, c->in, N - 1, "x", v);
+}
+
 /* Whole closed loop (R/simulator.py:199-241 without sleeps / visualisation). Returns #failed steps. */
 int rmpc_ref_closed_loop(const rmpc_problem *prob, const double z0[12], int nsteps, rmpc_trace *tr)
 {
@@ -604,6 +621,7 @@ int rmpc_ref_closed_loop(const rmpc_problem *prob, const double z0[12], int nste
             rmpc_ref_get_iterate(c, tr->xtraj ? tr->xtraj + (size_t) k * (N + 1) * NX : NULL,
                                  tr->utraj ? tr->utraj + (size_t) k * N * NU : NULL,
                                  tr->pitraj ? tr->pitraj + (size_t) k * N * NX : NULL);
+        if (prob->shift) rmpc_ref_shift(c);
     }
     rmpc_ref_destroy(c);
     return nfail;

@@ -1235,6 +1235,14 @@ void rmpc_oracle_get_iterate(const rmpc_oracle *s, double *xtraj, double *utraj,
     }
 }
 
+/* primal shift of the initial guess (rmpc_problem.shift): x_k <- x_{k+1}, u_k <- u_{k+1} for k < N-1, x_{N-1} <- x_N */
+void rmpc_oracle_shift(rmpc_oracle *s)
+{
+    const int N = s->N;
+    for (int i = 0; i + 1 < N; i++) memcpy(s->ux + NV * i, s->ux + NV * (i + 1), NV * sizeof(double));
+    memcpy(s->ux + NV * (N - 1) + NU, s->ux + NV * N, NX * sizeof(double));
+}
+
 int rmpc_oracle_n_lq_needed(const rmpc_oracle *s) { return s->n_lq_needed; }
 /* Debug/parity hook: per-iteration table of the LAST QP (8 columns: alpha_aff mu_aff sigma alpha mu res_stat res_eq
  * res_ineq; row k+1 = iteration k); returns the iteration count. */
@@ -1276,6 +1284,7 @@ int rmpc_oracle_closed_loop(const rmpc_problem *prob, const double z0[12], int n
             rmpc_oracle_get_iterate(s, tr->xtraj ? tr->xtraj + (size_t) k * (N + 1) * NX : NULL,
                                     tr->utraj ? tr->utraj + (size_t) k * N * NU : NULL,
                                     tr->pitraj ? tr->pitraj + (size_t) k * N * NX : NULL);
+        if (prob->shift) rmpc_oracle_shift(s);
     }
     if (s->n_lq_needed) fprintf(stderr, "rmpc_oracle: LQ fall-back factorisation used %d times\n", s->n_lq_needed);
     rmpc_oracle_destroy(s);

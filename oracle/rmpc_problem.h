@@ -39,6 +39,10 @@ typedef struct
     int term;          /* 0: no terminal constraint (the reference MPC as shipped) */
     double term_P[144]; /* symmetric 12 x 12, row-major, state order [q; qd] */
     double term_lh, term_uh;
+    /* 1: after every closed-loop step the primal iterate is shifted by one stage before the next solve, the usual acados MPC
+     * idiom (x_k <- x_{k+1}, u_k <- u_{k+1} for k < N-1, x_{N-1} <- x_N; multipliers and merit weights stay).  The reference
+     * never shifts (R/simulator.py:199-241): 0 is the reference behaviour.  SURVEY.md 8(f) #1. */
+    int shift;
 } rmpc_problem;
 
 /* Fill every field except model.surf / model.wcv / N / dt / solver_type with the reference defaults. */
@@ -75,6 +79,7 @@ static inline void rmpc_problem_defaults(rmpc_problem *p)
     for (int i = 0; i < 144; i++) p->term_P[i] = 0.0;
     p->term_lh = 0.0;
     p->term_uh = 0.0;
+    p->shift = 0;
 }
 
 /* Closed-loop trace written by both legs (any pointer may be NULL). Layouts are row-major.

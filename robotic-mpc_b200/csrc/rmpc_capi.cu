@@ -209,6 +209,19 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     return 0;
 }
 
+extern "C" int rmpc_set_option(rmpc_handle *h, const char *name, double value)
+{
+    if (!h || !name) return fail(h, RMPC_EINVAL, "rmpc_set_option: null argument");
+    const std::string f(name);
+    if (f == "shift")
+    {
+        if (value != 0.0 && value != 1.0) return fail(h, RMPC_EINVAL, "rmpc_set_option: shift must be 0 or 1");
+        h->W.shift = (int) value;
+        return 0;
+    }
+    return fail(h, RMPC_EINVAL, "rmpc_set_option: unknown option " + f);
+}
+
 extern "C" int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis)
 {
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_set_chain: null handle");

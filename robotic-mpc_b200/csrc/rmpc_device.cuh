@@ -2289,6 +2289,29 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
 /* ---------------------------------------------------------------------------------------------- closed loop (K5)
  * R/simulator.py:199-241: x = plant state; solver.set(0,'lbx'/'ubx',x); solve; u = solver.get(0,'u'); plant RK4.
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
+/* Primal shift of the initial guess between two closed-loop steps (RmpcWs.shift; the acados MPC idiom
+ * set(i, 'x', get(i+1, 'x')), set(i, 'u', get(i+1, 'u')) for i < N-1, set(N-1, 'x', get(N, 'x')) -- SURVEY.md 8(f) #1; the
+ * reference itself never shifts).  Multipliers and merit weights stay.  [u; x] of the stages are contiguous, so the shift
+ * is one move by NV doubles towards the front: ascending chunks of GL elements, each lane loads before it stores and no
+ * chunk writes what a later one still reads (NV > GL). */
+RD void nlp_shift(const RmpcDims &D, const Inst &I)
+{
+    const int N = D.N, lane = rd_lane();
+    double *ux = AR(ux);
+    const int n = NV * (N - 1);
+    for (int k0 = 0; k0 < n; k0 += GL)
+    {
+        const int k = k0 + lane;
+        double v = 0.0;
+        if (k < n) v = ux[k + NV];
+        rd_sync();
+        if (k < n) ux[k] = v;
+    }
+    rd_sync();
+    if (lane < NX) ux[NV * (N - 1) + 6 + lane] = ux[NV * N + 6 + lane];
+    rd_sync();
+}
+
 RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &W, long inst, GrpSmem &sm, int nsteps,
                          int advance = 1, unsigned pairmask = 0)
 {
@@ -2394,5 +2417,6 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
             sm_[RS_NSAMPLES] += 1.0;
         }
         rd_sync();
+        if (W.shift && advance) nlp_shift(D, I);
     }
 }

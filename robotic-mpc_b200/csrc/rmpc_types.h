@@ -191,6 +191,7 @@ typedef struct
     int step0;         /* index of the first step of this launch */
     const double *pe;  /* [B][RE_COUNT] terminal-set blocks, null: no terminal constraint (the reference MPC as shipped) */
     int rti_phase;     /* SQP_RTI only: 0 preparation + feedback in one solve, 1 preparation, 2 feedback (acados rti_phase) */
+    int shift;         /* closed loop: shift the primal iterate by one stage after every step (0: like the reference) */
 } RmpcWs;
 
 #ifdef __CUDACC__

@@ -50,6 +50,7 @@ def load_library() -> C.CDLL:
     lib.rmpc_solve.argtypes = [vp, vp]
     lib.rmpc_solve_rti_phase.argtypes = [vp, ip, vp]
     lib.rmpc_set_chain.argtypes = [vp, dp, dp]
+    lib.rmpc_set_option.argtypes = [vp, cp, C.c_double]
     lib.rmpc_closed_loop.argtypes = [vp, ip, vp]
     lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_steps_done.argtypes = [vp]
@@ -62,7 +63,7 @@ def load_library() -> C.CDLL:
 
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
                     "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
-                    "rmpc_launch_count", "rmpc_set_chain"]
+                    "rmpc_launch_count", "rmpc_set_chain", "rmpc_set_option"]
 
 
 class RmpcError(RuntimeError):
@@ -149,6 +150,10 @@ class Engine:
         lh = -alpha if lh is None else np.broadcast_to(np.asarray(lh, float), (self.B,))
         blk = np.concatenate([P.reshape(self.B, 144), lh[:, None], alpha[:, None]], axis=1)
         self.set("term", blk)
+
+    def set_option(self, name, value):
+        """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step."""
+        self._check(self.lib.rmpc_set_option(self.h, str(name).encode(), float(value)), f"rmpc_set_option({name})")
 
     def set_chain(self, xyzR=None, axis=None):
         """Kinematic chain of the arm for every instance: a ``robots.chain_table`` / ``robots.chain_from_urdf`` pair, or a

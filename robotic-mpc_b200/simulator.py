@@ -48,7 +48,8 @@ def _solver_options_dict(opts):
 class Simulator:
     def __init__(self, robot_name, dt, simulation_time, prediction_horizon, q_0, qdot_0, wcv, q_min, q_max, qdot_min, qdot_max,
                  surface_limits=None, surface_origin=None, surface_orientation_rpy=None, w_qddot=0.02, surface_coeffs=None,
-                 solver_options=None, w_u=0.01, px_ref=0.40, vy_ref=0.05, scene=True, terminal_constraint=None):
+                 solver_options=None, w_u=0.01, px_ref=0.40, vy_ref=0.05, scene=True, terminal_constraint=None,
+                 shift_initial_guess=False):
         self.name = robot_name
         self.robot_name = robot_name
         self.dt = dt
@@ -82,6 +83,7 @@ class Simulator:
                        N_horizon=self.prediction_horizon, Tf=self.dt * self.prediction_horizon, qmin=self.q_min,
                        qmax=self.q_max, dq_min=self.qdot_min, dq_max=self.qdot_max, w_u=self.w_u, w_qddot=self.w_qddot,
                        px_ref=self.px_ref, vy_ref=self.vy_ref, terminal_constraint=terminal_constraint)
+        self.mpc.shift_initial_guess = bool(shift_initial_guess)  # extension: primal shift between steps (off = reference)
         so = _solver_options_dict(solver_options)
         if so:
             self._apply_solver_options(so)

@@ -112,6 +112,9 @@ class MPC:
         self.ocp.constraints.lbx, self.ocp.constraints.ubx = self.qmin, self.qmax
         self.solver = None
         self.terminal = None
+        # shift the primal initial guess by one stage after every closed-loop step; the reference's loop
+        # does not (R/simulator.py:199-241), so the default is off
+        self.shift_initial_guess = False
         if terminal_constraint is not None:
             self.set_terminal_constraint(terminal_constraint)
 
@@ -149,7 +152,8 @@ class MPC:
     def static_key(self):
         o = self.ocp.solver_options
         chain = self.model.chain_key() if hasattr(self.model, "chain_key") else None
-        return (self.N_horizon, round(self.Tf / self.N_horizon, 15), self.terminal is not None, chain) + o.static_key()
+        return (self.N_horizon, round(self.Tf / self.N_horizon, 15), self.terminal is not None, chain,
+                bool(self.shift_initial_guess)) + o.static_key()
 
     def finalize_solver(self, device=0):
         """Creates the solver handle (a batch of one).  ``SimulationManager.run_all`` binds many ``MPC`` objects to one
@@ -161,10 +165,11 @@ class MPC:
 
 
 def bind_chain(engine, mpcs):
-    """Hand the kinematic chain of a batch to the engine (part of the static key: one chain per batch)."""
+    """Hand the batch-wide settings that are part of the static key to the engine: kinematic chain, shift option."""
     chain = getattr(mpcs[0].model, "chain", None)
     if chain is not None:
         engine.set_chain(*chain)
+    engine.set_option("shift", 1 if mpcs[0].shift_initial_guess else 0)
 
 
 def bind_terminal(engine, mpcs):

@@ -56,3 +56,8 @@ def plant_record(par, z):
     dp = C.POINTER(C.c_double)
     lib.rmpc_emu_plant_record(par.ctypes.data_as(dp), z.ctypes.data_as(dp), rec.ctypes.data_as(dp), y5.ctypes.data_as(dp))
     return rec, y5
+
+
+def set_shift(on):
+    """Process-global 'shift' option of the emulated closed loop (rmpc_set_option(h, "shift", .))."""
+    C.CDLL(str(SO)).rmpc_emu_set_shift(int(bool(on)))

@@ -25,6 +25,7 @@ void body(void *p, int)
     Job *j = (Job *) p;
     closed_loop_group(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
 }
+int g_shift = 0;
 bool g_custom_chain = false;
 RmpcChain g_chain;
 void current_chain(RmpcChain *ch)
@@ -42,6 +43,8 @@ extern "C" int rmpc_emu_set_chain(const double *xyzR, const int *axis)
     g_custom_chain = true;
     return 0;
 }
+
+extern "C" int rmpc_emu_set_shift(int on) { g_shift = on ? 1 : 0; return 0; }
 
 /* the per-sample plant record (RK_*, 28 doubles) and the task outputs y5 of one state, with the current chain */
 extern "C" int rmpc_emu_plant_record(const double *par, const double *z, double *rec, double *y5)
@@ -90,6 +93,7 @@ extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, c
     W.flags = (int *) calloc((size_t) B * 4, sizeof(int));
     W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
     W.nlog = nsteps; W.step0 = 0;
+    W.shift = g_shift;
     for (long i = 0; i < B; i++)
     {
         memcpy(W.z + i * NX, z0 + i * NX, NX * sizeof(double));

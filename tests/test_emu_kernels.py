@@ -91,3 +91,31 @@ def test_emulated_tracking_summary(oracle):
     np.testing.assert_allclose(s[0:5], sse, rtol=1e-10)
     np.testing.assert_allclose(s[5:10], itse, rtol=1e-10)
     assert s[18] == ns + 1
+
+
+@pytest.mark.parametrize("solver,N", [(1, 20), (0, 12), (1, 2)])
+def test_emulated_shifted_closed_loop_matches_reference(built, solver, N):
+    """Option "shift" (SURVEY.md 8(f) #1): the primal iterate moves one stage forward after every step.  The oracle is the
+    compiled acados driven through its own get / set between solves (oracle/ref_driver.c: rmpc_ref_shift), or the port."""
+    import oracle.pyoracle as o
+    import robotic_mpc_b200 as rm
+
+    rng = np.random.default_rng(31 + N)
+    surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal(6)
+    z0 = np.concatenate([o.README_Q0 + rng.uniform(-0.05, 0.05, 6), o.README_QD0 + rng.uniform(-0.1, 0.1, 6)])
+    st = o.SQP_RTI if solver == 1 else o.SQP
+    ns = 25
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    g = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf, shift=True), z0, ns)
+    g0 = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf), z0, ns)
+    assert np.abs(g["u"] - g0["u"]).max() > 1e-9  # shifting changes the closed loop (converged SQP: only at tolerance level)
+    p = o.PortLeg().closed_loop(o.make_problem(N=N, solver_type=st, surf=surf, shift=True), z0, ns)
+    assert np.abs(p["u"] - g["u"]).max() < 1e-9 and np.array_equal(p["sqp_iter"], g["sqp_iter"])
+    try:
+        emu.set_shift(True)
+        r = emu.closed_loop(rm.pack_params(1, 0.01, surf=surf[None]), z0[None], N, solver, ns, seed=5)
+    finally:
+        emu.set_shift(False)
+    assert np.abs(r["u"][0] - g["u"]).max() < 1e-9 and np.abs(r["z"][0] - g["z"]).max() < 1e-9
+    assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"])
+    assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"])

@@ -356,3 +356,40 @@ def test_set_chain_default_is_ur10_and_resets(oracle):
     with pytest.raises(rm.RmpcError):
         eng.set_chain(rb.chain_table("ur5")[0], [0, 1, 2, 3, 0, 0])
     eng.close()
+
+
+@pytest.mark.parametrize("solver,N,ns", [("SQP_RTI", 30, 40), ("SQP", 10, 15), ("SQP_RTI", 2, 10)])
+def test_shifted_initial_guess_matches_oracle(oracle, solver, N, ns):
+    """rmpc_set_option(h, "shift", 1): primal shift between closed-loop steps, against the compiled acados driven through its
+    own get / set between solves (or the port); off again = the unshifted run, bit for bit."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B = 5
+    surf, z0 = _inputs(o, B, 500 + N)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    eng = rm.Engine(B, N, solver, dt=0.01, nlog=ns)
+    eng.set_params(par)
+    eng.set_option("shift", 1)
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    ulog, zlog, slog = (eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog"))
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    for i in range(B):
+        g = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i], shift=True), z0[i], ns)
+        assert relerr(ulog[i], g["u"]) < RTOL and relerr(zlog[i], g["z"]) < RTOL
+        assert np.array_equal(slog[i, :, 0].astype(int), g["status"]) and np.array_equal(slog[i, :, 1].astype(int), g["sqp_iter"])
+    eng.set_option("shift", 0)
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    plain = _run(rm, B, N, solver, par, z0, ns)
+    assert np.array_equal(eng.get("ulog").cpu().numpy(), plain["ulog"])
+    assert np.abs(plain["ulog"] - ulog).max() > 1e-9
+    with pytest.raises(rm.RmpcError):
+        eng.set_option("shift", 2)
+    with pytest.raises(rm.RmpcError):
+        eng.set_option("warm_start", 1)
+    eng.close()

@@ -78,6 +78,8 @@ def test_solver_options_handling(capsys):
         rm.Simulator(**{**BASE, "robot_name": "ur3"})  # no built-in chain table
     s5 = rm.Simulator(**{**BASE, "robot_name": "ur5"})
     assert s5.static_key() != s.static_key()  # another chain = another batched launch
+    ssh = rm.Simulator(**{**BASE, "shift_initial_guess": True})
+    assert ssh.mpc.shift_initial_guess and ssh.static_key() != rm.Simulator(**BASE).static_key()
 
 
 def test_plan_groups_by_static_shape_and_rank():

@@ -140,3 +140,50 @@ def test_trajectory_optimizer_solver_interface(oracle):
     with pytest.raises(ValueError):
         mpcs[1].ocp.solver_options.nlp_solver_type = "SQP_RTI"
         rm.BatchedSolver(mpcs)
+
+
+def test_run_all_over_arms_and_options(oracle, tmp_path):
+    """SimulationManager over robot_name x shift_initial_guess x terminal set: one launch per combination (they are part of
+    the batching key), every instance equal to the oracle's sequential run on the same chain / option, poses reported for the
+    arm's own end-effector frame; export writes one table row per simulation."""
+    import robotic_mpc_b200 as rm
+    import robotic_mpc_b200.robots as rb
+
+    o = oracle
+    rng = np.random.default_rng(12)
+    coeff_sets = [dict(zip("abcdef", np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal(6))) for _ in range(2)]
+    base = _base(o, simulation_time=0.12)
+    base["q_0"] = np.array([0.0, -1.8, 1.9, -1.7, -1.57, 0.0])
+    base["qdot_0"] = np.array([0.2, 0.1, -0.1, 0.0, 0.0, 0.0])
+    base["prediction_horizon"] = 10
+    base["solver_options"] = {"nlp_solver_type": "SQP_RTI"}
+    m = rm.SimulationManager(base)
+    m.grid_search({"robot_name": ["ur5", "ur10"], "shift_initial_guess": [False, True],
+                   "terminal_constraint": [None, {"rho": 100.0}]}, surface_coeff_sets=coeff_sets)
+    res = m.run_all()
+    assert len(res) == 16 and m.last_run_info["launches"] == 8
+    leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
+    z0 = np.concatenate([base["q_0"], base["qdot_0"]])
+    try:
+        for r, spec in zip(res, m.simulations):
+            c = spec["config"]
+            chain = rb.chain_table(c["robot_name"])
+            leg.set_chain(*chain)
+            tkw = {}
+            if c["terminal_constraint"] is not None:
+                P, alpha = rm.terminal_constraint.default_terminal_set(wcv=200.0, Ts=0.01, rho=100.0)
+                tkw = dict(term_P=P, term_alpha=alpha)
+            surf = np.array([c["surface_coeffs"][k] for k in "abcdef"])
+            g = leg.closed_loop(o.make_problem(N=10, solver_type=o.SQP_RTI, surf=surf, shift=c["shift_initial_guess"], **tkw), z0, 12)
+            assert relerr(r["data"]["u"][:, 1:].T, g["u"]) < RTOL
+            assert relerr(np.vstack([r["data"]["q"], r["data"]["qdot"]]).T, g["z"]) < RTOL
+            assert np.array_equal(r["analysis"]["solver_status"], g["status"])
+            p, R = rb.forward_kinematics(chain[0], chain[1], r["data"]["q"][:, -1])
+            assert np.abs(r["data"]["ee_pose"][:3, -1] - p).max() < 1e-12
+    finally:
+        leg.set_chain(None)
+    files = m.export(tmp_path / "out", res)
+    import pandas as pd
+
+    t = pd.read_parquet(files[0])
+    assert len(t) == 16 and set(t["robot_name"]) == {"ur5", "ur10"} and len(files) == 2 + 16

@@ -121,6 +121,15 @@ int rmpc_solve(rmpc_handle *h, void *stream);
  * tests/test_oracle_port.py); set "z" between the two calls. */
 int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream);
 
+/* Checkpoint / resume of the whole batch: iterate, multipliers, merit weights, QP memory, plant state, flags, accumulated
+ * summaries and the step counter in one device blob of rmpc_state_size(h) doubles (the per-step logs are not part of it).
+ * A closed loop continued after rmpc_load_state is bit-identical to one that was never interrupted.  Batch counterpart of
+ * AcadosOcpSolver.store_iterate / load_iterate (T/acados_ocp_solver.py:1158-1440).  rmpc_load_state checks that the blob
+ * comes from a handle with the same B and N (RMPC_EINVAL otherwise) and synchronises the stream once to do so. */
+long long rmpc_state_size(const rmpc_handle *h);
+int rmpc_store_state(rmpc_handle *h, double *dev, void *stream);
+int rmpc_load_state(rmpc_handle *h, const double *dev, void *stream);
+
 /* nsteps closed-loop steps for all instances entirely on the device:
  *   x0 <- z; solve; u0; z <- RK4(z, u0); log; accumulate tracking-error sums.     R/simulator.py:199-241 */
 int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);

@@ -303,6 +303,60 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
     return 0;
 }
 
+/* ---- checkpoint / resume of the complete solver + plant state of the batch (AcadosOcpSolver.store_iterate / load_iterate,
+ * T/acados_ocp_solver.py:1158-1440, extended to everything a closed loop carries: iterate, multipliers, merit weights, QP
+ * memory, plant state, flags, accumulated summaries, step counter).  Blob = [magic, B, N, steps_done | slab | z | summary | flags]. */
+static const double RMPC_STATE_MAGIC = 20240611.0;
+extern "C" long long rmpc_state_size(const rmpc_handle *h)
+{
+    if (!h) return 0;
+    const long long B = h->D.B;
+    return 4 + B * h->W.slab_stride + B * NX + B * RS_COUNT + B * 2;
+}
+
+extern "C" int rmpc_store_state(rmpc_handle *h, double *dev, void *stream)
+{
+    if (!h || !dev) return fail(h, RMPC_EINVAL, "rmpc_store_state: null argument");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const size_t B = (size_t) h->D.B;
+    const double hdr[4] = {RMPC_STATE_MAGIC, (double) h->D.B, (double) h->D.N, (double) h->steps_done};
+    CU(cudaMemcpyAsync(dev, hdr, sizeof(hdr), cudaMemcpyHostToDevice, s)); /* pageable source: staged before the call returns */
+    double *p = dev + 4;
+    CU(cudaMemcpyAsync(p, h->W.slab, sizeof(double) * B * (size_t) h->W.slab_stride, cudaMemcpyDeviceToDevice, s));
+    p += B * (size_t) h->W.slab_stride;
+    CU(cudaMemcpyAsync(p, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s));
+    p += B * NX;
+    CU(cudaMemcpyAsync(p, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s));
+    p += B * RS_COUNT;
+    CU(cudaMemcpyAsync(p, h->W.flags, sizeof(int) * B * 4, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
+extern "C" int rmpc_load_state(rmpc_handle *h, const double *dev, void *stream)
+{
+    if (!h || !dev) return fail(h, RMPC_EINVAL, "rmpc_load_state: null argument");
+    CU(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t) stream;
+    const size_t B = (size_t) h->D.B;
+    double hdr[4] = {0, 0, 0, 0};
+    CU(cudaMemcpyAsync(hdr, dev, sizeof(hdr), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    if (hdr[0] != RMPC_STATE_MAGIC || hdr[1] != (double) h->D.B || hdr[2] != (double) h->D.N || hdr[3] < 0)
+        return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob was not stored by a handle with this B and N");
+    const double *p = dev + 4;
+    CU(cudaMemcpyAsync(h->W.slab, p, sizeof(double) * B * (size_t) h->W.slab_stride, cudaMemcpyDeviceToDevice, s));
+    p += B * (size_t) h->W.slab_stride;
+    CU(cudaMemcpyAsync(h->W.z, p, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s));
+    p += B * NX;
+    CU(cudaMemcpyAsync(h->W.summary, p, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s));
+    p += B * RS_COUNT;
+    CU(cudaMemcpyAsync(h->W.flags, p, sizeof(int) * B * 4, cudaMemcpyDeviceToDevice, s));
+    h->steps_done = (int) hdr[3];
+    h->W.step0 = h->steps_done;
+    return 0;
+}
+
 static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
 {
     const int grid = (h->D.B + RMPC_GROUPS_PER_CTA - 1) / RMPC_GROUPS_PER_CTA;

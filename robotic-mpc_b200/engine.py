@@ -51,6 +51,10 @@ def load_library() -> C.CDLL:
     lib.rmpc_solve_rti_phase.argtypes = [vp, ip, vp]
     lib.rmpc_set_chain.argtypes = [vp, dp, dp]
     lib.rmpc_set_option.argtypes = [vp, cp, C.c_double]
+    lib.rmpc_state_size.argtypes = [vp]
+    lib.rmpc_state_size.restype = C.c_longlong
+    lib.rmpc_store_state.argtypes = [vp, dp, vp]
+    lib.rmpc_load_state.argtypes = [vp, dp, vp]
     lib.rmpc_closed_loop.argtypes = [vp, ip, vp]
     lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_steps_done.argtypes = [vp]
@@ -63,7 +67,8 @@ def load_library() -> C.CDLL:
 
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
                     "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
-                    "rmpc_launch_count", "rmpc_set_chain", "rmpc_set_option"]
+                    "rmpc_launch_count", "rmpc_set_chain", "rmpc_set_option", "rmpc_state_size",
+                    "rmpc_store_state", "rmpc_load_state"]
 
 
 class RmpcError(RuntimeError):
@@ -150,6 +155,29 @@ class Engine:
         lh = -alpha if lh is None else np.broadcast_to(np.asarray(lh, float), (self.B,))
         blk = np.concatenate([P.reshape(self.B, 144), lh[:, None], alpha[:, None]], axis=1)
         self.set("term", blk)
+
+    def store_state(self):
+        """Checkpoint of the whole batch (solver memory, plant state, summaries, step counter) as one device tensor; see
+        ``load_state``.  ``tensor.cpu().numpy()`` / ``numpy.save`` make it a file (AcadosOcpSolver.store_iterate's role)."""
+        t = self.torch.empty(int(self.lib.rmpc_state_size(self.h)), dtype=self.torch.float64, device=self.tdev)
+        self._check(self.lib.rmpc_store_state(self.h, C.c_void_p(t.data_ptr()), self._stream()), "rmpc_store_state")
+        return t
+
+    def load_state(self, blob):
+        """Resume from a ``store_state`` blob of an engine with the same B and N: the continued closed loop is bit-identical
+        to an uninterrupted one."""
+        t = self.torch.as_tensor(blob, dtype=self.torch.float64).to(self.tdev).contiguous()
+        if t.numel() != int(self.lib.rmpc_state_size(self.h)):
+            raise ValueError(f"state blob has {t.numel()} doubles, this engine needs {int(self.lib.rmpc_state_size(self.h))}")
+        self._check(self.lib.rmpc_load_state(self.h, C.c_void_p(t.data_ptr()), self._stream()), "rmpc_load_state")
+        self.torch.cuda.current_stream(self.tdev).synchronize()  # t may be a temporary
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
 
     def set_option(self, name, value):
         """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step."""

@@ -169,3 +169,41 @@ def test_error_behaviour_of_the_entry_points(built):
     assert eng.lib.rmpc_steps_done(eng.h) == 0
     eng.close()
     eng.close()                             # idempotent
+
+
+def test_checkpoint_resume_is_bit_identical(built, tmp_path):
+    """rmpc_store_state / rmpc_load_state: a closed loop interrupted, saved to a file, and resumed in a NEW handle continues
+    bit for bit (iterate, multipliers, merit weights, QP memory, plant state, summaries, step counter travel in the blob)."""
+    import oracle.pyoracle as o
+    import robotic_mpc_b200 as rm
+
+    B, N = 6, 12
+    surf, z0 = _inputs(o, B, 81)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    for solver in ("SQP_RTI", "SQP"):
+        full = _closed_loop(rm, B, N, solver, par, z0, 16)
+        with rm.Engine(B, N, solver, dt=0.01, nlog=16) as eng:
+            eng.set_params(par)
+            eng.set_state(z0)
+            eng.reset()
+            eng.closed_loop(7)
+            blob = eng.store_state()
+            np.save(tmp_path / "ckpt.npy", blob.cpu().numpy())
+            eng.closed_loop(9)
+            assert np.array_equal(eng.get("ulog").cpu().numpy(), full["ulog"])
+        with rm.Engine(B, N, solver, dt=0.01, nlog=16) as eng2:
+            eng2.set_params(par)  # parameters belong to the problem, not to the state
+            eng2.load_state(np.load(tmp_path / "ckpt.npy"))
+            assert eng2.lib.rmpc_steps_done(eng2.h) == 7
+            eng2.closed_loop(9)
+            assert np.array_equal(eng2.get("ulog").cpu().numpy()[:, 7:], full["ulog"][:, 7:])
+            assert np.array_equal(eng2.get("z").cpu().numpy(), full["z"])
+            assert np.array_equal(eng2.get("summary").cpu().numpy()[:, :10], full["summary"][:, :10])
+            assert np.all(eng2.get("summary").cpu().numpy()[:, rm.RS["NSAMPLES"]] == 17)
+        with rm.Engine(B, N + 1, solver, dt=0.01) as other:  # same slab size (stage slots are padded to even), other N
+            with pytest.raises((ValueError, rm.RmpcError)):
+                other.load_state(blob)
+        with rm.Engine(B + 2, N, solver, dt=0.01) as other:
+            bad = np.zeros(int(other.lib.rmpc_state_size(other.h)))
+            with pytest.raises(rm.RmpcError):
+                other.load_state(bad)

@@ -336,7 +336,7 @@ def run_gpu(args):
         achieved_tf = flops_step / (kernel_ms * 1e-3) / 1e12
         traffic, traffic_src = ncu_dram_traffic() if (B == 4096 and N == 100) else (None, None)
         cb = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:  # reported at N = 1 only; multi-GPU runs carry cpu_baseline = null
             cb, _, _ = cpu_leg(N, 3, K)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,

@@ -28,13 +28,13 @@ _G = {}
 def _worker(job):
     from oracle import pyoracle as o
 
-    idx, N, st, ns, chain, term = job
+    idx, N, st, ns, chain, term, wkw = job
     leg = o.RefLeg() if o.REF_SO.exists() else o.PortLeg()
     if chain is not None:
         leg.set_chain(*chain)
     out = []
     for i in idx:
-        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i], **term), _G["z0"][i], ns)
+        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i], **term, **wkw), _G["z0"][i], ns)
         out.append((i, r["u"], r["z"], r["status"], r["sqp_iter"], r["qp_iter"]))
     return out
 
@@ -52,6 +52,8 @@ def main():
     ap.add_argument("--solver", default="SQP_RTI")
     ap.add_argument("--robot", default="ur10")
     ap.add_argument("--seed", type=int, default=44)
+    ap.add_argument("--w-u", type=float, default=0.01)
+    ap.add_argument("--w-qddot", type=float, default=0.02)
     ap.add_argument("--term-rho", type=float, default=0.0, help="> 0: terminal ellipsoid of the LQR with R = rho I (BASELINE configs[3])")
     a = ap.parse_args()
     B, N, K = a.batch, a.horizon, a.steps
@@ -68,7 +70,8 @@ def main():
         P, alpha = rm.terminal_constraint.default_terminal_set(wcv=200.0, Ts=0.01, rho=a.term_rho)
         term = dict(term_P=P, term_alpha=alpha, term_lh=-alpha)
         eng.set_terminal(P, alpha)
-    eng.set_params(rm.pack_params(B, 0.01, surf=surf))
+    wkw = dict(w_u=a.w_u, w_qddot=a.w_qddot)
+    eng.set_params(rm.pack_params(B, 0.01, surf=surf, **wkw))
     eng.set_state(z0)
     eng.reset()
     torch.cuda.synchronize()
@@ -83,7 +86,7 @@ def main():
     _G["surf"], _G["z0"] = surf, z0
     cores = os.cpu_count() or 1
     st = o.SQP_RTI if a.solver == "SQP_RTI" else o.SQP
-    jobs = [(list(range(c, B, cores * 4)), N, st, K, chain, term) for c in range(cores * 4)]
+    jobs = [(list(range(c, B, cores * 4)), N, st, K, chain, term, wkw) for c in range(cores * 4)]
     from multiprocessing import get_context
 
     t0 = time.time()
@@ -103,7 +106,7 @@ def main():
         qp_pm1 += int(d.max() <= 1)
     print(json.dumps({
         "what": "CUDA path vs compiled reference, closed loop, every instance", "oracle": "reference" if o.REF_SO.exists() else "port",
-        "robot": a.robot, "terminal_rho": a.term_rho, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
+        "robot": a.robot, "terminal_rho": a.term_rho, "w_u": a.w_u, "w_qddot": a.w_qddot, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
         "u_relerr": {"max": float(eu.max()), "p99": float(np.percentile(eu, 99)), "median": float(np.median(eu))},
         "z_relerr": {"max": float(ez.max()), "p99": float(np.percentile(ez, 99)), "median": float(np.median(ez))},
         "instances_over_1e-6": int((np.maximum(eu, ez) > 1e-6).sum()),

@@ -394,7 +394,7 @@ extern "C" int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream)
     if (nsteps == 0) return 0;
     /* One launch per closed-loop step by default: a launch boundary puts every instance of the batch back in the same
      * phase (linearise / factorise / substitute ...).  Measured on B200 (4096 x N=100): 447k steps/s at 1 step per
-     * launch, 367k at 5, 288k at 600 -- instances that drift into different phases compete for the memory system and the
+     * launch, 367k at 5, 288k at 600 (r1c); 722k / 704k / 660k at 1 / 2 / 3 steps per launch (r1k) -- instances that drift into different phases compete for the memory system and the
      * one-stage-ahead staging of the Riccati sweeps no longer hides the latency.  Launch overhead is ~0.05% of a step.
      * RMPC_STEPS_PER_LAUNCH overrides (experiments). */
     static const int chunk_env = []() { const char *e = getenv("RMPC_STEPS_PER_LAUNCH"); int v = e ? atoi(e) : 1; return v > 0 ? v : 1; }();

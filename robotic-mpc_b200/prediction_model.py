@@ -36,6 +36,7 @@ class SixDofRobot:
         self.robot_name = urdf_loader.name
         xyzR, axis = urdf_loader.chain
         self.chain = (np.ascontiguousarray(xyzR, dtype=float).reshape(8, 12), np.ascontiguousarray(axis, dtype=np.int32).reshape(6))
+        self._chain_key = None
         self.n_dof = 6
         self.Ts = float(Ts)
         self.Wcv = np.full(6, 200.0) if Wcv is None else np.asarray(Wcv, dtype=float).reshape(6)
@@ -46,13 +47,20 @@ class SixDofRobot:
         w, Ts = self.Wcv, self.Ts
         a22 = np.array([math.exp(-x * Ts) for x in w])
         a12 = (1.0 - a22) / w
-        I, Z = np.eye(6), np.zeros((6, 6))
-        self.Ad = np.block([[I, np.diag(a12)], [Z, np.diag(a22)]])
-        self.Bd = np.vstack([Ts * I - np.diag(a12), np.diag(1.0 - a22)])
+        k = np.arange(6)
+        Ad, Bd = np.zeros((12, 12)), np.zeros((12, 6))
+        Ad[k, k] = 1.0
+        Ad[k, 6 + k] = a12
+        Ad[6 + k, 6 + k] = a22
+        Bd[k, k] = Ts - a12
+        Bd[6 + k, k] = 1.0 - a22
+        self.Ad, self.Bd = Ad, Bd
 
     def chain_key(self):
         """Hashable identity of the kinematic chain (instances of one batched launch share it)."""
-        return (self.chain[0].tobytes(), self.chain[1].tobytes())
+        if self._chain_key is None:
+            self._chain_key = (self.chain[0].tobytes(), self.chain[1].tobytes())
+        return self._chain_key
 
     def forward_kinematics(self, q):
         """(p, R) of the end-effector frame at joint angles q -- host-side check of the table (R/prediction_model.py:126-132)."""

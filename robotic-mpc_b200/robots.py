@@ -12,6 +12,7 @@ into the fixed transforms so that ANY axis assignment runs through the same code
 """
 from __future__ import annotations
 
+import functools
 import xml.etree.ElementTree as ET
 
 import numpy as np
@@ -69,13 +70,22 @@ _ROBOTS = {"ur10": _UR10, "ur5": _UR5}
 
 
 def chain_table(robot_name):
-    """(xyzR [8,12], axis [6]) of a built-in robot ('ur10' frame ee_link, 'ur5' frame tool0 -- R/prediction_model.py:28-31)."""
+    """(xyzR [8,12], axis [6]) of a built-in robot ('ur10' frame ee_link, 'ur5' frame tool0 -- R/prediction_model.py:28-31).
+    The arrays are built once per robot and shared (read-only): a grid search constructs thousands of models."""
+    return _chain_table(str(robot_name).lower())
+
+
+@functools.lru_cache(maxsize=None)
+def _chain_table(name):
     try:
-        r = _ROBOTS[str(robot_name).lower()]
+        r = _ROBOTS[name]
     except KeyError:
-        raise ValueError(f"unknown robot {robot_name!r}: built-in chains are {sorted(_ROBOTS)}; use chain_from_urdf() for others")
+        raise ValueError(f"unknown robot {name!r}: built-in chains are {sorted(_ROBOTS)}; use chain_from_urdf() for others")
     rows = [_compose(r["root"])] + [_row(xyz, rpy) for xyz, rpy, _ in r["joints"]] + [_compose(r["ee"])]
-    return np.stack(rows), np.array([a for _, _, a in r["joints"]], dtype=np.int32)
+    xyzR, axis = np.stack(rows), np.array([a for _, _, a in r["joints"]], dtype=np.int32)
+    xyzR.setflags(write=False)
+    axis.setflags(write=False)
+    return xyzR, axis
 
 
 def chain_from_urdf(path, ee_frame, base_link=None):

@@ -15,15 +15,27 @@ class Robot:
         self._dt, self._N = float(dt), int(Nsim)
         self._z0, self._u0 = np.asarray(z0, float), np.asarray(u0, float)
         self.wcv = np.diag(np.asarray(wcv, float))
-        n = self._N + 1
-        self.z = np.zeros((12, n))
-        self.u = np.zeros((6, n))
-        self._ee_rpy_log = np.zeros((3, n))
-        self._ee_pose_log = np.zeros((12, n))
-        self._ee_velocity_log = np.zeros((6, n))
-        self.z[:, 0] = self._z0
-        self.u[:, 0] = self._u0
+        self._logs = None  # allocated on first access: a grid search builds thousands of these and most only get summaries
         self._integration_method_name = integration_method
+
+    def _alloc(self):
+        if self._logs is None:
+            n = self._N + 1
+            self._logs = {"z": np.zeros((12, n)), "u": np.zeros((6, n)), "_ee_rpy_log": np.zeros((3, n)),
+                          "_ee_pose_log": np.zeros((12, n)), "_ee_velocity_log": np.zeros((6, n))}
+            self._logs["z"][:, 0] = self._z0
+            self._logs["u"][:, 0] = self._u0
+        return self._logs
+
+    def _log_get(name):  # noqa: N805 -- property factory
+        return property(lambda self: self._alloc()[name], lambda self, v: self._alloc().__setitem__(name, v))
+
+    z = _log_get("z")
+    u = _log_get("u")
+    _ee_rpy_log = _log_get("_ee_rpy_log")
+    _ee_pose_log = _log_get("_ee_pose_log")
+    _ee_velocity_log = _log_get("_ee_velocity_log")
+    del _log_get
 
     def _load(self, zlog, ulog, plog, RK):
         """zlog [Nsim+1,12], ulog [Nsim,6], plog [Nsim+1,RK_COUNT] of this instance."""

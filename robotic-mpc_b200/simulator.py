@@ -260,45 +260,105 @@ def summary_from_row(row, w_task, nsteps=None):
     return out
 
 
+class _BatchRun:
+    """One batched closed loop in flight: engine + CUDA stream + the simulators it serves.  ``start`` uploads the problem
+    data, ``step(n)`` enqueues n closed-loop steps (asynchronous), ``finish`` downloads the results into the Simulator
+    objects and frees the engine.  Several of them can be in flight on different streams of one GPU."""
+
+    def __init__(self, sims, device=0, keep_logs=True, stream=None):
+        from .engine import Engine
+        from .trajectory_optimizer import bind_chain, bind_terminal
+        import torch
+
+        key = sims[0].static_key()
+        if any(s.static_key() != key for s in sims):
+            raise ValueError("run_batch: all simulators must share Nsim, horizon, dt, solver options, arm and terminal-set flag")
+        self.sims, self.keep_logs, self.torch = sims, keep_logs, torch
+        s0 = sims[0]
+        o = s0.mpc.ocp.solver_options
+        self.Nsim, self.done = s0.Nsim, 0
+        self.stream = stream
+        self.eng = Engine(len(sims), s0.prediction_horizon, o.nlp_solver_type, dt=s0.mpc.Tf / s0.mpc.N_horizon,
+                          nlog=self.Nsim if keep_logs else 0, device=device, max_iter=o.nlp_solver_max_iter,
+                          qp_iter_max=o.qp_solver_iter_max,
+                          tol=[o.nlp_solver_tol_stat, o.nlp_solver_tol_eq, o.nlp_solver_tol_ineq, o.nlp_solver_tol_comp],
+                          qp_tol=o.qp_tol, plant_dt=s0.dt)
+        try:
+            with self._on_stream():
+                bind_chain(self.eng, [s.mpc for s in sims])
+                bind_terminal(self.eng, [s.mpc for s in sims])
+                self.eng.set_params(np.stack([s.mpc.param_row() for s in sims]))
+                self.eng.set_state(np.stack([s.initial_state for s in sims]))
+                self.eng.reset()
+        except Exception:
+            self.eng.close()
+            raise
+
+    def _on_stream(self):
+        import contextlib
+
+        return self.torch.cuda.stream(self.stream) if self.stream is not None else contextlib.nullcontext()
+
+    def step(self, n=None):
+        n = self.Nsim - self.done if n is None else min(int(n), self.Nsim - self.done)
+        if n > 0:
+            with self._on_stream():
+                self.eng.closed_loop(n)
+            self.done += n
+        return self.done < self.Nsim
+
+    def finish(self):
+        try:
+            self.step()
+            with self._on_stream():
+                summ = self.eng.get("summary").cpu().numpy()
+                if self.keep_logs:
+                    zlog, ulog = self.eng.get("zlog").cpu().numpy(), self.eng.get("ulog").cpu().numpy()
+                    slog, plog = self.eng.get("slog").cpu().numpy(), self.eng.get("plog").cpu().numpy()
+            for i, s in enumerate(self.sims):
+                if self.keep_logs:
+                    s._load_logs(zlog[i], ulog[i], slog[i], plog[i], summ[i])
+                else:
+                    s._load_summary_only(summ[i])
+        finally:
+            self.eng.close()
+        return summ
+
+
 def run_batch(sims, device=0, keep_logs=True):
     """Run the closed loops of ``sims`` (all sharing one static key) as one batch on one GPU and load the results into
     the Simulator objects.  Returns the ``[B, RS_COUNT]`` summary array."""
-    from .engine import Engine
-
     if not sims:
         return np.zeros((0, RS["COUNT"]))
-    key = sims[0].static_key()
-    if any(s.static_key() != key for s in sims):
-        raise ValueError("run_batch: all simulators must share Nsim, horizon, dt and solver options")
-    s0 = sims[0]
-    o = s0.mpc.ocp.solver_options
-    B, Nsim = len(sims), s0.Nsim
-    eng = Engine(B, s0.prediction_horizon, o.nlp_solver_type, dt=s0.mpc.Tf / s0.mpc.N_horizon, nlog=Nsim if keep_logs else 0,
-                 device=device, max_iter=o.nlp_solver_max_iter, qp_iter_max=o.qp_solver_iter_max,
-                 tol=[o.nlp_solver_tol_stat, o.nlp_solver_tol_eq, o.nlp_solver_tol_ineq, o.nlp_solver_tol_comp],
-                 qp_tol=o.qp_tol, plant_dt=s0.dt)
+    return _BatchRun(sims, device=device, keep_logs=keep_logs).finish()
+
+
+def run_batches_concurrently(batches, device=0, keep_logs=True, chunk=25):
+    """Run several batches (lists of simulators, one static key each) of one GPU at the same time, each on its own CUDA stream:
+    a grid search usually yields a handful of groups that are each too small to fill the GPU (1024 instances occupy a fifth of
+    a B200), so their kernels are interleaved ``chunk`` closed-loop steps at a time.  Returns the summary arrays in order."""
+    import torch
+
+    batches = [b for b in batches]
+    if len(batches) <= 1:
+        return [run_batch(b, device=device, keep_logs=keep_logs) for b in batches]
+    runs = []
     try:
-        par = np.stack([s.mpc.param_row() for s in sims])
-        z0 = np.stack([s.initial_state for s in sims])
-        bind_chain(eng, [s.mpc for s in sims])
-        bind_terminal(eng, [s.mpc for s in sims])
-        if keep_logs:
-            eng.set_params(par)
-            eng.set_state(z0)
-            eng.reset()
-            eng.closed_loop(Nsim)
-            summ = eng.get("summary").cpu().numpy()
-            zlog, ulog = eng.get("zlog").cpu().numpy(), eng.get("ulog").cpu().numpy()
-            slog, plog = eng.get("slog").cpu().numpy(), eng.get("plog").cpu().numpy()
-            for i, s in enumerate(sims):
-                s._load_logs(zlog[i], ulog[i], slog[i], plog[i], summ[i])
-        else:
-            summ, _ = eng.run_host(par, z0, Nsim, want_u=False)
-            for i, s in enumerate(sims):
-                s._load_summary_only(summ[i])
+        with torch.cuda.device(device):
+            cur = torch.cuda.current_stream()
+            for b in batches:
+                st = torch.cuda.Stream()
+                st.wait_stream(cur)
+                runs.append(_BatchRun(b, device=device, keep_logs=keep_logs, stream=st))
+            active = list(runs)
+            while active:
+                active = [r for r in active if r.step(chunk)]
+            out = [r.finish() for r in runs]
+            runs = []
+            return out
     finally:
-        eng.close()
-    return summ
+        for r in runs:  # only on an error path: free what is still allocated
+            r.eng.close()
 
 
 class SimulationManager:
@@ -434,8 +494,9 @@ class SimulationManager:
             plan.append({"key": key, "indices": idx, "rank_chunks": chunks, "launches": launches})
         return plan
 
-    def run_all(self, return_results=True, device=None, max_batch=None, keep_logs=True):
-        """Run every queued simulation; one batched GPU launch per (static shape, rank).
+    def run_all(self, return_results=True, device=None, max_batch=None, keep_logs=True, concurrent=True):
+        """Run every queued simulation; one batched GPU run per (static shape, rank), all of a rank's runs in flight at the same
+        time on separate CUDA streams unless ``concurrent=False`` or ``max_batch`` splits them (memory-bound sweeps).
 
         ``return_results=True`` returns the reference's list of ``{'name','simulator','data','analysis','summary'}``
         (for instances solved by another rank only ``name`` and ``summary`` are filled).  ``keep_logs=False`` keeps
@@ -450,11 +511,21 @@ class SimulationManager:
         plan = self.plan_groups(sims, ws, max_batch)
         summaries = np.zeros((len(sims), RS["COUNT"]))
         launches = 0
+        concurrent = concurrent and not max_batch
+        if concurrent:
+            # all launches of this rank in flight at once, one stream each (groups of a grid search rarely fill the GPU alone)
+            flat = [[sims[i] for i in batch_idx] for g in plan for batch_idx in g["launches"][rank]]
+            rows = run_batches_concurrently(flat, device=device, keep_logs=keep_logs)
+            launches = len(flat)
+            it = iter(rows)
         for g in plan:
             local_rows = []
             for batch_idx in g["launches"][rank]:
-                local_rows.append(run_batch([sims[i] for i in batch_idx], device=device, keep_logs=keep_logs))
-                launches += 1
+                if concurrent:
+                    local_rows.append(next(it))
+                else:
+                    local_rows.append(run_batch([sims[i] for i in batch_idx], device=device, keep_logs=keep_logs))
+                    launches += 1
             local = np.concatenate(local_rows, 0) if local_rows else np.zeros((0, RS["COUNT"]))
             allrows = rdist.all_gather_rows(local, len(g["indices"])) if ws > 1 else local
             summaries[g["indices"]] = allrows

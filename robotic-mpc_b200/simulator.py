@@ -22,6 +22,7 @@ from itertools import product
 import numpy as np
 
 from . import distributed as rdist
+from .engine import RmpcError
 from .params import RK, RL, RS
 from .prediction_model import SixDofRobot
 from .simulation_model import Robot
@@ -346,10 +347,18 @@ def run_batches_concurrently(batches, device=0, keep_logs=True, chunk=25):
     try:
         with torch.cuda.device(device):
             cur = torch.cuda.current_stream()
-            for b in batches:
-                st = torch.cuda.Stream()
-                st.wait_stream(cur)
-                runs.append(_BatchRun(b, device=device, keep_logs=keep_logs, stream=st))
+            try:
+                for b in batches:
+                    st = torch.cuda.Stream()
+                    st.wait_stream(cur)
+                    runs.append(_BatchRun(b, device=device, keep_logs=keep_logs, stream=st))
+            except RmpcError as err:
+                if "allocation" not in str(err):
+                    raise
+                for r in runs:  # not enough device memory for all groups at once: one after the other instead
+                    r.eng.close()
+                runs = []
+                return [run_batch(b, device=device, keep_logs=keep_logs) for b in batches]
             active = list(runs)
             while active:
                 active = [r for r in active if r.step(chunk)]

@@ -61,18 +61,41 @@ def algorithmic_flops_per_mpc_step(N, n_ipm, n_fun=2.0):
     return N * 9128.0 + n_ipm * N * 17300.0 + n_fun * N * 2100.0
 
 
+def _ncu_capture_metrics(path):
+    """{metric: value in base units} of one committed ncu capture: either the 3-column `metric,unit,value` summary or ncu's
+    raw wide page (`--page raw --csv`: a header row of metric names, a row of units, a row of values)."""
+    import csv
+
+    scale = {"Tbyte": 1e12, "Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "ms": 1e-3, "us": 1e-6, "ns": 1e-9,
+             "s": 1.0, "msecond": 1e-3, "usecond": 1e-6, "nsecond": 1e-9, "second": 1.0}
+    rows = list(csv.reader(path.read_text().splitlines()))
+    out = {}
+    if rows and [c.strip() for c in rows[0][:3]] == ["metric", "unit", "value"]:
+        for r in rows[1:]:
+            if len(r) == 3:
+                try:
+                    out[r[0]] = float(r[2]) * scale.get(r[1], 1.0)
+                except ValueError:
+                    pass
+    elif len(rows) >= 3:
+        for name, unit, val in zip(rows[0], rows[1], rows[-1]):
+            try:
+                out[name] = float(val.replace(",", "")) * scale.get(unit, 1.0)
+            except ValueError:
+                pass
+    return out
+
+
 def ncu_dram_traffic():
-    """DRAM bytes (read + write) of ONE launch of the closed-loop kernel from the most recent committed `ncu --set full`
-    capture (profiles/r*_ncu_full_closed_loop_kernel.csv; same batch and horizon as the bench workload).  None if absent."""
-    best = sorted((ROOT / "profiles").glob("r*_ncu_full_closed_loop_kernel.csv"))
-    if not best:
-        return None, None
-    tot, unit_scale = 0.0, {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12}
-    for ln in best[-1].read_text().splitlines():
-        p = ln.split(",")
-        if len(p) == 3 and p[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-            tot += float(p[2]) * unit_scale.get(p[1], 1.0)
-    return (tot or None), best[-1].name
+    """DRAM bytes (read + write) of ONE launch of the closed-loop kernel from the newest committed `ncu --set full` capture
+    that actually holds the two counters (profiles/r*_ncu_full_closed_loop_kernel.csv; same batch and horizon as the bench
+    workload), with the duration of that profiled launch.  (None, None, None) if there is none."""
+    for f in sorted((ROOT / "profiles").glob("r*_ncu_full_closed_loop_kernel.csv"), reverse=True):
+        m = _ncu_capture_metrics(f)
+        rd, wr = m.get("dram__bytes_read.sum"), m.get("dram__bytes_write.sum")
+        if rd and wr:
+            return rd + wr, f.name, m.get("gpu__time_duration.sum")
+    return None, None, None
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -126,9 +149,12 @@ class ClockSampler:
 def _cpu_worker(args):
     """One single-threaded process: closed loops of `warm + steps` MPC steps for its instances; returns the wall
     time of the timed steps (per-step timing inside the C closed loop is acados' own time_tot for the ref leg)."""
-    kind, N, surfs, z0s, warm, steps = args
+    kind, N, surfs, z0s, warm, steps, core = args
     from oracle import pyoracle as o
     import ctypes as C
+
+    if core is not None and hasattr(os, "sched_setaffinity"):
+        os.sched_setaffinity(0, {core})  # one single-threaded process per host core, pinned (BASELINE.md 2)
 
     leg = o.RefLeg() if kind == "reference" else o.PortLeg()
     pre = "rmpc_ref" if kind == "reference" else "rmpc_oracle"
@@ -180,22 +206,33 @@ def cpu_leg(N, warm, steps, inst_per_core=None, seed=44, target_seconds=12.0):
     from multiprocessing import get_context
     from oracle import pyoracle as o
 
-    kind = "reference" if o.REF_SO.exists() else "port"
-    if kind == "port" and not o.PORT_SO.exists():
-        o.build(which=("port",))
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    import ctypes
+
+    kind, note = "reference", None
+    if not o.REF_SO.exists():
+        # the reference compiled in the build container (oracle/ref.mk) and its .so travels with the repo; if it is not there
+        # the CPU arm is the plain-C port of the same algorithm -- said loudly, in the line and on stderr
+        kind, note = "port", f"{o.REF_SO} is missing: timing the oracle port instead of the compiled reference"
+        print("bench.py: WARNING: " + note, file=sys.stderr)
+        if not o.PORT_SO.exists():
+            o.build(which=("port",))
+    lib_path = o.REF_SO if kind == "reference" else o.PORT_SO
+    ctypes.CDLL(str(lib_path))  # loaded in THIS process as well, so that the driver's record of loaded libraries shows the arm
+    cpus = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
+    cores = len(cpus)
     if inst_per_core is None:
         est = steps * 1.2e-3 * (N / 100.0)  # ~1.2 ms per N = 100 step and core
         inst_per_core = int(min(64, max(1, round(target_seconds / max(est, 1e-6)))))
     S = cores * inst_per_core
     surf, z0 = make_workload(S, seed)
-    jobs = [(kind, N, surf[c::cores], z0[c::cores], warm, steps) for c in range(cores)]
+    jobs = [(kind, N, surf[c::cores], z0[c::cores], warm, steps, cpus[c]) for c in range(cores)]
     with get_context("fork").Pool(cores) as pool:
         res = pool.map(_cpu_worker, jobs)
     tmax = max(r[0] for r in res)
     tot = sum(r[1] for r in res)
     lat = np.concatenate([np.asarray(r[2]) for r in res])
-    return {"value": tot / tmax, "unit": UNIT, "cores": cores, "kind": kind,
+    return {"value": tot / tmax, "unit": UNIT, "cores": cores, "kind": kind, "lib": str(lib_path.relative_to(ROOT)),
+            "pinned": hasattr(os, "sched_setaffinity"), "fallback_note": note,
             "sample": f"{S} instances ({inst_per_core} per core) x {steps} closed-loop steps from the initial state (the GPU arm's "
                       f"closed loop; {warm} untimed warm-up steps on a separate solver), N={N}, one single-threaded process "
                       f"per core, slowest process {tmax:.2f} s",

@@ -31,7 +31,12 @@ static_assert(sizeof(rmpc_dims) == sizeof(RmpcDims), "rmpc_dims / RmpcDims layou
 #ifndef RMPC_MIN_CTAS
 #define RMPC_MIN_CTAS 8
 #endif
-__global__ void __launch_bounds__(32 * RMPC_WARPS_PER_CTA, RMPC_MIN_CTAS)
+#ifdef RMPC_MAXNREG
+#define RMPC_KERNEL_BOUNDS __maxnreg__(RMPC_MAXNREG)
+#else
+#define RMPC_KERNEL_BOUNDS __launch_bounds__(32 * RMPC_WARPS_PER_CTA, RMPC_MIN_CTAS)
+#endif
+__global__ void RMPC_KERNEL_BOUNDS
 rmpc_closed_loop_kernel(const __grid_constant__ RmpcChain ch, const __grid_constant__ RmpcDims D, const __grid_constant__ RmpcWs W, int nsteps,
                         int advance)
 {
@@ -132,6 +137,27 @@ static int fail(rmpc_handle *h, int code, const std::string &msg)
         if (e_ != cudaSuccess) return fail(h, RMPC_ECUDA, std::string(#call ": ") + cudaGetErrorString(e_)); \
     } while (0)
 
+/* Every entry point runs on the handle's device and puts the caller's current device back on every exit path (PyTorch
+ * reads the current device from the runtime: an Engine on device k must not switch the process to k as a side effect). */
+struct DeviceGuard
+{
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = (cudaSetDevice(dev) == cudaSuccess);
+        else prev = -1; /* nothing to restore */
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+#define ON_DEVICE(h)                                                                          \
+    DeviceGuard dev_guard_((h)->device);                                                      \
+    if (!dev_guard_.ok) return fail((h), RMPC_ECUDA, "cudaSetDevice failed for the handle's device")
+
 static int grid_for(long n) { long g = (n + 255) / 256; return (int) (g < 1 ? 1 : (g > 148 * 8 ? 148 * 8 : g)); }
 
 extern "C" const char *rmpc_last_error(const rmpc_handle *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
@@ -142,7 +168,7 @@ extern "C" long long rmpc_launch_count(const rmpc_handle *h) { return h ? h->lau
 extern "C" int rmpc_destroy(rmpc_handle *h)
 {
     if (!h) return 0;
-    cudaSetDevice(h->device);
+    DeviceGuard g(h->device);
     for (void *p : h->owned) cudaFree(p);
     delete h;
     return 0;
@@ -159,7 +185,8 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || device < 0 || device >= ndev)
         return fail(nullptr, RMPC_ENODEV, "rmpc_create: no usable CUDA device (this library has no host fallback)");
-    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, RMPC_ENODEV, "rmpc_create: cudaSetDevice failed");
+    DeviceGuard dev_guard_(device);
+    if (!dev_guard_.ok) return fail(nullptr, RMPC_ENODEV, "rmpc_create: cudaSetDevice failed");
     if (cudaFuncSetAttribute(rmpc_closed_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int) (sizeof(GrpSmem) * RMPC_GROUPS_PER_CTA)) != cudaSuccess)
         return fail(nullptr, RMPC_ECUDA, "rmpc_create: cannot reserve the shared memory the closed-loop kernel needs");
@@ -201,6 +228,13 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
         cudaGetLastError();
         rmpc_destroy(h);
         return fail(nullptr, RMPC_ENOMEM, "rmpc_create: device allocation failed");
+    }
+    /* the zero fills above run on the legacy default stream; the caller's streams may be non-blocking ones that are not
+     * ordered against it, so they must have landed before the first rmpc_set / rmpc_reset on any stream */
+    if (cudaDeviceSynchronize() != cudaSuccess)
+    {
+        rmpc_destroy(h);
+        return fail(nullptr, RMPC_ECUDA, "rmpc_create: zero-initialisation of the workspaces failed");
     }
     h->W.par = h->par_dev;
     h->W.nlog = nlog;
@@ -245,7 +279,7 @@ static int strided(rmpc_handle *h, double *packed, double *strided_base, long st
 extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const double *dev, void *stream)
 {
     if (!h || !field || !dev) return fail(h, RMPC_EINVAL, "rmpc_set: null argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const long S = h->D.N + 1;
     const std::string f(field);
@@ -285,7 +319,7 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
 extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
 {
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_reset: null handle");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B, S = (size_t) h->D.N + 1;
     (void) S;
@@ -306,23 +340,42 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
 /* ---- checkpoint / resume of the complete solver + plant state of the batch (AcadosOcpSolver.store_iterate / load_iterate,
  * T/acados_ocp_solver.py:1158-1440, extended to everything a closed loop carries: iterate, multipliers, merit weights, QP
  * memory, plant state, flags, accumulated summaries, step counter).  Blob = [magic, B, N, steps_done | slab | z | summary | flags]. */
-static const double RMPC_STATE_MAGIC = 20240611.0;
+static const double RMPC_STATE_MAGIC = 20261104.0;
+#define RMPC_STATE_HDR 8
+/* header = [magic, B, N, steps_done, solver_type, terminal row on/off, shift option, checksum of the chain table]: a blob
+ * only loads into a handle whose solver semantics match (flags[] and the merit weights mean different things for SQP and
+ * SQP_RTI; the iterate of another arm or another shift setting continues a different closed loop).  NOT in the blob: the
+ * parameters ("par", terminal set, chain) -- set them again on the new handle -- and the per-step logs, whose rows below
+ * the resume point stay zero. */
+static double chain_checksum(const RmpcChain &ch)
+{
+    double s = 0.0;
+    const double *p = &ch.Rfix[0][0];
+    for (size_t k = 0; k < sizeof(RmpcChain) / sizeof(double); k++) s += (double) (k + 1) * p[k];
+    return s;
+}
+static void state_header(const rmpc_handle *h, double *hdr)
+{
+    hdr[0] = RMPC_STATE_MAGIC; hdr[1] = h->D.B; hdr[2] = h->D.N; hdr[3] = h->steps_done;
+    hdr[4] = h->D.solver_type; hdr[5] = h->pe_dev ? 1.0 : 0.0; hdr[6] = h->W.shift; hdr[7] = chain_checksum(h->ch);
+}
 extern "C" long long rmpc_state_size(const rmpc_handle *h)
 {
     if (!h) return 0;
     const long long B = h->D.B;
-    return 4 + B * h->W.slab_stride + B * NX + B * RS_COUNT + B * 2;
+    return RMPC_STATE_HDR + B * h->W.slab_stride + B * NX + B * RS_COUNT + B * 2;
 }
 
 extern "C" int rmpc_store_state(rmpc_handle *h, double *dev, void *stream)
 {
     if (!h || !dev) return fail(h, RMPC_EINVAL, "rmpc_store_state: null argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B;
-    const double hdr[4] = {RMPC_STATE_MAGIC, (double) h->D.B, (double) h->D.N, (double) h->steps_done};
+    double hdr[RMPC_STATE_HDR];
+    state_header(h, hdr);
     CU(cudaMemcpyAsync(dev, hdr, sizeof(hdr), cudaMemcpyHostToDevice, s)); /* pageable source: staged before the call returns */
-    double *p = dev + 4;
+    double *p = dev + RMPC_STATE_HDR;
     CU(cudaMemcpyAsync(p, h->W.slab, sizeof(double) * B * (size_t) h->W.slab_stride, cudaMemcpyDeviceToDevice, s));
     p += B * (size_t) h->W.slab_stride;
     CU(cudaMemcpyAsync(p, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s));
@@ -336,15 +389,20 @@ extern "C" int rmpc_store_state(rmpc_handle *h, double *dev, void *stream)
 extern "C" int rmpc_load_state(rmpc_handle *h, const double *dev, void *stream)
 {
     if (!h || !dev) return fail(h, RMPC_EINVAL, "rmpc_load_state: null argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B;
-    double hdr[4] = {0, 0, 0, 0};
+    double hdr[RMPC_STATE_HDR] = {0}, want[RMPC_STATE_HDR];
     CU(cudaMemcpyAsync(hdr, dev, sizeof(hdr), cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
-    if (hdr[0] != RMPC_STATE_MAGIC || hdr[1] != (double) h->D.B || hdr[2] != (double) h->D.N || hdr[3] < 0)
+    state_header(h, want);
+    if (hdr[0] != RMPC_STATE_MAGIC || hdr[1] != want[1] || hdr[2] != want[2] || hdr[3] < 0)
         return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob was not stored by a handle with this B and N");
-    const double *p = dev + 4;
+    if (hdr[4] != want[4]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another solver type");
+    if (hdr[5] != want[5]) return fail(h, RMPC_EINVAL, "rmpc_load_state: terminal row on in one handle and off in the other (set it before loading)");
+    if (hdr[6] != want[6]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another shift option");
+    if (hdr[7] != want[7]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another kinematic chain");
+    const double *p = dev + RMPC_STATE_HDR;
     CU(cudaMemcpyAsync(h->W.slab, p, sizeof(double) * B * (size_t) h->W.slab_stride, cudaMemcpyDeviceToDevice, s));
     p += B * (size_t) h->W.slab_stride;
     CU(cudaMemcpyAsync(h->W.z, p, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s));
@@ -370,7 +428,7 @@ static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
 extern "C" int rmpc_solve(rmpc_handle *h, void *stream)
 {
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve: null handle");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     h->W.rti_phase = 0;
     return launch_loop(h, 1, 0, (cudaStream_t) stream);
 }
@@ -380,7 +438,7 @@ extern "C" int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream)
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: null handle");
     if (h->D.solver_type != RMPC_SOLVER_SQP_RTI) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: rti_phase is only supported for SQP_RTI");
     if (phase < 0 || phase > 2) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: phase must be 0, 1 or 2");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     h->W.rti_phase = phase;
     int rc = launch_loop(h, 1, 0, (cudaStream_t) stream);
     h->W.rti_phase = 0;
@@ -390,7 +448,7 @@ extern "C" int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream)
 extern "C" int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream)
 {
     if (!h || nsteps < 0) return fail(h, RMPC_EINVAL, "rmpc_closed_loop: bad argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     if (nsteps == 0) return 0;
     /* One launch per closed-loop step by default: a launch boundary puts every instance of the batch back in the same
      * phase (linearise / factorise / substitute ...).  Measured on B200 (4096 x N=100): 447k steps/s at 1 step per
@@ -412,7 +470,7 @@ extern "C" int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream)
 extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *dev, void *stream)
 {
     if (!h || !field || !dev) return fail(h, RMPC_EINVAL, "rmpc_get: null argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const long B = h->D.B, S = h->D.N + 1;
     const std::string f(field);
@@ -462,7 +520,7 @@ extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const doubl
                              double *u_last_host, void *stream)
 {
     if (!h || !par_host || !z0_host || nsteps < 0) return fail(h, RMPC_EINVAL, "rmpc_run_host: bad argument");
-    CU(cudaSetDevice(h->device));
+    ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B;
     CU(cudaMemcpyAsync(h->par_dev, par_host, sizeof(double) * B * RP_COUNT, cudaMemcpyHostToDevice, s));

@@ -72,7 +72,14 @@ EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_devi
 
 
 class RmpcError(RuntimeError):
-    pass
+    """Error of the C ABI; ``code`` is the RMPC_E* return value (include/rmpc.h), None for host-side errors."""
+
+    def __init__(self, msg, code=None):
+        super().__init__(msg)
+        self.code = code
+
+
+RMPC_EINVAL, RMPC_ENODEV, RMPC_ENOMEM, RMPC_ECUDA = -1, -2, -3, -4
 
 
 class Engine:
@@ -102,14 +109,14 @@ class Engine:
         h = C.c_void_p()
         rc = self.lib.rmpc_create(C.byref(d), self.device, self.nlog, C.byref(h))
         if rc != 0:
-            raise RmpcError(f"rmpc_create failed ({rc}): {self.lib.rmpc_last_error(None).decode()}")
+            raise RmpcError(f"rmpc_create failed ({rc}): {self.lib.rmpc_last_error(None).decode()}", rc)
         self.h = h
         self.tdev = torch.device("cuda", self.device)
 
     # ------------------------------------------------------------------ helpers
     def _check(self, rc, what):
         if rc != 0:
-            raise RmpcError(f"{what} failed ({rc}): {self.lib.rmpc_last_error(self.h).decode()}")
+            raise RmpcError(f"{what} failed ({rc}): {self.lib.rmpc_last_error(self.h).decode()}", rc)
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.tdev).cuda_stream)

@@ -22,7 +22,7 @@ from itertools import product
 import numpy as np
 
 from . import distributed as rdist
-from .engine import RmpcError
+from .engine import RMPC_ENOMEM, RmpcError
 from .params import RK, RL, RS
 from .prediction_model import SixDofRobot
 from .simulation_model import Robot
@@ -352,12 +352,13 @@ def run_batches_concurrently(batches, device=0, keep_logs=True, chunk=25):
                     st = torch.cuda.Stream()
                     st.wait_stream(cur)
                     runs.append(_BatchRun(b, device=device, keep_logs=keep_logs, stream=st))
-            except RmpcError as err:
-                if "allocation" not in str(err):
+            except (RmpcError, torch.cuda.OutOfMemoryError) as err:
+                if isinstance(err, RmpcError) and err.code != RMPC_ENOMEM:
                     raise
                 for r in runs:  # not enough device memory for all groups at once: one after the other instead
                     r.eng.close()
                 runs = []
+                torch.cuda.empty_cache()  # the engines' cudaMalloc competes with torch's cached free blocks
                 return [run_batch(b, device=device, keep_logs=keep_logs) for b in batches]
             active = list(runs)
             while active:

@@ -371,7 +371,7 @@ def run_gpu(args):
         fp64_peak = fp64_peak_tflops(torch, dev)
         flops_step = algorithmic_flops_per_mpc_step(N, qp_iters_per_step) * B
         achieved_tf = flops_step / (kernel_ms * 1e-3) / 1e12
-        traffic, traffic_src = ncu_dram_traffic() if (B == 4096 and N == 100) else (None, None)
+        traffic, traffic_src, traffic_dur = ncu_dram_traffic() if (B == 4096 and N == 100) else (None, None, None)
         cb = None
         if not args.no_cpu_baseline and world == 1:  # reported at N = 1 only; multi-GPU runs carry cpu_baseline = null
             cb, _, _ = cpu_leg(N, 3, K)

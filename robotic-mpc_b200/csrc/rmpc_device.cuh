@@ -155,7 +155,11 @@ struct GrpSmem
 /* group-wide asynchronous copy of n doubles (n even, both sides 16-byte aligned) global -> shared */
 RD void stage_cp(double *dst, const double *src, const int n)
 {
-    for (int c = rd_lane(); c < n / 2; c += GL) rd_cp_async16(dst + 2 * c, src + 2 * c);
+    /* n is a compile-time constant at every call site: fully unrolled, the chunk offsets become immediates */
+    const int l2 = 2 * rd_lane();
+    RD_UNROLL
+    for (int c = 0; c < (n / 2 + GL - 1) / GL; c++)
+        if ((c + 1) * GL <= n / 2 || rd_lane() + c * GL < n / 2) rd_cp_async16(dst + l2 + 2 * GL * c, src + l2 + 2 * GL * c);
 }
 
 /* Flat group-wide vector updates with the loads of four strides issued before the first use (memory-level
@@ -226,7 +230,10 @@ struct Inst
  * the interior-point loop (different iteration counts); once apart, the warp issues every instruction twice at half
  * width.  At places that every group passes exactly once per step they wait for each other and run in lock step again. */
 #define PAIR_SYNC() rd_sync_mask(I.pair)
-#define AR(name) (I.arr0 + (long) RC_##name * I.Sp)
+/* stage-major slab (rmpc_types.h): AR(name) = array <name> of stage 0, SO(i) = offset of stage i's record */
+#define REC RMPC_REC
+#define SO(i) (REC * (i))
+#define AR(name) (I.arr0 + RC_##name)
 
 RD Inst inst_view(const RmpcWs &w, int N, long i)
 {
@@ -250,8 +257,8 @@ RD double psym(const double *P, int r, int c) { return r >= c ? P[(r * (r + 1)) 
  * lane and, with `grad`, writes the gradient 2 P x (the stage-N row of DCt).  Replaces the CasADi-generated
  * *_constr_h_e_fun[_jac_uxt_zt] pair that acados' BGH module would call (AC/ocp_nlp/ocp_nlp_constraints_bgh.c:
  * 1219-1445,1563-1619) for con_h_expr_e = x' P x with P from R/_terminal_constraint.py:96-116. */
-#define TERM_LO(N) (NB * (N))      /* slot of the lower side lh - h_e in the NB-wide per-stage arrays */
-#define TERM_UP(N) (NB * (N) + 12) /* slot of the upper side h_e - uh */
+#define TERM_LO(N) (SO(N))      /* slot of the lower side lh - h_e in the NB-wide per-stage arrays (stage N's record) */
+#define TERM_UP(N) (SO(N) + 12) /* slot of the upper side h_e - uh */
 RD double term_eval(const double *pe, const double *x, double *grad)
 {
     const int l = rd_lane();
@@ -610,10 +617,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
     for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
-        load18(AR(ux) + NV * i, v);
-        double *g = AR(rqz) + NV * i;
+        load18(AR(ux) + SO(i), v);
+        double *g = AR(rqz) + SO(i);
         LinEmit em;
-        em.Jc = AR(Jc) + NJ * i;
+        em.Jc = AR(Jc) + SO(i);
         em.g = g;
         const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
         RD_UNROLL
@@ -629,10 +636,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
         const double ci = stage_cost(par, dt, y5, v, v + 12);
         cost += ci;
-        AR(tux)[NV * i] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
+        AR(tux)[SO(i)] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
         /* dynamics gap b = Ad x + Bd u - x_next */
-        const double *xn = AR(ux) + NV * (i + 1) + 6;
-        double *b = AR(b) + NX * i, *d = AR(d) + NB * i;
+        const double *xn = AR(ux) + SO(i + 1) + 6;
+        double *b = AR(b) + SO(i), *d = AR(d) + SO(i);
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -651,10 +658,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
             for (int k = 0; k < NX; k++) (I.head + H_DX0)[k] = x0[k] - v[6 + k];
         }
     }
-    for (int k = lane; k < NV; k += GL) AR(rqz)[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
+    for (int k = lane; k < NV; k += GL) AR(rqz)[SO(N) + k] = 0.0; /* stage N: no cost (ny_e = 0) */
     if (I.pe)
     { /* terminal row: fun = [lh - h_e; h_e - uh], DCt = grad h_e (kept in Jc[N][0..11]) */
-        const double h = term_eval(I.pe, AR(ux) + NV * N + 6, AR(Jc) + NJ * N);
+        const double h = term_eval(I.pe, AR(ux) + SO(N) + 6, AR(Jc) + SO(N));
         if (lane == 0)
         {
             AR(d)[TERM_LO(N)] = I.pe[RE_LH] - h;
@@ -678,13 +685,13 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
     for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
-        load18(tux + NV * i, v);
+        load18(tux + SO(i), v);
         NoEmit ne;
         ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
         const double ci = stage_cost(par, D.dt, y5, v, v + 12);
         m += ci;
         csum += ci; /* the cost alone, summed like solver.get_cost() does (closed_loop_group) */
-        const double *xn = tux + NV * (i + 1) + 6, *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i;
+        const double *xn = tux + SO(i + 1) + 6, *wpi = AR(wpi) + SO(i), *wl = AR(wlam) + SO(i);
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -713,7 +720,7 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
     }
     if (I.pe)
     {
-        const double h = term_eval(I.pe, tux + NV * N + 6, nullptr);
+        const double h = term_eval(I.pe, tux + SO(N) + 6, nullptr);
         const double fl = I.pe[RE_LH] - h, fu = h - I.pe[RE_UH];
         if (lane == 0)
         {
@@ -736,8 +743,8 @@ RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
     double m = 0.0;
     for (int i = lane; i < N; i += GL)
     {
-        m += AR(tux)[NV * i];
-        const double *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i, *d = AR(d) + NB * i;
+        m += AR(tux)[SO(i)];
+        const double *wpi = AR(wpi) + SO(i), *wl = AR(wlam) + SO(i), *d = AR(d) + SO(i);
         if (i == 0)
         {
             const double *v = AR(ux), *xn = AR(ux) + NV + 6;
@@ -751,7 +758,7 @@ RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
         }
         else
         {
-            const double *b = AR(b) + NX * i;
+            const double *b = AR(b) + SO(i);
             RD_UNROLL
             for (int k = 0; k < 6; k++) m += fabs(wpi[k]) * fabs(b[k]) + fabs(wpi[6 + k]) * fabs(b[6 + k]);
         }
@@ -795,10 +802,10 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
     {
         double r[NV];
         RD_UNROLL
-        for (int k = 0; k < NV; k++) r[k] = AR(rqz)[NV * i + k];
+        for (int k = 0; k < NV; k++) r[k] = AR(rqz)[SO(i) + k];
         if (i < N)
         {
-            const double *lam = AR(lam) + NB * i, *pi = AR(pi) + NX * i, *d = AR(d) + NB * i;
+            const double *lam = AR(lam) + SO(i), *pi = AR(pi) + SO(i), *d = AR(d) + SO(i);
             RD_UNROLL
             for (int j = 0; j < 12; j++)
             {
@@ -813,7 +820,7 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
                 r[k] += par[RP_B1 + k] * pi[k] + par[RP_B2 + k] * pi[6 + k];
                 r[6 + k] += pi[k];
                 r[12 + k] += par[RP_A12 + k] * pi[k] + par[RP_A22 + k] * pi[6 + k];
-                re = rd_fmax(re, rd_fmax(fabs(AR(b)[NX * i + k]), fabs(AR(b)[NX * i + 6 + k])));
+                re = rd_fmax(re, rd_fmax(fabs(AR(b)[SO(i) + k]), fabs(AR(b)[SO(i) + 6 + k])));
             }
         }
         if (i == 0)
@@ -830,13 +837,13 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
         else
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[NX * (i - 1) + k];
+            for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[SO(i - 1) + k];
         }
         if (i == N && I.pe)
         { /* terminal row: adj += DCt (lam_l - lam_u) */
             const double ll = AR(lam)[TERM_LO(N)], lu = AR(lam)[TERM_UP(N)], fl = AR(d)[TERM_LO(N)], fu = AR(d)[TERM_UP(N)];
             RD_UNROLL
-            for (int k = 0; k < NX; k++) r[6 + k] -= (AR(Jc) + NJ * N)[k] * (ll - lu);
+            for (int k = 0; k < NX; k++) r[6 + k] -= (AR(Jc) + SO(N))[k] * (ll - lu);
             ri = rd_fmax(ri, rd_fmax(fl, fu));
             rc = rd_fmax(rc, rd_fmax(fabs(ll * fl), fabs(lu * fu)));
         }
@@ -883,7 +890,7 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
     {
         const int i = k / 12, j = k - 12 * i;
         if (i == 0 && j >= 6) continue;
-        double *lam = AR(slam) + NB * i, *t = AR(st) + NB * i;
+        double *lam = AR(slam) + SO(i), *t = AR(st) + SO(i);
         if (warm == 2)
         {
             if (lam[j] < 1e-1) lam[j] = 1e-1;
@@ -893,7 +900,7 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
         }
         else
         {
-            const double thr0 = 1e-1, dl = AR(d)[NB * i + j], du = AR(d)[NB * i + 12 + j];
+            const double thr0 = 1e-1, dl = AR(d)[SO(i) + j], du = AR(d)[SO(i) + 12 + j];
             double v = 0.0, tl = -dl, tu = -du;
             if (tl < thr0)
             {
@@ -901,7 +908,7 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
                 else { tl = thr0; v = dl + thr0; }
             }
             else if (tu < thr0) { tu = thr0; v = -du - thr0; }
-            AR(sux)[NV * i + j] = v;
+            AR(sux)[SO(i) + j] = v;
             t[j] = tl; t[12 + j] = tu;
             lam[j] = 1.0 / tl; lam[12 + j] = 1.0 / tu;
         }
@@ -967,9 +974,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
     for (int i = lane; i <= N; i += GL)
     {
         double v[NV], g[NV];
-        load18(ux + NV * i, v);
+        load18(ux + SO(i), v);
         RD_UNROLL
-        for (int k = 0; k < NV; k++) g[k] = rqz[NV * i + k];
+        for (int k = 0; k < NV; k++) g[k] = rqz[SO(i) + k];
         if (i == 0)
         {
             RD_UNROLL
@@ -978,9 +985,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         if (i < N)
         {
             /* H v: task part on x (stages >= 1), constant diagonal blocks */
-            if (i > 0) task_hess_mv(AR(Jc) + NJ * i, v + 6, g + 6);
-            const double *pin = pi + NX * i, *l = lam + NB * i, *tt = t + NB * i;
-            const double *xn = ux + NV * (i + 1) + 6;
+            if (i > 0) task_hess_mv(AR(Jc) + SO(i), v + 6, g + 6);
+            const double *pin = pi + SO(i), *l = lam + SO(i), *tt = t + SO(i);
+            const double *xn = ux + SO(i + 1) + 6;
             RD_UNROLL
             for (int k = 0; k < 6; k++)
             {
@@ -992,9 +999,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
                     g[6 + k] += pin[k];
                     g[12 + k] += hs * v[k] + hq * v[12 + k] + a12 * pin[k] + a22 * pin[6 + k];
                 }
-                const double r0 = b[NX * i + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
-                const double r1 = b[NX * i + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
-                if (WRITE) { rb[NX * i + k] = r0; rb[NX * i + 6 + k] = r1; }
+                const double r0 = b[SO(i) + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
+                const double r1 = b[SO(i) + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
+                if (WRITE) { rb[SO(i) + k] = r0; rb[SO(i) + 6 + k] = r1; }
                 n1 = rd_fmax(n1, rd_fmax(fabs(r0), fabs(r1)));
             }
             RD_UNROLL
@@ -1002,16 +1009,16 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
             {
                 if (i == 0 && j >= 6) continue;
                 g[j] += l[12 + j] - l[j];
-                const double dl = d[NB * i + j] + tt[j] - v[j], du = d[NB * i + 12 + j] + tt[12 + j] + v[j];
-                if (WRITE) { rd[NB * i + j] = dl; rd[NB * i + 12 + j] = du; }
+                const double dl = d[SO(i) + j] + tt[j] - v[j], du = d[SO(i) + 12 + j] + tt[12 + j] + v[j];
+                if (WRITE) { rd[SO(i) + j] = dl; rd[SO(i) + 12 + j] = du; }
                 double ml, mu_;
                 if (!LIN) { ml = l[j] * tt[j]; mu_ = l[12 + j] * tt[12 + j]; mu += ml + mu_; }
                 else
                 {
-                    ml = (m[NB * i + j] - mshift) + Lam[NB * i + j] * tt[j] + l[j] * T[NB * i + j];
-                    mu_ = (m[NB * i + 12 + j] - mshift) + Lam[NB * i + 12 + j] * tt[12 + j] + l[12 + j] * T[NB * i + 12 + j];
+                    ml = (m[SO(i) + j] - mshift) + Lam[SO(i) + j] * tt[j] + l[j] * T[SO(i) + j];
+                    mu_ = (m[SO(i) + 12 + j] - mshift) + Lam[SO(i) + 12 + j] * tt[12 + j] + l[12 + j] * T[SO(i) + 12 + j];
                 }
-                if (WRITE) { rm[NB * i + j] = ml; rm[NB * i + 12 + j] = mu_; }
+                if (WRITE) { rm[SO(i) + j] = ml; rm[SO(i) + 12 + j] = mu_; }
                 n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
                 n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
                 n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
@@ -1020,11 +1027,11 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         if (i > 0)
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) g[6 + k] -= pi[NX * (i - 1) + k];
+            for (int k = 0; k < NX; k++) g[6 + k] -= pi[SO(i - 1) + k];
         }
         if (i == N && I.pe)
         { /* general row C x of stage N: res_g += C' (lam_u - lam_l), res_d = d + t -+ C x, res_m */
-            const double *c = AR(Jc) + NJ * N;
+            const double *c = AR(Jc) + SO(N);
             const int ka = TERM_LO(N), kb = TERM_UP(N);
             double cx = 0.0;
             RD_UNROLL
@@ -1048,7 +1055,7 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         RD_UNROLL
         for (int k = 0; k < NV; k++)
         {
-            if (WRITE) rg[NV * i + k] = g[k];
+            if (WRITE) rg[SO(i) + k] = g[k];
             if ((i < N || k >= 6) && (i > 0 || k < 6)) n0 = rd_fmax(n0, fabs(g[k]));
         }
         if (i == 0 && g[0] != g[0]) nanflag = 1.0;
@@ -1104,13 +1111,13 @@ RD void smem_consts(const Inst &I, GrpSmem &sm, double dt)
 enum { FG_LAM = 0, FG_T = 24, FG_RD = 48, FG_RM = 72, FG_RG = 96, FG_RB = 114, FG_JC = 126 };
 RD void fac_stage_in(const Inst &I, double *dst, int ss)
 {
-    stage_cp(dst + FG_LAM, AR(slam) + NB * ss, NB);
-    stage_cp(dst + FG_T, AR(st) + NB * ss, NB);
-    stage_cp(dst + FG_RD, AR(res_d) + NB * ss, NB);
-    stage_cp(dst + FG_RM, AR(res_m) + NB * ss, NB);
-    stage_cp(dst + FG_RG, AR(res_g) + NV * ss, NV);
-    stage_cp(dst + FG_RB, AR(res_b) + NX * ss, NX);
-    if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
+    stage_cp(dst + FG_LAM, AR(slam) + SO(ss), NB);
+    stage_cp(dst + FG_T, AR(st) + SO(ss), NB);
+    stage_cp(dst + FG_RD, AR(res_d) + SO(ss), NB);
+    stage_cp(dst + FG_RM, AR(res_m) + SO(ss), NB);
+    stage_cp(dst + FG_RG, AR(res_g) + SO(ss), NV);
+    stage_cp(dst + FG_RB, AR(res_b) + SO(ss), NX);
+    if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + SO(ss), NJ);
 }
 
 RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
@@ -1128,14 +1135,14 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
     if (R.x)
     {
-        double *FN = AR(F) + (long) FS * N;
-        double pv = AR(res_g)[NV * N + 6 + xk];
+        double *FN = AR(F) + SO(N);
+        double pv = AR(res_g)[SO(N) + 6 + xk];
         double Prow[12];
         RD_UNROLL
         for (int c = 0; c < 12; c++) Prow[c] = (c == xk) ? reg : 0.0;
         if (I.pe)
         { /* general row of stage N (x_ocp_qp_kkt.c:859-868): P_N += C' Gamma C, p_N += C' gamma */
-            const double *cv = AR(Jc) + NJ * N;
+            const double *cv = AR(Jc) + SO(N);
             const int ka = TERM_LO(N), kb = TERM_UP(N);
             const double til = 1.0 / AR(st)[ka], tiu = 1.0 / AR(st)[kb];
             const double la = AR(slam)[ka], lb = AR(slam)[kb];
@@ -1157,7 +1164,7 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        double *F = AR(F) + (long) FS * ss;
+        double *F = AR(F) + SO(ss);
         const double *G = FS_STG(sm, ss & 1);
         if (ss > 0) fac_stage_in(I, FS_STG(sm, (ss - 1) & 1), ss - 1);
         rd_cp_commit();
@@ -1358,20 +1365,20 @@ template <int STORED>
 RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rb, const double *rd, const double *rm,
                      const double *X)
 {
-    stage_cp(dst + WG_RG, rg + NV * ss, NV);
-    if (ss > 0) stage_cp(dst + WG_JC, AR(Jc) + NJ * ss, NJ);
-    const double *F = AR(F) + (long) FS * ss;
+    stage_cp(dst + WG_RG, rg + SO(ss), NV);
+    if (ss > 0) stage_cp(dst + WG_JC, AR(Jc) + SO(ss), NJ);
+    const double *F = AR(F) + SO(ss);
     stage_cp(dst, F, RF_P);
     stage_cp(dst + RF_P, F + FS + RF_P, STORED ? RF_PV - RF_P : RF_PB - RF_P);
-    stage_cp(dst + WG_LAM, AR(slam) + NB * ss, NB);
-    stage_cp(dst + WG_T, AR(st) + NB * ss, NB);
-    stage_cp(dst + WG_RD, rd + NB * ss, NB);
-    stage_cp(dst + WG_RM, rm + NB * ss, NB);
-    stage_cp(dst + WG_RB, rb + NX * ss, NX);
+    stage_cp(dst + WG_LAM, AR(slam) + SO(ss), NB);
+    stage_cp(dst + WG_T, AR(st) + SO(ss), NB);
+    stage_cp(dst + WG_RD, rd + SO(ss), NB);
+    stage_cp(dst + WG_RM, rm + SO(ss), NB);
+    stage_cp(dst + WG_RB, rb + SO(ss), NX);
     if (STORED)
     {
-        stage_cp(dst + WG_ZU, X + NV * ss, 6);
-        stage_cp(dst + WG_PVEC, AR(pvec) + NX * (ss + 1), NX);
+        stage_cp(dst + WG_ZU, X + SO(ss), 6);
+        stage_cp(dst + WG_PVEC, AR(pvec) + SO(ss + 1), NX);
     }
 }
 
@@ -1456,8 +1463,8 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             else xn = a22 * sm.xv[6 + j] + b2 * duj + G[WG_RB + 6 + j];
         }
         rd_sync(); /* every lane has read xv, uv */
-        if (R.u) X[NV * ss + lane] = dul;
-        if (R.x) { sm.xv[xk] = xn; X[NV * (ss + 1) + 6 + xk] = xn; }
+        if (R.u) X[SO(ss) + lane] = dul;
+        if (R.x) { sm.xv[xk] = xn; X[SO(ss + 1) + 6 + xk] = xn; }
         if (lane < 5) sm.wv[lane] = wm;
         rd_sync();
         /* dpi = P+ dx+ + p+ */
@@ -1467,7 +1474,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             double a = STORED ? G[WG_PVEC + xk] : G[RF_PV + xk];
             RD_UNROLL
             for (int c = 0; c < 12; c++) a += psym(G + RF_P, xk, c) * sm.xv[c];
-            PI[NX * ss + xk] = a;
+            PI[SO(ss) + xk] = a;
             sm.dp[xk] = a;
             dpo = a;
         }
@@ -1475,7 +1482,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         double dlm = 0.0; /* dlam_ub - dlam_lb of the own slot */
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
-            const int ia = NB * ss + lane, ib = ia + 12;
+            const int ia = SO(ss) + lane, ib = ia + 12;
             const double la = G[WG_LAM + lane], lb = G[WG_LAM + 12 + lane], ta = G[WG_T + lane], tb = G[WG_T + 12 + lane];
             const double da = G[WG_RD + lane], db = G[WG_RD + 12 + lane], ma = G[WG_RM + lane] - mshift, mb = G[WG_RM + 12 + lane] - mshift;
             const double dla = -(ma + (la * dv) - (la * da)) / ta;
@@ -1525,11 +1532,11 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         dp_prev = dpo;
     }
     rd_cp_wait0();
-    if (R.u) X[NV * N + lane] = 0.0;
+    if (R.u) X[SO(N) + lane] = 0.0;
     double dlmN = 0.0;
     if (I.pe)
     { /* general row of stage N: dv = C dx_N, then the same multiplier / slack step, step length and sums */
-        const double *cv = AR(Jc) + NJ * N;
+        const double *cv = AR(Jc) + SO(N);
         const double dv = grp_sum(R.x ? cv[xk] * sm.xv[xk] : 0.0);
         const int ia = TERM_LO(N), ib = TERM_UP(N);
         const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
@@ -1549,7 +1556,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         }
         if (R.x) dlmN = cv[xk] * (dlb - dla);
     }
-    if (R.x) n0 = rd_fmax(n0, fabs(rg[NV * N + 6 + xk] + dlmN - dp_prev)); /* stage N: no cost, no box bounds */
+    if (R.x) n0 = rd_fmax(n0, fabs(rg[SO(N) + 6 + xk] + dlmN - dp_prev)); /* stage N: no cost, no box bounds */
     rd_sync();
     *alpha_out = -grp_max(-alpha);
     sums[0] = grp_sum(sB);
@@ -1571,21 +1578,21 @@ enum { BG_PB = 100, BG_RG = 112, BG_LAM = 130, BG_T = 154, BG_RD = 178, BG_RM = 
 template <int MODE, int USE_PB>
 RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rd, const double *rm)
 {
-    const double *F = AR(F) + (long) FS * ss;
+    const double *F = AR(F) + SO(ss);
     stage_cp(dst, F, RF_P);
     if (USE_PB) stage_cp(dst + BG_PB, F + RF_PB, NX);
-    stage_cp(dst + BG_RG, rg + NV * ss, NV);
-    stage_cp(dst + BG_LAM, AR(slam) + NB * ss, NB);
-    stage_cp(dst + BG_T, AR(st) + NB * ss, NB);
-    stage_cp(dst + BG_RD, rd + NB * ss, NB);
-    if (MODE == 0) stage_cp(dst + BG_RM, rm + NB * ss, NB);
+    stage_cp(dst + BG_RG, rg + SO(ss), NV);
+    stage_cp(dst + BG_LAM, AR(slam) + SO(ss), NB);
+    stage_cp(dst + BG_T, AR(st) + SO(ss), NB);
+    stage_cp(dst + BG_RD, rd + SO(ss), NB);
+    if (MODE == 0) stage_cp(dst + BG_RM, rm + SO(ss), NB);
     else
     {
-        stage_cp(dst + BG_RM, AR(res_m) + NB * ss, NB);
+        stage_cp(dst + BG_RM, AR(res_m) + SO(ss), NB);
         if (MODE == 1)
         {
-            stage_cp(dst + BG_DT, AR(dt_) + NB * ss, NB);
-            stage_cp(dst + BG_DLAM, AR(dlam) + NB * ss, NB);
+            stage_cp(dst + BG_DT, AR(dt_) + SO(ss), NB);
+            stage_cp(dst + BG_DLAM, AR(dlam) + SO(ss), NB);
         }
     }
 }
@@ -1603,7 +1610,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
     rd_cp_commit();
     if (R.x)
     {
-        double pv = rg[NV * N + 6 + xk];
+        double pv = rg[SO(N) + 6 + xk];
         if (I.pe)
         { /* general row of stage N: p_N += C' gamma with the complementarity right-hand side of the MODE */
             const int ia = TERM_LO(N), ib = TERM_UP(N);
@@ -1620,10 +1627,10 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
                 else { ma = AR(res_m)[ia] - sigma_mu; mb = AR(res_m)[ib] - sigma_mu; }
                 if (xk == 0) { AR(res_mc)[ia] = ma; AR(res_mc)[ib] = mb; }
             }
-            pv += (AR(Jc) + NJ * N)[xk] * ((ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb);
+            pv += (AR(Jc) + SO(N))[xk] * ((ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb);
         }
         sm.pv[xk] = pv;
-        AR(pvec)[NX * N + xk] = pv;
+        AR(pvec)[SO(N) + xk] = pv;
     }
     for (int ss = N - 1; ss >= 0; ss--)
     {
@@ -1639,17 +1646,17 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             if (USE_PB) pb = G[BG_PB + xk];
             else
             {
-                const double *Fn = AR(F) + (long) FS * (ss + 1);
+                const double *Fn = AR(F) + SO(ss + 1);
                 pb = 0.0;
                 RD_UNROLL
-                for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[NX * ss + c];
+                for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[SO(ss) + c];
             }
             sm.tv[xk] = sm.pv[xk] + pb;
         }
         double gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
-            const int ia = NB * ss + lane, ib = ia + 12;
+            const int ia = SO(ss) + lane, ib = ia + 12;
             const double la = G[BG_LAM + lane], lb = G[BG_LAM + 12 + lane], ta = G[BG_T + lane], tb = G[BG_T + 12 + lane];
             double ma, mb;
             if (MODE == 0) { ma = G[BG_RM + lane]; mb = G[BG_RM + 12 + lane]; }
@@ -1687,14 +1694,14 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             RD_UNROLL
             for (int k = 1; k < 6; k++)
                 if (k == lane) zl = z[k];
-            X[NV * ss + lane] = zl;
+            X[SO(ss) + lane] = zl;
         }
         if (R.x && !s0)
         {
             RD_UNROLL
             for (int k = 0; k < 6; k++) rx -= G[RF_LXU + xk * 6 + k] * z[k];
             sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
-            AR(pvec)[NX * ss + xk] = rx;
+            AR(pvec)[SO(ss) + xk] = rx;
         }
         rd_sync();
     }
@@ -1708,7 +1715,7 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
     double a = 1.0;
     for (int k = lane; k < N * NB; k += GL)
     {
-        const int i = k / NB, j = k - NB * i;
+        const int i = k / NB, j = k - SO(i);
         if (i == 0 && (j % 12) >= 6) continue;
         const double dl = dlam[k], dtt = dt[k];
         if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
@@ -1731,7 +1738,7 @@ RD void ipm_mu_sums(const RmpcDims &D, const Inst &I, const double *dlam, const 
     double sB = 0.0, sC = 0.0;
     for (int k = lane; k < N * NB; k += GL)
     {
-        const int i = k / NB, j = k - NB * i;
+        const int i = k / NB, j = k - SO(i);
         if (i == 0 && (j % 12) >= 6) continue;
         sB += AR(slam)[k] * dt[k] + dlam[k] * AR(st)[k];
         sC += dlam[k] * dt[k];
@@ -1794,31 +1801,31 @@ template <int UPD>
 RD void res_stage_in(const Inst &I, double *dst, int i, int N)
 {
     const bool cons = (i < N) || I.pe; /* stage N carries constraint slots only with a terminal row */
-    stage_cp(dst + QG_UX, AR(sux) + NV * i, NV);
-    stage_cp(dst + QG_RQZ, AR(rqz) + NV * i, NV);
-    if (UPD) stage_cp(dst + QG_DUX, AR(dux) + NV * i, NV);
+    stage_cp(dst + QG_UX, AR(sux) + SO(i), NV);
+    stage_cp(dst + QG_RQZ, AR(rqz) + SO(i), NV);
+    if (UPD) stage_cp(dst + QG_DUX, AR(dux) + SO(i), NV);
     if (i < N)
     {
-        stage_cp(dst + QG_XN, AR(sux) + NV * (i + 1) + 6, NX);
-        stage_cp(dst + QG_PI, AR(spi) + NX * i, NX);
-        stage_cp(dst + QG_B, AR(b) + NX * i, NX);
+        stage_cp(dst + QG_XN, AR(sux) + SO(i + 1) + 6, NX);
+        stage_cp(dst + QG_PI, AR(spi) + SO(i), NX);
+        stage_cp(dst + QG_B, AR(b) + SO(i), NX);
         if (UPD)
         {
-            stage_cp(dst + QG_DXN, AR(dux) + NV * (i + 1) + 6, NX);
-            stage_cp(dst + QG_DPI, AR(dpi) + NX * i, NX);
+            stage_cp(dst + QG_DXN, AR(dux) + SO(i + 1) + 6, NX);
+            stage_cp(dst + QG_DPI, AR(dpi) + SO(i), NX);
         }
     }
     if (cons)
     {
-        stage_cp(dst + QG_LAM, AR(slam) + NB * i, NB);
-        stage_cp(dst + QG_T, AR(st) + NB * i, NB);
-        stage_cp(dst + QG_D, AR(d) + NB * i, NB);
+        stage_cp(dst + QG_LAM, AR(slam) + SO(i), NB);
+        stage_cp(dst + QG_T, AR(st) + SO(i), NB);
+        stage_cp(dst + QG_D, AR(d) + SO(i), NB);
         if (UPD)
         {
-            stage_cp(dst + QG_DLAM, AR(dlam) + NB * i, NB);
-            stage_cp(dst + QG_DT, AR(dt_) + NB * i, NB);
+            stage_cp(dst + QG_DLAM, AR(dlam) + SO(i), NB);
+            stage_cp(dst + QG_DT, AR(dt_) + SO(i), NB);
         }
-        if (i > 0) stage_cp(dst + QG_JC, AR(Jc) + NJ * i, NJ);
+        if (i > 0) stage_cp(dst + QG_JC, AR(Jc) + SO(i), NJ);
     }
 }
 
@@ -1865,7 +1872,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             double la, lb, ta, tb;
             QF(QG_LAM, QG_DLAM, lane, la); QF(QG_LAM, QG_DLAM, 12 + lane, lb);
             QF(QG_T, QG_DT, lane, ta); QF(QG_T, QG_DT, 12 + lane, tb);
-            const int ia = NB * i + lane, ib = ia + 12;
+            const int ia = SO(i) + lane, ib = ia + 12;
             if (UPD) { AR(slam)[ia] = la; AR(slam)[ib] = lb; AR(st)[ia] = ta; AR(st)[ib] = tb; }
             const double dl = G[QG_D + lane] + ta - vl, du = G[QG_D + 12 + lane] + tb + vl;
             const double ml = la * ta, mu_ = lb * tb;
@@ -1882,7 +1889,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             double g = G[QG_RQZ + lane];
             g += hu * uj + hs * dj + b1 * pq + b2 * pd;
             g += dlm;
-            AR(res_g)[NV * i + lane] = g;
+            AR(res_g)[SO(i) + lane] = g;
             n0 = rd_fmax(n0, fabs(g));
             if (i == 0 && lane == 0 && g != g) nanflag = 1.0;
         }
@@ -1930,7 +1937,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
                     QF(QG_LAM, QG_DLAM, 0, la); QF(QG_LAM, QG_DLAM, 12, lb);
                     g += G[QG_JC + xk] * (lb - la);
                 }
-                AR(res_g)[NV * i + 6 + xk] = g;
+                AR(res_g)[SO(i) + 6 + xk] = g;
                 n0 = rd_fmax(n0, fabs(g));
             }
             if (mid)
@@ -1939,7 +1946,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
                 double r;
                 if (R.q) r = G[QG_B + j] - xn + (qj + a12 * dj) + b1 * uj;
                 else r = G[QG_B + 6 + j] - xn + a22 * dj + b2 * uj;
-                AR(res_b)[NX * i + xk] = r;
+                AR(res_b)[SO(i) + xk] = r;
                 n1 = rd_fmax(n1, fabs(r));
                 pprev = R.q ? pq : pd;
             }
@@ -1963,8 +1970,8 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
         }
         if (UPD)
         { /* write the moved primal iterate and multipliers of this stage back */
-            for (int c = lane; c < NV; c += GL) AR(sux)[NV * i + c] = G[QG_UX + c] + a * G[QG_DUX + c];
-            if (mid && lane < NX) AR(spi)[NX * i + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
+            for (int c = lane; c < NV; c += GL) AR(sux)[SO(i) + c] = G[QG_UX + c] + a * G[QG_DUX + c];
+            if (mid && lane < NX) AR(spi)[SO(i) + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
         }
         rd_sync(); /* the buffer of this stage is refilled by the next iteration */
     }
@@ -2308,7 +2315,7 @@ RD void nlp_shift(const RmpcDims &D, const Inst &I)
         if (k < n) ux[k] = v;
     }
     rd_sync();
-    if (lane < NX) ux[NV * (N - 1) + 6 + lane] = ux[NV * N + 6 + lane];
+    if (lane < NX) ux[SO(N - 1) + 6 + lane] = ux[SO(N) + 6 + lane];
     rd_sync();
 }
 
@@ -2349,7 +2356,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
             for (int i = lane; i < N; i += GL)
             {
                 double v[NV], y5[5];
-                load18(AR(ux) + NV * i, v);
+                load18(AR(ux) + SO(i), v);
                 NoEmit ne;
                 ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
                 cost += stage_cost(par, D.dt, y5, v, v + 12);

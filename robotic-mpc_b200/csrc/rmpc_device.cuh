@@ -122,11 +122,11 @@ RD double grp_max(double v)
 /* ---------------------------------------------------------------------------------------------- shared memory
  * one block per group (instance).  `buf` is carved per sweep:
  *   factorisation : P+ (12 x SM_PS) | Lxu (72) | Muu in (28) | L out (34) | two staging buffers of FS_STGN doubles
- *   forward / backward substitution : two staging buffers of SW_STGN doubles
+ *   forward / backward substitution : two staging buffers of SW_STGN doubles; update + residual sweep: three of QG_END
  * The staging buffers are filled one stage AHEAD by cp.async (LDGSTS), so that inside a stage every operand comes from
  * shared memory and the HBM / L2 latency of the streamed factors and residuals is off the critical path. */
 #define SM_PS 14 /* row stride of P: even (16-byte aligned pairs), 28 words -> rows 0..5 hit distinct banks */
-#define SM_BUF 752
+#define SM_BUF 812
 struct GrpSmem
 {
     double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
@@ -147,9 +147,9 @@ struct GrpSmem
 #define FS_LXU(sm) ((sm).buf + 168) /* Lxu of the current stage (for the Schur complement) */
 #define FS_MIN(sm) ((sm).buf + 240) /* lower 6x6 block Muu (21) + m_u (6) */
 #define FS_LOUT(sm) ((sm).buf + 268) /* L (21, packed with diagonal) + l_u (6) + 1/diag (6) */
-#define FS_STGN 164
+#define FS_STGN 162
 #define FS_STG(sm, k) ((sm).buf + 304 + (k) * FS_STGN)
-#define SW_STGN 376
+#define SW_STGN 406
 #define SW_STG(sm, k) ((sm).buf + (k) * SW_STGN)
 
 /* group-wide asynchronous copy of n doubles (n even, both sides 16-byte aligned) global -> shared */
@@ -162,58 +162,92 @@ RD void stage_cp(double *dst, const double *src, const int n)
         if ((c + 1) * GL <= n / 2 || rd_lane() + c * GL < n / 2) rd_cp_async16(dst + l2 + 2 * GL * c, src + l2 + 2 * GL * c);
 }
 
-/* Flat group-wide vector updates with the loads of four strides issued before the first use (memory-level
- * parallelism: these passes are pure streaming and otherwise wait for one load round trip per element). */
-#ifdef RMPC_EMU
-#define RD_RESTRICT
-#else
-#define RD_RESTRICT __restrict__
-#endif
-RD void grp_axpy(double *RD_RESTRICT y, const double *RD_RESTRICT x, double a, int n) /* y += a x */
+/* Stage-parallel vector passes over slices of the stage records (rmpc_types.h): lane l handles stages i0 + l, i0 + l + GL, ...
+ * and works on all W doubles of its stage at once (W even, every slice 16-byte aligned: 128-bit accesses), so each load of a
+ * stage is in flight before the first use and a pass over the horizon costs ceil(N / GL) round trips to memory. */
+template <int W>
+RD void ldv(const double *p, double *v)
 {
-    int k = rd_lane();
-    for (; k + 3 * GL < n; k += 4 * GL)
+    RD_UNROLL
+    for (int c = 0; c < W; c += 2)
     {
-        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
-        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
-        y[k] = y0 + a * x0; y[k + GL] = y1 + a * x1; y[k + 2 * GL] = y2 + a * x2; y[k + 3 * GL] = y3 + a * x3;
+        const rd_double2 t = *reinterpret_cast<const rd_double2 *>(p + c);
+        v[c] = t.x; v[c + 1] = t.y;
     }
-    for (; k < n; k += GL) y[k] += a * x[k];
 }
-RD void grp_xpay_to(double *RD_RESTRICT z, const double *RD_RESTRICT x, const double *RD_RESTRICT y, double a, int n) /* z = x + a y */
+template <int W>
+RD void stv(double *p, const double *v)
 {
-    int k = rd_lane();
-    for (; k + 3 * GL < n; k += 4 * GL)
+    RD_UNROLL
+    for (int c = 0; c < W; c += 2)
     {
-        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
-        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
-        z[k] = x0 + a * y0; z[k + GL] = x1 + a * y1; z[k + 2 * GL] = x2 + a * y2; z[k + 3 * GL] = x3 + a * y3;
+        rd_double2 t;
+        t.x = v[c]; t.y = v[c + 1];
+        *reinterpret_cast<rd_double2 *>(p + c) = t;
     }
-    for (; k < n; k += GL) z[k] = x[k] + a * y[k];
 }
-RD void grp_lerp(double *RD_RESTRICT y, const double *RD_RESTRICT x, double al, int k0, int n) /* y = (1-al) y + al x on [k0, n) */
+#define SO(i) (RMPC_REC * (i)) /* offset of stage i's record */
+/* a slice is processed in chunks of at most 12 doubles (6 128-bit loads per operand in flight, ~50 live registers) */
+#define ST_CH(W) ((W) > 18 ? (W) / 2 : (W))
+template <int W>
+RD void st_axpy(double *y0, const double *x0, double a, int i0, int i1) /* y += a x */
 {
-    int k = k0 + rd_lane();
-    for (; k + 3 * GL < n; k += 4 * GL)
-    {
-        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
-        const double y0 = y[k], y1 = y[k + GL], y2 = y[k + 2 * GL], y3 = y[k + 3 * GL];
-        y[k] = (1.0 - al) * y0 + al * x0; y[k + GL] = (1.0 - al) * y1 + al * x1;
-        y[k + 2 * GL] = (1.0 - al) * y2 + al * x2; y[k + 3 * GL] = (1.0 - al) * y3 + al * x3;
-    }
-    for (; k < n; k += GL) y[k] = (1.0 - al) * y[k] + al * x[k];
+    for (int i = i0 + rd_lane(); i < i1; i += GL)
+        RD_UNROLL
+        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
+        {
+            double x[ST_CH(W)], y[ST_CH(W)];
+            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
+            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
+            RD_UNROLL
+            for (int c = 0; c < ST_CH(W); c++) y[c] = y[c] + a * x[c];
+            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
+        }
 }
-/* y = max(y + a x, lo) on [k0, n)   (UPDATE_VAR_QP for lam / t) */
-RD void grp_axpy_floor(double *RD_RESTRICT y, const double *RD_RESTRICT x, double a, double lo, int k0, int n)
+template <int W>
+RD void st_xpay_to(double *z0, const double *x0, const double *y0, double a, int i0, int i1) /* z = x + a y */
 {
-    int k = k0 + rd_lane();
-    for (; k + 3 * GL < n; k += 4 * GL)
-    {
-        const double x0 = x[k], x1 = x[k + GL], x2 = x[k + 2 * GL], x3 = x[k + 3 * GL];
-        const double y0 = y[k] + a * x0, y1 = y[k + GL] + a * x1, y2 = y[k + 2 * GL] + a * x2, y3 = y[k + 3 * GL] + a * x3;
-        y[k] = y0 <= lo ? lo : y0; y[k + GL] = y1 <= lo ? lo : y1; y[k + 2 * GL] = y2 <= lo ? lo : y2; y[k + 3 * GL] = y3 <= lo ? lo : y3;
-    }
-    for (; k < n; k += GL) { const double v = y[k] + a * x[k]; y[k] = v <= lo ? lo : v; }
+    for (int i = i0 + rd_lane(); i < i1; i += GL)
+        RD_UNROLL
+        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
+        {
+            double x[ST_CH(W)], y[ST_CH(W)];
+            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
+            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
+            RD_UNROLL
+            for (int c = 0; c < ST_CH(W); c++) x[c] = x[c] + a * y[c];
+            stv<ST_CH(W)>(z0 + SO(i) + c0, x);
+        }
+}
+template <int W>
+RD void st_add(double *y0, const double *x0, int i0, int i1) /* y += x */
+{
+    for (int i = i0 + rd_lane(); i < i1; i += GL)
+        RD_UNROLL
+        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
+        {
+            double x[ST_CH(W)], y[ST_CH(W)];
+            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
+            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
+            RD_UNROLL
+            for (int c = 0; c < ST_CH(W); c++) y[c] += x[c];
+            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
+        }
+}
+template <int W>
+RD void st_lerp(double *y0, const double *x0, double al, int i0, int i1) /* y = (1 - al) y + al x */
+{
+    for (int i = i0 + rd_lane(); i < i1; i += GL)
+        RD_UNROLL
+        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
+        {
+            double x[ST_CH(W)], y[ST_CH(W)];
+            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
+            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
+            RD_UNROLL
+            for (int c = 0; c < ST_CH(W); c++) y[c] = (1.0 - al) * y[c] + al * x[c];
+            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
+        }
 }
 
 /* per-instance view (layout: rmpc_types.h): parameter row, slab head, first array, stage slots, plant state, flags */
@@ -232,7 +266,6 @@ struct Inst
 #define PAIR_SYNC() rd_sync_mask(I.pair)
 /* stage-major slab (rmpc_types.h): AR(name) = array <name> of stage 0, SO(i) = offset of stage i's record */
 #define REC RMPC_REC
-#define SO(i) (REC * (i))
 #define AR(name) (I.arr0 + RC_##name)
 
 RD Inst inst_view(const RmpcWs &w, int N, long i)
@@ -747,7 +780,7 @@ RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
         const double *wpi = AR(wpi) + SO(i), *wl = AR(wlam) + SO(i), *d = AR(d) + SO(i);
         if (i == 0)
         {
-            const double *v = AR(ux), *xn = AR(ux) + NV + 6;
+            const double *v = AR(ux), *xn = AR(ux) + SO(1) + 6;
             RD_UNROLL
             for (int k = 0; k < 6; k++)
             {
@@ -882,37 +915,66 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < (N + 1) * NV; k += GL) AR(sux)[k] = 0.0;
-    if (warm != 2)
-        for (int k = lane; k < N * NX; k += GL) AR(spi)[k] = 0.0;
-    rd_sync();
-    for (int k = lane; k < N * 12; k += GL)
+    /* stage-parallel: lane l initialises stages l, l + GL, ... (every array of a stage is in that stage's record) */
+    for (int i = lane; i <= N; i += GL)
     {
-        const int i = k / 12, j = k - 12 * i;
-        if (i == 0 && j >= 6) continue;
-        double *lam = AR(slam) + SO(i), *t = AR(st) + SO(i);
-        if (warm == 2)
+        double ux[NV];
+        RD_UNROLL
+        for (int k = 0; k < NV; k++) ux[k] = 0.0;
+        if (i < N)
         {
-            if (lam[j] < 1e-1) lam[j] = 1e-1;
-            if (lam[12 + j] < 1e-1) lam[12 + j] = 1e-1;
-            if (t[j] < 1e-1) t[j] = 1e-1;
-            if (t[12 + j] < 1e-1) t[12 + j] = 1e-1;
-        }
-        else
-        {
-            const double thr0 = 1e-1, dl = AR(d)[SO(i) + j], du = AR(d)[SO(i) + 12 + j];
-            double v = 0.0, tl = -dl, tu = -du;
-            if (tl < thr0)
+            if (warm != 2)
             {
-                if (tu < thr0) { v = 0.5 * (dl - du); tl = thr0; tu = thr0; }
-                else { tl = thr0; v = dl + thr0; }
+                double z[NX];
+                RD_UNROLL
+                for (int k = 0; k < NX; k++) z[k] = 0.0;
+                stv<NX>(AR(spi) + SO(i), z);
             }
-            else if (tu < thr0) { tu = thr0; v = -du - thr0; }
-            AR(sux)[SO(i) + j] = v;
-            t[j] = tl; t[12 + j] = tu;
-            lam[j] = 1.0 / tl; lam[12 + j] = 1.0 / tu;
+            /* bound slots in two halves of 6 (lower side j, upper side 12 + j): stage 0 only has the u half */
+            RD_UNROLL
+            for (int h = 0; h < 12; h += 6)
+            {
+                if (i == 0 && h >= 6) continue;
+                double la[6], lb[6], ta[6], tb[6];
+                double *pl = AR(slam) + SO(i) + h, *pt = AR(st) + SO(i) + h;
+                if (warm == 2)
+                {
+                    ldv<6>(pl, la); ldv<6>(pl + 12, lb); ldv<6>(pt, ta); ldv<6>(pt + 12, tb);
+                    RD_UNROLL
+                    for (int j = 0; j < 6; j++)
+                    {
+                        if (la[j] < 1e-1) la[j] = 1e-1;
+                        if (lb[j] < 1e-1) lb[j] = 1e-1;
+                        if (ta[j] < 1e-1) ta[j] = 1e-1;
+                        if (tb[j] < 1e-1) tb[j] = 1e-1;
+                    }
+                }
+                else
+                {
+                    double da[6], db[6];
+                    ldv<6>(AR(d) + SO(i) + h, da); ldv<6>(AR(d) + SO(i) + 12 + h, db);
+                    RD_UNROLL
+                    for (int j = 0; j < 6; j++)
+                    {
+                        const double thr0 = 1e-1, dl = da[j], du = db[j];
+                        double v = 0.0, tl = -dl, tu = -du;
+                        if (tl < thr0)
+                        {
+                            if (tu < thr0) { v = 0.5 * (dl - du); tl = thr0; tu = thr0; }
+                            else { tl = thr0; v = dl + thr0; }
+                        }
+                        else if (tu < thr0) { tu = thr0; v = -du - thr0; }
+                        ux[h + j] = v;
+                        ta[j] = tl; tb[j] = tu;
+                        la[j] = 1.0 / tl; lb[j] = 1.0 / tu;
+                    }
+                }
+                stv<6>(pl, la); stv<6>(pl + 12, lb); stv<6>(pt, ta); stv<6>(pt + 12, tb);
+            }
         }
+        stv<NV>(AR(sux) + SO(i), ux);
     }
+    rd_sync();
     if (I.pe && lane < 2)
     { /* general row of stage N (x_ocp_qp_ipm.c:1780-1817): t = +-C ux - d at ux = 0, clipped at 0.1; lam = mu0 / t */
         const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -1107,18 +1169,11 @@ RD void smem_consts(const Inst &I, GrpSmem &sm, double dt)
  *   Luu Luu' = Muu, Lxu = Mxu Luu^-T, l_u = Luu^-1 m_u, P = Mxx - Lxu Lxu', p = m_x - Lxu l_u
  * (the reference factorises P = Lxx Lxx' as well and carries Lxx; see the header of this file).  The complementarity
  * residual enters as res_m - tau_min (BACKUP_RES_M + COMPUTE_TAU_MIN_QP, x_core_qp_ipm_aux.c:457-475,533-553). */
-/* staging layout of one stage for the factorisation */
-enum { FG_LAM = 0, FG_T = 24, FG_RD = 48, FG_RM = 72, FG_RG = 96, FG_RB = 114, FG_JC = 126 };
-RD void fac_stage_in(const Inst &I, double *dst, int ss)
-{
-    stage_cp(dst + FG_LAM, AR(slam) + SO(ss), NB);
-    stage_cp(dst + FG_T, AR(st) + SO(ss), NB);
-    stage_cp(dst + FG_RD, AR(res_d) + SO(ss), NB);
-    stage_cp(dst + FG_RM, AR(res_m) + SO(ss), NB);
-    stage_cp(dst + FG_RG, AR(res_g) + SO(ss), NV);
-    stage_cp(dst + FG_RB, AR(res_b) + SO(ss), NX);
-    if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + SO(ss), NJ);
-}
+/* staging layout of one stage for the factorisation: the contiguous slice [res_b .. st] of the stage record */
+enum { FG_RB = RC_res_b - RC_res_b, FG_RG = RC_res_g - RC_res_b, FG_RD = RC_res_d - RC_res_b, FG_RM = RC_res_m - RC_res_b,
+       FG_JC = RC_Jc - RC_res_b, FG_LAM = RC_slam - RC_res_b, FG_T = RC_st - RC_res_b, FG_END = RC_F - RC_res_b };
+static_assert(FG_END == FS_STGN, "factorisation staging size");
+RD void fac_stage_in(const Inst &I, double *dst, int ss) { stage_cp(dst, AR(res_b) + SO(ss), FG_END); }
 
 RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
 {
@@ -1358,27 +1413,52 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
  *   sums[0] = sum lam dt + dlam t, sums[1] = sum dlam dt          (for COMPUTE_MU_AFF_QP, :424-441, see ipm_mu_aff)
  * STORED = 0: src_u = l_u and p+ from the factorisation (affine step); STORED = 1: src_u = z_u left in X[.][0:6] by
  * ipm_backward() and p+ = pvec.  rm enters as rm - mshift. */
-/* staging layout of one stage for the forward sweep: [0,100) = F[ss] (1/diag, l_u, Luu, Lxu), [100,190) = P, p of
- * F[ss+1] at their RF_* offsets, then the bound-slot data, res_b and (STORED) z_u, p of the corrector */
-enum { WG_LAM = 190, WG_T = 214, WG_RD = 238, WG_RM = 262, WG_RB = 286, WG_ZU = 298, WG_PVEC = 304, WG_RG = 316, WG_JC = 334 };
-template <int STORED>
+/* Staging of one stage for the forward sweep, KIND = 0 affine step, 1 corrector, 2 refinement (generic right-hand sides).
+ * KIND 0: the slice [res_b .. F low part] of the stage record, then [P PV] of the NEXT stage's record;
+ * KIND 1: the slice [dux .. F low part] (dux[0:6] = z_u left by ipm_backward, res_mc = the corrector's complementarity
+ *         right-hand side), then [P PV pvec] of the next stage's record -- two contiguous ranges each;
+ * KIND 2: the layout of KIND 1 filled piece by piece from the refinement arrays (rare path). */
+template <int KIND>
+struct WG
+{
+    enum
+    {
+        kBASE = KIND == 0 ? RC_res_b : RC_dux, /* record offset the first range starts at */
+        kZU = RC_dux - kBASE,                    /* KIND >= 1 */
+        kRM = (KIND == 0 ? RC_res_m : RC_res_mc) - kBASE,
+        kRB = RC_res_b - kBASE, kRG = RC_res_g - kBASE, kRD = RC_res_d - kBASE, kJC = RC_Jc - kBASE, kLAM = RC_slam - kBASE,
+        kT = RC_st - kBASE,
+        kF = RC_F - kBASE,          /* low part of the factor block: RF_INV, RF_LU, RF_LUU, RF_LXU */
+        kN1 = kF + RF_PB,           /* length of the first range */
+        kP = kN1,                   /* packed P of the next stage */
+        kPV = kP + (RF_PV - RF_P),  /* p of the next stage (affine step) */
+        kPVEC = kPV + NX,           /* pvec of the next stage (KIND >= 1) */
+        kN2 = KIND == 0 ? (RF_END - RF_P) : (RF_END - RF_P) + NX,
+        kEND = kN1 + kN2
+    };
+};
+static_assert(WG<1>::kEND <= SW_STGN && WG<0>::kEND <= SW_STGN, "forward staging size");
+template <int KIND>
 RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rb, const double *rd, const double *rm,
                      const double *X)
 {
-    stage_cp(dst + WG_RG, rg + SO(ss), NV);
-    if (ss > 0) stage_cp(dst + WG_JC, AR(Jc) + SO(ss), NJ);
-    const double *F = AR(F) + SO(ss);
-    stage_cp(dst, F, RF_P);
-    stage_cp(dst + RF_P, F + FS + RF_P, STORED ? RF_PV - RF_P : RF_PB - RF_P);
-    stage_cp(dst + WG_LAM, AR(slam) + SO(ss), NB);
-    stage_cp(dst + WG_T, AR(st) + SO(ss), NB);
-    stage_cp(dst + WG_RD, rd + SO(ss), NB);
-    stage_cp(dst + WG_RM, rm + SO(ss), NB);
-    stage_cp(dst + WG_RB, rb + SO(ss), NX);
-    if (STORED)
+    typedef WG<KIND> L;
+    if (KIND < 2)
     {
-        stage_cp(dst + WG_ZU, X + SO(ss), 6);
-        stage_cp(dst + WG_PVEC, AR(pvec) + SO(ss + 1), NX);
+        stage_cp(dst, I.arr0 + L::kBASE + SO(ss), L::kN1);
+        stage_cp(dst + L::kP, AR(F) + SO(ss + 1) + RF_P, L::kN2);
+    }
+    else
+    {
+        stage_cp(dst + L::kZU, X + SO(ss), 6);
+        stage_cp(dst + L::kRM, rm + SO(ss), NB);
+        stage_cp(dst + L::kRB, rb + SO(ss), NX);
+        stage_cp(dst + L::kRG, rg + SO(ss), NV);
+        stage_cp(dst + L::kRD, rd + SO(ss), NB);
+        if (ss > 0) stage_cp(dst + L::kJC, AR(Jc) + SO(ss), NJ);
+        stage_cp(dst + L::kLAM, AR(slam) + SO(ss), 2 * NB); /* slam and st are neighbours */
+        stage_cp(dst + L::kF, AR(F) + SO(ss), RF_PB);
+        stage_cp(dst + L::kP, AR(F) + SO(ss + 1) + RF_P, L::kN2);
     }
 }
 
@@ -1388,18 +1468,20 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
  * lin[0] = |r|_inf, lin[1] = NaN flag of r_u[0] at stage 0.  The other three residuals of that system (dynamics,
  * bounds, complementarity) are zero up to rounding BY CONSTRUCTION of dx+, dt and dlam in this sweep and are not
  * re-evaluated. */
-template <int STORED>
+template <int KIND>
 RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                     const double *rm, double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out,
                     double *sums, double *lin)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
+    typedef WG<KIND> L;
+    constexpr bool STORED = KIND != 0;
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
     const double a12 = C_A12(j), a22 = C_A22(j), b1 = C_B1(j), b2 = C_B2(j);
     const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
-    fwd_stage_in<STORED>(I, SW_STG(sm, 0), 0, rg, rb, rd, rm, X);
+    fwd_stage_in<KIND>(I, SW_STG(sm, 0), 0, rg, rb, rd, rm, X);
     rd_cp_commit();
     if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
     double alpha = 1.0, sB = 0.0, sC = 0.0;
@@ -1407,18 +1489,18 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
     for (int ss = 0; ss < N; ss++)
     {
         const double *G = SW_STG(sm, ss & 1);
-        if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
+        if (ss + 1 < N) fwd_stage_in<KIND>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
         rd_cp_commit();
         rd_cp_wait1();
         rd_sync();
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
-            double s = STORED ? G[WG_ZU + lane] : G[RF_LU + lane];
+            double s = STORED ? G[L::kZU + lane] : G[L::kF + RF_LU + lane];
             if (ss > 0)
             {
                 RD_UNROLL
-                for (int k = 0; k < 12; k++) s += G[RF_LXU + k * 6 + lane] * sm.xv[k];
+                for (int k = 0; k < 12; k++) s += G[L::kF + RF_LXU + k * 6 + lane] * sm.xv[k];
             }
             sm.uv[lane] = s;
         }
@@ -1427,11 +1509,11 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         if (ss > 0 && lane < 5)
         {
             RD_UNROLL
-            for (int k = 0; k < 6; k++) wm += G[WG_JC + 6 * lane + k] * sm.xv[k];
+            for (int k = 0; k < 6; k++) wm += G[L::kJC + 6 * lane + k] * sm.xv[k];
             if (lane == 4)
             {
                 RD_UNROLL
-                for (int k = 0; k < 6; k++) wm += G[WG_JC + 30 + k] * sm.xv[6 + k];
+                for (int k = 0; k < 6; k++) wm += G[L::kJC + 30 + k] * sm.xv[6 + k];
             }
         }
         rd_sync();
@@ -1442,9 +1524,9 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         RD_UNROLL
         for (int k = 5; k >= 0; k--)
         {
-            du[k] *= G[RF_INV + k];
+            du[k] *= G[L::kF + RF_INV + k];
             RD_UNROLL
-            for (int c = 0; c < k; c++) du[c] -= G[RF_LUU + (k * (k - 1)) / 2 + c] * du[k];
+            for (int c = 0; c < k; c++) du[c] -= G[L::kF + RF_LUU + (k * (k - 1)) / 2 + c] * du[k];
         }
         double duj = du[0], dul = du[0];
         RD_UNROLL
@@ -1459,8 +1541,8 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         double xn = 0.0;
         if (R.x)
         {
-            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[WG_RB + j];
-            else xn = a22 * sm.xv[6 + j] + b2 * duj + G[WG_RB + 6 + j];
+            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[L::kRB + j];
+            else xn = a22 * sm.xv[6 + j] + b2 * duj + G[L::kRB + 6 + j];
         }
         rd_sync(); /* every lane has read xv, uv */
         if (R.u) X[SO(ss) + lane] = dul;
@@ -1471,9 +1553,9 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         double dpo = 0.0;
         if (R.x)
         {
-            double a = STORED ? G[WG_PVEC + xk] : G[RF_PV + xk];
+            double a = STORED ? G[L::kPVEC + xk] : G[L::kPV + xk];
             RD_UNROLL
-            for (int c = 0; c < 12; c++) a += psym(G + RF_P, xk, c) * sm.xv[c];
+            for (int c = 0; c < 12; c++) a += psym(G + L::kP, xk, c) * sm.xv[c];
             PI[SO(ss) + xk] = a;
             sm.dp[xk] = a;
             dpo = a;
@@ -1483,8 +1565,8 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
             const int ia = SO(ss) + lane, ib = ia + 12;
-            const double la = G[WG_LAM + lane], lb = G[WG_LAM + 12 + lane], ta = G[WG_T + lane], tb = G[WG_T + 12 + lane];
-            const double da = G[WG_RD + lane], db = G[WG_RD + 12 + lane], ma = G[WG_RM + lane] - mshift, mb = G[WG_RM + 12 + lane] - mshift;
+            const double la = G[L::kLAM + lane], lb = G[L::kLAM + 12 + lane], ta = G[L::kT + lane], tb = G[L::kT + 12 + lane];
+            const double da = G[L::kRD + lane], db = G[L::kRD + 12 + lane], ma = G[L::kRM + lane] - mshift, mb = G[L::kRM + 12 + lane] - mshift;
             const double dla = -(ma + (la * dv) - (la * da)) / ta;
             const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
             const double dta = dv - da, dtb = -dv - db;
@@ -1499,16 +1581,16 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         }
         /* operands of the residual rows that live in the staging buffer (refilled after the barrier) */
         double rgu = 0.0, rgx = 0.0, jq[5] = {0, 0, 0, 0, 0}, jd = 0.0;
-        if (R.u) rgu = G[WG_RG + lane];
+        if (R.u) rgu = G[L::kRG + lane];
         if (R.x && ss > 0)
         {
-            rgx = G[WG_RG + 6 + xk];
+            rgx = G[L::kRG + 6 + xk];
             if (R.q)
             {
                 RD_UNROLL
-                for (int m = 0; m < 5; m++) jq[m] = G[WG_JC + 6 * m + j];
+                for (int m = 0; m < 5; m++) jq[m] = G[L::kJC + 6 * m + j];
             }
-            else jd = G[WG_JC + 30 + j];
+            else jd = G[L::kJC + 30 + j];
         }
         rd_sync(); /* dp, wv published; the staging buffer of this stage is refilled by the next iteration */
         if (R.u)
@@ -1572,28 +1654,28 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
  *   1  COMPUTE_CENTERING_CORRECTION_QP (:479-505): rm = res_m + dt_aff dlam_aff - sigma_mu, written to res_mc;
  *   2  COMPUTE_CENTERING_QP (:509-529):            rm = res_m - sigma_mu, written to res_mc.
  * USE_PB: P+ rb was stored by the factorisation (rb = res_b); otherwise it is recomputed from P+. */
-/* staging layout of one stage for the backward substitution: [0,100) = F[ss] (1/diag, -, Luu, Lxu), then P+ b, res_g,
- * lam, t, res_d and the complementarity data of the MODE */
-enum { BG_PB = 100, BG_RG = 112, BG_LAM = 130, BG_T = 154, BG_RD = 178, BG_RM = 202, BG_DT = 226, BG_DLAM = 250 };
+/* Staging of one stage for the backward substitution.  Hot form (USE_PB = 1: right-hand sides = the residual arrays of the
+ * record): the slice [res_g .. F.PB] of the stage record and, for the corrector's second-order term (MODE 1), [dlam dt] --
+ * two contiguous ranges.  Generic form (USE_PB = 0, refinement): the same layout filled piece by piece. */
+enum { BG_RG = RC_res_g - RC_res_g, BG_RD = RC_res_d - RC_res_g, BG_RM = RC_res_m - RC_res_g, BG_LAM = RC_slam - RC_res_g,
+       BG_T = RC_st - RC_res_g, BG_F = RC_F - RC_res_g, BG_PB = BG_F + RF_PB, BG_N1 = BG_F + RF_P,
+       BG_DLAM = BG_N1, BG_DT = BG_N1 + (RC_dt_ - RC_dlam), BG_END = BG_N1 + 2 * NB };
+static_assert(BG_END <= SW_STGN && RC_dt_ == RC_dlam + NB && RC_st == RC_slam + NB && RC_pvec == RC_F + RF_END, "backward staging size / record order");
 template <int MODE, int USE_PB>
 RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rd, const double *rm)
 {
-    const double *F = AR(F) + SO(ss);
-    stage_cp(dst, F, RF_P);
-    if (USE_PB) stage_cp(dst + BG_PB, F + RF_PB, NX);
-    stage_cp(dst + BG_RG, rg + SO(ss), NV);
-    stage_cp(dst + BG_LAM, AR(slam) + SO(ss), NB);
-    stage_cp(dst + BG_T, AR(st) + SO(ss), NB);
-    stage_cp(dst + BG_RD, rd + SO(ss), NB);
-    if (MODE == 0) stage_cp(dst + BG_RM, rm + SO(ss), NB);
+    if (USE_PB)
+    {
+        stage_cp(dst, AR(res_g) + SO(ss), BG_N1);
+        if (MODE == 1) stage_cp(dst + BG_DLAM, AR(dlam) + SO(ss), 2 * NB); /* dlam and dt_ are neighbours */
+    }
     else
     {
-        stage_cp(dst + BG_RM, AR(res_m) + SO(ss), NB);
-        if (MODE == 1)
-        {
-            stage_cp(dst + BG_DT, AR(dt_) + SO(ss), NB);
-            stage_cp(dst + BG_DLAM, AR(dlam) + SO(ss), NB);
-        }
+        stage_cp(dst + BG_RG, rg + SO(ss), NV);
+        stage_cp(dst + BG_RD, rd + SO(ss), NB);
+        stage_cp(dst + BG_RM, rm + SO(ss), NB);
+        stage_cp(dst + BG_LAM, AR(slam) + SO(ss), 2 * NB);
+        stage_cp(dst + BG_F, AR(F) + SO(ss), RF_PB);
     }
 }
 
@@ -1684,9 +1766,9 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
-            z[k] *= G[RF_INV + k];
+            z[k] *= G[BG_F + RF_INV + k];
             RD_UNROLL
-            for (int r = k + 1; r < 6; r++) z[r] -= G[RF_LUU + (r * (r - 1)) / 2 + k] * z[k];
+            for (int r = k + 1; r < 6; r++) z[r] -= G[BG_F + RF_LUU + (r * (r - 1)) / 2 + k] * z[k];
         }
         if (R.u)
         {
@@ -1699,7 +1781,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
         if (R.x && !s0)
         {
             RD_UNROLL
-            for (int k = 0; k < 6; k++) rx -= G[RF_LXU + xk * 6 + k] * z[k];
+            for (int k = 0; k < 6; k++) rx -= G[BG_F + RF_LXU + xk * 6 + k] * z[k];
             sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
             AR(pvec)[SO(ss) + xk] = rx;
         }
@@ -1708,18 +1790,20 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
     rd_cp_wait0();
 }
 
-/* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction) */
+/* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction).  Rare path: the bound slots
+ * are walked in flat order k = NB * stage + slot, lane l taking k = l, l + GL, ... -- the order the per-lane minimum / sums
+ * were always accumulated in (they feed the most ill-conditioned solves, where a changed rounding shows). */
 RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const double *dt)
 {
     const int N = D.N, lane = rd_lane();
     double a = 1.0;
     for (int k = lane; k < N * NB; k += GL)
     {
-        const int i = k / NB, j = k - SO(i);
+        const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        const double dl = dlam[k], dtt = dt[k];
-        if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
-        if (-a * dtt > AR(st)[k]) a = -AR(st)[k] / dtt;
+        const double dl = dlam[SO(i) + j], dtt = dt[SO(i) + j];
+        if (-a * dl > AR(slam)[SO(i) + j]) a = -AR(slam)[SO(i) + j] / dl;
+        if (-a * dtt > AR(st)[SO(i) + j]) a = -AR(st)[SO(i) + j] / dtt;
     }
     if (I.pe && lane < 2)
     {
@@ -1738,10 +1822,10 @@ RD void ipm_mu_sums(const RmpcDims &D, const Inst &I, const double *dlam, const 
     double sB = 0.0, sC = 0.0;
     for (int k = lane; k < N * NB; k += GL)
     {
-        const int i = k / NB, j = k - SO(i);
+        const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        sB += AR(slam)[k] * dt[k] + dlam[k] * AR(st)[k];
-        sC += dlam[k] * dt[k];
+        sB += AR(slam)[SO(i) + j] * dt[SO(i) + j] + dlam[SO(i) + j] * AR(st)[SO(i) + j];
+        sC += dlam[SO(i) + j] * dt[SO(i) + j];
     }
     if (I.pe && lane < 2)
     {
@@ -1760,73 +1844,26 @@ RD double ipm_mu_aff(double sum_lt, const double *sums, double alpha, double nc_
     return (sum_lt + alpha * sums[0] + alpha * alpha * sums[1]) * nc_inv;
 }
 
-/* UPDATE_VAR_QP (x_core_qp_ipm_aux.c:267-372): single damped step, lam / t floor */
-RDN void ipm_update(const RmpcDims &D, const Inst &I, double a)
-{
-    const int N = D.N, lane = rd_lane();
-    const double lmin = 1e-16;
-    grp_axpy(AR(sux), AR(dux), a, (N + 1) * NV);
-    grp_axpy(AR(spi), AR(dpi), a, N * NX);
-    /* stage 0 has bounds on u only: slots 0..5 and 12..17 */
-    if (lane < 12)
-    {
-        const int k = lane < 6 ? lane : lane + 6;
-        const double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
-        AR(slam)[k] = l <= lmin ? lmin : l;
-        AR(st)[k] = t <= lmin ? lmin : t;
-    }
-    grp_axpy_floor(AR(slam), AR(dlam), a, lmin, NB, N * NB);
-    grp_axpy_floor(AR(st), AR(dt_), a, lmin, NB, N * NB);
-    if (I.pe && lane >= 12 && lane < 14)
-    {
-        const int k = lane == 12 ? TERM_LO(N) : TERM_UP(N);
-        const double l = AR(slam)[k] + a * AR(dlam)[k], t = AR(st)[k] + a * AR(dt_)[k];
-        AR(slam)[k] = l <= lmin ? lmin : l;
-        AR(st)[k] = t <= lmin ? lmin : t;
-    }
-    rd_sync();
-}
-
 /* UPDATE_VAR_QP + OCP_QP_RES_COMPUTE in ONE stage-by-stage pass with staged operands (the hot pair of every interior-point
- * iteration; ipm_update + ipm_res<0, 1> are the same two steps as separate passes and stay for the rare paths).
+ * iteration).
  * UPD = 1: the iterate is first moved, (ux, pi) += a (dux, dpi), (lam, t) = max((lam, t) + a (dlam, dt), 1e-16), written
  * back, and the residuals are evaluated at the new point; UPD = 0: residuals at the current point (first call of a QP).
  * The 16 lanes of the group work on ONE stage at a time with the row roles of the Riccati sweeps (lane l < 6: rows u_l
  * and qd_l, lane 6 + j: row q_j; lane l < 12 also owns bound slot l), all operands of the stage are fetched one stage
  * ahead by cp.async into shared memory -- coalesced 16-byte copies instead of 16 lanes striding through 16 different
  * stages -- and the multiplier of the previous stage is carried in a register.  Returns sum lam t; norms as ipm_res. */
-enum { QG_UX = 0, QG_DUX = 18, QG_XN = 36, QG_DXN = 48, QG_RQZ = 60, QG_PI = 78, QG_DPI = 90, QG_LAM = 102, QG_DLAM = 126,
-       QG_T = 150, QG_DT = 174, QG_B = 198, QG_D = 210, QG_JC = 234, QG_END = 270 };
+enum { QG_UX = RC_sux, QG_PI = RC_spi, QG_RQZ = RC_rqz, QG_B = RC_b, QG_D = RC_d, QG_DPI = RC_dpi, QG_DLAM = RC_dlam, QG_DT = RC_dt_,
+       QG_DUX = RC_dux, QG_N0 = RC_dpi /* [sux .. d] */, QG_N1 = RC_dux + NV /* [sux .. dux] */, QG_JC = QG_N1, QG_LAM = QG_JC + NJ,
+       QG_T = QG_LAM + NB, QG_END = QG_T + NB };
+static_assert(RC_sux == 0 && RC_slam == RC_Jc + NJ && RC_st == RC_slam + NB, "record order assumed by the residual sweep");
+static_assert(3 * QG_END <= SM_BUF, "residual sweep staging size");
+#define RS_STG(sm, k) ((sm).buf + (k) * QG_END)
+/* two contiguous ranges of the stage record: [sux .. d] (UPD = 0) or [sux .. dux] (UPD = 1), and [Jc slam st] */
 template <int UPD>
-RD void res_stage_in(const Inst &I, double *dst, int i, int N)
+RD void res_stage_in(const Inst &I, double *dst, int i)
 {
-    const bool cons = (i < N) || I.pe; /* stage N carries constraint slots only with a terminal row */
-    stage_cp(dst + QG_UX, AR(sux) + SO(i), NV);
-    stage_cp(dst + QG_RQZ, AR(rqz) + SO(i), NV);
-    if (UPD) stage_cp(dst + QG_DUX, AR(dux) + SO(i), NV);
-    if (i < N)
-    {
-        stage_cp(dst + QG_XN, AR(sux) + SO(i + 1) + 6, NX);
-        stage_cp(dst + QG_PI, AR(spi) + SO(i), NX);
-        stage_cp(dst + QG_B, AR(b) + SO(i), NX);
-        if (UPD)
-        {
-            stage_cp(dst + QG_DXN, AR(dux) + SO(i + 1) + 6, NX);
-            stage_cp(dst + QG_DPI, AR(dpi) + SO(i), NX);
-        }
-    }
-    if (cons)
-    {
-        stage_cp(dst + QG_LAM, AR(slam) + SO(i), NB);
-        stage_cp(dst + QG_T, AR(st) + SO(i), NB);
-        stage_cp(dst + QG_D, AR(d) + SO(i), NB);
-        if (UPD)
-        {
-            stage_cp(dst + QG_DLAM, AR(dlam) + SO(i), NB);
-            stage_cp(dst + QG_DT, AR(dt_) + SO(i), NB);
-        }
-        if (i > 0) stage_cp(dst + QG_JC, AR(Jc) + SO(i), NJ);
-    }
+    stage_cp(dst, AR(sux) + SO(i), UPD ? QG_N1 : QG_N0);
+    stage_cp(dst + QG_JC, AR(Jc) + SO(i), NJ + 2 * NB);
 }
 
 template <int UPD>
@@ -1840,8 +1877,13 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
     const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
     const double lmin = 1e-16;
     double mu = 0.0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, n4 = 0, nanflag = 0, pprev = 0.0;
-    res_stage_in<UPD>(I, SW_STG(sm, 0), 0, N);
+    /* three staging buffers, filled TWO stages ahead: the dynamics residual of stage i needs the (moved) state of stage
+     * i + 1, which is part of that stage's own staged range and must have landed when stage i is processed */
+    res_stage_in<UPD>(I, RS_STG(sm, 0), 0);
     rd_cp_commit();
+    res_stage_in<UPD>(I, RS_STG(sm, 1), 1); /* N >= 2 */
+    rd_cp_commit();
+    int b0 = 0, b1i = 1, b2i = 2; /* buffers of stages i, i + 1, i + 2 */
 #define QV(off, doff, c) (UPD ? G[(off) + (c)] + a * G[(doff) + (c)] : G[(off) + (c)])
 #define QF(off, doff, c, out)                                                                 \
     do                                                                                        \
@@ -1852,11 +1894,12 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
     } while (0)
     for (int i = 0; i <= N; i++)
     {
-        const double *G = SW_STG(sm, i & 1);
-        if (i < N) res_stage_in<UPD>(I, SW_STG(sm, (i + 1) & 1), i + 1, N);
+        const double *G = RS_STG(sm, b0), *G1 = RS_STG(sm, b1i);
+        if (i + 2 <= N) res_stage_in<UPD>(I, RS_STG(sm, b2i), i + 2);
         rd_cp_commit();
         rd_cp_wait1();
         rd_sync();
+        { const int t_ = b0; b0 = b1i; b1i = b2i; b2i = t_; }
         const bool mid = i < N, x_on = i > 0;
         /* new values of this lane's joint: u_j, q_j, qd_j (the state is fixed at stage 0 of the reduced QP) */
         const double uj = mid ? QV(QG_UX, QG_DUX, j) : 0.0;
@@ -1942,7 +1985,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             }
             if (mid)
             {
-                const double xn = QV(QG_XN, QG_DXN, xk);
+                const double xn = UPD ? G1[QG_UX + 6 + xk] + a * G1[QG_DUX + 6 + xk] : G1[QG_UX + 6 + xk];
                 double r;
                 if (R.q) r = G[QG_B + j] - xn + (qj + a12 * dj) + b1 * uj;
                 else r = G[QG_B + 6 + j] - xn + a22 * dj + b2 * uj;
@@ -2019,10 +2062,11 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
                               AR(ib), AR(id), AR(im), pn);
                 if (pn[0] < 1e-5 && pn[1] < 1e-5 && pn[2] < 1e-5 && pn[3] < 1e-5 && !(pn[5] > 0.5)) break;
                 ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-                ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
-                for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
-                for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
-                for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
+                ipm_forward<2>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
+                st_add<NV>(AR(dux), AR(iux), 0, N + 1);
+                st_add<NX>(AR(dpi), AR(ipi), 0, N);
+                st_add<NB>(AR(dlam), AR(ilam), 0, N);
+                st_add<NB>(AR(dt_), AR(it), 0, N);
                 if (I.pe && lane < 2)
                 {
                     const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -2065,11 +2109,12 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
                           AR(im), inrm);
             double a2, s2[2], l2[2];
             ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-            ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
+            ipm_forward<2>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
             refined = 1;
-            for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
-            for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
-            for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
+            st_add<NV>(AR(dux), AR(iux), 0, N + 1);
+            st_add<NX>(AR(dpi), AR(ipi), 0, N);
+            st_add<NB>(AR(dlam), AR(ilam), 0, N);
+            st_add<NB>(AR(dt_), AR(it), 0, N);
             if (I.pe && lane < 2)
             {
                 const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -2130,19 +2175,31 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     *cost_valid = 0; /* set when the accepted trial point's cost is known from its merit evaluation */
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
-    for (int k = lane; k < N * NX; k += GL)
-    {
-        const double t0 = fabs(AR(spi)[k]);
-        if (nlp_iter == 0) AR(wpi)[k] = t0;
-        else { const double t1 = 0.5 * (t0 + AR(wpi)[k]); AR(wpi)[k] = t0 > t1 ? t0 : t1; }
+    for (int i = lane; i < N; i += GL)
+    { /* stage-parallel: merit weights of the dynamics multipliers and of the bound multipliers of stage i, 12 at a time */
+        RD_UNROLL
+        for (int h = 0; h < 3; h++)
+        {
+            const double *src = h == 0 ? AR(spi) + SO(i) : AR(slam) + SO(i) + 12 * (h - 1);
+            double *wdst = h == 0 ? AR(wpi) + SO(i) : AR(wlam) + SO(i) + 12 * (h - 1);
+            double t[12], w[12];
+            ldv<12>(src, t);
+            if (nlp_iter != 0 || (h > 0 && i == 0)) ldv<12>(wdst, w); /* the unused q slots of stage 0 keep their value */
+            RD_UNROLL
+            for (int k = 0; k < 12; k++)
+            {
+                if (h > 0 && i == 0 && k >= 6) continue;
+                const double t0 = h == 0 ? fabs(t[k]) : t[k];
+                if (nlp_iter == 0) w[k] = t0;
+                else { const double t1 = 0.5 * (t0 + w[k]); w[k] = t0 > t1 ? t0 : t1; }
+            }
+            stv<12>(wdst, w);
+        }
     }
-    for (int k = lane; k < N * NB + NB; k += GL)
-    {
-        const bool x0s = k >= N * NB;
-        const int kk = x0s ? k - N * NB : k;
-        if (!x0s && kk < NB && (kk % 12) >= 6) continue;
-        const double t0 = x0s ? (I.head + H_QLAMX0)[kk] : AR(slam)[kk];
-        double *w = x0s ? (I.head + H_WLAMX0) + kk : AR(wlam) + kk;
+    for (int kk = lane; kk < NB; kk += GL)
+    { /* the eliminated stage-0 state equalities */
+        const double t0 = (I.head + H_QLAMX0)[kk];
+        double *w = (I.head + H_WLAMX0) + kk;
         if (nlp_iter == 0) *w = t0;
         else { const double t1 = 0.5 * (t0 + *w); *w = t0 > t1 ? t0 : t1; }
     }
@@ -2159,7 +2216,7 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        grp_xpay_to(AR(tux), AR(ux), AR(sux), alpha, (N + 1) * NV);
+        st_xpay_to<NV>(AR(tux), AR(ux), AR(sux), alpha, 0, N + 1);
         rd_sync();
         m1 = nlp_merit(ch, D, I, AR(tux), I.z, &c1);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
@@ -2168,14 +2225,14 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     }
     *alpha_out = alpha;
     if (!accepted && ((m1 != m1) || (m1 - m1 != 0.0))) return 1;
-    grp_axpy(AR(ux), AR(sux), alpha, (N + 1) * NV);
-    grp_lerp(AR(pi), AR(spi), alpha, 0, N * NX);
+    st_axpy<NV>(AR(ux), AR(sux), alpha, 0, N + 1);
+    st_lerp<NX>(AR(pi), AR(spi), alpha, 0, N);
     if (lane < 12)
-    {
+    { /* stage 0 has bounds on u only: slots 0..5 and 12..17 */
         const int k = lane < 6 ? lane : lane + 6;
         AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
     }
-    grp_lerp(AR(lam), AR(slam), alpha, NB, N * NB);
+    st_lerp<NB>(AR(lam), AR(slam), alpha, 1, N);
     if (I.pe && lane >= 12 && lane < 14)
     {
         const int k = lane == 12 ? TERM_LO(N) : TERM_UP(N);
@@ -2198,12 +2255,23 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
     if (init_from_nlp && warm == 2)
     {
         /* ocp_nlp_initialize_qp_from_nlp (AC/ocp_nlp/ocp_nlp_common.c:3320-3340) + ocp_qp_compute_t at ux = 0 */
-        for (int k = lane; k < N * NX; k += GL) AR(spi)[k] = AR(pi)[k];
-        for (int k = lane; k < N * NB; k += GL)
+        for (int i = lane; i < N; i += GL)
         {
-            if (k < NB && (k % 12) >= 6) continue;
-            AR(slam)[k] = AR(lam)[k];
-            AR(st)[k] = -AR(d)[k];
+            double pi[NX];
+            ldv<NX>(AR(pi) + SO(i), pi);
+            stv<NX>(AR(spi) + SO(i), pi);
+            RD_UNROLL
+            for (int h = 0; h < NB; h += 6)
+            { /* 6 slots at a time; stage 0 only has the u slots 0..5 and 12..17 */
+                if (i == 0 && (h % 12) >= 6) continue;
+                double lam[6], dd[6];
+                ldv<6>(AR(lam) + SO(i) + h, lam);
+                ldv<6>(AR(d) + SO(i) + h, dd);
+                RD_UNROLL
+                for (int k = 0; k < 6; k++) dd[k] = -dd[k];
+                stv<6>(AR(slam) + SO(i) + h, lam);
+                stv<6>(AR(st) + SO(i) + h, dd);
+            }
         }
         if (I.pe && lane < 2)
         {
@@ -2298,21 +2366,18 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
 /* Primal shift of the initial guess between two closed-loop steps (RmpcWs.shift; the acados MPC idiom
  * set(i, 'x', get(i+1, 'x')), set(i, 'u', get(i+1, 'u')) for i < N-1, set(N-1, 'x', get(N, 'x')) -- SURVEY.md 8(f) #1; the
- * reference itself never shifts).  Multipliers and merit weights stay.  [u; x] of the stages are contiguous, so the shift
- * is one move by NV doubles towards the front: ascending chunks of GL elements, each lane loads before it stores and no
- * chunk writes what a later one still reads (NV > GL). */
+ * reference itself never shifts).  Multipliers and merit weights stay. */
 RD void nlp_shift(const RmpcDims &D, const Inst &I)
 {
     const int N = D.N, lane = rd_lane();
     double *ux = AR(ux);
-    const int n = NV * (N - 1);
-    for (int k0 = 0; k0 < n; k0 += GL)
-    {
-        const int k = k0 + lane;
-        double v = 0.0;
-        if (k < n) v = ux[k + NV];
+    for (int i0 = 0; i0 < N - 1; i0 += GL)
+    { /* [u; x] of stage i <- stage i + 1 for i < N - 1: chunks of GL stages, every lane loads before any lane stores */
+        const int i = i0 + lane;
+        double v[NV];
+        if (i < N - 1) ldv<NV>(ux + SO(i + 1), v);
         rd_sync();
-        if (k < n) ux[k] = v;
+        if (i < N - 1) stv<NV>(ux + SO(i), v);
     }
     rd_sync();
     if (lane < NX) ux[SO(N - 1) + 6 + lane] = ux[SO(N) + 6 + lane];

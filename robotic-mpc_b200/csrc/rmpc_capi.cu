@@ -62,7 +62,7 @@ __global__ void rmpc_init_iterate_kernel(const RmpcDims D, const RmpcWs W)
     {
         const long i = k / (S * NV), r = k % (S * NV);
         const int c = (int) (k % NV);
-        W.slab[i * W.slab_stride + rmpc_slab_off(D.N, RC_ux, NV, (int) (r / NV)) + c] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
+        W.slab[i * W.slab_stride + RMPC_HEAD + (long) RC_ux * W.Sp + r] = c >= 6 ? W.z[i * NX + c - 6] : 0.0;
     }
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < (long) D.B * 4; k += (long) gridDim.x * blockDim.x)
         W.flags[k] = (k % 4) < 2 ? 1 : 0;

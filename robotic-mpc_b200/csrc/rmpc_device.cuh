@@ -122,11 +122,11 @@ RD double grp_max(double v)
 /* ---------------------------------------------------------------------------------------------- shared memory
  * one block per group (instance).  `buf` is carved per sweep:
  *   factorisation : P+ (12 x SM_PS) | Lxu (72) | Muu in (28) | L out (34) | two staging buffers of FS_STGN doubles
- *   forward / backward substitution : two staging buffers of SW_STGN doubles; update + residual sweep: three of QG_END
+ *   forward / backward substitution : two staging buffers of SW_STGN doubles
  * The staging buffers are filled one stage AHEAD by cp.async (LDGSTS), so that inside a stage every operand comes from
  * shared memory and the HBM / L2 latency of the streamed factors and residuals is off the critical path. */
 #define SM_PS 14 /* row stride of P: even (16-byte aligned pairs), 28 words -> rows 0..5 hit distinct banks */
-#define SM_BUF 812
+#define SM_BUF 752
 struct GrpSmem
 {
     double cst[24];       /* a12(6) a22(6) b1(6) b2(6) of the exact-ZOH model */
@@ -147,9 +147,9 @@ struct GrpSmem
 #define FS_LXU(sm) ((sm).buf + 168) /* Lxu of the current stage (for the Schur complement) */
 #define FS_MIN(sm) ((sm).buf + 240) /* lower 6x6 block Muu (21) + m_u (6) */
 #define FS_LOUT(sm) ((sm).buf + 268) /* L (21, packed with diagonal) + l_u (6) + 1/diag (6) */
-#define FS_STGN 162
+#define FS_STGN 164
 #define FS_STG(sm, k) ((sm).buf + 304 + (k) * FS_STGN)
-#define SW_STGN 406
+#define SW_STGN 376
 #define SW_STG(sm, k) ((sm).buf + (k) * SW_STGN)
 
 /* group-wide asynchronous copy of n doubles (n even, both sides 16-byte aligned) global -> shared */
@@ -162,92 +162,79 @@ RD void stage_cp(double *dst, const double *src, const int n)
         if ((c + 1) * GL <= n / 2 || rd_lane() + c * GL < n / 2) rd_cp_async16(dst + l2 + 2 * GL * c, src + l2 + 2 * GL * c);
 }
 
-/* Stage-parallel vector passes over slices of the stage records (rmpc_types.h): lane l handles stages i0 + l, i0 + l + GL, ...
- * and works on all W doubles of its stage at once (W even, every slice 16-byte aligned: 128-bit accesses), so each load of a
- * stage is in flight before the first use and a pass over the horizon costs ceil(N / GL) round trips to memory. */
-template <int W>
-RD void ldv(const double *p, double *v)
+/* Flat group-wide vector updates over whole arrays (n even, both sides 16-byte aligned): 128-bit accesses, and the loads of
+ * four strides -- eight doubles per operand and lane -- are issued before the first use.  These passes are pure streaming;
+ * what they cost is round trips to memory, so each trip carries as much as the registers allow. */
+#ifdef RMPC_EMU
+#define RD_RESTRICT
+#else
+#define RD_RESTRICT __restrict__
+#endif
+#define RD_V2(p) reinterpret_cast<rd_double2 *>(p)
+#define RD_CV2(p) reinterpret_cast<const rd_double2 *>(p)
+template <class F>
+RD void grp_map2(double *RD_RESTRICT y, const double *RD_RESTRICT x, int k0, int n, F f) /* y[k] = f(x[k], y[k]) on [k0, n) */
 {
-    RD_UNROLL
-    for (int c = 0; c < W; c += 2)
+    rd_double2 *y2 = RD_V2(y + k0);
+    const rd_double2 *x2 = RD_CV2(x + k0);
+    const int n2 = (n - k0) / 2;
+    int k = rd_lane();
+    for (; k + 3 * GL < n2; k += 4 * GL)
     {
-        const rd_double2 t = *reinterpret_cast<const rd_double2 *>(p + c);
-        v[c] = t.x; v[c + 1] = t.y;
+        const rd_double2 x0 = x2[k], x1 = x2[k + GL], xx2 = x2[k + 2 * GL], x3 = x2[k + 3 * GL];
+        rd_double2 y0 = y2[k], y1 = y2[k + GL], yy2 = y2[k + 2 * GL], y3 = y2[k + 3 * GL];
+        y0.x = f(x0.x, y0.x); y0.y = f(x0.y, y0.y); y1.x = f(x1.x, y1.x); y1.y = f(x1.y, y1.y);
+        yy2.x = f(xx2.x, yy2.x); yy2.y = f(xx2.y, yy2.y); y3.x = f(x3.x, y3.x); y3.y = f(x3.y, y3.y);
+        y2[k] = y0; y2[k + GL] = y1; y2[k + 2 * GL] = yy2; y2[k + 3 * GL] = y3;
+    }
+    for (; k < n2; k += GL)
+    {
+        const rd_double2 x0 = x2[k];
+        rd_double2 y0 = y2[k];
+        y0.x = f(x0.x, y0.x); y0.y = f(x0.y, y0.y);
+        y2[k] = y0;
     }
 }
-template <int W>
-RD void stv(double *p, const double *v)
+RD void grp_axpy(double *RD_RESTRICT y, const double *RD_RESTRICT x, double a, int n) /* y += a x */
 {
-    RD_UNROLL
-    for (int c = 0; c < W; c += 2)
+    grp_map2(y, x, 0, n, [a](double xv, double yv) { return yv + a * xv; });
+}
+RD void grp_xpay_to(double *RD_RESTRICT z, const double *RD_RESTRICT x, const double *RD_RESTRICT y, double a, int n) /* z = x + a y */
+{
+    rd_double2 *z2 = RD_V2(z);
+    const rd_double2 *x2 = RD_CV2(x), *y2 = RD_CV2(y);
+    const int n2 = n / 2;
+    int k = rd_lane();
+    for (; k + 3 * GL < n2; k += 4 * GL)
     {
-        rd_double2 t;
-        t.x = v[c]; t.y = v[c + 1];
-        *reinterpret_cast<rd_double2 *>(p + c) = t;
+        const rd_double2 x0 = x2[k], x1 = x2[k + GL], xx2 = x2[k + 2 * GL], x3 = x2[k + 3 * GL];
+        const rd_double2 y0 = y2[k], y1 = y2[k + GL], yy2 = y2[k + 2 * GL], y3 = y2[k + 3 * GL];
+        rd_double2 r0, r1, r2, r3;
+        r0.x = x0.x + a * y0.x; r0.y = x0.y + a * y0.y; r1.x = x1.x + a * y1.x; r1.y = x1.y + a * y1.y;
+        r2.x = xx2.x + a * yy2.x; r2.y = xx2.y + a * yy2.y; r3.x = x3.x + a * y3.x; r3.y = x3.y + a * y3.y;
+        z2[k] = r0; z2[k + GL] = r1; z2[k + 2 * GL] = r2; z2[k + 3 * GL] = r3;
+    }
+    for (; k < n2; k += GL)
+    {
+        const rd_double2 x0 = x2[k], y0 = y2[k];
+        rd_double2 r0;
+        r0.x = x0.x + a * y0.x; r0.y = x0.y + a * y0.y;
+        z2[k] = r0;
     }
 }
-#define SO(i) (RMPC_REC * (i)) /* offset of stage i's record */
-/* a slice is processed in chunks of at most 12 doubles (6 128-bit loads per operand in flight, ~50 live registers) */
-#define ST_CH(W) ((W) > 18 ? (W) / 2 : (W))
-template <int W>
-RD void st_axpy(double *y0, const double *x0, double a, int i0, int i1) /* y += a x */
+RD void grp_lerp(double *RD_RESTRICT y, const double *RD_RESTRICT x, double al, int k0, int n) /* y = (1-al) y + al x on [k0, n) */
 {
-    for (int i = i0 + rd_lane(); i < i1; i += GL)
-        RD_UNROLL
-        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
-        {
-            double x[ST_CH(W)], y[ST_CH(W)];
-            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
-            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
-            RD_UNROLL
-            for (int c = 0; c < ST_CH(W); c++) y[c] = y[c] + a * x[c];
-            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
-        }
+    grp_map2(y, x, k0, n, [al](double xv, double yv) { return (1.0 - al) * yv + al * xv; });
 }
-template <int W>
-RD void st_xpay_to(double *z0, const double *x0, const double *y0, double a, int i0, int i1) /* z = x + a y */
+/* Leineweber merit-weight update w = t0 (first SQP iteration) or max(t0, (t0 + w) / 2) with t0 = t or |t|, on [k0, n) */
+RD void grp_weights(double *RD_RESTRICT w, const double *RD_RESTRICT t, int first, int use_abs, int k0, int n)
 {
-    for (int i = i0 + rd_lane(); i < i1; i += GL)
-        RD_UNROLL
-        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
-        {
-            double x[ST_CH(W)], y[ST_CH(W)];
-            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
-            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
-            RD_UNROLL
-            for (int c = 0; c < ST_CH(W); c++) x[c] = x[c] + a * y[c];
-            stv<ST_CH(W)>(z0 + SO(i) + c0, x);
-        }
-}
-template <int W>
-RD void st_add(double *y0, const double *x0, int i0, int i1) /* y += x */
-{
-    for (int i = i0 + rd_lane(); i < i1; i += GL)
-        RD_UNROLL
-        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
-        {
-            double x[ST_CH(W)], y[ST_CH(W)];
-            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
-            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
-            RD_UNROLL
-            for (int c = 0; c < ST_CH(W); c++) y[c] += x[c];
-            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
-        }
-}
-template <int W>
-RD void st_lerp(double *y0, const double *x0, double al, int i0, int i1) /* y = (1 - al) y + al x */
-{
-    for (int i = i0 + rd_lane(); i < i1; i += GL)
-        RD_UNROLL
-        for (int c0 = 0; c0 < W; c0 += ST_CH(W))
-        {
-            double x[ST_CH(W)], y[ST_CH(W)];
-            ldv<ST_CH(W)>(x0 + SO(i) + c0, x);
-            ldv<ST_CH(W)>(y0 + SO(i) + c0, y);
-            RD_UNROLL
-            for (int c = 0; c < ST_CH(W); c++) y[c] = (1.0 - al) * y[c] + al * x[c];
-            stv<ST_CH(W)>(y0 + SO(i) + c0, y);
-        }
+    grp_map2(w, t, k0, n, [first, use_abs](double tv, double wv) {
+        const double t0 = use_abs ? fabs(tv) : tv;
+        if (first) return t0;
+        const double t1 = 0.5 * (t0 + wv);
+        return t0 > t1 ? t0 : t1;
+    });
 }
 
 /* per-instance view (layout: rmpc_types.h): parameter row, slab head, first array, stage slots, plant state, flags */
@@ -264,9 +251,7 @@ struct Inst
  * the interior-point loop (different iteration counts); once apart, the warp issues every instruction twice at half
  * width.  At places that every group passes exactly once per step they wait for each other and run in lock step again. */
 #define PAIR_SYNC() rd_sync_mask(I.pair)
-/* stage-major slab (rmpc_types.h): AR(name) = array <name> of stage 0, SO(i) = offset of stage i's record */
-#define REC RMPC_REC
-#define AR(name) (I.arr0 + RC_##name)
+#define AR(name) (I.arr0 + (long) RC_##name * I.Sp)
 
 RD Inst inst_view(const RmpcWs &w, int N, long i)
 {
@@ -290,8 +275,8 @@ RD double psym(const double *P, int r, int c) { return r >= c ? P[(r * (r + 1)) 
  * lane and, with `grad`, writes the gradient 2 P x (the stage-N row of DCt).  Replaces the CasADi-generated
  * *_constr_h_e_fun[_jac_uxt_zt] pair that acados' BGH module would call (AC/ocp_nlp/ocp_nlp_constraints_bgh.c:
  * 1219-1445,1563-1619) for con_h_expr_e = x' P x with P from R/_terminal_constraint.py:96-116. */
-#define TERM_LO(N) (SO(N))      /* slot of the lower side lh - h_e in the NB-wide per-stage arrays (stage N's record) */
-#define TERM_UP(N) (SO(N) + 12) /* slot of the upper side h_e - uh */
+#define TERM_LO(N) (NB * (N))      /* slot of the lower side lh - h_e in the NB-wide per-stage arrays */
+#define TERM_UP(N) (NB * (N) + 12) /* slot of the upper side h_e - uh */
 RD double term_eval(const double *pe, const double *x, double *grad)
 {
     const int l = rd_lane();
@@ -650,10 +635,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
     for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
-        load18(AR(ux) + SO(i), v);
-        double *g = AR(rqz) + SO(i);
+        load18(AR(ux) + NV * i, v);
+        double *g = AR(rqz) + NV * i;
         LinEmit em;
-        em.Jc = AR(Jc) + SO(i);
+        em.Jc = AR(Jc) + NJ * i;
         em.g = g;
         const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
         RD_UNROLL
@@ -669,10 +654,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
         const double ci = stage_cost(par, dt, y5, v, v + 12);
         cost += ci;
-        AR(tux)[SO(i)] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
+        AR(tux)[NV * i] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
         /* dynamics gap b = Ad x + Bd u - x_next */
-        const double *xn = AR(ux) + SO(i + 1) + 6;
-        double *b = AR(b) + SO(i), *d = AR(d) + SO(i);
+        const double *xn = AR(ux) + NV * (i + 1) + 6;
+        double *b = AR(b) + NX * i, *d = AR(d) + NB * i;
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -691,10 +676,10 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
             for (int k = 0; k < NX; k++) (I.head + H_DX0)[k] = x0[k] - v[6 + k];
         }
     }
-    for (int k = lane; k < NV; k += GL) AR(rqz)[SO(N) + k] = 0.0; /* stage N: no cost (ny_e = 0) */
+    for (int k = lane; k < NV; k += GL) AR(rqz)[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
     if (I.pe)
     { /* terminal row: fun = [lh - h_e; h_e - uh], DCt = grad h_e (kept in Jc[N][0..11]) */
-        const double h = term_eval(I.pe, AR(ux) + SO(N) + 6, AR(Jc) + SO(N));
+        const double h = term_eval(I.pe, AR(ux) + NV * N + 6, AR(Jc) + NJ * N);
         if (lane == 0)
         {
             AR(d)[TERM_LO(N)] = I.pe[RE_LH] - h;
@@ -718,13 +703,13 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
     for (int i = lane; i < N; i += GL)
     {
         double v[NV], y5[5];
-        load18(tux + SO(i), v);
+        load18(tux + NV * i, v);
         NoEmit ne;
         ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
         const double ci = stage_cost(par, D.dt, y5, v, v + 12);
         m += ci;
         csum += ci; /* the cost alone, summed like solver.get_cost() does (closed_loop_group) */
-        const double *xn = tux + SO(i + 1) + 6, *wpi = AR(wpi) + SO(i), *wl = AR(wlam) + SO(i);
+        const double *xn = tux + NV * (i + 1) + 6, *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i;
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
@@ -753,7 +738,7 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
     }
     if (I.pe)
     {
-        const double h = term_eval(I.pe, tux + SO(N) + 6, nullptr);
+        const double h = term_eval(I.pe, tux + NV * N + 6, nullptr);
         const double fl = I.pe[RE_LH] - h, fu = h - I.pe[RE_UH];
         if (lane == 0)
         {
@@ -776,11 +761,11 @@ RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
     double m = 0.0;
     for (int i = lane; i < N; i += GL)
     {
-        m += AR(tux)[SO(i)];
-        const double *wpi = AR(wpi) + SO(i), *wl = AR(wlam) + SO(i), *d = AR(d) + SO(i);
+        m += AR(tux)[NV * i];
+        const double *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i, *d = AR(d) + NB * i;
         if (i == 0)
         {
-            const double *v = AR(ux), *xn = AR(ux) + SO(1) + 6;
+            const double *v = AR(ux), *xn = AR(ux) + NV + 6;
             RD_UNROLL
             for (int k = 0; k < 6; k++)
             {
@@ -791,7 +776,7 @@ RDN double nlp_merit_lin(const RmpcDims &D, const Inst &I_, const double *x0)
         }
         else
         {
-            const double *b = AR(b) + SO(i);
+            const double *b = AR(b) + NX * i;
             RD_UNROLL
             for (int k = 0; k < 6; k++) m += fabs(wpi[k]) * fabs(b[k]) + fabs(wpi[6 + k]) * fabs(b[6 + k]);
         }
@@ -835,10 +820,10 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
     {
         double r[NV];
         RD_UNROLL
-        for (int k = 0; k < NV; k++) r[k] = AR(rqz)[SO(i) + k];
+        for (int k = 0; k < NV; k++) r[k] = AR(rqz)[NV * i + k];
         if (i < N)
         {
-            const double *lam = AR(lam) + SO(i), *pi = AR(pi) + SO(i), *d = AR(d) + SO(i);
+            const double *lam = AR(lam) + NB * i, *pi = AR(pi) + NX * i, *d = AR(d) + NB * i;
             RD_UNROLL
             for (int j = 0; j < 12; j++)
             {
@@ -853,7 +838,7 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
                 r[k] += par[RP_B1 + k] * pi[k] + par[RP_B2 + k] * pi[6 + k];
                 r[6 + k] += pi[k];
                 r[12 + k] += par[RP_A12 + k] * pi[k] + par[RP_A22 + k] * pi[6 + k];
-                re = rd_fmax(re, rd_fmax(fabs(AR(b)[SO(i) + k]), fabs(AR(b)[SO(i) + 6 + k])));
+                re = rd_fmax(re, rd_fmax(fabs(AR(b)[NX * i + k]), fabs(AR(b)[NX * i + 6 + k])));
             }
         }
         if (i == 0)
@@ -870,13 +855,13 @@ RDN void nlp_residuals(const RmpcDims &D, const Inst &I_, double *res)
         else
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[SO(i - 1) + k];
+            for (int k = 0; k < NX; k++) r[6 + k] -= AR(pi)[NX * (i - 1) + k];
         }
         if (i == N && I.pe)
         { /* terminal row: adj += DCt (lam_l - lam_u) */
             const double ll = AR(lam)[TERM_LO(N)], lu = AR(lam)[TERM_UP(N)], fl = AR(d)[TERM_LO(N)], fu = AR(d)[TERM_UP(N)];
             RD_UNROLL
-            for (int k = 0; k < NX; k++) r[6 + k] -= (AR(Jc) + SO(N))[k] * (ll - lu);
+            for (int k = 0; k < NX; k++) r[6 + k] -= (AR(Jc) + NJ * N)[k] * (ll - lu);
             ri = rd_fmax(ri, rd_fmax(fl, fu));
             rc = rd_fmax(rc, rd_fmax(fabs(ll * fl), fabs(lu * fu)));
         }
@@ -915,66 +900,85 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
-    /* stage-parallel: lane l initialises stages l, l + GL, ... (every array of a stage is in that stage's record) */
-    for (int i = lane; i <= N; i += GL)
     {
-        double ux[NV];
-        RD_UNROLL
-        for (int k = 0; k < NV; k++) ux[k] = 0.0;
-        if (i < N)
-        {
-            if (warm != 2)
-            {
-                double z[NX];
-                RD_UNROLL
-                for (int k = 0; k < NX; k++) z[k] = 0.0;
-                stv<NX>(AR(spi) + SO(i), z);
-            }
-            /* bound slots in two halves of 6 (lower side j, upper side 12 + j): stage 0 only has the u half */
-            RD_UNROLL
-            for (int h = 0; h < 12; h += 6)
-            {
-                if (i == 0 && h >= 6) continue;
-                double la[6], lb[6], ta[6], tb[6];
-                double *pl = AR(slam) + SO(i) + h, *pt = AR(st) + SO(i) + h;
-                if (warm == 2)
-                {
-                    ldv<6>(pl, la); ldv<6>(pl + 12, lb); ldv<6>(pt, ta); ldv<6>(pt + 12, tb);
-                    RD_UNROLL
-                    for (int j = 0; j < 6; j++)
-                    {
-                        if (la[j] < 1e-1) la[j] = 1e-1;
-                        if (lb[j] < 1e-1) lb[j] = 1e-1;
-                        if (ta[j] < 1e-1) ta[j] = 1e-1;
-                        if (tb[j] < 1e-1) tb[j] = 1e-1;
-                    }
-                }
-                else
-                {
-                    double da[6], db[6];
-                    ldv<6>(AR(d) + SO(i) + h, da); ldv<6>(AR(d) + SO(i) + 12 + h, db);
-                    RD_UNROLL
-                    for (int j = 0; j < 6; j++)
-                    {
-                        const double thr0 = 1e-1, dl = da[j], du = db[j];
-                        double v = 0.0, tl = -dl, tu = -du;
-                        if (tl < thr0)
-                        {
-                            if (tu < thr0) { v = 0.5 * (dl - du); tl = thr0; tu = thr0; }
-                            else { tl = thr0; v = dl + thr0; }
-                        }
-                        else if (tu < thr0) { tu = thr0; v = -du - thr0; }
-                        ux[h + j] = v;
-                        ta[j] = tl; tb[j] = tu;
-                        la[j] = 1.0 / tl; lb[j] = 1.0 / tu;
-                    }
-                }
-                stv<6>(pl, la); stv<6>(pl + 12, lb); stv<6>(pt, ta); stv<6>(pt + 12, tb);
-            }
-        }
-        stv<NV>(AR(sux) + SO(i), ux);
+        rd_double2 zz;
+        zz.x = 0.0; zz.y = 0.0;
+        for (int k = lane; k < (N + 1) * NV / 2; k += GL) RD_V2(AR(sux))[k] = zz;
+        if (warm != 2)
+            for (int k = lane; k < N * NX / 2; k += GL) RD_V2(AR(spi))[k] = zz;
     }
     rd_sync();
+    /* stage-parallel over the bound slots: lane l takes stages l, l + GL, ..., six slots (lower side j, upper side 12 + j)
+     * at a time with 128-bit accesses; stage 0 only has the u half */
+    for (int i = lane; i < N; i += GL)
+    {
+        RD_UNROLL
+        for (int h = 0; h < 12; h += 6)
+        {
+            if (i == 0 && h >= 6) continue;
+            double la[6], lb[6], ta[6], tb[6];
+            double *pl = AR(slam) + NB * i + h, *pt = AR(st) + NB * i + h;
+            if (warm == 2)
+            {
+                RD_UNROLL
+                for (int c = 0; c < 6; c += 2)
+                {
+                    const rd_double2 a0 = *RD_CV2(pl + c), a1 = *RD_CV2(pl + 12 + c), a2 = *RD_CV2(pt + c), a3 = *RD_CV2(pt + 12 + c);
+                    la[c] = a0.x; la[c + 1] = a0.y; lb[c] = a1.x; lb[c + 1] = a1.y;
+                    ta[c] = a2.x; ta[c + 1] = a2.y; tb[c] = a3.x; tb[c + 1] = a3.y;
+                }
+                RD_UNROLL
+                for (int j = 0; j < 6; j++)
+                {
+                    if (la[j] < 1e-1) la[j] = 1e-1;
+                    if (lb[j] < 1e-1) lb[j] = 1e-1;
+                    if (ta[j] < 1e-1) ta[j] = 1e-1;
+                    if (tb[j] < 1e-1) tb[j] = 1e-1;
+                }
+            }
+            else
+            {
+                double da[6], db[6];
+                const double *pd = AR(d) + NB * i + h;
+                RD_UNROLL
+                for (int c = 0; c < 6; c += 2)
+                {
+                    const rd_double2 a0 = *RD_CV2(pd + c), a1 = *RD_CV2(pd + 12 + c);
+                    da[c] = a0.x; da[c + 1] = a0.y; db[c] = a1.x; db[c + 1] = a1.y;
+                }
+                RD_UNROLL
+                for (int j = 0; j < 6; j++)
+                {
+                    const double thr0 = 1e-1, dl = da[j], du = db[j];
+                    double v = 0.0, tl = -dl, tu = -du;
+                    if (tl < thr0)
+                    {
+                        if (tu < thr0) { v = 0.5 * (dl - du); tl = thr0; tu = thr0; }
+                        else { tl = thr0; v = dl + thr0; }
+                    }
+                    else if (tu < thr0) { tu = thr0; v = -du - thr0; }
+                    da[j] = v;
+                    ta[j] = tl; tb[j] = tu;
+                    la[j] = 1.0 / tl; lb[j] = 1.0 / tu;
+                }
+                RD_UNROLL
+                for (int c = 0; c < 6; c += 2)
+                {
+                    rd_double2 v2;
+                    v2.x = da[c]; v2.y = da[c + 1];
+                    *RD_V2(AR(sux) + NV * i + h + c) = v2;
+                }
+            }
+            RD_UNROLL
+            for (int c = 0; c < 6; c += 2)
+            {
+                rd_double2 a0, a1, a2, a3;
+                a0.x = la[c]; a0.y = la[c + 1]; a1.x = lb[c]; a1.y = lb[c + 1];
+                a2.x = ta[c]; a2.y = ta[c + 1]; a3.x = tb[c]; a3.y = tb[c + 1];
+                *RD_V2(pl + c) = a0; *RD_V2(pl + 12 + c) = a1; *RD_V2(pt + c) = a2; *RD_V2(pt + 12 + c) = a3;
+            }
+        }
+    }
     if (I.pe && lane < 2)
     { /* general row of stage N (x_ocp_qp_ipm.c:1780-1817): t = +-C ux - d at ux = 0, clipped at 0.1; lam = mu0 / t */
         const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -1036,9 +1040,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
     for (int i = lane; i <= N; i += GL)
     {
         double v[NV], g[NV];
-        load18(ux + SO(i), v);
+        load18(ux + NV * i, v);
         RD_UNROLL
-        for (int k = 0; k < NV; k++) g[k] = rqz[SO(i) + k];
+        for (int k = 0; k < NV; k++) g[k] = rqz[NV * i + k];
         if (i == 0)
         {
             RD_UNROLL
@@ -1047,9 +1051,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         if (i < N)
         {
             /* H v: task part on x (stages >= 1), constant diagonal blocks */
-            if (i > 0) task_hess_mv(AR(Jc) + SO(i), v + 6, g + 6);
-            const double *pin = pi + SO(i), *l = lam + SO(i), *tt = t + SO(i);
-            const double *xn = ux + SO(i + 1) + 6;
+            if (i > 0) task_hess_mv(AR(Jc) + NJ * i, v + 6, g + 6);
+            const double *pin = pi + NX * i, *l = lam + NB * i, *tt = t + NB * i;
+            const double *xn = ux + NV * (i + 1) + 6;
             RD_UNROLL
             for (int k = 0; k < 6; k++)
             {
@@ -1061,9 +1065,9 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
                     g[6 + k] += pin[k];
                     g[12 + k] += hs * v[k] + hq * v[12 + k] + a12 * pin[k] + a22 * pin[6 + k];
                 }
-                const double r0 = b[SO(i) + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
-                const double r1 = b[SO(i) + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
-                if (WRITE) { rb[SO(i) + k] = r0; rb[SO(i) + 6 + k] = r1; }
+                const double r0 = b[NX * i + k] - xn[k] + (v[6 + k] + a12 * v[12 + k]) + b1 * v[k];
+                const double r1 = b[NX * i + 6 + k] - xn[6 + k] + a22 * v[12 + k] + b2 * v[k];
+                if (WRITE) { rb[NX * i + k] = r0; rb[NX * i + 6 + k] = r1; }
                 n1 = rd_fmax(n1, rd_fmax(fabs(r0), fabs(r1)));
             }
             RD_UNROLL
@@ -1071,16 +1075,16 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
             {
                 if (i == 0 && j >= 6) continue;
                 g[j] += l[12 + j] - l[j];
-                const double dl = d[SO(i) + j] + tt[j] - v[j], du = d[SO(i) + 12 + j] + tt[12 + j] + v[j];
-                if (WRITE) { rd[SO(i) + j] = dl; rd[SO(i) + 12 + j] = du; }
+                const double dl = d[NB * i + j] + tt[j] - v[j], du = d[NB * i + 12 + j] + tt[12 + j] + v[j];
+                if (WRITE) { rd[NB * i + j] = dl; rd[NB * i + 12 + j] = du; }
                 double ml, mu_;
                 if (!LIN) { ml = l[j] * tt[j]; mu_ = l[12 + j] * tt[12 + j]; mu += ml + mu_; }
                 else
                 {
-                    ml = (m[SO(i) + j] - mshift) + Lam[SO(i) + j] * tt[j] + l[j] * T[SO(i) + j];
-                    mu_ = (m[SO(i) + 12 + j] - mshift) + Lam[SO(i) + 12 + j] * tt[12 + j] + l[12 + j] * T[SO(i) + 12 + j];
+                    ml = (m[NB * i + j] - mshift) + Lam[NB * i + j] * tt[j] + l[j] * T[NB * i + j];
+                    mu_ = (m[NB * i + 12 + j] - mshift) + Lam[NB * i + 12 + j] * tt[12 + j] + l[12 + j] * T[NB * i + 12 + j];
                 }
-                if (WRITE) { rm[SO(i) + j] = ml; rm[SO(i) + 12 + j] = mu_; }
+                if (WRITE) { rm[NB * i + j] = ml; rm[NB * i + 12 + j] = mu_; }
                 n2 = rd_fmax(n2, rd_fmax(fabs(dl), fabs(du)));
                 n3 = rd_fmax(n3, rd_fmax(fabs(ml), fabs(mu_)));
                 n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
@@ -1089,11 +1093,11 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         if (i > 0)
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) g[6 + k] -= pi[SO(i - 1) + k];
+            for (int k = 0; k < NX; k++) g[6 + k] -= pi[NX * (i - 1) + k];
         }
         if (i == N && I.pe)
         { /* general row C x of stage N: res_g += C' (lam_u - lam_l), res_d = d + t -+ C x, res_m */
-            const double *c = AR(Jc) + SO(N);
+            const double *c = AR(Jc) + NJ * N;
             const int ka = TERM_LO(N), kb = TERM_UP(N);
             double cx = 0.0;
             RD_UNROLL
@@ -1117,7 +1121,7 @@ RDN double ipm_res(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, const d
         RD_UNROLL
         for (int k = 0; k < NV; k++)
         {
-            if (WRITE) rg[SO(i) + k] = g[k];
+            if (WRITE) rg[NV * i + k] = g[k];
             if ((i < N || k >= 6) && (i > 0 || k < 6)) n0 = rd_fmax(n0, fabs(g[k]));
         }
         if (i == 0 && g[0] != g[0]) nanflag = 1.0;
@@ -1169,11 +1173,18 @@ RD void smem_consts(const Inst &I, GrpSmem &sm, double dt)
  *   Luu Luu' = Muu, Lxu = Mxu Luu^-T, l_u = Luu^-1 m_u, P = Mxx - Lxu Lxu', p = m_x - Lxu l_u
  * (the reference factorises P = Lxx Lxx' as well and carries Lxx; see the header of this file).  The complementarity
  * residual enters as res_m - tau_min (BACKUP_RES_M + COMPUTE_TAU_MIN_QP, x_core_qp_ipm_aux.c:457-475,533-553). */
-/* staging layout of one stage for the factorisation: the contiguous slice [res_b .. st] of the stage record */
-enum { FG_RB = RC_res_b - RC_res_b, FG_RG = RC_res_g - RC_res_b, FG_RD = RC_res_d - RC_res_b, FG_RM = RC_res_m - RC_res_b,
-       FG_JC = RC_Jc - RC_res_b, FG_LAM = RC_slam - RC_res_b, FG_T = RC_st - RC_res_b, FG_END = RC_F - RC_res_b };
-static_assert(FG_END == FS_STGN, "factorisation staging size");
-RD void fac_stage_in(const Inst &I, double *dst, int ss) { stage_cp(dst, AR(res_b) + SO(ss), FG_END); }
+/* staging layout of one stage for the factorisation */
+enum { FG_LAM = 0, FG_T = 24, FG_RD = 48, FG_RM = 72, FG_RG = 96, FG_RB = 114, FG_JC = 126 };
+RD void fac_stage_in(const Inst &I, double *dst, int ss)
+{
+    stage_cp(dst + FG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + FG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + FG_RD, AR(res_d) + NB * ss, NB);
+    stage_cp(dst + FG_RM, AR(res_m) + NB * ss, NB);
+    stage_cp(dst + FG_RG, AR(res_g) + NV * ss, NV);
+    stage_cp(dst + FG_RB, AR(res_b) + NX * ss, NX);
+    if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
+}
 
 RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
 {
@@ -1190,14 +1201,14 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
     if (R.x)
     {
-        double *FN = AR(F) + SO(N);
-        double pv = AR(res_g)[SO(N) + 6 + xk];
+        double *FN = AR(F) + (long) FS * N;
+        double pv = AR(res_g)[NV * N + 6 + xk];
         double Prow[12];
         RD_UNROLL
         for (int c = 0; c < 12; c++) Prow[c] = (c == xk) ? reg : 0.0;
         if (I.pe)
         { /* general row of stage N (x_ocp_qp_kkt.c:859-868): P_N += C' Gamma C, p_N += C' gamma */
-            const double *cv = AR(Jc) + SO(N);
+            const double *cv = AR(Jc) + NJ * N;
             const int ka = TERM_LO(N), kb = TERM_UP(N);
             const double til = 1.0 / AR(st)[ka], tiu = 1.0 / AR(st)[kb];
             const double la = AR(slam)[ka], lb = AR(slam)[kb];
@@ -1219,7 +1230,7 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
-        double *F = AR(F) + SO(ss);
+        double *F = AR(F) + (long) FS * ss;
         const double *G = FS_STG(sm, ss & 1);
         if (ss > 0) fac_stage_in(I, FS_STG(sm, (ss - 1) & 1), ss - 1);
         rd_cp_commit();
@@ -1413,52 +1424,27 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
  *   sums[0] = sum lam dt + dlam t, sums[1] = sum dlam dt          (for COMPUTE_MU_AFF_QP, :424-441, see ipm_mu_aff)
  * STORED = 0: src_u = l_u and p+ from the factorisation (affine step); STORED = 1: src_u = z_u left in X[.][0:6] by
  * ipm_backward() and p+ = pvec.  rm enters as rm - mshift. */
-/* Staging of one stage for the forward sweep, KIND = 0 affine step, 1 corrector, 2 refinement (generic right-hand sides).
- * KIND 0: the slice [res_b .. F low part] of the stage record, then [P PV] of the NEXT stage's record;
- * KIND 1: the slice [dux .. F low part] (dux[0:6] = z_u left by ipm_backward, res_mc = the corrector's complementarity
- *         right-hand side), then [P PV pvec] of the next stage's record -- two contiguous ranges each;
- * KIND 2: the layout of KIND 1 filled piece by piece from the refinement arrays (rare path). */
-template <int KIND>
-struct WG
-{
-    enum
-    {
-        kBASE = KIND == 0 ? RC_res_b : RC_dux, /* record offset the first range starts at */
-        kZU = RC_dux - kBASE,                    /* KIND >= 1 */
-        kRM = (KIND == 0 ? RC_res_m : RC_res_mc) - kBASE,
-        kRB = RC_res_b - kBASE, kRG = RC_res_g - kBASE, kRD = RC_res_d - kBASE, kJC = RC_Jc - kBASE, kLAM = RC_slam - kBASE,
-        kT = RC_st - kBASE,
-        kF = RC_F - kBASE,          /* low part of the factor block: RF_INV, RF_LU, RF_LUU, RF_LXU */
-        kN1 = kF + RF_PB,           /* length of the first range */
-        kP = kN1,                   /* packed P of the next stage */
-        kPV = kP + (RF_PV - RF_P),  /* p of the next stage (affine step) */
-        kPVEC = kPV + NX,           /* pvec of the next stage (KIND >= 1) */
-        kN2 = KIND == 0 ? (RF_END - RF_P) : (RF_END - RF_P) + NX,
-        kEND = kN1 + kN2
-    };
-};
-static_assert(WG<1>::kEND <= SW_STGN && WG<0>::kEND <= SW_STGN, "forward staging size");
-template <int KIND>
+/* staging layout of one stage for the forward sweep: [0,100) = F[ss] (1/diag, l_u, Luu, Lxu), [100,190) = P, p of
+ * F[ss+1] at their RF_* offsets, then the bound-slot data, res_b and (STORED) z_u, p of the corrector */
+enum { WG_LAM = 190, WG_T = 214, WG_RD = 238, WG_RM = 262, WG_RB = 286, WG_ZU = 298, WG_PVEC = 304, WG_RG = 316, WG_JC = 334 };
+template <int STORED>
 RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rb, const double *rd, const double *rm,
                      const double *X)
 {
-    typedef WG<KIND> L;
-    if (KIND < 2)
+    stage_cp(dst + WG_RG, rg + NV * ss, NV);
+    if (ss > 0) stage_cp(dst + WG_JC, AR(Jc) + NJ * ss, NJ);
+    const double *F = AR(F) + (long) FS * ss;
+    stage_cp(dst, F, RF_P);
+    stage_cp(dst + RF_P, F + FS + RF_P, STORED ? RF_PV - RF_P : RF_PB - RF_P);
+    stage_cp(dst + WG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + WG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + WG_RD, rd + NB * ss, NB);
+    stage_cp(dst + WG_RM, rm + NB * ss, NB);
+    stage_cp(dst + WG_RB, rb + NX * ss, NX);
+    if (STORED)
     {
-        stage_cp(dst, I.arr0 + L::kBASE + SO(ss), L::kN1);
-        stage_cp(dst + L::kP, AR(F) + SO(ss + 1) + RF_P, L::kN2);
-    }
-    else
-    {
-        stage_cp(dst + L::kZU, X + SO(ss), 6);
-        stage_cp(dst + L::kRM, rm + SO(ss), NB);
-        stage_cp(dst + L::kRB, rb + SO(ss), NX);
-        stage_cp(dst + L::kRG, rg + SO(ss), NV);
-        stage_cp(dst + L::kRD, rd + SO(ss), NB);
-        if (ss > 0) stage_cp(dst + L::kJC, AR(Jc) + SO(ss), NJ);
-        stage_cp(dst + L::kLAM, AR(slam) + SO(ss), 2 * NB); /* slam and st are neighbours */
-        stage_cp(dst + L::kF, AR(F) + SO(ss), RF_PB);
-        stage_cp(dst + L::kP, AR(F) + SO(ss + 1) + RF_P, L::kN2);
+        stage_cp(dst + WG_ZU, X + NV * ss, 6);
+        stage_cp(dst + WG_PVEC, AR(pvec) + NX * (ss + 1), NX);
     }
 }
 
@@ -1468,20 +1454,18 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
  * lin[0] = |r|_inf, lin[1] = NaN flag of r_u[0] at stage 0.  The other three residuals of that system (dynamics,
  * bounds, complementarity) are zero up to rounding BY CONSTRUCTION of dx+, dt and dlam in this sweep and are not
  * re-evaluated. */
-template <int KIND>
+template <int STORED>
 RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const double *rg, const double *rb, const double *rd,
                     const double *rm, double mshift, double *X, double *PI, double *DL, double *DT, double *alpha_out,
                     double *sums, double *lin)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
-    typedef WG<KIND> L;
-    constexpr bool STORED = KIND != 0;
     const int N = D.N, lane = rd_lane();
     const Role R = make_role(I.par);
     const int j = R.j, xk = R.xk;
     const double a12 = C_A12(j), a22 = C_A22(j), b1 = C_B1(j), b2 = C_B2(j);
     const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
-    fwd_stage_in<KIND>(I, SW_STG(sm, 0), 0, rg, rb, rd, rm, X);
+    fwd_stage_in<STORED>(I, SW_STG(sm, 0), 0, rg, rb, rd, rm, X);
     rd_cp_commit();
     if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
     double alpha = 1.0, sB = 0.0, sC = 0.0;
@@ -1489,18 +1473,18 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
     for (int ss = 0; ss < N; ss++)
     {
         const double *G = SW_STG(sm, ss & 1);
-        if (ss + 1 < N) fwd_stage_in<KIND>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
+        if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
         rd_cp_commit();
         rd_cp_wait1();
         rd_sync();
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
-            double s = STORED ? G[L::kZU + lane] : G[L::kF + RF_LU + lane];
+            double s = STORED ? G[WG_ZU + lane] : G[RF_LU + lane];
             if (ss > 0)
             {
                 RD_UNROLL
-                for (int k = 0; k < 12; k++) s += G[L::kF + RF_LXU + k * 6 + lane] * sm.xv[k];
+                for (int k = 0; k < 12; k++) s += G[RF_LXU + k * 6 + lane] * sm.xv[k];
             }
             sm.uv[lane] = s;
         }
@@ -1509,11 +1493,11 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         if (ss > 0 && lane < 5)
         {
             RD_UNROLL
-            for (int k = 0; k < 6; k++) wm += G[L::kJC + 6 * lane + k] * sm.xv[k];
+            for (int k = 0; k < 6; k++) wm += G[WG_JC + 6 * lane + k] * sm.xv[k];
             if (lane == 4)
             {
                 RD_UNROLL
-                for (int k = 0; k < 6; k++) wm += G[L::kJC + 30 + k] * sm.xv[6 + k];
+                for (int k = 0; k < 6; k++) wm += G[WG_JC + 30 + k] * sm.xv[6 + k];
             }
         }
         rd_sync();
@@ -1524,9 +1508,9 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         RD_UNROLL
         for (int k = 5; k >= 0; k--)
         {
-            du[k] *= G[L::kF + RF_INV + k];
+            du[k] *= G[RF_INV + k];
             RD_UNROLL
-            for (int c = 0; c < k; c++) du[c] -= G[L::kF + RF_LUU + (k * (k - 1)) / 2 + c] * du[k];
+            for (int c = 0; c < k; c++) du[c] -= G[RF_LUU + (k * (k - 1)) / 2 + c] * du[k];
         }
         double duj = du[0], dul = du[0];
         RD_UNROLL
@@ -1541,22 +1525,22 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         double xn = 0.0;
         if (R.x)
         {
-            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[L::kRB + j];
-            else xn = a22 * sm.xv[6 + j] + b2 * duj + G[L::kRB + 6 + j];
+            if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[WG_RB + j];
+            else xn = a22 * sm.xv[6 + j] + b2 * duj + G[WG_RB + 6 + j];
         }
         rd_sync(); /* every lane has read xv, uv */
-        if (R.u) X[SO(ss) + lane] = dul;
-        if (R.x) { sm.xv[xk] = xn; X[SO(ss + 1) + 6 + xk] = xn; }
+        if (R.u) X[NV * ss + lane] = dul;
+        if (R.x) { sm.xv[xk] = xn; X[NV * (ss + 1) + 6 + xk] = xn; }
         if (lane < 5) sm.wv[lane] = wm;
         rd_sync();
         /* dpi = P+ dx+ + p+ */
         double dpo = 0.0;
         if (R.x)
         {
-            double a = STORED ? G[L::kPVEC + xk] : G[L::kPV + xk];
+            double a = STORED ? G[WG_PVEC + xk] : G[RF_PV + xk];
             RD_UNROLL
-            for (int c = 0; c < 12; c++) a += psym(G + L::kP, xk, c) * sm.xv[c];
-            PI[SO(ss) + xk] = a;
+            for (int c = 0; c < 12; c++) a += psym(G + RF_P, xk, c) * sm.xv[c];
+            PI[NX * ss + xk] = a;
             sm.dp[xk] = a;
             dpo = a;
         }
@@ -1564,9 +1548,9 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         double dlm = 0.0; /* dlam_ub - dlam_lb of the own slot */
         if (lane < 12 && !(ss == 0 && lane >= 6))
         {
-            const int ia = SO(ss) + lane, ib = ia + 12;
-            const double la = G[L::kLAM + lane], lb = G[L::kLAM + 12 + lane], ta = G[L::kT + lane], tb = G[L::kT + 12 + lane];
-            const double da = G[L::kRD + lane], db = G[L::kRD + 12 + lane], ma = G[L::kRM + lane] - mshift, mb = G[L::kRM + 12 + lane] - mshift;
+            const int ia = NB * ss + lane, ib = ia + 12;
+            const double la = G[WG_LAM + lane], lb = G[WG_LAM + 12 + lane], ta = G[WG_T + lane], tb = G[WG_T + 12 + lane];
+            const double da = G[WG_RD + lane], db = G[WG_RD + 12 + lane], ma = G[WG_RM + lane] - mshift, mb = G[WG_RM + 12 + lane] - mshift;
             const double dla = -(ma + (la * dv) - (la * da)) / ta;
             const double dlb = -(mb + (lb * (-dv)) - (lb * db)) / tb;
             const double dta = dv - da, dtb = -dv - db;
@@ -1581,16 +1565,16 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         }
         /* operands of the residual rows that live in the staging buffer (refilled after the barrier) */
         double rgu = 0.0, rgx = 0.0, jq[5] = {0, 0, 0, 0, 0}, jd = 0.0;
-        if (R.u) rgu = G[L::kRG + lane];
+        if (R.u) rgu = G[WG_RG + lane];
         if (R.x && ss > 0)
         {
-            rgx = G[L::kRG + 6 + xk];
+            rgx = G[WG_RG + 6 + xk];
             if (R.q)
             {
                 RD_UNROLL
-                for (int m = 0; m < 5; m++) jq[m] = G[L::kJC + 6 * m + j];
+                for (int m = 0; m < 5; m++) jq[m] = G[WG_JC + 6 * m + j];
             }
-            else jd = G[L::kJC + 30 + j];
+            else jd = G[WG_JC + 30 + j];
         }
         rd_sync(); /* dp, wv published; the staging buffer of this stage is refilled by the next iteration */
         if (R.u)
@@ -1614,11 +1598,11 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         dp_prev = dpo;
     }
     rd_cp_wait0();
-    if (R.u) X[SO(N) + lane] = 0.0;
+    if (R.u) X[NV * N + lane] = 0.0;
     double dlmN = 0.0;
     if (I.pe)
     { /* general row of stage N: dv = C dx_N, then the same multiplier / slack step, step length and sums */
-        const double *cv = AR(Jc) + SO(N);
+        const double *cv = AR(Jc) + NJ * N;
         const double dv = grp_sum(R.x ? cv[xk] * sm.xv[xk] : 0.0);
         const int ia = TERM_LO(N), ib = TERM_UP(N);
         const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
@@ -1638,7 +1622,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         }
         if (R.x) dlmN = cv[xk] * (dlb - dla);
     }
-    if (R.x) n0 = rd_fmax(n0, fabs(rg[SO(N) + 6 + xk] + dlmN - dp_prev)); /* stage N: no cost, no box bounds */
+    if (R.x) n0 = rd_fmax(n0, fabs(rg[NV * N + 6 + xk] + dlmN - dp_prev)); /* stage N: no cost, no box bounds */
     rd_sync();
     *alpha_out = -grp_max(-alpha);
     sums[0] = grp_sum(sB);
@@ -1654,28 +1638,28 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
  *   1  COMPUTE_CENTERING_CORRECTION_QP (:479-505): rm = res_m + dt_aff dlam_aff - sigma_mu, written to res_mc;
  *   2  COMPUTE_CENTERING_QP (:509-529):            rm = res_m - sigma_mu, written to res_mc.
  * USE_PB: P+ rb was stored by the factorisation (rb = res_b); otherwise it is recomputed from P+. */
-/* Staging of one stage for the backward substitution.  Hot form (USE_PB = 1: right-hand sides = the residual arrays of the
- * record): the slice [res_g .. F.PB] of the stage record and, for the corrector's second-order term (MODE 1), [dlam dt] --
- * two contiguous ranges.  Generic form (USE_PB = 0, refinement): the same layout filled piece by piece. */
-enum { BG_RG = RC_res_g - RC_res_g, BG_RD = RC_res_d - RC_res_g, BG_RM = RC_res_m - RC_res_g, BG_LAM = RC_slam - RC_res_g,
-       BG_T = RC_st - RC_res_g, BG_F = RC_F - RC_res_g, BG_PB = BG_F + RF_PB, BG_N1 = BG_F + RF_P,
-       BG_DLAM = BG_N1, BG_DT = BG_N1 + (RC_dt_ - RC_dlam), BG_END = BG_N1 + 2 * NB };
-static_assert(BG_END <= SW_STGN && RC_dt_ == RC_dlam + NB && RC_st == RC_slam + NB && RC_pvec == RC_F + RF_END, "backward staging size / record order");
+/* staging layout of one stage for the backward substitution: [0,100) = F[ss] (1/diag, -, Luu, Lxu), then P+ b, res_g,
+ * lam, t, res_d and the complementarity data of the MODE */
+enum { BG_PB = 100, BG_RG = 112, BG_LAM = 130, BG_T = 154, BG_RD = 178, BG_RM = 202, BG_DT = 226, BG_DLAM = 250 };
 template <int MODE, int USE_PB>
 RD void bwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const double *rd, const double *rm)
 {
-    if (USE_PB)
-    {
-        stage_cp(dst, AR(res_g) + SO(ss), BG_N1);
-        if (MODE == 1) stage_cp(dst + BG_DLAM, AR(dlam) + SO(ss), 2 * NB); /* dlam and dt_ are neighbours */
-    }
+    const double *F = AR(F) + (long) FS * ss;
+    stage_cp(dst, F, RF_P);
+    if (USE_PB) stage_cp(dst + BG_PB, F + RF_PB, NX);
+    stage_cp(dst + BG_RG, rg + NV * ss, NV);
+    stage_cp(dst + BG_LAM, AR(slam) + NB * ss, NB);
+    stage_cp(dst + BG_T, AR(st) + NB * ss, NB);
+    stage_cp(dst + BG_RD, rd + NB * ss, NB);
+    if (MODE == 0) stage_cp(dst + BG_RM, rm + NB * ss, NB);
     else
     {
-        stage_cp(dst + BG_RG, rg + SO(ss), NV);
-        stage_cp(dst + BG_RD, rd + SO(ss), NB);
-        stage_cp(dst + BG_RM, rm + SO(ss), NB);
-        stage_cp(dst + BG_LAM, AR(slam) + SO(ss), 2 * NB);
-        stage_cp(dst + BG_F, AR(F) + SO(ss), RF_PB);
+        stage_cp(dst + BG_RM, AR(res_m) + NB * ss, NB);
+        if (MODE == 1)
+        {
+            stage_cp(dst + BG_DT, AR(dt_) + NB * ss, NB);
+            stage_cp(dst + BG_DLAM, AR(dlam) + NB * ss, NB);
+        }
     }
 }
 
@@ -1692,7 +1676,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
     rd_cp_commit();
     if (R.x)
     {
-        double pv = rg[SO(N) + 6 + xk];
+        double pv = rg[NV * N + 6 + xk];
         if (I.pe)
         { /* general row of stage N: p_N += C' gamma with the complementarity right-hand side of the MODE */
             const int ia = TERM_LO(N), ib = TERM_UP(N);
@@ -1709,10 +1693,10 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
                 else { ma = AR(res_m)[ia] - sigma_mu; mb = AR(res_m)[ib] - sigma_mu; }
                 if (xk == 0) { AR(res_mc)[ia] = ma; AR(res_mc)[ib] = mb; }
             }
-            pv += (AR(Jc) + SO(N))[xk] * ((ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb);
+            pv += (AR(Jc) + NJ * N)[xk] * ((ma - la * rd[ia]) / ta - (mb - lb * rd[ib]) / tb);
         }
         sm.pv[xk] = pv;
-        AR(pvec)[SO(N) + xk] = pv;
+        AR(pvec)[NX * N + xk] = pv;
     }
     for (int ss = N - 1; ss >= 0; ss--)
     {
@@ -1728,17 +1712,17 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             if (USE_PB) pb = G[BG_PB + xk];
             else
             {
-                const double *Fn = AR(F) + SO(ss + 1);
+                const double *Fn = AR(F) + (long) FS * (ss + 1);
                 pb = 0.0;
                 RD_UNROLL
-                for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[SO(ss) + c];
+                for (int c = 0; c < 12; c++) pb += psym(Fn + RF_P, xk, c) * rb[NX * ss + c];
             }
             sm.tv[xk] = sm.pv[xk] + pb;
         }
         double gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
-            const int ia = SO(ss) + lane, ib = ia + 12;
+            const int ia = NB * ss + lane, ib = ia + 12;
             const double la = G[BG_LAM + lane], lb = G[BG_LAM + 12 + lane], ta = G[BG_T + lane], tb = G[BG_T + 12 + lane];
             double ma, mb;
             if (MODE == 0) { ma = G[BG_RM + lane]; mb = G[BG_RM + 12 + lane]; }
@@ -1766,9 +1750,9 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
-            z[k] *= G[BG_F + RF_INV + k];
+            z[k] *= G[RF_INV + k];
             RD_UNROLL
-            for (int r = k + 1; r < 6; r++) z[r] -= G[BG_F + RF_LUU + (r * (r - 1)) / 2 + k] * z[k];
+            for (int r = k + 1; r < 6; r++) z[r] -= G[RF_LUU + (r * (r - 1)) / 2 + k] * z[k];
         }
         if (R.u)
         {
@@ -1776,23 +1760,21 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             RD_UNROLL
             for (int k = 1; k < 6; k++)
                 if (k == lane) zl = z[k];
-            X[SO(ss) + lane] = zl;
+            X[NV * ss + lane] = zl;
         }
         if (R.x && !s0)
         {
             RD_UNROLL
-            for (int k = 0; k < 6; k++) rx -= G[BG_F + RF_LXU + xk * 6 + k] * z[k];
+            for (int k = 0; k < 6; k++) rx -= G[RF_LXU + xk * 6 + k] * z[k];
             sm.pv[xk] = rx; /* tv, not pv, is what the other lanes read after the last barrier */
-            AR(pvec)[SO(ss) + xk] = rx;
+            AR(pvec)[NX * ss + xk] = rx;
         }
         rd_sync();
     }
     rd_cp_wait0();
 }
 
-/* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction).  Rare path: the bound slots
- * are walked in flat order k = NB * stage + slot, lane l taking k = l, l + GL, ... -- the order the per-lane minimum / sums
- * were always accumulated in (they feed the most ill-conditioned solves, where a changed rounding shows). */
+/* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction) */
 RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const double *dt)
 {
     const int N = D.N, lane = rd_lane();
@@ -1801,9 +1783,9 @@ RD double ipm_alpha(const RmpcDims &D, const Inst &I, const double *dlam, const 
     {
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        const double dl = dlam[SO(i) + j], dtt = dt[SO(i) + j];
-        if (-a * dl > AR(slam)[SO(i) + j]) a = -AR(slam)[SO(i) + j] / dl;
-        if (-a * dtt > AR(st)[SO(i) + j]) a = -AR(st)[SO(i) + j] / dtt;
+        const double dl = dlam[k], dtt = dt[k];
+        if (-a * dl > AR(slam)[k]) a = -AR(slam)[k] / dl;
+        if (-a * dtt > AR(st)[k]) a = -AR(st)[k] / dtt;
     }
     if (I.pe && lane < 2)
     {
@@ -1824,8 +1806,8 @@ RD void ipm_mu_sums(const RmpcDims &D, const Inst &I, const double *dlam, const 
     {
         const int i = k / NB, j = k - NB * i;
         if (i == 0 && (j % 12) >= 6) continue;
-        sB += AR(slam)[SO(i) + j] * dt[SO(i) + j] + dlam[SO(i) + j] * AR(st)[SO(i) + j];
-        sC += dlam[SO(i) + j] * dt[SO(i) + j];
+        sB += AR(slam)[k] * dt[k] + dlam[k] * AR(st)[k];
+        sC += dlam[k] * dt[k];
     }
     if (I.pe && lane < 2)
     {
@@ -1852,18 +1834,38 @@ RD double ipm_mu_aff(double sum_lt, const double *sums, double alpha, double nc_
  * and qd_l, lane 6 + j: row q_j; lane l < 12 also owns bound slot l), all operands of the stage are fetched one stage
  * ahead by cp.async into shared memory -- coalesced 16-byte copies instead of 16 lanes striding through 16 different
  * stages -- and the multiplier of the previous stage is carried in a register.  Returns sum lam t; norms as ipm_res. */
-enum { QG_UX = RC_sux, QG_PI = RC_spi, QG_RQZ = RC_rqz, QG_B = RC_b, QG_D = RC_d, QG_DPI = RC_dpi, QG_DLAM = RC_dlam, QG_DT = RC_dt_,
-       QG_DUX = RC_dux, QG_N0 = RC_dpi /* [sux .. d] */, QG_N1 = RC_dux + NV /* [sux .. dux] */, QG_JC = QG_N1, QG_LAM = QG_JC + NJ,
-       QG_T = QG_LAM + NB, QG_END = QG_T + NB };
-static_assert(RC_sux == 0 && RC_slam == RC_Jc + NJ && RC_st == RC_slam + NB, "record order assumed by the residual sweep");
-static_assert(3 * QG_END <= SM_BUF, "residual sweep staging size");
-#define RS_STG(sm, k) ((sm).buf + (k) * QG_END)
-/* two contiguous ranges of the stage record: [sux .. d] (UPD = 0) or [sux .. dux] (UPD = 1), and [Jc slam st] */
+enum { QG_UX = 0, QG_DUX = 18, QG_XN = 36, QG_DXN = 48, QG_RQZ = 60, QG_PI = 78, QG_DPI = 90, QG_LAM = 102, QG_DLAM = 126,
+       QG_T = 150, QG_DT = 174, QG_B = 198, QG_D = 210, QG_JC = 234, QG_END = 270 };
 template <int UPD>
-RD void res_stage_in(const Inst &I, double *dst, int i)
+RD void res_stage_in(const Inst &I, double *dst, int i, int N)
 {
-    stage_cp(dst, AR(sux) + SO(i), UPD ? QG_N1 : QG_N0);
-    stage_cp(dst + QG_JC, AR(Jc) + SO(i), NJ + 2 * NB);
+    const bool cons = (i < N) || I.pe; /* stage N carries constraint slots only with a terminal row */
+    stage_cp(dst + QG_UX, AR(sux) + NV * i, NV);
+    stage_cp(dst + QG_RQZ, AR(rqz) + NV * i, NV);
+    if (UPD) stage_cp(dst + QG_DUX, AR(dux) + NV * i, NV);
+    if (i < N)
+    {
+        stage_cp(dst + QG_XN, AR(sux) + NV * (i + 1) + 6, NX);
+        stage_cp(dst + QG_PI, AR(spi) + NX * i, NX);
+        stage_cp(dst + QG_B, AR(b) + NX * i, NX);
+        if (UPD)
+        {
+            stage_cp(dst + QG_DXN, AR(dux) + NV * (i + 1) + 6, NX);
+            stage_cp(dst + QG_DPI, AR(dpi) + NX * i, NX);
+        }
+    }
+    if (cons)
+    {
+        stage_cp(dst + QG_LAM, AR(slam) + NB * i, NB);
+        stage_cp(dst + QG_T, AR(st) + NB * i, NB);
+        stage_cp(dst + QG_D, AR(d) + NB * i, NB);
+        if (UPD)
+        {
+            stage_cp(dst + QG_DLAM, AR(dlam) + NB * i, NB);
+            stage_cp(dst + QG_DT, AR(dt_) + NB * i, NB);
+        }
+        if (i > 0) stage_cp(dst + QG_JC, AR(Jc) + NJ * i, NJ);
+    }
 }
 
 template <int UPD>
@@ -1877,13 +1879,8 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
     const double hu = sm.hc[j], hs = sm.hc[6 + j], hq = sm.hc[12 + j];
     const double lmin = 1e-16;
     double mu = 0.0, n0 = 0, n1 = 0, n2 = 0, n3 = 0, n4 = 0, nanflag = 0, pprev = 0.0;
-    /* three staging buffers, filled TWO stages ahead: the dynamics residual of stage i needs the (moved) state of stage
-     * i + 1, which is part of that stage's own staged range and must have landed when stage i is processed */
-    res_stage_in<UPD>(I, RS_STG(sm, 0), 0);
+    res_stage_in<UPD>(I, SW_STG(sm, 0), 0, N);
     rd_cp_commit();
-    res_stage_in<UPD>(I, RS_STG(sm, 1), 1); /* N >= 2 */
-    rd_cp_commit();
-    int b0 = 0, b1i = 1, b2i = 2; /* buffers of stages i, i + 1, i + 2 */
 #define QV(off, doff, c) (UPD ? G[(off) + (c)] + a * G[(doff) + (c)] : G[(off) + (c)])
 #define QF(off, doff, c, out)                                                                 \
     do                                                                                        \
@@ -1894,12 +1891,11 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
     } while (0)
     for (int i = 0; i <= N; i++)
     {
-        const double *G = RS_STG(sm, b0), *G1 = RS_STG(sm, b1i);
-        if (i + 2 <= N) res_stage_in<UPD>(I, RS_STG(sm, b2i), i + 2);
+        const double *G = SW_STG(sm, i & 1);
+        if (i < N) res_stage_in<UPD>(I, SW_STG(sm, (i + 1) & 1), i + 1, N);
         rd_cp_commit();
         rd_cp_wait1();
         rd_sync();
-        { const int t_ = b0; b0 = b1i; b1i = b2i; b2i = t_; }
         const bool mid = i < N, x_on = i > 0;
         /* new values of this lane's joint: u_j, q_j, qd_j (the state is fixed at stage 0 of the reduced QP) */
         const double uj = mid ? QV(QG_UX, QG_DUX, j) : 0.0;
@@ -1915,7 +1911,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             double la, lb, ta, tb;
             QF(QG_LAM, QG_DLAM, lane, la); QF(QG_LAM, QG_DLAM, 12 + lane, lb);
             QF(QG_T, QG_DT, lane, ta); QF(QG_T, QG_DT, 12 + lane, tb);
-            const int ia = SO(i) + lane, ib = ia + 12;
+            const int ia = NB * i + lane, ib = ia + 12;
             if (UPD) { AR(slam)[ia] = la; AR(slam)[ib] = lb; AR(st)[ia] = ta; AR(st)[ib] = tb; }
             const double dl = G[QG_D + lane] + ta - vl, du = G[QG_D + 12 + lane] + tb + vl;
             const double ml = la * ta, mu_ = lb * tb;
@@ -1932,7 +1928,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             double g = G[QG_RQZ + lane];
             g += hu * uj + hs * dj + b1 * pq + b2 * pd;
             g += dlm;
-            AR(res_g)[SO(i) + lane] = g;
+            AR(res_g)[NV * i + lane] = g;
             n0 = rd_fmax(n0, fabs(g));
             if (i == 0 && lane == 0 && g != g) nanflag = 1.0;
         }
@@ -1980,16 +1976,16 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
                     QF(QG_LAM, QG_DLAM, 0, la); QF(QG_LAM, QG_DLAM, 12, lb);
                     g += G[QG_JC + xk] * (lb - la);
                 }
-                AR(res_g)[SO(i) + 6 + xk] = g;
+                AR(res_g)[NV * i + 6 + xk] = g;
                 n0 = rd_fmax(n0, fabs(g));
             }
             if (mid)
             {
-                const double xn = UPD ? G1[QG_UX + 6 + xk] + a * G1[QG_DUX + 6 + xk] : G1[QG_UX + 6 + xk];
+                const double xn = QV(QG_XN, QG_DXN, xk);
                 double r;
                 if (R.q) r = G[QG_B + j] - xn + (qj + a12 * dj) + b1 * uj;
                 else r = G[QG_B + 6 + j] - xn + a22 * dj + b2 * uj;
-                AR(res_b)[SO(i) + xk] = r;
+                AR(res_b)[NX * i + xk] = r;
                 n1 = rd_fmax(n1, fabs(r));
                 pprev = R.q ? pq : pd;
             }
@@ -2013,8 +2009,8 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
         }
         if (UPD)
         { /* write the moved primal iterate and multipliers of this stage back */
-            for (int c = lane; c < NV; c += GL) AR(sux)[SO(i) + c] = G[QG_UX + c] + a * G[QG_DUX + c];
-            if (mid && lane < NX) AR(spi)[SO(i) + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
+            for (int c = lane; c < NV; c += GL) AR(sux)[NV * i + c] = G[QG_UX + c] + a * G[QG_DUX + c];
+            if (mid && lane < NX) AR(spi)[NX * i + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
         }
         rd_sync(); /* the buffer of this stage is refilled by the next iteration */
     }
@@ -2062,11 +2058,10 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
                               AR(ib), AR(id), AR(im), pn);
                 if (pn[0] < 1e-5 && pn[1] < 1e-5 && pn[2] < 1e-5 && pn[3] < 1e-5 && !(pn[5] > 0.5)) break;
                 ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-                ipm_forward<2>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
-                st_add<NV>(AR(dux), AR(iux), 0, N + 1);
-                st_add<NX>(AR(dpi), AR(ipi), 0, N);
-                st_add<NB>(AR(dlam), AR(ilam), 0, N);
-                st_add<NB>(AR(dt_), AR(it), 0, N);
+                ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
+                for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
+                for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
+                for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
                 if (I.pe && lane < 2)
                 {
                     const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -2109,12 +2104,11 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
                           AR(im), inrm);
             double a2, s2[2], l2[2];
             ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-            ipm_forward<2>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
+            ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
             refined = 1;
-            st_add<NV>(AR(dux), AR(iux), 0, N + 1);
-            st_add<NX>(AR(dpi), AR(ipi), 0, N);
-            st_add<NB>(AR(dlam), AR(ilam), 0, N);
-            st_add<NB>(AR(dt_), AR(it), 0, N);
+            for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
+            for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
+            for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
             if (I.pe && lane < 2)
             {
                 const int k = lane ? TERM_UP(N) : TERM_LO(N);
@@ -2175,27 +2169,15 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     *cost_valid = 0; /* set when the accepted trial point's cost is known from its merit evaluation */
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
     const int N = D.N, lane = rd_lane();
-    for (int i = lane; i < N; i += GL)
-    { /* stage-parallel: merit weights of the dynamics multipliers and of the bound multipliers of stage i, 12 at a time */
-        RD_UNROLL
-        for (int h = 0; h < 3; h++)
-        {
-            const double *src = h == 0 ? AR(spi) + SO(i) : AR(slam) + SO(i) + 12 * (h - 1);
-            double *wdst = h == 0 ? AR(wpi) + SO(i) : AR(wlam) + SO(i) + 12 * (h - 1);
-            double t[12], w[12];
-            ldv<12>(src, t);
-            if (nlp_iter != 0 || (h > 0 && i == 0)) ldv<12>(wdst, w); /* the unused q slots of stage 0 keep their value */
-            RD_UNROLL
-            for (int k = 0; k < 12; k++)
-            {
-                if (h > 0 && i == 0 && k >= 6) continue;
-                const double t0 = h == 0 ? fabs(t[k]) : t[k];
-                if (nlp_iter == 0) w[k] = t0;
-                else { const double t1 = 0.5 * (t0 + w[k]); w[k] = t0 > t1 ? t0 : t1; }
-            }
-            stv<12>(wdst, w);
-        }
+    grp_weights(AR(wpi), AR(spi), nlp_iter == 0, 1, 0, N * NX);
+    if (lane < 12)
+    { /* stage 0 has bounds on u only: slots 0..5 and 12..17 */
+        const int k = lane < 6 ? lane : lane + 6;
+        const double t0 = AR(slam)[k];
+        if (nlp_iter == 0) AR(wlam)[k] = t0;
+        else { const double t1 = 0.5 * (t0 + AR(wlam)[k]); AR(wlam)[k] = t0 > t1 ? t0 : t1; }
     }
+    grp_weights(AR(wlam), AR(slam), nlp_iter == 0, 0, NB, N * NB);
     for (int kk = lane; kk < NB; kk += GL)
     { /* the eliminated stage-0 state equalities */
         const double t0 = (I.head + H_QLAMX0)[kk];
@@ -2216,7 +2198,7 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        st_xpay_to<NV>(AR(tux), AR(ux), AR(sux), alpha, 0, N + 1);
+        grp_xpay_to(AR(tux), AR(ux), AR(sux), alpha, (N + 1) * NV);
         rd_sync();
         m1 = nlp_merit(ch, D, I, AR(tux), I.z, &c1);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
@@ -2225,14 +2207,14 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
     }
     *alpha_out = alpha;
     if (!accepted && ((m1 != m1) || (m1 - m1 != 0.0))) return 1;
-    st_axpy<NV>(AR(ux), AR(sux), alpha, 0, N + 1);
-    st_lerp<NX>(AR(pi), AR(spi), alpha, 0, N);
+    grp_axpy(AR(ux), AR(sux), alpha, (N + 1) * NV);
+    grp_lerp(AR(pi), AR(spi), alpha, 0, N * NX);
     if (lane < 12)
-    { /* stage 0 has bounds on u only: slots 0..5 and 12..17 */
+    {
         const int k = lane < 6 ? lane : lane + 6;
         AR(lam)[k] = (1.0 - alpha) * AR(lam)[k] + alpha * AR(slam)[k];
     }
-    st_lerp<NB>(AR(lam), AR(slam), alpha, 1, N);
+    grp_lerp(AR(lam), AR(slam), alpha, NB, N * NB);
     if (I.pe && lane >= 12 && lane < 14)
     {
         const int k = lane == 12 ? TERM_LO(N) : TERM_UP(N);
@@ -2255,23 +2237,12 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
     if (init_from_nlp && warm == 2)
     {
         /* ocp_nlp_initialize_qp_from_nlp (AC/ocp_nlp/ocp_nlp_common.c:3320-3340) + ocp_qp_compute_t at ux = 0 */
-        for (int i = lane; i < N; i += GL)
+        for (int k = lane; k < N * NX; k += GL) AR(spi)[k] = AR(pi)[k];
+        for (int k = lane; k < N * NB; k += GL)
         {
-            double pi[NX];
-            ldv<NX>(AR(pi) + SO(i), pi);
-            stv<NX>(AR(spi) + SO(i), pi);
-            RD_UNROLL
-            for (int h = 0; h < NB; h += 6)
-            { /* 6 slots at a time; stage 0 only has the u slots 0..5 and 12..17 */
-                if (i == 0 && (h % 12) >= 6) continue;
-                double lam[6], dd[6];
-                ldv<6>(AR(lam) + SO(i) + h, lam);
-                ldv<6>(AR(d) + SO(i) + h, dd);
-                RD_UNROLL
-                for (int k = 0; k < 6; k++) dd[k] = -dd[k];
-                stv<6>(AR(slam) + SO(i) + h, lam);
-                stv<6>(AR(st) + SO(i) + h, dd);
-            }
+            if (k < NB && (k % 12) >= 6) continue;
+            AR(slam)[k] = AR(lam)[k];
+            AR(st)[k] = -AR(d)[k];
         }
         if (I.pe && lane < 2)
         {
@@ -2366,21 +2337,24 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
  * Plant: zdot = [qd; -W qd + W u] (R/simulation_model.py:79-83) decouples per joint, RK4 (:111-117) on lanes 0..5. */
 /* Primal shift of the initial guess between two closed-loop steps (RmpcWs.shift; the acados MPC idiom
  * set(i, 'x', get(i+1, 'x')), set(i, 'u', get(i+1, 'u')) for i < N-1, set(N-1, 'x', get(N, 'x')) -- SURVEY.md 8(f) #1; the
- * reference itself never shifts).  Multipliers and merit weights stay. */
+ * reference itself never shifts).  Multipliers and merit weights stay.  [u; x] of the stages are contiguous, so the shift
+ * is one move by NV doubles towards the front: ascending chunks of GL elements, each lane loads before it stores and no
+ * chunk writes what a later one still reads (NV > GL). */
 RD void nlp_shift(const RmpcDims &D, const Inst &I)
 {
     const int N = D.N, lane = rd_lane();
     double *ux = AR(ux);
-    for (int i0 = 0; i0 < N - 1; i0 += GL)
-    { /* [u; x] of stage i <- stage i + 1 for i < N - 1: chunks of GL stages, every lane loads before any lane stores */
-        const int i = i0 + lane;
-        double v[NV];
-        if (i < N - 1) ldv<NV>(ux + SO(i + 1), v);
+    const int n = NV * (N - 1);
+    for (int k0 = 0; k0 < n; k0 += GL)
+    {
+        const int k = k0 + lane;
+        double v = 0.0;
+        if (k < n) v = ux[k + NV];
         rd_sync();
-        if (i < N - 1) stv<NV>(ux + SO(i), v);
+        if (k < n) ux[k] = v;
     }
     rd_sync();
-    if (lane < NX) ux[SO(N - 1) + 6 + lane] = ux[SO(N) + 6 + lane];
+    if (lane < NX) ux[NV * (N - 1) + 6 + lane] = ux[NV * N + 6 + lane];
     rd_sync();
 }
 
@@ -2421,7 +2395,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
             for (int i = lane; i < N; i += GL)
             {
                 double v[NV], y5[5];
-                load18(AR(ux) + SO(i), v);
+                load18(AR(ux) + NV * i, v);
                 NoEmit ne;
                 ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
                 cost += stage_cost(par, D.dt, y5, v, v + 12);

@@ -1,13 +1,13 @@
 /* robotic-mpc_b200/csrc/rmpc_types.h -- plain-data structures shared by the host side of the C-ABI and the kernels.
  *
- * Layout of a batch in HBM: one contiguous SLAB per instance, and inside the slab one contiguous RECORD per stage
- * ("stage-major"): every per-stage array of the solver is a fixed slice of the stage record (RC_<name> below), so a
- * Riccati sweep fetches the operands of a stage as one or two contiguous byte ranges.  A GROUP of RMPC_G lanes (half a
- * warp by default) owns one instance for the whole closed loop.  Block widths:
+ * Layout of a batch in HBM ("instance-major"): every array below is [B][...] with one contiguous chunk per
+ * instance; a GROUP of RMPC_G lanes (half a warp by default) owns one instance for the whole closed loop, so inside
+ * a chunk the fastest index is the one the lanes sweep (component within a stage block for the Riccati sweeps,
+ * stage index for the stage-parallel passes).  Stage blocks use fixed strides:
  *     NV = 18 ([u(6); x(12)], stage N keeps the same slot layout with u unused)
  *     NX = 12,  NB = 24 ([lower(12); upper(12)] over [u(6); q(6)], stage 0 uses only the u slots in the QP)
  *     NJ = 36 (scaled task Jacobian: 5 rows x 6 joint-angle columns + the 6 joint-velocity entries of row 5)
- *     FS = 202 (Riccati factor block of one stage, RF_* offsets below)
+ *     FS = 208 (Riccati factor block of one stage, RF_* offsets below)
  */
 #ifndef RMPC_TYPES_H
 #define RMPC_TYPES_H
@@ -17,7 +17,7 @@
 #define RMPC_NV 18
 #define RMPC_NB 24
 #define RMPC_NJ 36
-#define RMPC_FS 202
+#define RMPC_FS 208
 
 #define RMPC_SQP 0
 #define RMPC_SQP_RTI 1
@@ -30,9 +30,9 @@ enum
     RF_LU = 6,    /* 6 : l_u */
     RF_LUU = 12,  /* 15: strict lower part of Luu, row-major packed (row r at r(r-1)/2) */
     RF_LXU = 28,  /* 72: Lxu, 12 x 6 row-major, rows in state order [q; qd] */
-    RF_PB = 100,  /* 12: P+ b  (P of the NEXT stage times this stage's res_b) */
-    RF_P = 112,   /* 78: P, packed lower, row r at r(r+1)/2 */
-    RF_PV = 190,  /* 12: p */
+    RF_P = 100,   /* 78: P, packed lower, row r at r(r+1)/2 */
+    RF_PV = 178,  /* 12: p */
+    RF_PB = 190,  /* 12: P+ b  (P of the NEXT stage times this stage's res_b) */
     RF_END = 202
 };
 
@@ -125,27 +125,23 @@ typedef struct
 } RmpcDims;
 
 /* Per-instance "slab": all solver data of ONE instance is contiguous in HBM,
- *     slab = [ head (RMPC_HEAD doubles) | record of stage 0 | record of stage 1 | ... | record of stage N ],
- * record = RMPC_REC doubles = every per-stage array side by side, in the order below.  Element c of array <name> at stage s
- * is slab[RMPC_HEAD + RMPC_REC * s + RC_<name> + c]: the kernels address everything from one base pointer with
- * COMPILE-TIME offsets and one multiply by the stage index.
- * The order is chosen so that what ONE Riccati sweep reads at a stage is a contiguous range (16-byte aligned: every
- * width below is even), fetched with a handful of unrolled 16-byte asynchronous copies at immediate offsets:
- *     residual + update   [sux .. dux] and [Jc slam st]          factorisation   [res_b .. st]
- *     forward (affine)    [res_b .. F low part]  + next [P PV]   backward        [res_g .. F.PB] and [dlam dt]
- *     forward (corrector) [dux .. F low part]    + next [P PV pvec]
- * then the NLP iterate and its linearisation, and last the rarely touched refinement / trial arrays. */
+ *     slab = [ head (RMPC_HEAD doubles) | array 0 | array 1 | ... ],   array k = [Sp stage slots][width_k doubles],
+ * Sp = number of stage slots N + 1 rounded up to even (16-byte alignment of every array).  Array k starts at
+ * RMPC_HEAD + RC_k * Sp with RC_k a COMPILE-TIME constant (the summed widths of the arrays before it), so the kernels
+ * address everything from one base pointer and the register holding Sp -- no table of 40 pointers to keep alive.
+ * Within an array the stage index is the slow one: lanes that sweep stages in parallel (stage-parallel passes) and
+ * lanes that sweep the components of one stage (Riccati sweeps) both touch neighbouring 128-byte lines. */
 #define RMPC_WS_ARRAYS(X)                                                                                             \
-    X(sux, RMPC_NV) X(spi, RMPC_NX) X(rqz, RMPC_NV) X(b, RMPC_NX) X(d, RMPC_NB)                                       \
-    X(dpi, RMPC_NX) X(dlam, RMPC_NB) X(dt_, RMPC_NB) X(dux, RMPC_NV)                                                  \
-    X(res_mc, RMPC_NB) X(res_b, RMPC_NX) X(res_g, RMPC_NV) X(res_d, RMPC_NB) X(res_m, RMPC_NB)                        \
-    X(Jc, RMPC_NJ) X(slam, RMPC_NB) X(st, RMPC_NB)                                                                    \
-    X(F, RMPC_FS) X(pvec, RMPC_NX)                                                                                    \
     X(ux, RMPC_NV) X(pi, RMPC_NX) X(lam, RMPC_NB) X(wpi, RMPC_NX) X(wlam, RMPC_NB)                                    \
+    X(Jc, RMPC_NJ) X(rqz, RMPC_NV) X(b, RMPC_NX) X(d, RMPC_NB)                                                        \
+    X(sux, RMPC_NV) X(spi, RMPC_NX) X(slam, RMPC_NB) X(st, RMPC_NB)                                                   \
+    X(dux, RMPC_NV) X(dpi, RMPC_NX) X(dlam, RMPC_NB) X(dt_, RMPC_NB)                                                  \
+    X(res_g, RMPC_NV) X(res_b, RMPC_NX) X(res_d, RMPC_NB) X(res_m, RMPC_NB) X(res_mc, RMPC_NB) X(pvec, RMPC_NX)       \
+    X(F, RMPC_FS)                                                                                                     \
     X(ig, RMPC_NV) X(ib, RMPC_NX) X(id, RMPC_NB) X(im, RMPC_NB) X(iux, RMPC_NV) X(ipi, RMPC_NX) X(ilam, RMPC_NB)      \
     X(it, RMPC_NB) X(tux, RMPC_NV)
 
-/* RC_<name> = offset of <name> inside a stage record (doubles); RMPC_REC = record length, a multiple of 4 doubles */
+/* RC_<name> = doubles per stage slot of all arrays before <name>; RC_TOTAL = doubles per stage slot of a slab */
 enum
 {
 #define X(name, w) RCW_##name = (w),
@@ -163,8 +159,7 @@ enum
 #define X(name, w) RC_##name = (int) __builtin_offsetof(struct rmpc_rc_helper_, name),
     RMPC_WS_ARRAYS(X)
 #undef X
-    RC_TOTAL = (int) sizeof(struct rmpc_rc_helper_),
-    RMPC_REC = (RC_TOTAL + 3) / 4 * 4
+    RC_TOTAL = (int) sizeof(struct rmpc_rc_helper_)
 };
 
 /* small per-instance arrays at the head of the slab */
@@ -183,8 +178,8 @@ typedef struct
 {
     const double *par; /* [B][RP_COUNT] */
     double *slab;      /* [B][slab_stride] per-instance slabs (layout above) */
-    long slab_stride;  /* doubles per instance = RMPC_HEAD + RMPC_REC * (N + 1), rounded up to a 128-byte line */
-    int Sp;            /* stage records per slab: N + 1 */
+    long slab_stride;  /* doubles per instance = RMPC_HEAD + RC_TOTAL * Sp, rounded up to a 128-byte line */
+    int Sp;            /* stage slots per array: N + 1 rounded up to even */
     double *z;         /* [B][12] plant state */
     int *flags;        /* [B][4]: first_call, qp_warm2_pending, n_lq_needed, reserved */
     /* logs (may be null) */
@@ -204,9 +199,9 @@ typedef struct
 #else
 #define RMPC_HD
 #endif
-RMPC_HD static inline int rmpc_slab_sp(int N) { return N + 1; }
-RMPC_HD static inline long rmpc_slab_stride(int N) { return ((long) RMPC_HEAD + (long) RMPC_REC * rmpc_slab_sp(N) + 15) / 16 * 16; }
-/* offset inside a slab of element 0 of stage s of the array whose RC_ constant is rc (w = its width, unused) */
-RMPC_HD static inline long rmpc_slab_off(int N, int rc, int w, int s) { (void) N; (void) w; return (long) RMPC_HEAD + (long) RMPC_REC * s + rc; }
+RMPC_HD static inline int rmpc_slab_sp(int N) { return (N + 2) & ~1; }
+RMPC_HD static inline long rmpc_slab_stride(int N) { return ((long) RMPC_HEAD + (long) RC_TOTAL * rmpc_slab_sp(N) + 15) / 16 * 16; }
+/* offset inside a slab of element 0 of stage s of the array whose RC_ constant is rc and width is w */
+RMPC_HD static inline long rmpc_slab_off(int N, int rc, int w, int s) { return (long) RMPC_HEAD + (long) rc * rmpc_slab_sp(N) + (long) w * s; }
 
 #endif

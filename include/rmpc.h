@@ -25,6 +25,8 @@
 #ifndef RMPC_H
 #define RMPC_H
 
+#include "rmpc_fields.h" /* RP_* RT_* RL_* RK_* RS_* RE_* RQ_*: layouts of the blocks exchanged as arrays of doubles */
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -73,7 +75,8 @@ int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
  *                    x_k <- x_{k+1}, u_k <- u_{k+1} for k < N-1, x_{N-1} <- x_N; multipliers and merit weights stay -- i.e. the
  *                    loop `for i < N-1: solver.set(i,'x',solver.get(i+1,'x')); solver.set(i,'u',solver.get(i+1,'u'));
  *                    solver.set(N-1,'x',solver.get(N,'x'))` an acados MPC runs between two solves.  Default 0: the reference's
- *                    loop keeps the unshifted iterate (R/simulator.py:199-241). */
+ *                    loop keeps the unshifted iterate (R/simulator.py:199-241).
+ *   "statistics" 0 | 1  keep the per-iteration statistics table of the last full-SQP solve (rmpc_get "sqp_stat"). */
 int rmpc_set_option(rmpc_handle *h, const char *name, double value);
 
 /* Replaces <name>_acados_free + _free_capsule. */
@@ -87,11 +90,27 @@ long long rmpc_device_bytes(const rmpc_handle *h);
 
 /* Setters (copy [B][n] doubles from a device pointer).  Replaces AcadosOcpSolver.set / constraints_set / cost_set
  * (T/acados_ocp_solver.py:1743-1819).  Fields:
- *   "par"   n = 72   per-instance parameter block (layout: RP_* in csrc/rmpc_types.h; pack with params.pack_params)
+ *   "par"   n = RP_COUNT  per-instance parameter block (layout RP_* in rmpc_fields.h; Python: params.pack_params).  Setting
+ *                         it discards every per-stage override made before.
  *   "z"     n = 12   plant state = x0 of the next solve (the reference sets lbx_0 = ubx_0 = x, R/simulator.py:210-211)
  *   "x"     n = 12   state iterate of `stage` (0..N)        solver.set(stage, 'x', .)
  *   "u"     n = 6    control iterate of `stage` (0..N-1)    solver.set(stage, 'u', .)
  *   "pi"    n = 12   dynamics multipliers of `stage`        solver.set(stage, 'pi', .)
+ * Named fields of the cost and constraint modules -- AcadosOcpSolver.cost_set / constraints_set
+ * (T/acados_ocp_solver.py:1863-2035) -> ocp_nlp_cost_model_set / ocp_nlp_constraints_model_set
+ * (acados_c/ocp_nlp_interface.c:516-560,637-760).  `stage` = -1: every stage (writes a slice of "par" and drops that field's
+ * per-stage overrides); `stage` in 0..N-1: that stage only (kept in a per-stage table [B][N][RT_COUNT] the first such call
+ * creates; time-varying references and bounds):
+ *   "yref"  n = 18   reference of the 18 outputs y = [g1..g5, u(6), qddot(6), manip]  cost_set(stage, 'yref', .)
+ *   "lbu", "ubu"  n = 6   control bounds                                             constraints_set(stage, 'lbu' | 'ubu', .)
+ *   "lbx", "ubx"  n = 6   bounds on q at stages 1..N-1; at stage 0: n = 12, the initial state (= "z"; the reference sets
+ *                         both to the plant state)                                   constraints_set(stage, 'lbx' | 'ubx', .)
+ * Per instance only (`stage` must be -1; they change what the reference bakes into the generated functions / keeps equal on
+ * all stages, R/trajectory_optimizer.py:139-156), synchronise the stream where marked (s):
+ *   "W_diag"      n = 18  diagonal of W: 5 task weights, 6 x (2 w_u), 6 x w_qddot, entry 17 ignored (weight 0)   (s)
+ *   "surf_coeffs" n = 6   a..f of the target surface (R/surface.py:14-30)
+ *   "wcv"         n = 6   velocity-loop bandwidths; the exact-ZOH coefficients a12, a22, b1, b2 are recomputed on the host
+ *                         with libm's exp, as the reference computes them (R/prediction_model.py:87-115)          (s)
  * Terminal ellipsoid lh_e <= x_N' P_e x_N <= alpha_e at stage N (BASELINE config 4; P_e, alpha_e from
  * R/_terminal_constraint.py:96-116 terminal_ellipsoid_from_lqr; the acados equivalent is constraints.lh_e / uh_e with
  * con_h_expr_e, i.e. ocp_nlp_constraints_model_set(.., N, "lh" / "uh", ..), acados_solver.in.c:2109-2116).  The first of
@@ -139,15 +158,22 @@ int rmpc_closed_loop(rmpc_handle *h, int nsteps, void *stream);
  *   "x" [B][12], "u" [B][6], "pi" [B][12], "lam" [B][24] ([lower(12); upper(12)] over [u; q]) of `stage`;
  *       with a terminal row, "lam" of stage N holds its multipliers in entries 0 (lower) and 12 (upper)
  *   "z" [B][12] plant state
- *   "stats" [B][12]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
- *                    alpha, qp_status, device time of the solve in seconds (RL_* in csrc/rmpc_types.h); needs nlog > 0
- *   "zlog" [B][nlog+1][12], "ulog" [B][nlog][6], "slog" [B][nlog][12]   closed-loop logs
+ *   "stats" [B][RL_COUNT]  record of the last step: status, sqp_iter, qp_iter, cost, res_stat, res_eq, res_ineq, res_comp,
+ *                    alpha, qp_status, device times of the solve in seconds (RL_* in rmpc_fields.h); needs nlog > 0
+ *   "zlog" [B][nlog+1][12], "ulog" [B][nlog][6], "slog" [B][nlog][RL_COUNT]   closed-loop logs
  *   "plog" [B][nlog+1][28]  per-sample plant record computed from zlog: pose of frame ee_link (12), rpy (3), WORLD
- *                    twist (6), tracking errors e1..e5 (5), task-frame z (RK_* in csrc/rmpc_types.h)
+ *                    twist (6), tracking errors e1..e5 (5), task-frame z (RK_* in rmpc_fields.h)
  *                    -- the logs of R/simulation_model.py:60-77,85-91 and the error series of R/simulator.py:265-344
- *   "summary" [B][20]  RS_* in csrc/rmpc_types.h: sum e^2 (5), ITSE (5), failures, sqp/qp iteration totals,
+ *   "summary" [B][20]  RS_* in rmpc_fields.h: sum e^2 (5), ITSE (5), failures, sqp/qp iteration totals,
  *                      max KKT residuals (4), last cost, number of samples
  *   "flags" [B][4] as doubles: first_call, qp_warm_pending, LQ-fallback triggers, reserved
+ *   "par" [B][RP_COUNT]; "yref" [B][18], "lbu" / "ubu" / "lbx" / "ubx" [B][6] of `stage`: the values that stage uses
+ *   "sqp_stat" [B][max_iter + 2][RQ_COUNT]  per-iteration table of the last full-SQP solve (acados' mem->stat rows: KKT
+ *                    residuals at iterate k; QP status, QP iterations, step length of the step that led to it); needs
+ *                    rmpc_set_option(h, "statistics", 1)                      get_stats('statistics')
+ * The step record ("stats", rows of "slog"; RL_*) carries acados' timing breakdown of each instance's own solve, measured on
+ * the GPU's global timer: time_tot, time_lin, time_qp (= solver call + xcond), time_glob, plus the interior-point phases
+ * (factorisation, forward sweeps, backward substitutions, update + residuals) -- AC/ocp_nlp/ocp_nlp_common.c:4610-4681.
  */
 int rmpc_get(rmpc_handle *h, const char *field, int stage, double *dev, void *stream);
 

@@ -42,7 +42,7 @@ class RmpcProblem(C.Structure):
                 ("q_min", C.c_double * 6), ("q_max", C.c_double * 6), ("u_min", C.c_double * 6),
                 ("u_max", C.c_double * 6), ("model", Ur10Params),
                 ("term", C.c_int), ("term_P", C.c_double * 144), ("term_lh", C.c_double), ("term_uh", C.c_double),
-                ("shift", C.c_int)]
+                ("shift", C.c_int), ("cond_N", C.c_int), ("as_rti_level_p1", C.c_int), ("as_rti_iter", C.c_int)]
 
 
 class RmpcTrace(C.Structure):
@@ -59,7 +59,7 @@ README_QD0 = np.array([1.0, 2.0, 1.0, 0.0, 0.0, 0.0])
 def make_problem(N=20, solver_type=SQP_RTI, dt=0.01, surf=None, wcv=200.0, w_u=0.01, w_qddot=0.02,
                  px_ref=0.40, vy_ref=0.05, q_min=None, q_max=None, qdot_min=None, qdot_max=None,
                  max_iter=100, qp_iter_max=50, tol=1e-6, qp_tol=1e-8, term_P=None, term_alpha=None,
-                 term_lh=None, shift=False) -> RmpcProblem:
+                 term_lh=None, shift=False, cond_N=None, as_rti_level=None, as_rti_iter=1) -> RmpcProblem:
     """Problem with the reference defaults unless overridden."""
     p = RmpcProblem()
     p.N, p.solver_type, p.max_iter, p.qp_iter_max = int(N), int(solver_type), int(max_iter), int(qp_iter_max)
@@ -79,6 +79,10 @@ def make_problem(N=20, solver_type=SQP_RTI, dt=0.01, surf=None, wcv=200.0, w_u=0
     p.model.Ts = dt
     p.model.t_ee[:] = [0.0, 0.0, 0.1]
     p.shift = int(bool(shift))
+    # reference leg only: partial condensing and AS-RTI level (acados enum: 0 = A .. 3 = D, 4 = standard RTI)
+    p.cond_N = 0 if cond_N is None else int(cond_N)
+    p.as_rti_level_p1 = 0 if as_rti_level is None else int(as_rti_level) + 1
+    p.as_rti_iter = int(as_rti_iter)
     if term_P is not None:
         # terminal ellipsoid x_N' P x_N <= alpha (R/_terminal_constraint.py:96-116); lower side -alpha unless given
         P = np.asarray(term_P, float).reshape(12, 12)
@@ -222,3 +226,68 @@ class Model:
         self.lib.ur10_tracking_errors(C.byref(P), _dp(_np(pose)), _dp(_np(twist)), C.c_double(px_ref),
                                       C.c_double(vy_ref), _dp(e), C.byref(ptz))
         return e, ptz.value
+
+
+class RefSolver:
+    """Step-wise handle on the compiled reference (oracle/_ref): create -> [model_set ...] -> step ... -> close, the way
+    R/simulator.py:203-226 drives one AcadosOcpSolver.  TEST INFRASTRUCTURE."""
+
+    def __init__(self, prob: RmpcProblem, x0):
+        self.lib = RefLeg().lib
+        self.lib.rmpc_ref_create.restype = C.c_void_p
+        self.lib.rmpc_ref_destroy.argtypes = [C.c_void_p]
+        self.lib.rmpc_ref_step.argtypes = [C.c_void_p, c_dp, c_dp, c_ip, c_ip, c_dp, c_dp, c_dp]
+        self.lib.rmpc_ref_model_set.argtypes = [C.c_void_p, C.c_int, C.c_char_p, c_dp]
+        self.lib.rmpc_ref_statistics.argtypes = [C.c_void_p, c_dp, C.c_int, c_ip]
+        self.lib.rmpc_ref_times.argtypes = [C.c_void_p, c_dp]
+        self.lib.rmpc_ref_get_iterate.argtypes = [C.c_void_p, c_dp, c_dp, c_dp]
+        self.N = prob.N
+        self.prob = prob
+        x0 = _np(x0)
+        self.h = C.c_void_p(self.lib.rmpc_ref_create(C.byref(prob), _dp(x0)))
+        if not self.h:
+            raise RuntimeError("rmpc_ref_create failed")
+
+    def model_set(self, stage, field, value):
+        v = _np(value)
+        if field == "W":
+            v = _np(np.asarray(value, float).reshape(18, 18).T)  # column-major
+        rc = self.lib.rmpc_ref_model_set(self.h, int(stage), field.encode(), _dp(v))
+        if rc != 0:
+            raise RuntimeError(f"rmpc_ref_model_set({stage}, {field}) -> {rc}")
+
+    def step(self, x):
+        x, u = _np(x), np.zeros(6)
+        sqp, qp = C.c_int(0), C.c_int(0)
+        res, cost, tt = np.zeros(4), C.c_double(0), C.c_double(0)
+        st = self.lib.rmpc_ref_step(self.h, _dp(x), _dp(u), C.byref(sqp), C.byref(qp), _dp(res), C.byref(cost), C.byref(tt))
+        return dict(u=u, status=int(st), sqp_iter=sqp.value, qp_iter=qp.value, res=res, cost=cost.value, time_tot=tt.value)
+
+    def statistics(self):
+        """AcadosOcpSolver.get_stats('statistics') of the last solve: [(stat_n + 1), rows]."""
+        buf, sn = np.zeros(16 * 256), C.c_int(0)
+        rows = self.lib.rmpc_ref_statistics(self.h, _dp(buf), buf.size, C.byref(sn))
+        if rows < 0:
+            raise RuntimeError("statistics buffer too small")
+        return buf[:(sn.value + 1) * rows].reshape(sn.value + 1, rows).copy()
+
+    def times(self):
+        t = np.zeros(6)
+        self.lib.rmpc_ref_times(self.h, _dp(t))
+        return dict(zip(("time_tot", "time_lin", "time_qp", "time_qp_solver_call", "time_qp_xcond", "time_glob"), t))
+
+    def iterate(self):
+        x, u, pi = np.zeros((self.N + 1, 12)), np.zeros((self.N, 6)), np.zeros((self.N, 12))
+        self.lib.rmpc_ref_get_iterate(self.h, _dp(x), _dp(u), _dp(pi))
+        return x, u, pi
+
+    def close(self):
+        if self.h:
+            self.lib.rmpc_ref_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -307,7 +307,7 @@ rmpc_ref *rmpc_ref_create(const rmpc_problem *prob, const double x0[12])
         /* warm_start_first_qp_from_nlp is False in python => template does not set it */
         double lm = 0.0;
         ocp_nlp_solver_opts_set(cf, o, "levenberg_marquardt", &lm);
-        int cond_N = N; /* qp_solver_cond_N = None -> N: no condensing */
+        int cond_N = (p->cond_N > 0 && p->cond_N < N) ? p->cond_N : N; /* qp_solver_cond_N = None -> N: no condensing */
         ocp_nlp_solver_opts_set(cf, o, "qp_cond_N", &cond_N);
         int ext_qp_res = 0;
         ocp_nlp_solver_opts_set(cf, o, "ext_qp_res", &ext_qp_res);
@@ -363,7 +363,7 @@ rmpc_ref *rmpc_ref_create(const rmpc_problem *prob, const double x0[12])
         }
         else
         {
-            int as_rti_iter = 1, as_rti_level = 4, rti_log = 0, rti_log_avail = 0;
+            int as_rti_iter = p->as_rti_iter > 0 ? p->as_rti_iter : 1, as_rti_level = p->as_rti_level_p1 > 0 ? p->as_rti_level_p1 - 1 : 4, rti_log = 0, rti_log_avail = 0;
             ocp_nlp_solver_opts_set(cf, o, "as_rti_iter", &as_rti_iter);
             ocp_nlp_solver_opts_set(cf, o, "as_rti_level", &as_rti_level);
             ocp_nlp_solver_opts_set(cf, o, "rti_log_residuals", &rti_log);
@@ -538,6 +538,38 @@ int rmpc_ref_step(rmpc_ref *c, const double x[12], double u0[6], int *sqp_iter, 
         ocp_nlp_get(c->solver, "cost_value", cost);
     }
     return status;
+}
+
+/* AcadosOcpSolver.cost_set / constraints_set between two solves (T/acados_ocp_solver.py:1863-2035): the reference's own
+ * ocp_nlp_cost_model_set / ocp_nlp_constraints_model_set (acados_c/ocp_nlp_interface.c:516-560,637-760).
+ * field: "yref" (18), "W" (18 x 18 column-major), "lbu" / "ubu" (6), "lbx" / "ubx" (12 at stage 0, 6 on q at stages 1..N-1). */
+int rmpc_ref_model_set(rmpc_ref *c, int stage, const char *field, const double *value)
+{
+    if (!strcmp(field, "yref") || !strcmp(field, "W"))
+        return ocp_nlp_cost_model_set(c->config, c->dims, c->in, stage, field, (void *) value);
+    return ocp_nlp_constraints_model_set(c->config, c->dims, c->in, c->out, stage, field, (void *) value);
+}
+
+/* the statistics table of the last solve as AcadosOcpSolver.get_stats('statistics') returns it: out[(stat_n + 1) x rows],
+ * row 0 = iteration index (ocp_nlp_get "statistics", AC/ocp_nlp/ocp_nlp_sqp.c:960-975); returns rows, *stat_n_out = stat_n */
+int rmpc_ref_statistics(rmpc_ref *c, double *out, int max_doubles, int *stat_n_out)
+{
+    int it = 0, stat_n = 0, stat_m = 0;
+    ocp_nlp_get(c->solver, "nlp_iter", &it);
+    ocp_nlp_get(c->solver, "stat_n", &stat_n);
+    ocp_nlp_get(c->solver, "stat_m", &stat_m);
+    const int rows = stat_m < it + 1 ? stat_m : it + 1;
+    if (stat_n_out) *stat_n_out = stat_n;
+    if ((stat_n + 1) * rows > max_doubles) return -1;
+    ocp_nlp_get(c->solver, "statistics", out);
+    return rows;
+}
+
+/* acados' own timing breakdown of the last solve: time_tot, time_lin, time_qp, time_qp_solver_call, time_qp_xcond, time_glob */
+void rmpc_ref_times(rmpc_ref *c, double t[6])
+{
+    static const char *names[6] = {"time_tot", "time_lin", "time_qp_sol", "time_qp_solver_call", "time_qp_xcond", "time_glob"};
+    for (int k = 0; k < 6; k++) ocp_nlp_get(c->solver, names[k], &t[k]);
 }
 
 /* opts 'rti_phase' (0 preparation + feedback, 1 preparation, 2 feedback; AC/ocp_nlp/ocp_nlp_sqp_rti.c:1140-1170), as

@@ -43,6 +43,12 @@ typedef struct
      * idiom (x_k <- x_{k+1}, u_k <- u_{k+1} for k < N-1, x_{N-1} <- x_N; multipliers and merit weights stay).  The reference
      * never shifts (R/simulator.py:199-241): 0 is the reference behaviour.  SURVEY.md 8(f) #1. */
     int shift;
+    /* reference leg only (the port and the device implement cond_N = N, plain RTI): qp_solver_cond_N (0 = N: no condensing;
+     * SURVEY.md 8(f) #2, H/cond/x_part_cond.c) and the AS-RTI options as_rti_level (0 = 4 = STANDARD_RTI; levels A..D are
+     * 0..3 in acados' enum, offset by one here so that 0 can mean "default": 1 = LEVEL A ... 4 = LEVEL D) / as_rti_iter. */
+    int cond_N;
+    int as_rti_level_p1;
+    int as_rti_iter;
 } rmpc_problem;
 
 /* Fill every field except model.surf / model.wcv / N / dt / solver_type with the reference defaults. */
@@ -80,6 +86,9 @@ static inline void rmpc_problem_defaults(rmpc_problem *p)
     p->term_lh = 0.0;
     p->term_uh = 0.0;
     p->shift = 0;
+    p->cond_N = 0;
+    p->as_rti_level_p1 = 0;
+    p->as_rti_iter = 1;
 }
 
 /* Closed-loop trace written by both legs (any pointer may be NULL). Layouts are row-major.

@@ -10,6 +10,7 @@
  */
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -99,6 +100,26 @@ __global__ void rmpc_plant_logs_kernel(const RmpcChain ch, const double *par, co
     }
 }
 
+/* per-stage table [B][N][RT_COUNT] <- the per-instance values of the parameter block, for every stage (cols: 0 all, 1 yref,
+ * 2 lower bounds, 3 upper bounds) */
+__global__ void rmpc_stage_table_fill_kernel(double *stg, const double *par, long B, int N, int cols)
+{
+    const long tot = B * N * RT_COUNT;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
+    {
+        const long i = k / ((long) N * RT_COUNT);
+        const int c = (int) (k % RT_COUNT);
+        const double *p = par + i * RP_COUNT;
+        const int grp = c < RT_LB ? 1 : (c < RT_UB ? 2 : 3);
+        if (cols && cols != grp) continue;
+        double v;
+        if (c < RT_LB) v = p[RP_YREF + c];
+        else if (c < RT_UB) v = (c - RT_LB) < 6 ? p[RP_UMIN + c - RT_LB] : p[RP_QMIN + c - RT_LB - 6];
+        else v = (c - RT_UB) < 6 ? p[RP_UMAX + c - RT_UB] : p[RP_QMAX + c - RT_UB - 6];
+        stg[k] = v;
+    }
+}
+
 __global__ void rmpc_flags_to_double_kernel(const int *flags, double *out, long n)
 {
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long) gridDim.x * blockDim.x) out[k] = flags[k];
@@ -118,6 +139,8 @@ struct rmpc_handle
     std::vector<void *> owned;
     double *par_dev;
     double *pe_dev; /* [B][RE_COUNT] terminal-set blocks, allocated by the first "P_e" / "alpha_e" / "lh_e" / "term" set */
+    double *stg_dev; /* [B][N][RT_COUNT] per-stage references and bounds, allocated by the first per-stage (stage >= 0) set */
+    double *sqpstat_dev; /* [B][max_iter + 2][RQ_COUNT], allocated by rmpc_set_option("statistics", 1) */
     std::string err;
 };
 
@@ -197,6 +220,8 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     h->device = device; h->nlog = nlog; h->steps_done = 0; h->bytes = 0; h->launches = 0;
     h->par_dev = nullptr;
     h->pe_dev = nullptr;
+    h->stg_dev = nullptr;
+    h->sqpstat_dev = nullptr;
     const size_t B = (size_t) dims->B, S = (size_t) dims->N + 1;
     auto dalloc = [&](size_t n_doubles, void **p) -> bool {
         const size_t bytes = n_doubles * sizeof(double);
@@ -253,6 +278,23 @@ extern "C" int rmpc_set_option(rmpc_handle *h, const char *name, double value)
         h->W.shift = (int) value;
         return 0;
     }
+    if (f == "statistics")
+    {
+        if (value != 0.0 && value != 1.0) return fail(h, RMPC_EINVAL, "rmpc_set_option: statistics must be 0 or 1");
+        if (value == 1.0 && !h->sqpstat_dev)
+        {
+            ON_DEVICE(h);
+            const size_t bytes = sizeof(double) * (size_t) h->D.B * (size_t) (h->D.max_iter + 2) * RQ_COUNT;
+            void *p = nullptr;
+            if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set_option: device allocation failed"); }
+            if (cudaMemset(p, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return fail(h, RMPC_ECUDA, "rmpc_set_option: cudaMemset failed");
+            h->owned.push_back(p);
+            h->bytes += (long long) bytes;
+            h->sqpstat_dev = (double *) p;
+        }
+        h->W.sqpstat = value == 1.0 ? h->sqpstat_dev : nullptr;
+        return 0;
+    }
     return fail(h, RMPC_EINVAL, "rmpc_set_option: unknown option " + f);
 }
 
@@ -276,6 +318,31 @@ static int strided(rmpc_handle *h, double *packed, double *strided_base, long st
     return 0;
 }
 
+/* dst[i * dstride + doff + c] = src[i * sstride + soff + c], c < n */
+__global__ void rmpc_strided2_kernel(const double *src, long sstride, long soff, double *dst, long dstride, long doff, long B, int n)
+{
+    const long tot = B * n;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
+    {
+        const long i = k / n, c = k % n;
+        dst[i * dstride + doff + c] = src[i * sstride + soff + c];
+    }
+}
+static int strided2(rmpc_handle *h, const double *src, long sstride, long soff, double *dst, long dstride, long doff, int n, cudaStream_t s)
+{
+    rmpc_strided2_kernel<<<grid_for((long) h->D.B * n), 256, 0, s>>>(src, sstride, soff, dst, dstride, doff, h->D.B, n);
+    h->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+static int stage_table_fill(rmpc_handle *h, int cols, cudaStream_t s)
+{
+    rmpc_stage_table_fill_kernel<<<grid_for((long) h->D.B * h->D.N * RT_COUNT), 256, 0, s>>>(h->stg_dev, h->par_dev, h->D.B, h->D.N, cols);
+    h->launches++;
+    CU(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const double *dev, void *stream)
 {
     if (!h || !field || !dev) return fail(h, RMPC_EINVAL, "rmpc_set: null argument");
@@ -283,7 +350,101 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
     cudaStream_t s = (cudaStream_t) stream;
     const long S = h->D.N + 1;
     const std::string f(field);
-    if (f == "par") { CU(cudaMemcpyAsync(h->par_dev, dev, sizeof(double) * h->D.B * RP_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "par")
+    {
+        CU(cudaMemcpyAsync(h->par_dev, dev, sizeof(double) * h->D.B * RP_COUNT, cudaMemcpyDeviceToDevice, s));
+        if (h->stg_dev) return stage_table_fill(h, 0, s); /* a new parameter block resets every per-stage override */
+        return 0;
+    }
+    /* ---- named fields of the cost / constraint modules (AcadosOcpSolver.cost_set / constraints_set,
+     * T/acados_ocp_solver.py:1863-2035 -> ocp_nlp_cost_model_set / ocp_nlp_constraints_model_set,
+     * acados_c/ocp_nlp_interface.c:516-560,637-760).  stage = -1: every stage (a slice of the parameter block);
+     * stage >= 0: that stage only (the per-stage table, created on first use from the parameter block). */
+    if (f == "yref" || f == "lbu" || f == "ubu" || f == "lbx" || f == "ubx")
+    {
+        const bool is_y = f == "yref", is_u = f == "lbu" || f == "ubu", lower = f == "lbu" || f == "lbx";
+        if (!is_y && !is_u && stage == 0)
+        { /* lbx_0 = ubx_0 = x0: the initial-state constraint, [B][12] (the reference sets both to the plant state) */
+            CU(cudaMemcpyAsync(h->W.z, dev, sizeof(double) * h->D.B * NX, cudaMemcpyDeviceToDevice, s));
+            return 0;
+        }
+        if (stage < -1 || stage >= h->D.N)
+            return fail(h, RMPC_EINVAL, "rmpc_set: " + f + " exists for stages 0..N-1 (stage N has no cost and no box bounds), -1 = every stage");
+        const int n = is_y ? 18 : 6;
+        if (stage < 0)
+        {
+            const long off = is_y ? RP_YREF : (is_u ? (lower ? RP_UMIN : RP_UMAX) : (lower ? RP_QMIN : RP_QMAX));
+            int rc = strided(h, (double *) dev, h->par_dev, RP_COUNT, off, n, 0, s);
+            if (rc) return rc;
+            if (h->stg_dev) return stage_table_fill(h, is_y ? 1 : (lower ? 2 : 3), s);
+            return 0;
+        }
+        if (!h->stg_dev)
+        {
+            const size_t bytes = sizeof(double) * (size_t) h->D.B * (size_t) h->D.N * RT_COUNT;
+            void *p = nullptr;
+            if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set: device allocation failed"); }
+            h->owned.push_back(p);
+            h->bytes += (long long) bytes;
+            h->stg_dev = (double *) p;
+            int rc = stage_table_fill(h, 0, s);
+            if (rc) return rc;
+            h->W.stg = h->stg_dev;
+        }
+        const long off = (long) stage * RT_COUNT + (is_y ? RT_YREF : ((lower ? RT_LB : RT_UB) + (is_u ? 0 : 6)));
+        return strided(h, (double *) dev, h->stg_dev, (long) h->D.N * RT_COUNT, off, n, 0, s);
+    }
+    if (f == "W_diag" || f == "surf_coeffs" || f == "wcv")
+    {
+        if (stage != -1) return fail(h, RMPC_EINVAL, "rmpc_set: " + f + " is per instance, not per stage: pass stage = -1");
+        if (f == "surf_coeffs") return strided(h, (double *) dev, h->par_dev, RP_COUNT, RP_SURF, 6, 0, s);
+        /* both need host arithmetic on the values (and libm's exp for the exact-ZOH coefficients, like the reference's own
+         * Python): device -> host, transform, host -> device; synchronises the stream */
+        const size_t B = (size_t) h->D.B;
+        const int n = f == "wcv" ? 6 : 18;
+        std::vector<double> in(B * n), out;
+        CU(cudaMemcpyAsync(in.data(), dev, sizeof(double) * B * n, cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        if (f == "wcv")
+        { /* R/prediction_model.py:87-115: a22 = exp(-w Ts), a12 = (1 - a22) / w, b1 = Ts - a12, b2 = 1 - a22 */
+            out.resize(B * 30);
+            const double Ts = h->D.dt;
+            for (size_t i = 0; i < B; i++)
+                for (int k = 0; k < 6; k++)
+                {
+                    const double w = in[i * 6 + k], a22 = std::exp(-w * Ts), a12 = (1.0 - a22) / w;
+                    double *o = out.data() + i * 30;
+                    o[k] = a12; o[6 + k] = a22; o[12 + k] = Ts - a12; o[18 + k] = 1.0 - a22; o[24 + k] = w;
+                }
+            double *tmp = nullptr;
+            if (cudaMalloc((void **) &tmp, sizeof(double) * B * 30) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set: device allocation failed"); }
+            cudaError_t e = cudaMemcpyAsync(tmp, out.data(), sizeof(double) * B * 30, cudaMemcpyHostToDevice, s);
+            int rc = e == cudaSuccess ? strided(h, tmp, h->par_dev, RP_COUNT, RP_A12, 30, 0, s) : RMPC_ECUDA;
+            cudaStreamSynchronize(s);
+            cudaFree(tmp);
+            if (e != cudaSuccess) return fail(h, RMPC_ECUDA, std::string("rmpc_set: ") + cudaGetErrorString(e));
+            return rc;
+        }
+        /* W_diag [B][18]: entries 0..4 task weights, 5..10 = 2 w_u per joint, 11..16 = w_qddot per joint, 17 ignored (the
+         * manipulability output has weight 0, R/trajectory_optimizer.py:139-152) */
+        out.resize(B * 17);
+        for (size_t i = 0; i < B; i++)
+        {
+            const double *w = in.data() + i * 18;
+            double *o = out.data() + i * 17;
+            for (int k = 0; k < 6; k++) { o[k] = 0.5 * w[5 + k]; o[6 + k] = w[11 + k]; }
+            for (int k = 0; k < 5; k++) o[12 + k] = w[k];
+        }
+        double *tmp = nullptr;
+        if (cudaMalloc((void **) &tmp, sizeof(double) * B * 17) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set: device allocation failed"); }
+        cudaError_t e = cudaMemcpyAsync(tmp, out.data(), sizeof(double) * B * 17, cudaMemcpyHostToDevice, s);
+        int rc = e == cudaSuccess ? strided2(h, tmp, 17, 0, h->par_dev, RP_COUNT, RP_WU, 12, s) : RMPC_ECUDA;
+        if (!rc) rc = strided2(h, tmp, 17, 12, h->par_dev, RP_COUNT, RP_WTASK, 5, s);
+        cudaStreamSynchronize(s);
+        cudaFree(tmp);
+        if (e != cudaSuccess) return fail(h, RMPC_ECUDA, std::string("rmpc_set: ") + cudaGetErrorString(e));
+        return rc;
+    }
     if (f == "z") { CU(cudaMemcpyAsync(h->W.z, dev, sizeof(double) * h->D.B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "P_e" || f == "alpha_e" || f == "lh_e" || f == "term")
     {
@@ -486,6 +647,24 @@ extern "C" int rmpc_get(rmpc_handle *h, const char *field, int stage, double *de
         return strided(h, dev, h->W.slab, st, rmpc_slab_off(h->D.N, RC_lam, NB, stage), NB, 1, s);
     }
     if (f == "lamx0") return strided(h, dev, h->W.slab, h->W.slab_stride, H_LAMX0, NB, 1, s);
+    if (f == "par") { CU(cudaMemcpyAsync(dev, h->par_dev, sizeof(double) * B * RP_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
+    if (f == "sqp_stat")
+    {
+        if (!h->sqpstat_dev) return fail(h, RMPC_EINVAL, "rmpc_get: per-iteration statistics are off (rmpc_set_option(h, \"statistics\", 1))");
+        CU(cudaMemcpyAsync(dev, h->sqpstat_dev, sizeof(double) * B * (h->D.max_iter + 2) * RQ_COUNT, cudaMemcpyDeviceToDevice, s));
+        return 0;
+    }
+    if (f == "yref" || f == "lbu" || f == "ubu" || f == "lbx" || f == "ubx")
+    { /* the value a stage uses: its row of the per-stage table if there is one, else the parameter block */
+        const bool is_y = f == "yref", is_u = f == "lbu" || f == "ubu", lower = f == "lbu" || f == "lbx";
+        if (stage < 0 || stage >= h->D.N || (!is_y && !is_u && stage == 0))
+            return fail(h, RMPC_EINVAL, "rmpc_get: stage out of range for field " + f);
+        const int n = is_y ? 18 : 6;
+        if (h->stg_dev)
+            return strided(h, dev, h->stg_dev, (long) h->D.N * RT_COUNT,
+                           (long) stage * RT_COUNT + (is_y ? RT_YREF : ((lower ? RT_LB : RT_UB) + (is_u ? 0 : 6))), n, 1, s);
+        return strided(h, dev, h->par_dev, RP_COUNT, is_y ? RP_YREF : (is_u ? (lower ? RP_UMIN : RP_UMAX) : (lower ? RP_QMIN : RP_QMAX)), n, 1, s);
+    }
     if (f == "z") { CU(cudaMemcpyAsync(dev, h->W.z, sizeof(double) * B * NX, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "summary") { CU(cudaMemcpyAsync(dev, h->W.summary, sizeof(double) * B * RS_COUNT, cudaMemcpyDeviceToDevice, s)); return 0; }
     if (f == "flags")

@@ -242,6 +242,7 @@ struct Inst
 {
     const double *par;
     const double *pe; /* terminal-set block (RE_*), null without a terminal constraint */
+    const double *stg; /* [N][RT_COUNT] per-stage references and bounds, null: every stage uses the parameter row */
     double *head, *arr0, *z;
     int *flags;
     int Sp;
@@ -256,12 +257,12 @@ struct Inst
 RD Inst inst_view(const RmpcWs &w, int N, long i)
 {
     Inst v;
-    (void) N;
     v.head = w.slab + i * w.slab_stride;
     v.arr0 = v.head + RMPC_HEAD;
     v.Sp = w.Sp;
     v.par = w.par + i * RP_COUNT;
     v.pe = w.pe ? w.pe + i * RE_COUNT : nullptr;
+    v.stg = w.stg ? w.stg + i * (long) N * RT_COUNT : nullptr;
     v.z = w.z + i * NX;
     v.flags = w.flags + i * 4;
     v.pair = rd_mask();
@@ -554,7 +555,7 @@ RD StageConst stage_const(const double *par, double dt, int i)
     StageConst c;
     c.cu = par[RP_B2 + i] / dt;
     c.cq = (par[RP_A22 + i] - 1.0) / dt;
-    const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
+    const double wq = par[RP_WQDD + i], wu = 2.0 * par[RP_WU + i];
     c.hu = dt * (wu + wq * c.cu * c.cu);
     c.hs = dt * (wq * c.cu * c.cq);
     c.hq = dt * (wq * c.cq * c.cq);
@@ -563,17 +564,21 @@ RD StageConst stage_const(const double *par, double dt, int i)
 
 /* stage cost dt * 1/2 |y - yref|^2_W from the five task outputs and (u, qd): ocp_nlp_cost_nls_compute_fun
  * (AC/ocp_nlp/ocp_nlp_cost_nls.c:1045-1133) */
-RD double stage_cost(const double *par, double dt, const double *y5, const double *u, const double *qd)
+/* yr = the 18 references of the stage: the stage's row of the per-stage table, else RP_YREF of the parameter block
+ * (the reference's yref = [0, 1, 0, px_ref, vy_ref, 0 ...]: y - 0.0 is y bit for bit) */
+RD const double *yref_of(const double *par, const double *stg, int i) { return stg ? stg + (long) RT_COUNT * i + RT_YREF : par + RP_YREF; }
+RD double stage_cost(const double *par, const double *yr, double dt, const double *y5, const double *u, const double *qd)
 {
-    const double r0 = y5[0], r1 = y5[1] - 1.0, r2 = y5[2], r3 = y5[3] - par[RP_PXREF], r4 = y5[4] - par[RP_VYREF];
+    const double r0 = y5[0] - yr[0], r1 = y5[1] - yr[1], r2 = y5[2] - yr[2], r3 = y5[3] - yr[3], r4 = y5[4] - yr[4];
     double f = par[RP_WTASK] * r0 * r0 + par[RP_WTASK + 1] * r1 * r1 + par[RP_WTASK + 2] * r2 * r2 + par[RP_WTASK + 3] * r3 * r3 +
                par[RP_WTASK + 4] * r4 * r4;
-    const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
     RD_UNROLL
     for (int i = 0; i < 6; i++)
     {
-        const double a = (par[RP_B2 + i] * u[i] + (par[RP_A22 + i] - 1.0) * qd[i]) / dt;
-        f += wu * u[i] * u[i] + wq * a * a;
+        const double wq = par[RP_WQDD + i], wu = 2.0 * par[RP_WU + i];
+        const double a = (par[RP_B2 + i] * u[i] + (par[RP_A22 + i] - 1.0) * qd[i]) / dt - yr[11 + i];
+        const double ru = u[i] - yr[5 + i];
+        f += wu * ru * ru + wq * a * a;
     }
     return dt * (0.5 * f);
 }
@@ -585,17 +590,17 @@ RD void load18(const double *src, double *v)
 }
 
 /* lower/upper bound of slot j in [0,12) of a path stage: [u_min|q_min], [u_max|q_max] */
-RD double lb_of(const double *par, int j) { return j < 6 ? par[RP_UMIN + j] : par[RP_QMIN + j - 6]; }
-RD double ub_of(const double *par, int j) { return j < 6 ? par[RP_UMAX + j] : par[RP_QMAX + j - 6]; }
+RD double lb_of(const double *par, const double *sp, int j) { return sp ? sp[RT_LB + j] : (j < 6 ? par[RP_UMIN + j] : par[RP_QMIN + j - 6]); }
+RD double ub_of(const double *par, const double *sp, int j) { return sp ? sp[RT_UB + j] : (j < 6 ? par[RP_UMAX + j] : par[RP_QMAX + j - 6]); }
 
 struct LinEmit
 {
     double *Jc, *g;
-    const double *par;
+    const double *par, *yr;
     double dt, wr[5], sw[5], gqd0[6];
     RDM void begin(const double *y5)
     {
-        const double res[5] = {y5[0], y5[1] - 1.0, y5[2], y5[3] - par[RP_PXREF], y5[4] - par[RP_VYREF]};
+        const double res[5] = {y5[0] - yr[0], y5[1] - yr[1], y5[2] - yr[2], y5[3] - yr[3], y5[4] - yr[4]};
         RD_UNROLL
         for (int m = 0; m < 5; m++)
         {
@@ -640,19 +645,21 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         LinEmit em;
         em.Jc = AR(Jc) + NJ * i;
         em.g = g;
-        const double wq = par[RP_WQDD], wu = 2.0 * par[RP_WU];
+        const double *sp = I.stg ? I.stg + (long) RT_COUNT * i : nullptr, *yr = yref_of(par, I.stg, i);
         RD_UNROLL
         for (int k = 0; k < 6; k++)
         {
+            const double wq = par[RP_WQDD + k], wu = 2.0 * par[RP_WU + k];
             const double cu = par[RP_B2 + k] / dt, cq = (par[RP_A22 + k] - 1.0) / dt;
-            const double a = cu * v[k] + cq * v[12 + k]; /* qddot_k */
-            g[k] = dt * (wu * v[k] + wq * cu * a);
+            const double a = (cu * v[k] + cq * v[12 + k]) - yr[11 + k]; /* qddot_k - its reference */
+            g[k] = dt * (wu * (v[k] - yr[5 + k]) + wq * cu * a);
             em.gqd0[k] = dt * (wq * cq * a);
         }
         em.par = par;
+        em.yr = yr;
         em.dt = dt;
         ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
-        const double ci = stage_cost(par, dt, y5, v, v + 12);
+        const double ci = stage_cost(par, yr, dt, y5, v, v + 12);
         cost += ci;
         AR(tux)[NV * i] = ci; /* kept for the merit value at this iterate (nlp_merit_lin): tux is free until the line search */
         /* dynamics gap b = Ad x + Bd u - x_next */
@@ -668,7 +675,7 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         for (int j = 0; j < 12; j++)
         {
             if (i == 0 && j >= 6) { d[j] = 0.0; d[12 + j] = 0.0; }
-            else { d[j] = lb_of(par, j) - v[j]; d[12 + j] = v[j] - ub_of(par, j); }
+            else { d[j] = lb_of(par, sp, j) - v[j]; d[12 + j] = v[j] - ub_of(par, sp, j); }
         }
         if (i == 0)
         {
@@ -706,7 +713,8 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
         load18(tux + NV * i, v);
         NoEmit ne;
         ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
-        const double ci = stage_cost(par, D.dt, y5, v, v + 12);
+        const double *sp = I.stg ? I.stg + (long) RT_COUNT * i : nullptr;
+        const double ci = stage_cost(par, yref_of(par, I.stg, i), D.dt, y5, v, v + 12);
         m += ci;
         csum += ci; /* the cost alone, summed like solver.get_cost() does (closed_loop_group) */
         const double *xn = tux + NV * (i + 1) + 6, *wpi = AR(wpi) + NX * i, *wl = AR(wlam) + NB * i;
@@ -721,7 +729,7 @@ RDN double nlp_merit(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, con
         for (int j = 0; j < 12; j++)
         {
             if (i == 0 && j >= 6) continue;
-            const double fl = lb_of(par, j) - v[j], fu = v[j] - ub_of(par, j);
+            const double fl = lb_of(par, sp, j) - v[j], fu = v[j] - ub_of(par, sp, j);
             if (fl > 0.0) m += fabs(wl[j]) * fl;
             if (fu > 0.0) m += fabs(wl[12 + j]) * fu;
         }
@@ -2028,22 +2036,29 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
  * (0 ok, 2 max iter, 3 min step, 1 NaN).  The Householder-LQ fall-back of lq_fact = 1 is not implemented: its
  * trigger (linear-system residual > 1e-5, :2246-2276) is evaluated and counted in flags[2] so that any instance
  * that would have taken it is visible to the caller. */
-RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters)
+RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters, double *tq)
 {
     const int N = D.N, lane = rd_lane();
     const double tol = D.qp_tol, alpha_min = 1e-8, tau_min = 1e-16;
     const double nc_inv = 1.0 / (double) (NB * (N - 1) + 12 + (I.pe ? 2 : 0));
+    /* device timers of the phases (tq[0] factorisation, [1] forward sweeps, [2] backward substitutions, [3] initialisation +
+     * update / residual sweeps): read on the GPU's global timer at the phase boundaries, a handful of reads per iteration */
+    double t0 = rd_time(), t1;
+#define TQ(k) do { t1 = rd_time(); tq[k] += t1 - t0; t0 = t1; } while (0)
     ipm_init(D, I, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
     double sum_lt = ipm_res_sweep<0>(D, I, sm, 0.0, nrm);
     double mu = nc_inv * sum_lt;
+    TQ(3);
     int kk;
     for (kk = 0; kk < D.qp_iter_max && alpha > alpha_min && (nrm[0] > tol || nrm[1] > tol || nrm[2] > tol || nrm[4] > tol); kk++)
     {
         /* affine (predictor) step */
         ipm_factor(D, I, sm);
+        TQ(0);
         double lin[2];
         ipm_forward<0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);
+        TQ(1);
         if ((lin[0] == 0.0 && lin[1] > 0.5) || lin[0] > 1e-5)
         {
             /* Inaccurate factorisation (x_ocp_qp_ipm.c:2246-2276).  HPIPM re-factorises this iteration with Householder
@@ -2078,15 +2093,19 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         sigma_mu = sigma_mu > tau_min ? sigma_mu : tau_min;
         /* corrector: centering + second-order correction */
         ipm_backward<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
+        TQ(2);
         double clin[2];
         ipm_forward<1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, clin);
+        TQ(1);
         /* conditional predictor-corrector */
         const double mu_aff0 = mu_aff;
         mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         if (mu_aff > 2.0 * mu_aff0)
         {
             ipm_backward<2, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), nullptr, sigma_mu, AR(dux));
+            TQ(2);
             ipm_forward<1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_mc), 0.0, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, clin);
+            TQ(1);
         }
         /* iterative refinement of the corrector step, itref_corr_max = 2 */
         int refined = 0;
@@ -2121,7 +2140,9 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         if (a < 1.0) a = a * ((1.0 - a) * 0.99 + a * 0.9999999);
         sum_lt = ipm_res_sweep<1>(D, I, sm, a, nrm); /* UPDATE_VAR_QP + OCP_QP_RES_COMPUTE */
         mu = nc_inv * sum_lt;
+        TQ(3); /* incl. the rare refinement passes of this iteration */
     }
+#undef TQ
     *iters = kk;
     if (kk == D.qp_iter_max) return 2;
     if (alpha <= alpha_min) return 3;
@@ -2227,12 +2248,13 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
 
 /* ocp_qp_xcond_solve (AC/ocp_qp/ocp_qp_xcond_solver.c:518-576): reduce -> IPM -> restore.  warm start bookkeeping:
  * flags[1] != 0 until the first QP of the instance's lifetime has been solved (reference quirk, see ipm_init). */
-RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp, int *iters)
+RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp, int *iters, double *tq)
 {
     const int N = D.N, lane = rd_lane();
     const int warm = I.flags[1] ? 2 : 0;
     rd_sync();
     if (lane == 0) I.flags[1] = 0;
+    const double tx0 = rd_time();
     qp_reduce(D, I);
     if (init_from_nlp && warm == 2)
     {
@@ -2252,8 +2274,11 @@ RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp
         }
         rd_sync();
     }
-    const int st = ipm_solve_qp(D, I, sm, warm, iters);
+    const double tx1 = rd_time();
+    const int st = ipm_solve_qp(D, I, sm, warm, iters, tq);
+    const double tx2 = rd_time();
     qp_restore(D, I);
+    tq[4] += (tx1 - tx0) + (rd_time() - tx2); /* time_qp_xcond */
     return st;
 }
 
@@ -2262,7 +2287,13 @@ struct StepOut
     int status, sqp_iter, qp_iter, qp_status;
     int cost_valid; /* cost holds the NLS cost at the returned iterate (else closed_loop_group evaluates it) */
     double res[4], alpha, cost;
+    double t_lin, t_qp, t_glob, tq[5]; /* device timers: linearisation, QP (tq: factor, forward, backward, residual, xcond), globalisation */
 };
+RD void step_timers_clear(StepOut &o)
+{
+    o.t_lin = o.t_qp = o.t_glob = 0.0;
+    o.tq[0] = o.tq[1] = o.tq[2] = o.tq[3] = o.tq[4] = 0.0;
+}
 
 /* ocp_nlp_sqp_rti, PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
 /* phase (opts->rti_phase, :1140-1170): 0 = both, 1 = PREPARATION only -- everything that does not depend on x0: model
@@ -2273,6 +2304,8 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
 {
     o.sqp_iter = 0; o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0; o.status = 0;
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0;
+    step_timers_clear(o);
+    double tt = rd_time();
     if (phase != 2)
     {
         o.cost = nlp_linearise(ch, D, I, I.z);
@@ -2287,11 +2320,13 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
         o.cost = (I.head + H_LINCOST)[0];
     }
     o.cost_valid = 1; /* cost at the iterate the step starts from; replaced below once the iterate moves */
+    { const double t = rd_time(); o.t_lin = t - tt; tt = t; }
     if (phase == 1) return;
     const int first = I.flags[0];
     rd_sync();
     int it = 0;
-    const int qs = qp_solve(D, I, sm, first, &it);
+    const int qs = qp_solve(D, I, sm, first, &it, o.tq);
+    { const double t = rd_time(); o.t_qp = t - tt; tt = t; }
     PAIR_SYNC();
     o.sqp_iter = 1; o.qp_iter = it; o.qp_status = qs;
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0; /* rti_log_residuals = 0: the reference reports zeros */
@@ -2301,33 +2336,53 @@ RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
     if (nlp_line_search_update(ch, D, I, 1, &o.alpha, &o.cost, &o.cost_valid)) o.cost_valid = 1;
     if (rd_lane() == 0) I.flags[0] = 0;
     rd_sync();
+    o.t_glob = rd_time() - tt;
     o.status = 0;
 }
 
 /* ocp_nlp_sqp (AC/ocp_nlp/ocp_nlp_sqp.c:474-801) with check_termination (:351-443) */
-RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o)
+RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o, double *stat)
 {
     o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0; o.cost = 0.0; o.cost_valid = 0;
+    step_timers_clear(o);
+    /* stat: rows of acados' mem->stat for this solve (RQ_*, AC/ocp_nlp/ocp_nlp_sqp.c:573-576,700-701,788), null: not kept */
+    const bool log = stat && rd_lane() == 0;
+    if (log)
+        for (int k = 0; k < RQ_COUNT; k++) stat[k] = 0.0;
     for (int it = 0; it <= D.max_iter; it++)
     {
         o.sqp_iter = it;
         double cost = 0.0;
+        double tt = rd_time();
         if (it != D.max_iter)
         {
             cost = nlp_linearise(ch, D, I, I.z);
             o.cost = cost; o.cost_valid = 1; /* every exit before the next update returns this iterate */
             nlp_residuals(D, I, o.res);
+            if (log)
+                for (int k = 0; k < 4; k++) stat[RQ_COUNT * it + RQ_RES + k] = o.res[k];
         }
+        { const double t = rd_time(); o.t_lin += t - tt; tt = t; }
         const double *r = o.res;
         if (r[0] != r[0] || r[1] != r[1] || r[2] != r[2] || r[3] != r[3]) { o.status = 1; return; }
         if (it >= D.max_iter) { o.status = 2; return; }
         if (r[0] < D.tol[0] && r[1] < D.tol[1] && r[2] < D.tol[2] && r[3] < D.tol[3]) { o.status = 0; return; }
         if (cost <= -1e10) { o.status = 6; return; }
         int qi = 0;
-        const int qs = qp_solve(D, I, sm, 0, &qi);
+        const int qs = qp_solve(D, I, sm, 0, &qi, o.tq);
+        { const double t = rd_time(); o.t_qp += t - tt; tt = t; }
         o.qp_iter += qi; o.qp_status = qs;
+        if (log)
+        {
+            for (int k = 0; k < RQ_COUNT; k++) stat[RQ_COUNT * (it + 1) + k] = 0.0;
+            stat[RQ_COUNT * (it + 1) + RQ_QP_STATUS] = qs;
+            stat[RQ_COUNT * (it + 1) + RQ_QP_ITER] = qi;
+        }
         if (qs != 0 && qs != 2) { o.sqp_iter = it + 1; o.status = 4; return; }
-        if (nlp_line_search_update(ch, D, I, it, &o.alpha, &o.cost, &o.cost_valid)) { o.cost = cost; o.cost_valid = 1; o.status = 1; return; }
+        const int ls = nlp_line_search_update(ch, D, I, it, &o.alpha, &o.cost, &o.cost_valid);
+        o.t_glob += rd_time() - tt;
+        if (log) stat[RQ_COUNT * (it + 1) + RQ_ALPHA] = o.alpha;
+        if (ls) { o.cost = cost; o.cost_valid = 1; o.status = 1; return; }
     }
     o.status = 2;
 }
@@ -2384,7 +2439,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         PAIR_SYNC();
         const double t_begin = rd_time();
         if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o, advance ? 0 : W.rti_phase);
-        else solve_sqp(ch, D, I, sm, o);
+        else solve_sqp(ch, D, I, sm, o, W.sqpstat ? W.sqpstat + inst * (long) (D.max_iter + 2) * RQ_COUNT : nullptr);
         const double t_solve = rd_time() - t_begin; /* stands in for get_stats('time_tot') (R/simulator.py:220) */
         /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679).  The solve usually knows it
          * already (linearisation of an iterate it did not move, or the merit evaluation of the accepted trial point). */
@@ -2398,7 +2453,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
                 load18(AR(ux) + NV * i, v);
                 NoEmit ne;
                 ur10_task<false>(ch, par, v + 6, v + 12, y5, ne);
-                cost += stage_cost(par, D.dt, y5, v, v + 12);
+                cost += stage_cost(par, yref_of(par, I.stg, i), D.dt, y5, v, v + 12);
             }
             cost = grp_sum(cost);
         }
@@ -2437,7 +2492,10 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
                 double *sl = W.slog + (inst * W.nlog + gs) * RL_COUNT;
                 sl[RL_STATUS] = o.status; sl[RL_SQP_ITER] = o.sqp_iter; sl[RL_QP_ITER] = o.qp_iter; sl[RL_COST] = cost;
                 sl[RL_RES] = o.res[0]; sl[RL_RES + 1] = o.res[1]; sl[RL_RES + 2] = o.res[2]; sl[RL_RES + 3] = o.res[3];
-                sl[RL_ALPHA] = o.alpha; sl[RL_QP_STATUS] = o.qp_status; sl[RL_TIME] = t_solve; sl[RL_TIME + 1] = 0.0;
+                sl[RL_ALPHA] = o.alpha; sl[RL_QP_STATUS] = o.qp_status; sl[RL_TIME] = t_solve;
+                sl[RL_TIME_LIN] = o.t_lin; sl[RL_TIME_QP] = o.t_qp; sl[RL_TIME_GLOB] = o.t_glob;
+                sl[RL_TIME_QP_FACT] = o.tq[0]; sl[RL_TIME_QP_FWD] = o.tq[1]; sl[RL_TIME_QP_BWD] = o.tq[2]; sl[RL_TIME_QP_RES] = o.tq[3];
+                sl[RL_TIME_XCOND] = o.tq[4]; sl[RL_COUNT - 1] = 0.0;
             }
             if (W.summary)
             {

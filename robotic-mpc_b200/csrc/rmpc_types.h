@@ -36,75 +36,11 @@ enum
     RF_END = 202
 };
 
-/* per-instance parameter block (doubles) */
-enum
-{
-    RP_SURF = 0,    /* a b c d e f                                   R/surface.py:14-30 */
-    RP_A12 = 6,     /* (1-a22)/w                                     R/prediction_model.py:87-115 */
-    RP_A22 = 12,    /* exp(-w Ts) */
-    RP_B1 = 18,     /* Ts - a12 */
-    RP_B2 = 24,     /* 1 - a22 */
-    RP_WCV = 30,    /* plant bandwidths                              R/simulation_model.py:79-83 */
-    RP_WU = 36,     /* w_u                                           R/trajectory_optimizer.py:148 */
-    RP_WQDD = 37,   /* w_qddot                                       R/trajectory_optimizer.py:150 */
-    RP_PXREF = 38,
-    RP_VYREF = 39,
-    RP_WTASK = 40,  /* 5 task weights (50 each)                      R/trajectory_optimizer.py:44-48 */
-    RP_UMIN = 45,
-    RP_UMAX = 51,
-    RP_QMIN = 57,
-    RP_QMAX = 63,
-    RP_TEE = 69,    /* task-frame offset in the EE frame             R/prediction_model.py:9 */
-    RP_COUNT = 72
-};
-
-/* per-step log record (doubles) written by the closed loop */
-enum
-{
-    RL_STATUS = 0, RL_SQP_ITER = 1, RL_QP_ITER = 2, RL_COST = 3,
-    RL_RES = 4,     /* 4: stat eq ineq comp (zeros for SQP_RTI, like the reference) */
-    RL_ALPHA = 8,   /* accepted line-search step of the last SQP iteration */
-    RL_QP_STATUS = 9,
-    RL_TIME = 10,   /* seconds this instance's solve took on the device (GPU global timer), stands in for time_tot */
-    RL_COUNT = 12
-};
-
-/* per-sample plant record computed from the logged plant states (R/simulation_model.py:60-77, R/simulator.py:265-344) */
-enum
-{
-    RK_POSE = 0,    /* 12: p_ee(3), R_ee row-major(9) of frame ee_link */
-    RK_RPY = 12,    /* 3 : roll pitch yaw of R_ee */
-    RK_TWIST = 15,  /* 6 : WORLD twist J qd */
-    RK_ERR = 21,    /* 5 : tracking errors e1..e5 */
-    RK_PTZ = 26,    /* 1 : z of the task-frame origin */
-    RK_COUNT = 28
-};
-
-/* summary row per instance accumulated on device (R/simulator.py:347-390 metrics + solver_stats) */
-enum
-{
-    RS_SSE = 0,      /* 5: sum e_k^2 over the Nsim+1 logged samples */
-    RS_ITSE = 5,     /* 5: sum t * e_k^2 * dt */
-    RS_NFAIL = 10,   /* steps with status != 0 */
-    RS_SQP_ITERS = 11,
-    RS_QP_ITERS = 12,
-    RS_MAX_RES = 13, /* 4: max over steps of each KKT residual */
-    RS_COST_LAST = 17,
-    RS_NSAMPLES = 18,
-    RS_COUNT = 20
-};
-
-/* per-instance terminal-set block (doubles), optional: h_e(x_N) = x_N' P x_N with lh <= h_e <= uh at stage N
- * (R/_terminal_constraint.py:96-116 gives P, alpha = uh; acados BGH nh_e = 1).  In the per-stage solver arrays the row
- * uses slot 0 (lower side) and slot 12 (upper side) of stage N -- free there, stage N has no box bounds -- and its
- * gradient 2 P x_N (the row of DCt) is kept in Jc[N][0..11]. */
-enum
-{
-    RE_P = 0,     /* 144: P, symmetric, row-major, state order [q; qd] */
-    RE_LH = 144,
-    RE_UH = 145,
-    RE_COUNT = 146
-};
+/* RP_* (parameter block), RT_* (per-stage table), RL_* (step record), RK_* (plant record), RS_* (summary), RE_* (terminal
+ * set; in the per-stage solver arrays the terminal row uses slot 0 (lower side) and slot 12 (upper side) of stage N -- free
+ * there, stage N has no box bounds -- and its gradient 2 P x_N, the row of DCt, is kept in Jc[N][0..11]), RQ_* (SQP
+ * statistics): public, part of the C ABI */
+#include "../../include/rmpc_fields.h"
 
 typedef struct
 {
@@ -192,6 +128,8 @@ typedef struct
     const double *pe;  /* [B][RE_COUNT] terminal-set blocks, null: no terminal constraint (the reference MPC as shipped) */
     int rti_phase;     /* SQP_RTI only: 0 preparation + feedback in one solve, 1 preparation, 2 feedback (acados rti_phase) */
     int shift;         /* closed loop: shift the primal iterate by one stage after every step (0: like the reference) */
+    const double *stg; /* [B][N][RT_COUNT] per-stage references and bounds, null: every stage uses "par" */
+    double *sqpstat;   /* [B][max_iter + 2][RQ_COUNT] per-iteration statistics of the last SQP solve, null: not kept */
 } RmpcWs;
 
 #ifdef __CUDACC__

@@ -11,7 +11,7 @@ from pathlib import Path
 
 import numpy as np
 
-from .params import RK, RL, RP, RS
+from .params import RK, RL, RP, RQ, RS
 
 HERE = Path(__file__).resolve().parent
 LIB_PATH = Path(os.environ.get("RMPC_LIB", HERE / "librmpc.so"))  # RMPC_LIB: A/B builds of the same library
@@ -141,7 +141,14 @@ class Engine:
 
     # ------------------------------------------------------------------ setters
     def set(self, field, value, stage=0):
-        n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12, "P_e": 144, "alpha_e": 1, "lh_e": 1, "term": 146}[field]
+        """``rmpc_set``: copy a ``[B, n]`` array into the engine.  Per-instance blocks ("par", "z", the terminal set), the
+        iterate ("x", "u", "pi" of ``stage``) and the named cost / constraint fields: "yref" [B, 18], "lbu" / "ubu" [B, 6],
+        "lbx" / "ubx" [B, 6] (on q; stage 0: [B, 12] = the initial state) with ``stage = -1`` for every stage or a stage
+        index for that stage only; "W_diag" [B, 18], "surf_coeffs" [B, 6], "wcv" [B, 6] per instance (``stage = -1``)."""
+        n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12, "P_e": 144, "alpha_e": 1, "lh_e": 1, "term": 146,
+             "yref": 18, "lbu": 6, "ubu": 6, "lbx": 6, "ubx": 6, "W_diag": 18, "surf_coeffs": 6, "wcv": 6}[field]
+        if field in ("lbx", "ubx") and stage == 0:
+            n = 12
         t = self._dev(value, (self.B, n))
         self._check(self.lib.rmpc_set(self.h, field.encode(), int(stage), C.c_void_p(t.data_ptr()), self._stream()),
                     f"rmpc_set({field})")
@@ -187,7 +194,8 @@ class Engine:
         return False
 
     def set_option(self, name, value):
-        """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step."""
+        """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step;
+        'statistics' (0 | 1) = keep the per-iteration table of the last full-SQP solve (``get('sqp_stat')``)."""
         self._check(self.lib.rmpc_set_option(self.h, str(name).encode(), float(value)), f"rmpc_set_option({name})")
 
     def set_chain(self, xyzR=None, axis=None):
@@ -236,7 +244,8 @@ class Engine:
         shape = {"x": (B, 12), "u": (B, 6), "pi": (B, 12), "lam": (B, 24), "lamx0": (B, 24), "z": (B, 12),
                  "stats": (B, RL["COUNT"]), "summary": (B, RS["COUNT"]), "flags": (B, 4),
                  "zlog": (B, nl + 1, 12), "ulog": (B, nl, 6), "slog": (B, nl, RL["COUNT"]),
-                 "plog": (B, nl + 1, RK["COUNT"])}[field]
+                 "plog": (B, nl + 1, RK["COUNT"]), "par": (B, RP["COUNT"]), "yref": (B, 18), "lbu": (B, 6), "ubu": (B, 6),
+                 "lbx": (B, 6), "ubx": (B, 6), "sqp_stat": (B, self.dims.max_iter + 2, RQ["COUNT"])}[field]
         out = self.torch.empty(shape, dtype=self.torch.float64, device=self.tdev)
         self._check(self.lib.rmpc_get(self.h, field.encode(), int(stage), C.c_void_p(out.data_ptr()), self._stream()),
                     f"rmpc_get({field})")

@@ -16,7 +16,7 @@ import uuid
 
 import numpy as np
 
-from .params import RL, pack_params
+from .params import RL, RQ, pack_params
 
 _SUPPORTED_FIXED = {  # option -> the only value(s) the engine implements (the reference never uses another one)
     "qp_solver": ("PARTIAL_CONDENSING_HPIPM",),
@@ -212,6 +212,9 @@ class BatchedSolver:
         self.engine.reset()
         self._stats = None
         self.rti_phase = 0
+        self._last_phase = 0
+        if o.nlp_solver_type == "SQP":
+            self.engine.set_option("statistics", 1)  # get_stats('statistics') of the last solve, like acados keeps it
 
     def options_set(self, field, value):
         """``AcadosOcpSolver.options_set`` (T/acados_ocp_solver.py:2220-2340) for the one runtime option the hot path has:
@@ -227,21 +230,63 @@ class BatchedSolver:
     def view(self, i):
         return SolverView(self, i)
 
-    # ---- AcadosOcpSolver.set (T/acados_ocp_solver.py:1743-1819)
+    # ---- AcadosOcpSolver.set / cost_set / constraints_set (T/acados_ocp_solver.py:1743-1819,1863-2035)
     def set(self, stage, field, value):
-        if field in ("lbx", "ubx"):
-            if stage != 0:
-                raise NotImplementedError("only the stage-0 state bounds (= the initial-state constraint) can be set")
-            self.engine.set_state(value)  # the reference always sets lbx_0 = ubx_0 = x (R/simulator.py:210-211)
-        elif field in ("x", "u", "pi"):
+        """Iterate fields 'x', 'u', 'pi'; everything else is routed like acados does: cost fields to ``cost_set``,
+        constraint fields to ``constraints_set``."""
+        if field in ("x", "u", "pi"):
             self.engine.set(field, value, stage=stage)
+            self._stats = None
+        elif field in ("yref", "W"):
+            self.cost_set(stage, field, value)
+        elif field in ("lbx", "ubx", "lbu", "ubu"):
+            self.constraints_set(stage, field, value)
+        elif field == "p":
+            raise NotImplementedError("set(stage, 'p', .): the formulation has no runtime parameter vector; the surface is "
+                                      "set per instance with set_surface(coeffs)")
         else:
-            raise NotImplementedError(f"set(..., {field!r}): per-stage {field} is part of the per-instance parameter block; "
-                                      "rebuild the batch with new MPC parameters")
+            raise NotImplementedError(f"set(..., {field!r})")
+
+    def cost_set(self, stage, field, value):
+        """``AcadosOcpSolver.cost_set`` -> ``ocp_nlp_cost_model_set`` (acados_c/ocp_nlp_interface.c:516-560).
+        'yref': ``[B, 18]`` (or ``[18]``) reference of ``stage`` (0..N-1).  'W': ``[18, 18]`` / ``[B, 18, 18]`` diagonal weight
+        matrix (or its ``[B, 18]`` diagonal); the engine keeps W per INSTANCE, so a call for any stage sets every stage --
+        like the reference, whose W is the same matrix on all stages (R/trajectory_optimizer.py:139-156)."""
+        if field == "yref":
+            self.engine.set("yref", np.broadcast_to(np.asarray(value, float), (self.B, 18)), stage=stage)
+        elif field == "W":
+            w = np.asarray(value, float)
+            if w.shape[-2:] == (18, 18) and w.ndim >= 2:
+                if np.abs(w - np.einsum("...ii->...i", w)[..., None] * np.eye(18)).max() > 0:
+                    raise NotImplementedError("cost_set('W'): only diagonal weight matrices (the reference's W is diagonal)")
+                w = np.einsum("...ii->...i", w)
+            w = np.broadcast_to(w, (self.B, 18))
+            for blk in (w[:, 5:11], w[:, 11:17]):
+                if np.any(blk < 0):
+                    raise ValueError("cost_set('W'): weights must be non-negative")
+            self.engine.set("W_diag", w, stage=-1)
+        else:
+            raise NotImplementedError(f"cost_set(..., {field!r}): fields 'yref' and 'W'")
+        self._stats = None
+
+    def constraints_set(self, stage, field, value):
+        """``AcadosOcpSolver.constraints_set`` -> ``ocp_nlp_constraints_model_set`` (acados_c/ocp_nlp_interface.c:637-760).
+        'lbx' / 'ubx' at stage 0: the initial-state constraint ``[B, 12]`` (the reference sets both to the plant state,
+        R/simulator.py:210-211); at stages 1..N-1: bounds on q ``[B, 6]``; 'lbu' / 'ubu' at stages 0..N-1: ``[B, 6]``."""
+        if field not in ("lbx", "ubx", "lbu", "ubu"):
+            raise NotImplementedError(f"constraints_set(..., {field!r}): fields 'lbx', 'ubx', 'lbu', 'ubu'")
+        n = 12 if (field in ("lbx", "ubx") and stage == 0) else 6
+        self.engine.set(field, np.broadcast_to(np.asarray(value, float), (self.B, n)), stage=stage)
+        self._stats = None
+
+    def set_surface(self, coeffs):
+        """Surface coefficients a..f per instance (``[B, 6]``): what the reference bakes into the generated cost function."""
+        self.engine.set("surf_coeffs", np.broadcast_to(np.asarray(coeffs, float), (self.B, 6)), stage=-1)
         self._stats = None
 
     def solve(self):
         self.engine.solve(rti_phase=self.rti_phase)
+        self._last_phase = self.rti_phase
         self._stats = self.engine.get("stats").cpu().numpy()
         return self._stats[:, RL["STATUS"]].astype(int)
 
@@ -256,16 +301,53 @@ class BatchedSolver:
             raise RuntimeError("call solve() first")
         return self._stats
 
+    _TIME_FIELDS = {"time_tot": "TIME", "time_lin": "TIME_LIN", "time_qp": "TIME_QP", "time_glob": "TIME_GLOB",
+                    "time_qp_xcond": "TIME_XCOND"}
+    _ZERO_TIME_FIELDS = ("time_sim", "time_sim_ad", "time_sim_la", "time_reg", "time_qpscaling", "time_solution_sensitivities")
+
     def get_stats(self, field):
+        """``AcadosOcpSolver.get_stats`` (T/acados_ocp_solver.py:1461-1661) for the batch: ``[B]`` arrays; 'statistics' a list of
+        B tables in acados' layout (row 0 = iteration index, then for SQP: res_stat, res_eq, res_ineq, res_comp, qp_stat,
+        qp_iter, alpha; for SQP_RTI: qp_stat, qp_iter).  Times are DEVICE times of each instance's own solve (GPU global
+        timer), split like acados splits its own (AC/ocp_nlp/ocp_nlp_common.c:4610-4681); 'time_qp_phases' adds the
+        interior-point breakdown ``[B, 4]`` = factorisation, forward sweeps, backward substitutions, update + residuals."""
         s = self._need_stats()
-        if field == "sqp_iter":
+        if field in ("sqp_iter", "nlp_iter"):
             return s[:, RL["SQP_ITER"]].astype(int)
         if field == "qp_iter":
             return s[:, RL["QP_ITER"]].astype(int)
-        if field == "time_tot":
-            return s[:, RL["TIME"]].copy()
-        if field == "statistics":
-            return s.copy()
+        if field == "qp_stat":
+            return s[:, RL["QP_STATUS"]].astype(int)
+        if field == "alpha":
+            return s[:, RL["ALPHA"]].copy()
+        if field == "residuals":
+            return self.get_residuals()
+        if field in self._TIME_FIELDS:
+            return s[:, RL[self._TIME_FIELDS[field]]].copy()
+        if field == "time_qp_solver_call":
+            return s[:, RL["TIME_QP"]] - s[:, RL["TIME_XCOND"]]
+        if field in self._ZERO_TIME_FIELDS:
+            return np.zeros(self.B)  # no integrator, regularisation, scaling or sensitivity module on this path
+        if field == "time_preparation":
+            return s[:, RL["TIME_LIN"]].copy() if self._last_phase != 2 else np.zeros(self.B)
+        if field == "time_feedback":
+            return s[:, RL["TIME"]] - (s[:, RL["TIME_LIN"]] if self._last_phase == 0 else 0.0)
+        if field == "time_qp_phases":
+            return s[:, RL["TIME_QP_FACT"]:RL["TIME_QP_RES"] + 1].copy()
+        if field == "record":
+            return s.copy()  # the engine's own RL_* record of the last solve
+        if field in ("statistics", "stat_m", "stat_n"):
+            rti = self.mpcs[0].ocp.solver_options.nlp_solver_type == "SQP_RTI"
+            if field == "stat_n":
+                return 2 if rti else RQ["COUNT"]
+            if field == "stat_m":
+                return 2 if rti else self.mpcs[0].ocp.solver_options.nlp_solver_max_iter + 1
+            it = s[:, RL["SQP_ITER"]].astype(int)
+            if rti:
+                return [np.array([[0.0, 1.0], [0.0, s[i, RL["QP_STATUS"]]], [0.0, s[i, RL["QP_ITER"]]]])[:, :it[i] + 1]
+                        for i in range(self.B)]
+            tab = self.engine.get("sqp_stat").cpu().numpy()
+            return [np.vstack([np.arange(it[i] + 1, dtype=float)[None, :], tab[i, :it[i] + 1, :].T]) for i in range(self.B)]
         raise NotImplementedError(f"get_stats({field!r})")
 
     def get_residuals(self):
@@ -290,14 +372,29 @@ class SolverView:
         setter(cur)
 
     def set(self, stage, field, value):
-        if field in ("lbx", "ubx"):
-            if stage != 0:
-                raise NotImplementedError("only the stage-0 state bounds (= the initial-state constraint) can be set")
-            self._row_update("z", value, 0, self.batch.engine.set_state)
-        elif field in ("x", "u", "pi"):
+        if field in ("x", "u", "pi"):
             self._row_update(field, value, stage, lambda a: self.batch.engine.set(field, a, stage=stage))
+        elif field == "yref":
+            self.cost_set(stage, field, value)
+        elif field in ("lbx", "ubx", "lbu", "ubu"):
+            self.constraints_set(stage, field, value)
         else:
             raise NotImplementedError(f"set(..., {field!r})")
+        self.batch._stats = None
+
+    def cost_set(self, stage, field, value):
+        if field != "yref":
+            raise NotImplementedError("cost_set on one instance of a batch: 'yref' (W is set for the whole batch)")
+        self._row_update("yref", value, stage, lambda a: self.batch.engine.set("yref", a, stage=stage))
+        self.batch._stats = None
+
+    def constraints_set(self, stage, field, value):
+        if field in ("lbx", "ubx") and stage == 0:
+            self._row_update("z", value, 0, self.batch.engine.set_state)
+        elif field in ("lbx", "ubx", "lbu", "ubu"):
+            self._row_update(field, value, stage, lambda a: self.batch.engine.set(field, a, stage=stage))
+        else:
+            raise NotImplementedError(f"constraints_set(..., {field!r})")
         self.batch._stats = None
 
     def options_set(self, field, value):
@@ -310,8 +407,10 @@ class SolverView:
         return self.batch.get(stage, field)[self.i]
 
     def get_stats(self, field):
+        if field in ("stat_m", "stat_n"):
+            return self.batch.get_stats(field)
         v = self.batch.get_stats(field)[self.i]
-        return v if field == "statistics" else v.item()
+        return v if isinstance(v, np.ndarray) and v.ndim > 0 else (v.item() if hasattr(v, "item") else v)
 
     def get_residuals(self):
         return self.batch.get_residuals()[self.i]

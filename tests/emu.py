@@ -22,7 +22,7 @@ def closed_loop(par, z0, N, solver_type, nsteps, dt=0.01, seed=1, max_iter=100, 
     D = Dims(B, N, solver_type, max_iter, qp_iter_max, (C.c_double * 4)(tol, tol, tol, tol), qp_tol, dt, dt)
     par = np.ascontiguousarray(par, np.float64)
     z0 = np.ascontiguousarray(z0, np.float64)
-    out = dict(z=np.zeros((B, nsteps + 1, 12)), u=np.zeros((B, nsteps, 6)), slog=np.zeros((B, nsteps, 12)),
+    out = dict(z=np.zeros((B, nsteps + 1, 12)), u=np.zeros((B, nsteps, 6)), slog=np.zeros((B, nsteps, 20)),
                summary=np.zeros((B, 20)), flags=np.zeros((B, 4), np.int32))
     dp = C.POINTER(C.c_double)
     pe = None

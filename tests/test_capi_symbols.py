@@ -59,3 +59,15 @@ def test_bad_arguments(built):
     d.B, d.solver_type = 2, 7
     assert lib.rmpc_create(C.byref(d), 0, 0, C.byref(h)) == -1
     assert lib.rmpc_create(None, 0, 0, C.byref(h)) == -1
+
+
+def test_field_layouts_match_public_header():
+    """robotic-mpc_b200/params.py mirrors the enums of include/rmpc_fields.h (the layouts a C caller fills)."""
+    import robotic_mpc_b200.params as pm
+
+    hdr = (ROOT / "include" / "rmpc_fields.h").read_text()
+    vals = {m.group(1): int(m.group(2)) for m in re.finditer(r"\b(R[PTLKSEQ]_[A-Z0-9_]+)\s*=\s*(\d+)", hdr)}
+    for prefix, table in (("RP", pm.RP), ("RT", pm.RT), ("RL", pm.RL), ("RK", pm.RK), ("RS", pm.RS), ("RE", pm.RE), ("RQ", pm.RQ)):
+        for key, v in table.items():
+            assert vals[f"{prefix}_{key}"] == v, (prefix, key)
+    assert pm.pack_params(3, 0.01).shape == (3, vals["RP_COUNT"])

@@ -1,0 +1,194 @@
+"""The named cost / constraint fields of the C ABI (lbu, ubu, lbx, ubx, W_diag, yref, surf_coeffs, wcv) with an
+honoured `stage` argument, and the statistics / timing getters, through the reference's own solver-interface names
+(AcadosOcpSolver.set / cost_set / constraints_set / get_stats, T/acados_ocp_solver.py:1461-1661,1743-2035).  The checker is
+the compiled reference driven through ocp_nlp_cost_model_set / ocp_nlp_constraints_model_set (oracle/ref_driver.c:
+rmpc_ref_model_set).  Tolerance 1e-6 relative (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-6
+
+
+def relerr(a, b):
+    return float(np.abs(np.asarray(a) - np.asarray(b)).max() / max(np.abs(b).max(), 1e-300))
+
+
+def _inputs(o, B, seed):
+    rng = np.random.default_rng(seed)
+    surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal((B, 6))
+    z0 = np.concatenate([o.README_Q0 + rng.uniform(-0.05, 0.05, (B, 6)), o.README_QD0 + rng.uniform(-0.1, 0.1, (B, 6))], 1)
+    return surf, z0
+
+
+def _need_ref(o):
+    if not o.REF_SO.exists():
+        pytest.skip("needs the compiled reference (oracle/_ref)")
+
+
+class _Model:
+    Ts = 0.01
+    Wcv = np.full(6, 200.0)
+    translation = (0.0, 0.0, 0.1)
+
+
+def _mpcs(rm, surf, z0, N, solver):
+    from robotic_mpc_b200.surface import Surface
+
+    qd = np.array([2.16, 2.16, np.pi, 3.20, 3.20, 3.20])
+    out = []
+    for i in range(len(z0)):
+        s = Surface(coefficients=dict(zip("abcdef", surf[i])))
+        m = rm.MPC(s, z0[i], _Model(), N, N * 0.01, -2 * np.pi * np.ones(6), 2 * np.pi * np.ones(6), -qd, qd, 0.01, 0.02, px_ref=0.40,
+                   vy_ref=0.05)
+        m.ocp.solver_options.nlp_solver_type = solver
+        out.append(m)
+    return out
+
+
+@pytest.mark.parametrize("solver", ["SQP_RTI", "SQP"])
+def test_stage_yref_and_bounds_mid_loop_match_reference(oracle, solver):
+    """An externally driven loop that, between two solves, changes `yref` at single stages (a time-varying reference), then
+    tightens `ubu` at one stage and `lbx` / `ubx` on q at another -- through BatchedSolver.cost_set / constraints_set / set --
+    against the compiled reference doing the same through ocp_nlp_cost_model_set / ocp_nlp_constraints_model_set."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    _need_ref(o)
+    B, N, ns = 6, 20, 8
+    surf, z0 = _inputs(o, B, 31)
+    bs = rm.BatchedSolver(_mpcs(rm, surf, z0, N, solver))
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    refs = [o.RefSolver(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i]) for i in range(B)]
+    model = o.Model(refs[0].lib)
+    z = z0.copy()
+    wcv = np.full(6, 200.0)
+    yref = np.zeros(18)
+    yref[1], yref[3], yref[4] = 1.0, 0.40, 0.05
+    worst = 0.0
+    for k in range(ns):
+        if k == 2:  # a different px / vy reference on the second half of the horizon, stage by stage; one u reference
+            for s in range(N // 2, N):
+                y = yref.copy()
+                y[3], y[4] = 0.40 + 0.002 * (s - N // 2), 0.03
+                if s == N - 3:
+                    y[5 + 1] = 0.3
+                bs.cost_set(s, "yref", y)
+                for r in refs:
+                    r.model_set(s, "yref", y)
+        if k == 4:  # per-stage bounds: u of stage 1 capped, q box of stage 5 tightened around the current iterate
+            ub = np.array([2.16, 1.2, np.pi, 3.20, 3.20, 3.20])
+            bs.constraints_set(1, "ubu", ub)
+            x5 = bs.get(5, "x")[:, :6]
+            bs.set(5, "lbx", x5 - 0.01)
+            bs.constraints_set(5, "ubx", x5 + 0.01)
+            for i, r in enumerate(refs):
+                r.model_set(1, "ubu", ub)
+                r.model_set(5, "lbx", x5[i] - 0.01)
+                r.model_set(5, "ubx", x5[i] + 0.01)
+        bs.set(0, "lbx", z)
+        bs.set(0, "ubx", z)
+        status = bs.solve()
+        u = bs.get(0, "u")
+        for i, r in enumerate(refs):
+            g = r.step(z[i])
+            assert status[i] == g["status"], (k, i, status[i], g["status"])
+            assert relerr(u[i], g["u"]) < RTOL, (k, i, relerr(u[i], g["u"]))
+            assert bs.get_stats("sqp_iter")[i] == g["sqp_iter"] and bs.get_stats("qp_iter")[i] == g["qp_iter"], (k, i)
+            assert abs(bs.get_cost()[i] - g["cost"]) <= RTOL * abs(g["cost"])
+            worst = max(worst, relerr(u[i], g["u"]))
+            z[i] = model.plant_rk4(wcv, 0.01, z[i], g["u"])
+    xr, ur, _ = refs[0].iterate()
+    assert relerr(bs.get(N, "x")[0], xr[N]) < RTOL and relerr(bs.get(N // 2, "u")[0], ur[N // 2]) < RTOL
+    # the setters are visible through the getters; stage -1 (every stage) resets the per-stage overrides of that field
+    assert np.allclose(bs.engine.get("yref", stage=N - 3).cpu().numpy()[:, 6], 0.3)
+    bs.engine.set("yref", np.broadcast_to(yref, (B, 18)), stage=-1)
+    assert np.array_equal(bs.engine.get("yref", stage=N - 3).cpu().numpy(), np.broadcast_to(yref, (B, 18)))
+    assert np.allclose(bs.engine.get("ubu", stage=1).cpu().numpy()[:, 1], 1.2)
+    for r in refs:
+        r.close()
+    print(f"per-stage setters, {solver}: worst relative deviation of u0 {worst:.2e}")
+
+
+def test_per_instance_named_fields_equal_the_parameter_block(oracle):
+    """W_diag / surf_coeffs / wcv / lbu / ubu / lbx / ubx / yref with stage = -1 write the same parameter block pack_params
+    builds (bit for bit, incl. the exact-ZOH coefficients libm's exp gives), and a closed loop run after them is identical."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 8, 12, 6
+    surf, z0 = _inputs(o, B, 5)
+    rng = np.random.default_rng(9)
+    wcv = 200.0 + 20.0 * rng.standard_normal((B, 6))
+    w_u, w_q = 0.01 * (1 + rng.uniform(0, 1, (B, 6))), 0.02 * (1 + rng.uniform(0, 1, (B, 6)))
+    qd = np.array([2.0, 2.0, 3.0, 3.1, 3.1, 3.1])
+    par = rm.pack_params(B, 0.01, surf=surf, wcv=wcv, w_u=w_u, w_qddot=w_q, px_ref=0.41, vy_ref=0.04, w_task=[50, 40, 30, 20, 60],
+                         q_min=-3.0, q_max=3.0, qdot_min=-qd, qdot_max=qd)
+    a = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=ns)
+    a.set_params(par)
+    b = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=ns)
+    b.set_params(rm.pack_params(B, 0.01))
+    W = np.zeros((B, 18))
+    W[:, :5], W[:, 5:11], W[:, 11:17] = [50, 40, 30, 20, 60], 2 * w_u, w_q
+    y = np.zeros((B, 18))
+    y[:, 1], y[:, 3], y[:, 4] = 1.0, 0.41, 0.04
+    b.set("W_diag", W, stage=-1)
+    b.set("surf_coeffs", surf, stage=-1)
+    b.set("wcv", wcv, stage=-1)
+    b.set("yref", y, stage=-1)
+    b.set("lbu", np.broadcast_to(-qd, (B, 6)), stage=-1)
+    b.set("ubu", np.broadcast_to(qd, (B, 6)), stage=-1)
+    b.set("lbx", np.full((B, 6), -3.0), stage=-1)
+    b.set("ubx", np.full((B, 6), 3.0), stage=-1)
+    assert np.array_equal(b.get("par").cpu().numpy(), par)
+    for e in (a, b):
+        e.set_state(z0)
+        e.reset()
+        e.closed_loop(ns)
+    assert np.array_equal(a.get("ulog").cpu().numpy(), b.get("ulog").cpu().numpy())
+    with pytest.raises(rm.RmpcError):
+        b.set("W_diag", W, stage=3)  # per instance, not per stage
+    with pytest.raises(rm.RmpcError):
+        b.set("yref", y, stage=N)  # stage N has no cost
+    a.close()
+    b.close()
+
+
+def test_statistics_table_and_timers_match_acados_layout(oracle):
+    """get_stats('statistics') has acados' layout and values (row 0 iteration index; SQP: res_stat, res_eq, res_ineq,
+    res_comp, qp_stat, qp_iter, alpha per iteration; SQP_RTI: qp_stat, qp_iter), and the device timers split time_tot the way
+    acados splits its own: time_lin + time_qp + time_glob <= time_tot, time_qp = time_qp_solver_call + time_qp_xcond."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    _need_ref(o)
+    B, N = 4, 20
+    surf, z0 = _inputs(o, B, 12)
+    for solver, st in (("SQP", o.SQP), ("SQP_RTI", o.SQP_RTI)):
+        bs = rm.BatchedSolver(_mpcs(rm, surf, z0, N, solver))
+        bs.set(0, "lbx", z0)
+        bs.solve()
+        tabs = bs.get_stats("statistics")
+        for i in range(B):
+            r = o.RefSolver(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i])
+            r.step(z0[i])
+            ref = r.statistics()
+            assert tabs[i].shape == ref.shape, (solver, tabs[i].shape, ref.shape)
+            assert np.array_equal(tabs[i][0], ref[0])
+            if solver == "SQP":
+                assert np.abs(tabs[i][1:5] - ref[1:5]).max() < 1e-8          # KKT residuals per iteration
+                assert np.array_equal(tabs[i][5:7], ref[5:7])                # qp_stat, qp_iter per iteration
+                assert np.abs(tabs[i][7] - ref[7]).max() < 1e-12             # accepted step lengths
+            else:
+                assert np.array_equal(tabs[i], ref)
+            r.close()
+        assert bs.get_stats("stat_n") == (7 if solver == "SQP" else 2)
+        view = bs.view(1)
+        assert np.array_equal(view.get_stats("statistics"), tabs[1])
+        t = {k: bs.get_stats(k) for k in ("time_tot", "time_lin", "time_qp", "time_glob", "time_qp_solver_call", "time_qp_xcond")}
+        ph = bs.get_stats("time_qp_phases")
+        assert np.all(t["time_tot"] > 0) and np.all(t["time_lin"] > 0) and np.all(t["time_qp"] > 0) and np.all(t["time_glob"] > 0)
+        assert np.all(t["time_lin"] + t["time_qp"] + t["time_glob"] <= t["time_tot"] * (1 + 1e-9) + 2e-6)
+        assert np.allclose(t["time_qp_solver_call"] + t["time_qp_xcond"], t["time_qp"])
+        assert np.all(ph > 0) and np.all(ph.sum(axis=1) <= t["time_qp"] * (1 + 1e-9) + 2e-6)
+        assert isinstance(view.get_stats("time_lin"), float) and bs.get_stats("time_sim").shape == (B,)

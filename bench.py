@@ -277,6 +277,68 @@ def fp64_peak_tflops(torch, dev):
     return 2.0 * n ** 3 / best / 1e12
 
 
+def instance_latency(rm, torch, par_d, z0_d, N, local, L):
+    """Per-INSTANCE solve latency and phase breakdown from the device timers of the step record (RL_TIME..., acados'
+    time_tot / time_lin / time_qp / time_glob measured per instance on the GPU's global timer), over L closed-loop steps of
+    the same workload on a second handle that keeps logs (the timed handle has none)."""
+    B = par_d.shape[0]
+    eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=L, device=local)
+    eng.set_params(par_d)
+    eng.set_state(z0_d)
+    eng.reset()
+    eng.closed_loop(L)
+    sl = eng.get("slog").cpu().numpy()
+    eng.close()
+    RL = rm.RL
+    t = sl[:, :, RL["TIME"]] * 1e3
+    tot = sl[:, :, RL["TIME"]].sum()
+    ph = {k: float(sl[:, :, RL[k]].sum() / tot) for k in ("TIME_LIN", "TIME_QP", "TIME_GLOB", "TIME_QP_FACT", "TIME_QP_FWD",
+                                                          "TIME_QP_BWD", "TIME_QP_RES", "TIME_XCOND")}
+    return {"p50": float(np.percentile(t, 50)), "p99": float(np.percentile(t, 99)), "max": float(t.max()), "mean": float(t.mean()),
+            "steps": L, "samples": int(t.size),
+            "what": "time_tot of ONE instance's solve inside the batched kernel (RL_TIME, GPU global timer), all instances x "
+                    f"the first {L} closed-loop steps",
+            "phase_fraction_of_time_tot": {"lin": ph["TIME_LIN"], "qp": ph["TIME_QP"], "glob": ph["TIME_GLOB"],
+                                           "qp_factorize": ph["TIME_QP_FACT"], "qp_forward": ph["TIME_QP_FWD"],
+                                           "qp_backward": ph["TIME_QP_BWD"], "qp_update_residuals": ph["TIME_QP_RES"],
+                                           "qp_xcond": ph["TIME_XCOND"]}}
+
+
+def external_loop(rm, torch, N, local, batches=(1, 64, 4096), steps=40):
+    """The EXTERNALLY driven loop (plant outside the GPU): every step x0 comes from host memory and u0 goes back to host
+    memory through rmpc_step_host (H2D x0 -> solve kernel -> D2H u0, one synchronisation per step), as a captured CUDA graph
+    and as plain enqueues.  The x0 sequence is the state log of the on-device closed loop of the same instances, so the solver
+    sees what a real plant would send; the returned controls are checked against the on-device loop's."""
+    out = []
+    for B in batches:
+        surf, z0 = make_workload(B, 91)
+        par = rm.pack_params(B, 0.01, surf=surf)
+        eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=steps, device=local)
+        eng.set_params(par)
+        eng.set_state(z0)
+        eng.reset()
+        eng.closed_loop(steps)
+        zlog = np.ascontiguousarray(eng.get("zlog").cpu().numpy().transpose(1, 0, 2))
+        ulog = eng.get("ulog").cpu().numpy()
+        for graph in (1, 0):
+            eng.set_option("graph", graph)
+            eng.set_state(z0)
+            eng.reset()
+            u = np.empty((B, 6))
+            ts, same = [], True
+            for k in range(steps):
+                t0 = time.perf_counter()
+                eng.step_host(zlog[k], u)
+                ts.append(time.perf_counter() - t0)
+                same = same and bool(np.array_equal(u, ulog[:, k]))
+            ts = np.array(ts[3:]) * 1e3
+            out.append({"B": B, "graph": bool(graph), "ms_p50": float(np.percentile(ts, 50)), "ms_p99": float(np.percentile(ts, 99)),
+                        "mpc_steps_per_s": float(B / (ts.mean() * 1e-3)), "h2d_bytes_per_step": B * 96, "d2h_bytes_per_step": B * 48,
+                        "u0_equals_on_device_loop": same})
+        eng.close()
+    return out
+
+
 def run_gpu(args):
     import torch
     import robotic_mpc_b200 as rm
@@ -290,6 +352,10 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     B, N, K, Wm = args.batch, args.horizon, args.steps, args.warmup
+    if args.scaling == "strong":  # total work fixed: the batch is split across the ranks
+        if B % world:
+            raise SystemExit(f"--scaling strong needs --batch ({B}) divisible by the number of GPUs ({world})")
+        B //= world
     surf, z0 = make_workload(B, 44 + rank)
     par = rm.pack_params(B, 0.01, surf=surf)
     eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=0, device=local)
@@ -317,13 +383,17 @@ def run_gpu(args):
     launches = eng.launch_count - launches0
     t_ms = ev[0].elapsed_time(ev[K])
     per_step = np.array([ev[k].elapsed_time(ev[k + 1]) for k in range(K)])
+    summ = eng.get("summary")
+    mine = torch.tensor([t_ms, float(summ[:, rm.RS["QP_ITERS"]].sum()), float(summ[:, rm.RS["NFAIL"]].sum())], dtype=torch.float64,
+                        device=dev)
+    per_rank = mine[None, :]
     if world > 1:
         dist.barrier()
-        t = torch.tensor([t_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_ms = float(t.item())
+        per_rank = torch.empty((world, 3), dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(per_rank, mine[None, :].contiguous())
+    per_rank = per_rank.cpu().numpy()
+    t_ms = float(per_rank[:, 0].max())
     clocks = sampler.stop() if sampler else None
-    summ = eng.get("summary")
     gather_ms = None
     if world > 1:
         # the only collective of the path: gather the per-instance result summaries (NCCL over NVLink)
@@ -375,18 +445,26 @@ def run_gpu(args):
         cb = None
         if not args.no_cpu_baseline and world == 1:  # reported at N = 1 only; multi-GPU runs carry cpu_baseline = null
             cb, _, _ = cpu_leg(N, 3, K)
+        inst_lat = instance_latency(rm, torch, par_d, z0_d, N, local, min(K, 40))
+        ext = None
+        if world == 1 and not args.no_external:
+            ext = external_loop(rm, torch, N, local, batches=sorted({1, 64, B}))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
-            "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": t_ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"BASELINE configs[2]: {B} random surfaces per GPU, UR10 N={N} SQP_RTI, closed loop "
+            "config": {"workload": f"BASELINE configs[2]: {B} random surfaces per GPU ({args.scaling} scaling), UR10 N={N} SQP_RTI, closed loop "
                                    f"of {K} steps from the initial state (a step = one MPC step of all {B} instances)",
                        "batch_per_gpu": B, "horizon": N, "solver": "SQP_RTI", "dt": 0.01,
                        "l2": f"working set {eng.device_bytes / 2**30:.2f} GiB per GPU, far larger than the 126 MB L2 "
                              "(inputs larger than L2, no flush needed)",
                        "e2e_note": "h2d/d2h bytes are per job (K steps) divided by K"},
             "latency_ms": {"p50": float(np.percentile(per_step, 50)), "p99": float(np.percentile(per_step, 99)),
-                           "max": float(per_step.max()), "what": "one batched MPC step (all instances), CUDA events"},
+                           "max": float(per_step.max()), "what": "one batched MPC step (all instances of rank 0), CUDA events"},
+            "instance_latency_ms": inst_lat,
+            "per_rank": {"t_ms": [float(v) for v in per_rank[:, 0]], "qp_iters_per_mpc_step": [float(v) / (B * K) for v in per_rank[:, 1]],
+                         "solver_failures": [int(v) for v in per_rank[:, 2]]},
+            "external_loop": ext,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d / K, "d2h_bytes_per_step": d2h / K,
                     "seconds": e2e_s},
             "gpu_launches": int(launches),
@@ -423,6 +501,9 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--horizon", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-external", action="store_true", help="skip the externally driven loop measurement (rmpc_step_host)")
+    ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
+                    help="weak: --batch instances PER GPU (default); strong: --batch instances in total, split across the GPUs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -76,6 +76,7 @@ int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
  *                    loop `for i < N-1: solver.set(i,'x',solver.get(i+1,'x')); solver.set(i,'u',solver.get(i+1,'u'));
  *                    solver.set(N-1,'x',solver.get(N,'x'))` an acados MPC runs between two solves.  Default 0: the reference's
  *                    loop keeps the unshifted iterate (R/simulator.py:199-241).
+ *   "graph"  0 | 1   rmpc_step_host replays a captured CUDA graph (default 1) or enqueues copy, kernel, copy one by one
  *   "statistics" 0 | 1  keep the per-iteration statistics table of the last full-SQP solve (rmpc_get "sqp_stat"). */
 int rmpc_set_option(rmpc_handle *h, const char *name, double value);
 
@@ -180,11 +181,19 @@ int rmpc_get(rmpc_handle *h, const char *field, int stage, double *dev, void *st
 /* Number of closed-loop steps taken since create / reset. */
 int rmpc_steps_done(const rmpc_handle *h);
 
-/* Host-buffer convenience used for end-to-end measurements: upload par [B][72] and z0 [B][12] from host memory,
+/* Host-buffer convenience used for end-to-end measurements: upload par [B][RP_COUNT] and z0 [B][12] from host memory,
  * reset, run nsteps closed-loop steps, download the summary [B][20] and the last applied control [B][6] to host
  * memory; synchronises the stream before returning.  Any output pointer may be NULL. */
 int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host, int nsteps, double *summary_host,
                   double *u_last_host, void *stream);
+
+/* One step of an EXTERNALLY driven MPC loop with host buffers -- the reference's per-step sequence
+ *     solver.set(0,'lbx',x); solver.set(0,'ubx',x); status = solver.solve(); u = solver.get(0,'u')      R/simulator.py:209-217
+ * for the whole batch in one call: copy x0 [B][12] from host memory, solve, copy u0 [B][6] (and, when stats_host is not
+ * NULL and the handle has nlog > 0, the step record [B][RL_COUNT]) back to host memory; synchronises the stream before
+ * returning.  The plant is the caller's (the on-device plant does not advance).  The copy-solve-copy sequence is captured
+ * once into a CUDA graph and replayed (rmpc_set_option "graph" 0 turns that off); stream NULL = a stream owned by the handle. */
+int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_host, double *stats_host, void *stream);
 
 /* Kernels launched by this handle so far (for bench accounting). */
 long long rmpc_launch_count(const rmpc_handle *h);

@@ -141,6 +141,15 @@ struct rmpc_handle
     double *pe_dev; /* [B][RE_COUNT] terminal-set blocks, allocated by the first "P_e" / "alpha_e" / "lh_e" / "term" set */
     double *stg_dev; /* [B][N][RT_COUNT] per-stage references and bounds, allocated by the first per-stage (stage >= 0) set */
     double *sqpstat_dev; /* [B][max_iter + 2][RQ_COUNT], allocated by rmpc_set_option("statistics", 1) */
+    /* rmpc_step_host: pinned staging of x0 / u0 / step record, the stream used when the caller passes NULL (a captured
+     * sequence cannot live on the legacy stream), and the instantiated graph with the launch arguments it was captured with */
+    double *pin_z = nullptr, *pin_u = nullptr, *pin_st = nullptr;
+    cudaStream_t own_stream = nullptr;
+    cudaGraphExec_t gexec = nullptr;
+    cudaStream_t gstream = nullptr;
+    RmpcWs gW;
+    RmpcDims gD;
+    int use_graph = 1;
     std::string err;
 };
 
@@ -193,6 +202,11 @@ extern "C" int rmpc_destroy(rmpc_handle *h)
     if (!h) return 0;
     DeviceGuard g(h->device);
     for (void *p : h->owned) cudaFree(p);
+    if (h->gexec) cudaGraphExecDestroy(h->gexec);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    if (h->pin_z) cudaFreeHost(h->pin_z);
+    if (h->pin_u) cudaFreeHost(h->pin_u);
+    if (h->pin_st) cudaFreeHost(h->pin_st);
     delete h;
     return 0;
 }
@@ -276,6 +290,12 @@ extern "C" int rmpc_set_option(rmpc_handle *h, const char *name, double value)
     {
         if (value != 0.0 && value != 1.0) return fail(h, RMPC_EINVAL, "rmpc_set_option: shift must be 0 or 1");
         h->W.shift = (int) value;
+        return 0;
+    }
+    if (f == "graph")
+    {
+        if (value != 0.0 && value != 1.0) return fail(h, RMPC_EINVAL, "rmpc_set_option: graph must be 0 or 1");
+        h->use_graph = (int) value;
         return 0;
     }
     if (f == "statistics")
@@ -716,5 +736,79 @@ extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const doubl
                              sizeof(double) * 6, B, cudaMemcpyDeviceToHost, s));
     }
     CU(cudaStreamSynchronize(s));
+    return 0;
+}
+
+/* H2D x0 -> one solve -> D2H u0 (+ step record) on stream s, from / to the handle's pinned staging buffers */
+static int step_host_enqueue(rmpc_handle *h, cudaStream_t s)
+{
+    const size_t B = (size_t) h->D.B;
+    CU(cudaMemcpyAsync(h->W.z, h->pin_z, sizeof(double) * B * NX, cudaMemcpyHostToDevice, s));
+    int rc = launch_loop(h, 1, 0, s);
+    if (rc) return rc;
+    CU(cudaMemcpy2DAsync(h->pin_u, sizeof(double) * 6, h->W.slab + rmpc_slab_off(h->D.N, RC_ux, NV, 0), sizeof(double) * h->W.slab_stride,
+                         sizeof(double) * 6, B, cudaMemcpyDeviceToHost, s));
+    if (h->nlog > 0 && h->steps_done < h->nlog)
+        CU(cudaMemcpy2DAsync(h->pin_st, sizeof(double) * RL_COUNT, h->W.slog + (size_t) h->steps_done * RL_COUNT,
+                             sizeof(double) * h->nlog * RL_COUNT, sizeof(double) * RL_COUNT, B, cudaMemcpyDeviceToHost, s));
+    return 0;
+}
+
+static void step_graph_drop(rmpc_handle *h)
+{
+    if (h->gexec) cudaGraphExecDestroy(h->gexec);
+    h->gexec = nullptr;
+}
+
+extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_host, double *stats_host, void *stream)
+{
+    if (!h || !x0_host || !u0_host) return fail(h, RMPC_EINVAL, "rmpc_step_host: null argument");
+    if (stats_host && !(h->nlog > 0 && h->steps_done < h->nlog))
+        return fail(h, RMPC_EINVAL, "rmpc_step_host: the step record needs a handle created with nlog > 0");
+    ON_DEVICE(h);
+    const size_t B = (size_t) h->D.B;
+    if (!h->pin_z)
+    {
+        CU(cudaHostAlloc((void **) &h->pin_z, sizeof(double) * B * NX, cudaHostAllocDefault));
+        CU(cudaHostAlloc((void **) &h->pin_u, sizeof(double) * B * 6, cudaHostAllocDefault));
+        CU(cudaHostAlloc((void **) &h->pin_st, sizeof(double) * B * RL_COUNT, cudaHostAllocDefault));
+        CU(cudaStreamCreate(&h->own_stream));
+    }
+    cudaStream_t s = stream ? (cudaStream_t) stream : h->own_stream;
+    std::memcpy(h->pin_z, x0_host, sizeof(double) * B * NX);
+    h->W.rti_phase = 0;
+    h->W.step0 = h->steps_done;
+    if (h->use_graph)
+    {
+        /* the captured sequence is valid as long as the launch arguments are the ones it was captured with */
+        if (h->gexec && (h->gstream != s || std::memcmp(&h->gW, &h->W, sizeof(RmpcWs)) != 0 || std::memcmp(&h->gD, &h->D, sizeof(RmpcDims)) != 0))
+            step_graph_drop(h);
+        if (!h->gexec)
+        {
+            cudaGraph_t g = nullptr;
+            CU(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+            int rc = step_host_enqueue(h, s);
+            cudaError_t e = cudaStreamEndCapture(s, &g);
+            if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+            if (e != cudaSuccess) return fail(h, RMPC_ECUDA, std::string("rmpc_step_host: cudaStreamEndCapture: ") + cudaGetErrorString(e));
+            e = cudaGraphInstantiate(&h->gexec, g, 0);
+            cudaGraphDestroy(g);
+            if (e != cudaSuccess) { h->gexec = nullptr; return fail(h, RMPC_ECUDA, std::string("rmpc_step_host: cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
+            std::memcpy(&h->gW, &h->W, sizeof(RmpcWs));
+            std::memcpy(&h->gD, &h->D, sizeof(RmpcDims));
+            h->gstream = s;
+        }
+        else
+            h->launches++; /* the capture counted its own launch */
+        CU(cudaGraphLaunch(h->gexec, s));
+    }
+    else
+    {
+        int rc = step_host_enqueue(h, s);
+        if (rc) return rc;
+    }
+    CU(cudaStreamSynchronize(s));
+    std::memcpy(u0_host, h->pin_u, sizeof(double) * B * 6);
+    if (stats_host) std::memcpy(stats_host, h->pin_st, sizeof(double) * B * RL_COUNT);
     return 0;
 }

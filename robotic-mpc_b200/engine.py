@@ -59,6 +59,7 @@ def load_library() -> C.CDLL:
     lib.rmpc_get.argtypes = [vp, cp, ip, dp, vp]
     lib.rmpc_steps_done.argtypes = [vp]
     lib.rmpc_run_host.argtypes = [vp, dp, dp, ip, dp, dp, vp]
+    lib.rmpc_step_host.argtypes = [vp, dp, dp, dp, vp]
     lib.rmpc_launch_count.argtypes = [vp]
     lib.rmpc_launch_count.restype = C.c_longlong
     _lib = lib
@@ -68,7 +69,7 @@ def load_library() -> C.CDLL:
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
                     "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
                     "rmpc_launch_count", "rmpc_set_chain", "rmpc_set_option", "rmpc_state_size",
-                    "rmpc_store_state", "rmpc_load_state"]
+                    "rmpc_store_state", "rmpc_load_state", "rmpc_step_host"]
 
 
 class RmpcError(RuntimeError):
@@ -195,7 +196,8 @@ class Engine:
 
     def set_option(self, name, value):
         """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step;
-        'statistics' (0 | 1) = keep the per-iteration table of the last full-SQP solve (``get('sqp_stat')``)."""
+        'statistics' (0 | 1) = keep the per-iteration table of the last full-SQP solve (``get('sqp_stat')``); 'graph' (0 | 1) =
+        ``step_host`` replays a captured CUDA graph (default) or enqueues its copies and kernel one by one."""
         self._check(self.lib.rmpc_set_option(self.h, str(name).encode(), float(value)), f"rmpc_set_option({name})")
 
     def set_chain(self, xyzR=None, axis=None):
@@ -237,6 +239,24 @@ class Engine:
                                            u.ctypes.data_as(C.c_void_p) if want_u else None, self._stream()),
                     "rmpc_run_host")
         return summ, u
+
+    def step_host(self, x0, u0=None, stats=None, stream=False):
+        """One step of an externally driven loop with host buffers: x0 [B, 12] in, u0 [B, 6] (and, with ``stats`` [B, RL_COUNT]
+        and nlog > 0, the step record) out -- ``solver.set(0,'lbx',x); solver.set(0,'ubx',x); solver.solve();
+        solver.get(0,'u')`` of R/simulator.py:209-217 for the batch in one call.  ``u0`` / ``stats`` are filled in place when
+        given (float64, C-contiguous); returns u0.  ``stream=True`` uses torch's current stream instead of the handle's own."""
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        if x0.shape != (self.B, 12):
+            raise ValueError(f"expected shape {(self.B, 12)}, got {x0.shape}")
+        if u0 is None:
+            u0 = np.empty((self.B, 6))
+        for a, shp in ((u0, (self.B, 6)), (stats, (self.B, RL["COUNT"]))):
+            if a is not None and not (a.dtype == np.float64 and a.flags.c_contiguous and a.shape == shp):
+                raise ValueError(f"output buffer must be a C-contiguous float64 array of shape {shp}")
+        self._check(self.lib.rmpc_step_host(self.h, x0.ctypes.data_as(C.c_void_p), u0.ctypes.data_as(C.c_void_p),
+                                            stats.ctypes.data_as(C.c_void_p) if stats is not None else None,
+                                            self._stream() if stream else None), "rmpc_step_host")
+        return u0
 
     # ------------------------------------------------------------------ getters
     def get(self, field, stage=0):

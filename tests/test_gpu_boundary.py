@@ -192,3 +192,53 @@ def test_statistics_table_and_timers_match_acados_layout(oracle):
         assert np.allclose(t["time_qp_solver_call"] + t["time_qp_xcond"], t["time_qp"])
         assert np.all(ph > 0) and np.all(ph.sum(axis=1) <= t["time_qp"] * (1 + 1e-9) + 2e-6)
         assert isinstance(view.get_stats("time_lin"), float) and bs.get_stats("time_sim").shape == (B,)
+
+
+@pytest.mark.parametrize("graph", [1, 0])
+def test_step_host_equals_set_solve_get(oracle, graph):
+    """rmpc_step_host (host x0 in, host u0 + step record out, CUDA-graph replay or plain enqueue) gives bit for bit what the
+    set('z') / solve() / get('u', 0) sequence gives, in an externally driven loop whose plant runs on the host; changing a
+    per-stage reference in between (new launch arguments) re-captures the graph."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 5, 16, 6
+    surf, z0 = _inputs(o, B, 77)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    a = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=1)
+    b = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=1)
+    b.set_option("graph", graph)
+    for e in (a, b):
+        e.set_params(par)
+        e.set_state(z0)
+        e.reset()
+    model = o.Model(o.PortLeg().lib)
+    z = z0.copy()
+    u = np.empty((B, 6))
+    st = np.empty((B, rm.RL["COUNT"]))
+    for k in range(ns):
+        if k == 3:
+            y = np.zeros((B, 18))
+            y[:, 1], y[:, 3], y[:, 4] = 1.0, 0.42, 0.03
+            for e in (a, b):
+                e.set("yref", y, stage=N - 2)
+        a.set_state(z)
+        a.solve()
+        ua = a.get("u", 0).cpu().numpy()
+        sa = a.get("stats").cpu().numpy()
+        n0 = b.launch_count
+        assert b.step_host(z, u, st) is u
+        assert b.launch_count - n0 == 1  # one solve kernel per step, captured or not
+        assert np.array_equal(u, ua), k
+        tcols = slice(rm.RL["TIME"], rm.RL["TIME_XCOND"] + 1)
+        sa[:, tcols] = st[:, tcols] = 0.0  # device times differ from run to run
+        assert np.array_equal(st, sa), k
+        for i in range(B):
+            z[i] = model.plant_rk4(np.full(6, 200.0), 0.01, z[i], u[i])
+    with pytest.raises(ValueError):
+        b.step_host(z[:2])
+    c = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=0)
+    with pytest.raises(rm.RmpcError):
+        c.step_host(z, u, st)  # the step record needs nlog > 0
+    for e in (a, b, c):
+        e.close()

@@ -812,3 +812,19 @@ extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_
     if (stats_host) std::memcpy(stats_host, h->pin_st, sizeof(double) * B * RL_COUNT);
     return 0;
 }
+
+#ifdef RMPC_SECPROF
+/* experiments only (-DRMPC_SECPROF builds): cycles per code section of the sweeps, see SECPROF_* in rmpc_device.cuh */
+extern "C" int rmpc_debug_secprof(double *out64, int clear)
+{
+    unsigned long long v[64];
+    if (cudaMemcpyFromSymbol(v, rmpc_secprof, sizeof(v)) != cudaSuccess) return RMPC_ECUDA;
+    for (int k = 0; k < 64; k++) out64[k] = (double) v[k];
+    if (clear)
+    {
+        memset(v, 0, sizeof(v));
+        if (cudaMemcpyToSymbol(rmpc_secprof, v, sizeof(v)) != cudaSuccess) return RMPC_ECUDA;
+    }
+    return 0;
+}
+#endif

@@ -119,9 +119,22 @@ RD double grp_max(double v)
     return v;
 }
 
+/* Section profiler of the sweeps (experiments only, -DRMPC_SECPROF): lane 0 of every group accumulates SM clock cycles per
+ * code section of a stage and adds them to rmpc_secprof[base + k] at the end of the sweep; read with rmpc_debug_secprof(). */
+#if defined(RMPC_SECPROF) && !defined(RMPC_EMU)
+__device__ unsigned long long rmpc_secprof[64];
+#define SECPROF_BEGIN long long sp_a[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, sp_t = clock64()
+#define SEC(k) do { const long long t_ = clock64(); sp_a[k] += t_ - sp_t; sp_t = t_; } while (0)
+#define SECPROF_END(base) do { if (rd_lane() == 0) for (int k_ = 0; k_ < 10; k_++) atomicAdd(&rmpc_secprof[(base) + k_], (unsigned long long) sp_a[k_]); } while (0)
+#else
+#define SECPROF_BEGIN do { } while (0)
+#define SEC(k) do { } while (0)
+#define SECPROF_END(base) do { } while (0)
+#endif
+
 /* ---------------------------------------------------------------------------------------------- shared memory
  * one block per group (instance).  `buf` is carved per sweep:
- *   factorisation : P+ (12 x SM_PS) | Lxu (72) | Muu in (28) | L out (34) | two staging buffers of FS_STGN doubles
+ *   factorisation : P+ (12 x SM_PS) | Lxu (72) | Muu in (28) | (36 free) | two staging buffers of FS_STGN doubles
  *   forward / backward substitution : two staging buffers of SW_STGN doubles
  * The staging buffers are filled one stage AHEAD by cp.async (LDGSTS), so that inside a stage every operand comes from
  * shared memory and the HBM / L2 latency of the streamed factors and residuals is off the critical path. */
@@ -146,7 +159,6 @@ struct GrpSmem
 #define FS_P(sm) ((sm).buf)         /* cost-to-go matrix of stage ss+1, full symmetric, state order [q; qd] */
 #define FS_LXU(sm) ((sm).buf + 168) /* Lxu of the current stage (for the Schur complement) */
 #define FS_MIN(sm) ((sm).buf + 240) /* lower 6x6 block Muu (21) + m_u (6) */
-#define FS_LOUT(sm) ((sm).buf + 268) /* L (21, packed with diagonal) + l_u (6) + 1/diag (6) */
 #define FS_STGN 164
 #define FS_STG(sm, k) ((sm).buf + 304 + (k) * FS_STGN)
 #define SW_STGN 376
@@ -1194,6 +1206,14 @@ RD void fac_stage_in(const Inst &I, double *dst, int ss)
     if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
 }
 
+/* Shape of the stage body: every section LOADS its operands into registers first, computes, and STORES last, and the lanes
+ * run one straight-line instruction stream (roles differ by coefficients, ca / cb / jcol, not by branches) -- shared-memory
+ * stores in the middle of a section and divergent blocks both stop the compiler from batching the loads, and a stage then
+ * costs one shared-memory round trip per operand (measured: 8650 cycles per stage for one warp alone, profiles/r2k_*).
+ * Three group barriers per stage:
+ *   S1  [P+, p+ of the previous stage, staged operands]  barrier terms, P+ b, Muu row, m_u, row of [B A]' P+ [B A] + H  -> Min
+ *   S2  own Mxx row -> P (the row of P+ is dead now); 6 x 6 Cholesky in every lane; Lxu row, p                        -> Lxu, pv
+ *   S3  own row: P = Mxx - Lxu Lxu'                                                                                  -> P, F  */
 RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
@@ -1203,7 +1223,8 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     const int j = R.j, xk = R.xk;
     const StageConst sc = stage_const(par, D.dt, j);
     const double reg = 1e-15, tau_min = 1e-16;
-    double *P = FS_P(sm), *Lxu = FS_LXU(sm), *Min = FS_MIN(sm), *Lo = FS_LOUT(sm);
+    double *P = FS_P(sm), *Lxu = FS_LXU(sm), *Min = FS_MIN(sm);
+    const int slot = lane < 12 ? lane : lane - 12; /* bound slot of the lane (lanes 12.. mirror lanes 0.., results unused) */
     fac_stage_in(I, FS_STG(sm, (N - 1) & 1), N - 1);
     rd_cp_commit();
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
@@ -1235,6 +1256,7 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
             if (c <= xk) FN[RF_P + (xk * (xk + 1)) / 2 + c] = Prow[c];
         FN[RF_PV + xk] = pv;
     }
+    SECPROF_BEGIN;
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
@@ -1242,186 +1264,241 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
         const double *G = FS_STG(sm, ss & 1);
         if (ss > 0) fac_stage_in(I, FS_STG(sm, (ss - 1) & 1), ss - 1);
         rd_cp_commit();
+        SEC(0);
         rd_cp_wait1();
         rd_sync();
-        /* (1) barrier terms of the bound slot owned by this lane (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
-        double Gam = 0.0, gam = 0.0;
-        if (lane < 12 && !(s0 && lane >= 6))
+        SEC(1);
+        /* ------------------------------------------------------------------------------------------------ S1 */
+        double pj[12], pd[12]; /* rows q_j and qd_j of P+ */
+        RD_UNROLL
+        for (int c = 0; c < 12; c += 2)
         {
-            const double *lam = G + FG_LAM, *t = G + FG_T, *rd = G + FG_RD, *rm = G + FG_RM;
-            const double til = 1.0 / t[lane], tiu = 1.0 / t[12 + lane];
-            Gam = til * lam[lane] + tiu * lam[12 + lane];
-            gam = til * ((rm[lane] - tau_min) - lam[lane] * rd[lane]) - tiu * ((rm[12 + lane] - tau_min) - lam[12 + lane] * rd[12 + lane]);
+            const rd_double2 a2 = *RD_CV2(&P[j * SM_PS + c]), b2v = *RD_CV2(&P[(6 + j) * SM_PS + c]);
+            pj[c] = a2.x; pj[c + 1] = a2.y; pd[c] = b2v.x; pd[c + 1] = b2v.y;
         }
-        /* (2) tv = P+ b + p+ ; P+ b is kept for the corrector solves */
-        if (R.x)
+        const double pvq = sm.pv[j], pvd = sm.pv[6 + j];
+        /* (1) barrier terms of the lane's bound slot (slot l: u_l for l < 6, q_{l-6} for 6 <= l < 12) */
+        const bool act = lane < 12 && !(s0 && lane >= 6);
+        double Gam, gam;
         {
-            double a = 0.0;
-            RD_UNROLL
-            for (int c = 0; c < 12; c += 2)
-            {
-                const rd_double2 pr = *reinterpret_cast<const rd_double2 *>(&P[xk * SM_PS + c]);
-                a += pr.x * G[FG_RB + c];
-                a += pr.y * G[FG_RB + c + 1];
-            }
-            F[RF_PB + xk] = a;
-            sm.tv[xk] = a + sm.pv[xk];
+            const double la = G[FG_LAM + slot], lb = G[FG_LAM + 12 + slot], ta = G[FG_T + slot], tb = G[FG_T + 12 + slot];
+            const double da = G[FG_RD + slot], db = G[FG_RD + 12 + slot], ma = G[FG_RM + slot], mb = G[FG_RM + 12 + slot];
+            const double til = 1.0 / (act ? ta : 1.0), tiu = 1.0 / (act ? tb : 1.0);
+            const double Gv = til * la + tiu * lb;
+            const double gv = til * ((ma - tau_min) - la * da) - tiu * ((mb - tau_min) - lb * db);
+            Gam = act ? Gv : 0.0;
+            gam = act ? gv : 0.0;
         }
-        rd_sync();
-        /* (3a) control rows: Muu row j and m_u */
-        if (R.u)
+        /* (2) tv = P+ b + p+ for both rows of the joint; P+ b of the own row is kept for the corrector solves */
+        double aq = 0.0, ad = 0.0;
+        RD_UNROLL
+        for (int c = 0; c < 12; c += 2)
         {
-            const double b1j = C_B1(j), b2j = C_B2(j);
-            RD_UNROLL
-            for (int c = 0; c < 6; c++)
-            {
-                const double eq = b1j * P[j * SM_PS + c] + b2j * P[(6 + j) * SM_PS + c];
-                const double ed = b1j * P[j * SM_PS + 6 + c] + b2j * P[(6 + j) * SM_PS + 6 + c];
-                double row = C_B1(c) * eq + C_B2(c) * ed;
-                if (c == j) row += reg + Gam + sc.hu;
-                if (c <= j) Min[(j * (j + 1)) / 2 + c] = row;
-            }
-            Min[21 + j] = G[FG_RG + j] + gam + (b1j * sm.tv[j] + b2j * sm.tv[6 + j]);
+            const rd_double2 b2v = *RD_CV2(&G[FG_RB + c]);
+            aq += pj[c] * b2v.x;
+            aq += pj[c + 1] * b2v.y;
+            ad += pd[c] * b2v.x;
+            ad += pd[c + 1] * b2v.y;
         }
-        rd_sync();
-        /* (3b) 6 x 6 Cholesky + forward substitution of m_u, redundantly in every lane (BLASFEO dpotrf_l: a
-         *      non-positive pivot zeroes its column); lane j < 6 publishes row j */
+        const double tvq = aq + pvq, tvd = ad + pvd;
+        const double b1j = C_B1(j), b2j = C_B2(j);
+        /* (3a) control row: Muu row j and m_u */
+        double mrow[6];
+        RD_UNROLL
+        for (int c = 0; c < 6; c++)
         {
-            double Lu[21], lu[6], inv[6];
-            RD_UNROLL
-            for (int k = 0; k < 21; k++) Lu[k] = Min[k];
-            RD_UNROLL
-            for (int k = 0; k < 6; k++) lu[k] = Min[21 + k];
-#define LU(r, c) Lu[((r) * ((r) + 1)) / 2 + (c)]
-            RD_UNROLL
-            for (int c = 0; c < 6; c++)
-            {
-                const double dj = LU(c, c);
-                const double iv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
-                inv[c] = iv;
-                LU(c, c) = dj * iv;
-                RD_UNROLL
-                for (int r = c + 1; r < 6; r++) LU(r, c) *= iv;
-                lu[c] *= iv;
-                RD_UNROLL
-                for (int k = c + 1; k < 6; k++)
-                {
-                    RD_UNROLL
-                    for (int r = k; r < 6; r++) LU(r, k) -= LU(r, c) * LU(k, c);
-                    lu[k] -= lu[c] * LU(k, c);
-                }
-            }
-            if (R.u)
-            {
-                double ivj = 0.0, luj = 0.0;
-                RD_UNROLL
-                for (int c = 0; c < 6; c++)
-                    if (c == j) { ivj = inv[c]; luj = lu[c]; }
-                F[RF_INV + j] = ivj > 0.0 ? ivj : rd_inf();
-                F[RF_LU + j] = luj;
-                Lo[21 + j] = luj;
-                Lo[27 + j] = ivj;
-                RD_UNROLL
-                for (int r = 0; r < 6; r++)
-                    RD_UNROLL
-                    for (int c = 0; c <= r; c++)
-                        if (r == j)
-                        {
-                            Lo[(r * (r + 1)) / 2 + c] = LU(r, c);
-                            if (c < r) F[RF_LUU + (r * (r - 1)) / 2 + c] = LU(r, c);
-                        }
-            }
-#undef LU
+            const double eq = b1j * pj[c] + b2j * pd[c];
+            const double ed = b1j * pj[6 + c] + b2j * pd[6 + c];
+            double row = C_B1(c) * eq + C_B2(c) * ed;
+            if (c == j) row += reg + Gam + sc.hu;
+            mrow[c] = row;
         }
-        rd_sync();
-        if (s0) continue;
-        /* (3c) state rows: e = row of [B A]' P+, then Mxu, Lxu, p */
-        double e[12], Lx[6], pk = 0.0;
-        if (R.x)
-        {
-            RD_UNROLL
-            for (int c = 0; c < 12; c++)
-                e[c] = R.q ? P[j * SM_PS + c] : (R.ca * P[j * SM_PS + c] + R.cb * P[(6 + j) * SM_PS + c]);
-            RD_UNROLL
-            for (int c = 0; c < 6; c++)
-            {
-                double v = C_B1(c) * e[c] + C_B2(c) * e[6 + c];
-                if (!R.q && c == j) v += sc.hs;
-                RD_UNROLL
-                for (int k = 0; k < c; k++) v -= Lx[k] * Lo[(c * (c + 1)) / 2 + k];
-                Lx[c] = v * Lo[27 + c];
-            }
-            pk = G[FG_RG + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
-            RD_UNROLL
-            for (int c = 0; c < 6; c++) pk -= Lx[c] * Lo[21 + c];
-            RD_UNROLL
-            for (int c = 0; c < 6; c++)
-            {
-                Lxu[xk * 6 + c] = Lx[c];
-                F[RF_LXU + xk * 6 + c] = Lx[c];
-            }
-        }
-        rd_sync();
-        /* (3d) Schur complement row: P[xk][:] = Mxx[xk][:] - Lxu[xk][:] Lxu' */
-        if (R.x)
+        const double mu_ = G[FG_RG + j] + gam + (b1j * tvq + b2j * tvd);
+        /* (3c') state row: e = row of [B A]' P+, v = e B (+ S), Mxx row = e A + H, right-hand side */
+        double v[6], Pn[12], pk = 0.0;
+        if (!s0)
         {
             const double *Jc = G + FG_JC;
-            double Pn[12];
+            double e[12], jcol[5];
+            RD_UNROLL
+            for (int c = 0; c < 12; c++) e[c] = R.ca * pj[c] + R.cb * pd[c];
+            RD_UNROLL
+            for (int m = 0; m < 5; m++) jcol[m] = R.q ? Jc[6 * m + j] : (m == 4 ? Jc[30 + j] : 0.0);
             RD_UNROLL
             for (int c = 0; c < 6; c++)
             {
+                double vv = C_B1(c) * e[c] + C_B2(c) * e[6 + c];
+                if (!R.q && c == j) vv += sc.hs;
+                v[c] = vv;
                 Pn[c] = e[c];
                 Pn[6 + c] = C_A12(c) * e[c] + C_A22(c) * e[6 + c];
             }
-            if (R.q)
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
             {
+                double a = 0.0;
                 RD_UNROLL
-                for (int c = 0; c < 6; c++)
-                {
-                    double a = 0.0;
-                    RD_UNROLL
-                    for (int m = 0; m < 5; m++) a += Jc[6 * m + j] * Jc[6 * m + c];
-                    Pn[c] += a;
-                    Pn[6 + c] += Jc[24 + j] * Jc[30 + c];
-                }
+                for (int m = 0; m < 5; m++) a += jcol[m] * Jc[6 * m + c];
+                Pn[c] += a;
+                Pn[6 + c] += jcol[4] * Jc[30 + c];
             }
-            else
+            pk = G[FG_RG + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * tvq + R.cb * tvd);
+        }
+        if (R.x) F[RF_PB + xk] = R.q ? aq : ad;
+        if (R.u)
+        {
+            RD_UNROLL
+            for (int c = 0; c < 6; c++)
+                if (c <= j) Min[(j * (j + 1)) / 2 + c] = mrow[c];
+            Min[21 + j] = mu_;
+        }
+        SEC(2);
+        rd_sync();
+        SEC(3);
+        /* ------------------------------------------------------------------------------------------------ S2 */
+        if (R.x && !s0)
+        { /* every lane has read P+: the own row now holds the Mxx row (diagonal: + reg + Gamma | hq) */
+            RD_UNROLL
+            for (int c = 0; c < 12; c += 2)
             {
-                RD_UNROLL
-                for (int c = 0; c < 6; c++)
-                {
-                    Pn[c] += Jc[30 + j] * Jc[24 + c];
-                    Pn[6 + c] += Jc[30 + j] * Jc[30 + c];
-                }
+                rd_double2 w2;
+                w2.x = Pn[c]; w2.y = Pn[c + 1];
+                *RD_V2(&P[xk * SM_PS + c]) = w2;
+            }
+            P[xk * SM_PS + xk] += reg + (R.q ? Gam : sc.hq);
+        }
+        /* (3b) 6 x 6 Cholesky + forward substitution of m_u, redundantly in every lane (BLASFEO dpotrf_l: a
+         *      non-positive pivot zeroes its column) */
+        double Lu[21], lu[6], inv[6];
+        {
+            double mv[28];
+            RD_UNROLL
+            for (int k = 0; k < 28; k += 2)
+            {
+                const rd_double2 m2 = *RD_CV2(&Min[k]);
+                mv[k] = m2.x; mv[k + 1] = m2.y;
             }
             RD_UNROLL
-            for (int c = 0; c < 12; c++)
-                if (c == xk) Pn[c] += reg + (R.q ? Gam : sc.hq);
+            for (int k = 0; k < 21; k++) Lu[k] = mv[k];
             RD_UNROLL
-            for (int c = 0; c < 12; c++)
+            for (int k = 0; k < 6; k++) lu[k] = mv[21 + k];
+        }
+#define LU(r, c) Lu[((r) * ((r) + 1)) / 2 + (c)]
+        RD_UNROLL
+        for (int c = 0; c < 6; c++)
+        {
+            const double dj = LU(c, c);
+            const double iv = dj > 0.0 ? rd_rsqrt(dj) : 0.0;
+            inv[c] = iv;
+            LU(c, c) = dj * iv;
+            RD_UNROLL
+            for (int r = c + 1; r < 6; r++) LU(r, c) *= iv;
+            lu[c] *= iv;
+            RD_UNROLL
+            for (int k = c + 1; k < 6; k++)
             {
-                double a = Pn[c];
                 RD_UNROLL
-                for (int k = 0; k < 6; k += 2)
-                {
-                    const rd_double2 lc = *reinterpret_cast<const rd_double2 *>(&Lxu[c * 6 + k]);
-                    a -= Lx[k] * lc.x;
-                    a -= Lx[k + 1] * lc.y;
-                }
-                Pn[c] = a;
+                for (int r = k; r < 6; r++) LU(r, k) -= LU(r, c) * LU(k, c);
+                lu[k] -= lu[c] * LU(k, c);
             }
+        }
+        if (lane == 12 % GL)
+        { /* one lane publishes 1 / diag, l_u and the strict lower part of Luu: F[RF_INV .. RF_LXU) with 128-bit stores */
+            double o[28];
             RD_UNROLL
-            for (int c = 0; c < 12; c++)
+            for (int k = 0; k < 6; k++) { o[RF_INV + k] = inv[k] > 0.0 ? inv[k] : rd_inf(); o[RF_LU + k] = lu[k]; }
+            RD_UNROLL
+            for (int r = 1; r < 6; r++)
+                RD_UNROLL
+                for (int c = 0; c < r; c++) o[RF_LUU + (r * (r - 1)) / 2 + c] = LU(r, c);
+            o[27] = 0.0;
+            RD_UNROLL
+            for (int k = 0; k < 28; k += 2)
             {
-                P[xk * SM_PS + c] = Pn[c];
-                if (c <= xk) F[RF_P + (xk * (xk + 1)) / 2 + c] = Pn[c];
+                rd_double2 w2;
+                w2.x = o[k]; w2.y = o[k + 1];
+                *RD_V2(&F[k]) = w2;
+            }
+        }
+        SEC(4);
+        if (s0) continue;
+        /* (3c) Lxu row = v Luu^-T, p = m_x - Lxu l_u */
+        double Lx[6];
+        RD_UNROLL
+        for (int c = 0; c < 6; c++)
+        {
+            double vv = v[c];
+            RD_UNROLL
+            for (int k = 0; k < c; k++) vv -= Lx[k] * LU(c, k);
+            Lx[c] = vv * inv[c];
+        }
+        RD_UNROLL
+        for (int c = 0; c < 6; c++) pk -= Lx[c] * lu[c];
+#undef LU
+        if (R.x)
+        {
+            RD_UNROLL
+            for (int c = 0; c < 6; c += 2)
+            {
+                rd_double2 w2;
+                w2.x = Lx[c]; w2.y = Lx[c + 1];
+                *RD_V2(&Lxu[xk * 6 + c]) = w2;
+                *RD_V2(&F[RF_LXU + xk * 6 + c]) = w2;
             }
             sm.pv[xk] = pk;
             F[RF_PV + xk] = pk;
         }
+        SEC(5);
         rd_sync();
+        SEC(6);
+        /* ------------------------------------------------------------------------------------------------ S3
+         * Schur complement row: P[xk][:] = Mxx[xk][:] - Lxu[xk][:] Lxu'; the rows of Lxu are fetched three at a time */
+        if (R.x)
+        {
+            double Pr[12];
+            RD_UNROLL
+            for (int c = 0; c < 12; c += 2)
+            {
+                const rd_double2 a2 = *RD_CV2(&P[xk * SM_PS + c]);
+                Pr[c] = a2.x; Pr[c + 1] = a2.y;
+            }
+            RD_UNROLL
+            for (int c0 = 0; c0 < 12; c0 += 3)
+            {
+                rd_double2 l2[3][3];
+                RD_UNROLL
+                for (int u = 0; u < 3; u++)
+                    RD_UNROLL
+                    for (int k = 0; k < 3; k++) l2[u][k] = *RD_CV2(&Lxu[(c0 + u) * 6 + 2 * k]);
+                RD_UNROLL
+                for (int u = 0; u < 3; u++)
+                {
+                    double a = Pr[c0 + u];
+                    RD_UNROLL
+                    for (int k = 0; k < 3; k++)
+                    {
+                        a -= Lx[2 * k] * l2[u][k].x;
+                        a -= Lx[2 * k + 1] * l2[u][k].y;
+                    }
+                    Pr[c0 + u] = a;
+                }
+            }
+            RD_UNROLL
+            for (int c = 0; c < 12; c += 2)
+            {
+                rd_double2 w2;
+                w2.x = Pr[c]; w2.y = Pr[c + 1];
+                *RD_V2(&P[xk * SM_PS + c]) = w2;
+            }
+            RD_UNROLL
+            for (int c = 0; c < 12; c++)
+                if (c <= xk) F[RF_P + (xk * (xk + 1)) / 2 + c] = Pr[c];
+        }
+        SEC(7);
     }
     rd_cp_wait0();
+    rd_sync(); /* the factor blocks written by single lanes (stage 0: lane 12) are read by every lane of the next sweep */
+    SECPROF_END(0);
 }
 
 /* Forward sweep of the Riccati recursion (H/ocp_qp/x_ocp_qp_kkt.c:970-1005 and :1671-1721) fused with everything that
@@ -1478,13 +1555,16 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
     if (R.x) { sm.xv[xk] = 0.0; X[6 + xk] = 0.0; }
     double alpha = 1.0, sB = 0.0, sC = 0.0;
     double n0 = 0.0, nanflag = 0.0, dp_prev = 0.0;
+    SECPROF_BEGIN;
     for (int ss = 0; ss < N; ss++)
     {
         const double *G = SW_STG(sm, ss & 1);
         if (ss + 1 < N) fwd_stage_in<STORED>(I, SW_STG(sm, (ss + 1) & 1), ss + 1, rg, rb, rd, rm, X);
         rd_cp_commit();
+        SEC(0);
         rd_cp_wait1();
         rd_sync();
+        SEC(1);
         /* s = src_u + Lxu' dx (lane c < 6) */
         if (R.u)
         {
@@ -1509,6 +1589,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             }
         }
         rd_sync();
+        SEC(2);
         /* du = -Luu^-T s, redundantly in every lane */
         double du[6];
         RD_UNROLL
@@ -1536,11 +1617,13 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             if (R.q) xn = (sm.xv[j] + a12 * sm.xv[6 + j]) + b1 * duj + G[WG_RB + j];
             else xn = a22 * sm.xv[6 + j] + b2 * duj + G[WG_RB + 6 + j];
         }
+        SEC(3);
         rd_sync(); /* every lane has read xv, uv */
         if (R.u) X[NV * ss + lane] = dul;
         if (R.x) { sm.xv[xk] = xn; X[NV * (ss + 1) + 6 + xk] = xn; }
         if (lane < 5) sm.wv[lane] = wm;
         rd_sync();
+        SEC(4);
         /* dpi = P+ dx+ + p+ */
         double dpo = 0.0;
         if (R.x)
@@ -1552,6 +1635,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             sm.dp[xk] = a;
             dpo = a;
         }
+        SEC(5);
         /* multiplier / slack step of this lane's bound slot, step length, second-order sums */
         double dlm = 0.0; /* dlam_ub - dlam_lb of the own slot */
         if (lane < 12 && !(ss == 0 && lane >= 6))
@@ -1571,6 +1655,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             sC += dla * dta + dlb * dtb;
             dlm = dlb - dla;
         }
+        SEC(6);
         /* operands of the residual rows that live in the staging buffer (refilled after the barrier) */
         double rgu = 0.0, rgx = 0.0, jq[5] = {0, 0, 0, 0, 0}, jd = 0.0;
         if (R.u) rgu = G[WG_RG + lane];
@@ -1604,8 +1689,10 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             n0 = rd_fmax(n0, fabs(r));
         }
         dp_prev = dpo;
+        SEC(7);
     }
     rd_cp_wait0();
+    SECPROF_END(STORED ? 20 : 10);
     if (R.u) X[NV * N + lane] = 0.0;
     double dlmN = 0.0;
     if (I.pe)
@@ -1706,14 +1793,17 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
         sm.pv[xk] = pv;
         AR(pvec)[NX * N + xk] = pv;
     }
+    SECPROF_BEGIN;
     for (int ss = N - 1; ss >= 0; ss--)
     {
         const bool s0 = (ss == 0);
         const double *G = SW_STG(sm, ss & 1);
         if (ss > 0) bwd_stage_in<MODE, USE_PB>(I, SW_STG(sm, (ss - 1) & 1), ss - 1, rg, rd, rm);
         rd_cp_commit();
+        SEC(0);
         rd_cp_wait1();
         rd_sync();
+        SEC(1);
         if (R.x)
         {
             double pb;
@@ -1727,6 +1817,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             }
             sm.tv[xk] = sm.pv[xk] + pb;
         }
+        SEC(2);
         double gam = 0.0;
         if (lane < 12 && !(s0 && lane >= 6))
         {
@@ -1747,10 +1838,12 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             gam = (ma - la * G[BG_RD + lane]) / ta - (mb - lb * G[BG_RD + 12 + lane]) / tb;
         }
         rd_sync();
+        SEC(3);
         double rx = 0.0;
         if (R.u) sm.uv[lane] = G[BG_RG + lane] + gam + (b1 * sm.tv[j] + b2 * sm.tv[6 + j]);
         if (R.x && !s0) rx = G[BG_RG + 6 + xk] + (R.q ? gam : 0.0) + (R.ca * sm.tv[j] + R.cb * sm.tv[6 + j]);
         rd_sync();
+        SEC(4);
         /* TRSV_LNN_MN(18, 6): z_u = Luu^-1 r_u (redundantly in every lane), r_x -= Lxu z_u */
         double z[6];
         RD_UNROLL
@@ -1778,8 +1871,10 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             AR(pvec)[NX * ss + xk] = rx;
         }
         rd_sync();
+        SEC(5);
     }
     rd_cp_wait0();
+    SECPROF_END(30);
 }
 
 /* COMPUTE_ALPHA_QP as a separate pass (only needed after an iterative-refinement correction) */
@@ -1897,13 +1992,16 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
         if (UPD) { q_ = q_ + a * G[(doff) + (c)]; q_ = q_ <= lmin ? lmin : q_; }              \
         (out) = q_;                                                                           \
     } while (0)
+    SECPROF_BEGIN;
     for (int i = 0; i <= N; i++)
     {
         const double *G = SW_STG(sm, i & 1);
         if (i < N) res_stage_in<UPD>(I, SW_STG(sm, (i + 1) & 1), i + 1, N);
         rd_cp_commit();
+        SEC(0);
         rd_cp_wait1();
         rd_sync();
+        SEC(1);
         const bool mid = i < N, x_on = i > 0;
         /* new values of this lane's joint: u_j, q_j, qd_j (the state is fixed at stage 0 of the reduced QP) */
         const double uj = mid ? QV(QG_UX, QG_DUX, j) : 0.0;
@@ -1930,6 +2028,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             n4 = rd_fmax(n4, rd_fmax(fabs(ml - 1e-16), fabs(mu_ - 1e-16)));
             dlm = lb - la;
         }
+        SEC(2);
         /* control row u_j */
         if (R.u && mid)
         {
@@ -1940,6 +2039,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             n0 = rd_fmax(n0, fabs(g));
             if (i == 0 && lane == 0 && g != g) nanflag = 1.0;
         }
+        SEC(3);
         /* state row (q_j on lanes 6..11, qd_j on lanes 0..5), dynamics residual of the same row */
         if (R.x)
         {
@@ -1998,6 +2098,7 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
                 pprev = R.q ? pq : pd;
             }
         }
+        SEC(4);
         if (!mid && I.pe && lane == 12)
         { /* general row of stage N: res_d = d + t -+ C x, res_m; its two slots are moved here as well */
             double cx = 0.0, la, lb, ta, tb;
@@ -2021,7 +2122,9 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
             if (mid && lane < NX) AR(spi)[NX * i + lane] = G[QG_PI + lane] + a * G[QG_DPI + lane];
         }
         rd_sync(); /* the buffer of this stage is refilled by the next iteration */
+        SEC(5);
     }
+    SECPROF_END(UPD ? 50 : 40);
 #undef QV
 #undef QF
     rd_cp_wait0();
@@ -2054,7 +2157,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
     for (kk = 0; kk < D.qp_iter_max && alpha > alpha_min && (nrm[0] > tol || nrm[1] > tol || nrm[2] > tol || nrm[4] > tol); kk++)
     {
         /* affine (predictor) step */
-        ipm_factor(D, I, sm);
+                ipm_factor(D, I, sm);
         TQ(0);
         double lin[2];
         ipm_forward<0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);

@@ -906,7 +906,7 @@ static int ipm_solve_qp(rmpc_oracle *s, int warm)
         int step_nan = 0;
         for (size_t k = 0; k < (size_t) NV * (N + 1) && !step_nan; k++) step_nan = isnan(s->dux[k]) || isinf(s->dux[k]);
         for (size_t k = 0; k < (size_t) NX * N && !step_nan; k++) step_nan = isnan(s->dpi[k]) || isinf(s->dpi[k]);
-        if ((inrm[0] == 0.0 && isnan(s->ig[0])) || any_gt(inrm, 1e-5) || step_nan)
+        if ((inrm[0] == 0.0 && isnan(s->ig[0])) || any_gt(inrm, 1e-5) || step_nan || getenv("RMPC_ORACLE_FORCE_LQ"))
         { /* inaccurate factorisation: refactorise this iteration with LQ (:2246-2276) */
             s->n_lq_needed++;
             ipm_fact_lq_solve(s);

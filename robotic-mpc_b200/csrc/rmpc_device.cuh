@@ -1501,6 +1501,202 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     SECPROF_END(0);
 }
 
+/* Householder-LQ re-factorisation of one interior-point iteration, OCP_QP_FACT_LQ_SOLVE_KKT_STEP
+ * (H/ocp_qp/x_ocp_qp_kkt.c:1201-1541), the fall-back of lq_fact = 1 when the Cholesky route left a linear-system residual
+ * above 1e-5 (H/ocp_qp/x_ocp_qp_ipm.c:2246-2276).  The stage factor L (lower, L L' = the Riccati matrix of the stage) is
+ * obtained WITHOUT forming that matrix -- no subtraction Mxx - Lxu Lxu', no squared condition number: it is the triangular
+ * factor of the LQ decomposition of
+ *     [ Lh | diag(sqrt(Gamma_box)) | C' sqrt(Gamma_g) (stage N) | [B A]' Lxx+ ],     Lh Lh' = H + reg I   (:1263-1320),
+ * with the diagonal made positive.  BLASFEO's GELQF_PD_LLA is a blocked, structure-exploiting Householder LQ; this is the
+ * textbook unblocked one in the operation order of oracle/rmpc_oracle.c (lq_lower) -- same factor up to rounding.
+ * What the sweeps with stored factors need is then written in the usual factor block: 1 / diag Luu, Luu, Lxu, P = Lxx Lxx'
+ * (no cancellation in that product) and P+ b; the step itself follows from ipm_backward<0, 1> + ipm_forward<1> (:1322,
+ * 1469-1512).  A rare path (active terminal row): written for clarity, rows of the stage matrix are owned by
+ * lanes (row r: lane r mod GL), operands come straight from HBM, one barrier per Householder step.
+ * Shared memory: T = the Lh block, packed lower (column i is only touched by reflector i and becomes column i of L);
+ * W = the other blocks, nv x 24, [box 0..11 | BA 12..23] (stage N: column 0 = the general row); LN = Lxx of stage ss + 1. */
+#define LQ_T(sm) ((sm).buf)
+#define LQ_KW 24
+#define LQ_W(sm) ((sm).buf + 172)
+#define LQ_LN(sm) ((sm).buf + 172 + 18 * LQ_KW)
+#define LQ_D(sm) ((sm).buf + 172 + 18 * LQ_KW + 78) /* 18: positive diagonal of L */
+#define TL(r, c) T[((r) * ((r) + 1)) / 2 + (c)]
+RDN void ipm_factor_lq(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
+{
+    const Inst I = I_;
+    const int N = D.N, lane = rd_lane();
+    const double reg = 1e-15;
+    double *T = LQ_T(sm), *W = LQ_W(sm), *LN = LQ_LN(sm), *Dg = LQ_D(sm);
+    for (int ss = N; ss >= 0; ss--)
+    {
+        const int nu = ss < N ? 6 : 0, nx = ss > 0 ? 12 : 0, nv = nu + nx, nb = ss == N ? 0 : (ss == 0 ? 6 : 12);
+        const double *Jc = AR(Jc) + NJ * ss;
+        double *F = AR(F) + (long) FS * ss;
+        /* (a) rows of the compound matrix */
+        for (int r = lane; r < nv; r += GL)
+        {
+            const int vr = r + (6 - nu); /* index in [u; q; qd] */
+            for (int c = 0; c <= r; c++)
+            {
+                const int vc = c + (6 - nu);
+                double h = 0.0;
+                if (ss < N)
+                {
+                    if (vr < 6) h = (vc == vr) ? sm.hc[vr] : 0.0;
+                    else if (ss > 0)
+                    {
+                        if (vr < 12)
+                        {
+                            if (vc >= 6)
+                                for (int m = 0; m < 5; m++) h += Jc[6 * m + (vr - 6)] * Jc[6 * m + (vc - 6)];
+                        }
+                        else if (vc < 6) h = (vc == vr - 12) ? sm.hc[6 + vc] : 0.0;
+                        else if (vc < 12) h = Jc[30 + (vr - 12)] * Jc[24 + (vc - 6)];
+                        else h = Jc[30 + (vr - 12)] * Jc[30 + (vc - 12)] + (vc == vr ? sm.hc[12 + (vr - 12)] : 0.0);
+                    }
+                }
+                TL(r, c) = h + (c == r ? reg : 0.0);
+            }
+            double *w = W + LQ_KW * r;
+            for (int k = 0; k < LQ_KW; k++) w[k] = 0.0;
+            if (r < nb)
+            { /* box rows, idxb = 0 .. nb-1: sqrt(Gamma_lb + Gamma_ub) on the diagonal of the block */
+                const double tl = 1.0 / AR(st)[NB * ss + r], tu = 1.0 / AR(st)[NB * ss + 12 + r];
+                double g = tl * AR(slam)[NB * ss + r] + tu * AR(slam)[NB * ss + 12 + r];
+                g = g >= 0.0 ? g : 0.0;
+                g = sqrt(g);
+                w[r] = g > 0.0 ? g : 0.0;
+            }
+            if (ss == N && I.pe)
+            { /* general row of stage N: DCt sqrt(Gamma_g) */
+                const int ka = TERM_LO(N), kb = TERM_UP(N);
+                double g = (1.0 / AR(st)[ka]) * AR(slam)[ka] + (1.0 / AR(st)[kb]) * AR(slam)[kb];
+                g = g >= 0.0 ? g : 0.0;
+                w[0] = Jc[r] * sqrt(g);
+            }
+            if (ss < N)
+            { /* TRMM_RLNN: [B A]' Lxx+, rows of [B A]' = ca e_q + cb e_qd */
+                const int jj = vr % 6;
+                const double ca = vr < 6 ? C_B1(jj) : (vr < 12 ? 1.0 : C_A12(jj)), cb = vr < 6 ? C_B2(jj) : (vr < 12 ? 0.0 : C_A22(jj));
+                for (int c = 0; c < 12; c++)
+                {
+                    double a = 0.0;
+                    if (jj >= c) a += ca * LN[(jj * (jj + 1)) / 2 + c];
+                    if ((vr < 6 || vr >= 12) && 6 + jj >= c) a += cb * LN[((6 + jj) * (7 + jj)) / 2 + c];
+                    w[12 + c] = a;
+                }
+            }
+        }
+        /* P+ b = Lxx+ (Lxx+' res_b), kept for the corrector solves */
+        if (ss < N && lane < NX)
+        {
+            const double *b = AR(res_b) + NX * ss;
+            double tmp[NX];
+            for (int c = 0; c < NX; c++)
+            {
+                double a = 0.0;
+                for (int k = c; k < NX; k++) a += LN[(k * (k + 1)) / 2 + c] * b[k];
+                tmp[c] = a;
+            }
+            double a = 0.0;
+            for (int k = 0; k <= lane; k++) a += LN[(lane * (lane + 1)) / 2 + k] * tmp[k];
+            F[RF_PB + lane] = a;
+        }
+        rd_sync();
+        /* (b) Lh = chol(H + reg I) in place, column by column (POTRF_L: a non-positive pivot zeroes its column) */
+        for (int jc = 0; jc < nv; jc++)
+        {
+            double dj = TL(jc, jc);
+            for (int k = 0; k < jc; k++) dj -= TL(jc, k) * TL(jc, k);
+            double inv;
+            if (dj > 0.0) { dj = sqrt(dj); inv = 1.0 / dj; }
+            else { dj = 0.0; inv = 0.0; }
+            double a0 = 0.0, a1 = 0.0;
+            const int r0 = lane, r1 = lane + GL;
+            if (r0 > jc && r0 < nv)
+            {
+                a0 = TL(r0, jc);
+                for (int k = 0; k < jc; k++) a0 -= TL(r0, k) * TL(jc, k);
+            }
+            if (r1 > jc && r1 < nv)
+            {
+                a1 = TL(r1, jc);
+                for (int k = 0; k < jc; k++) a1 -= TL(r1, k) * TL(jc, k);
+            }
+            rd_sync();
+            if (r0 == jc) TL(jc, jc) = dj;
+            if (r0 > jc && r0 < nv) TL(r0, jc) = a0 * inv;
+            if (r1 == jc) TL(jc, jc) = dj;
+            if (r1 > jc && r1 < nv) TL(r1, jc) = a1 * inv;
+            rd_sync();
+        }
+        /* (c) Householder reflectors, row by row */
+        for (int i = 0; i < nv; i++)
+        {
+            const double *wi = W + LQ_KW * i;
+            const double d0 = TL(i, i);
+            double sigma = 0.0;
+            for (int k = 0; k < LQ_KW; k++) sigma += wi[k] * wi[k];
+            double diag = d0, sg = 1.0;
+            if (sigma > 0.0)
+            {
+                const double mu = sqrt(d0 * d0 + sigma);
+                const double v0 = d0 <= 0.0 ? d0 - mu : -sigma / (d0 + mu);
+                const double beta = 2.0 * v0 * v0 / (sigma + v0 * v0);
+                for (int r = lane; r < nv; r += GL)
+                    if (r > i)
+                    {
+                        double *wr = W + LQ_KW * r;
+                        double w = TL(r, i);
+                        for (int k = 0; k < LQ_KW; k++) w += wr[k] * (wi[k] / v0);
+                        w *= beta;
+                        TL(r, i) -= w;
+                        for (int k = 0; k < LQ_KW; k++) wr[k] -= w * (wi[k] / v0);
+                    }
+                diag = mu;
+            }
+            else if (d0 < 0.0)
+            { /* untouched row with a negative diagonal: the column changes sign */
+                sg = -1.0;
+                for (int r = lane; r < nv; r += GL)
+                    if (r > i) TL(r, i) = -TL(r, i);
+            }
+            if (lane == i % GL) Dg[i] = sg * diag;
+            rd_sync();
+        }
+        /* (d) factor block of the stage: 1 / diag Luu, Luu, Lxu, P = Lxx Lxx' */
+        if (nu)
+        {
+            if (lane < 6)
+            {
+                const double dd = Dg[lane];
+                F[RF_INV + lane] = dd > 0.0 ? 1.0 / dd : rd_inf();
+                F[RF_LU + lane] = 0.0;
+                for (int c = 0; c < lane; c++) F[RF_LUU + (lane * (lane - 1)) / 2 + c] = TL(lane, c);
+            }
+            if (nx && lane < NX)
+                for (int c = 0; c < 6; c++) F[RF_LXU + lane * 6 + c] = TL(6 + lane, c);
+        }
+        if (nx && lane < NX)
+        {
+            const int r = lane;
+            for (int c = 0; c <= r; c++)
+            {
+                double a = 0.0;
+                for (int k = 0; k <= c; k++)
+                    a += (k == r ? Dg[nu + r] : TL(nu + r, nu + k)) * (k == c ? Dg[nu + c] : TL(nu + c, nu + k));
+                F[RF_P + (r * (r + 1)) / 2 + c] = a;
+            }
+            F[RF_PV + r] = 0.0;
+        }
+        rd_sync();
+        if (nx && lane < NX) /* Lxx of this stage for the next one */
+            for (int c = 0; c <= lane; c++) LN[(lane * (lane + 1)) / 2 + c] = (c == lane) ? Dg[nu + lane] : TL(nu + lane, nu + c);
+        rd_sync();
+    }
+}
+#undef TL
+
 /* Forward sweep of the Riccati recursion (H/ocp_qp/x_ocp_qp_kkt.c:970-1005 and :1671-1721) fused with everything that
  * only depends on the step of one stage:
  *   du = -Luu^-T (src_u + Lxu' dx),  dx+ = A dx + B du + rb,  dpi = P+ dx+ + p+,
@@ -1536,7 +1732,7 @@ RD void fwd_stage_in(const Inst &I, double *dst, int ss, const double *rg, const
 /* The sweep also evaluates, at no extra pass over the data, the stationarity residual of the LINEAR system it solves,
  *   r = rg + H dv + [B A]' dpi - [0; dpi-] + dlam_ub - dlam_lb          (OCP_QP_RES_COMPUTE_LIN, H/ocp_qp/x_ocp_qp_res.c:535-685)
  * whose inf-norm drives the LQ-fallback trigger and the iterative refinement (x_ocp_qp_ipm.c:2228-2276,2493-2594):
- * lin[0] = |r|_inf, lin[1] = NaN flag of r_u[0] at stage 0.  The other three residuals of that system (dynamics,
+ * lin[0] = |r|_inf, lin[1] = NaN flag of r (any row: the max skips NaNs like HPIPM's norm does).  The other three residuals of that system (dynamics,
  * bounds, complementarity) are zero up to rounding BY CONSTRUCTION of dx+, dt and dlam in this sweep and are not
  * re-evaluated. */
 template <int STORED>
@@ -1674,7 +1870,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
         {
             const double r = rgu + hu * dul + hs * xo + b1 * sm.dp[j] + b2 * sm.dp[6 + j] + dlm;
             n0 = rd_fmax(n0, fabs(r));
-            if (ss == 0 && lane == 0 && r != r) nanflag = 1.0;
+            if (r != r) nanflag = 1.0;
         }
         if (R.x && ss > 0)
         {
@@ -1687,6 +1883,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
             }
             else r = rgx + jd * sm.wv[4] + hs * dul + hq * xo + a12 * sm.dp[j] + a22 * sm.dp[6 + j] - dp_prev;
             n0 = rd_fmax(n0, fabs(r));
+            if (r != r) nanflag = 1.0;
         }
         dp_prev = dpo;
         SEC(7);
@@ -1729,7 +1926,7 @@ RDN void ipm_forward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doubl
 /* Backward substitution with stored factors, first half of OCP_QP_SOLVE_KKT_STEP (H/ocp_qp/x_ocp_qp_kkt.c:
  * 1543-1665) incl. COMPUTE_GAMMA_QP (x_core_qp_ipm_aux.c:133-160): leaves z_u = Luu^-1 r_u in X[.][0:6] and the
  * Riccati vectors p_ss in pvec.  The complementarity right-hand side depends on MODE:
- *   0  rm given (iterative refinement);
+ *   0  rm - sigma_mu with rm given (iterative refinement: sigma_mu = 0; LQ route: the affine right-hand side res_m - tau_min);
  *   1  COMPUTE_CENTERING_CORRECTION_QP (:479-505): rm = res_m + dt_aff dlam_aff - sigma_mu, written to res_mc;
  *   2  COMPUTE_CENTERING_QP (:509-529):            rm = res_m - sigma_mu, written to res_mc.
  * USE_PB: P+ rb was stored by the factorisation (rb = res_b); otherwise it is recomputed from P+. */
@@ -1777,7 +1974,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             const int ia = TERM_LO(N), ib = TERM_UP(N);
             const double la = AR(slam)[ia], lb = AR(slam)[ib], ta = AR(st)[ia], tb = AR(st)[ib];
             double ma, mb;
-            if (MODE == 0) { ma = rm[ia]; mb = rm[ib]; }
+            if (MODE == 0) { ma = rm[ia] - sigma_mu; mb = rm[ib] - sigma_mu; }
             else
             {
                 if (MODE == 1)
@@ -1824,7 +2021,7 @@ RDN void ipm_backward(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const doub
             const int ia = NB * ss + lane, ib = ia + 12;
             const double la = G[BG_LAM + lane], lb = G[BG_LAM + 12 + lane], ta = G[BG_T + lane], tb = G[BG_T + 12 + lane];
             double ma, mb;
-            if (MODE == 0) { ma = G[BG_RM + lane]; mb = G[BG_RM + 12 + lane]; }
+            if (MODE == 0) { ma = G[BG_RM + lane] - sigma_mu; mb = G[BG_RM + 12 + lane] - sigma_mu; }
             else
             {
                 if (MODE == 1)
@@ -2136,9 +2333,8 @@ RDN double ipm_res_sweep(const RmpcDims &D, const Inst &I_, GrpSmem &sm, const d
 /* d_ocp_qp_ipm_solve (H/ocp_qp/x_ocp_qp_ipm.c:2626-3018) with OCP_QP_IPM_DELTA_STEP (:2155-2622) for the option set
  * acados resolves: Mehrotra predictor-corrector, conditional second centering solve, up to two
  * refinement steps on the corrector, single damped step, lam/t floor 1e-16.  Returns the acados QP status
- * (0 ok, 2 max iter, 3 min step, 1 NaN).  The Householder-LQ fall-back of lq_fact = 1 is not implemented: its
- * trigger (linear-system residual > 1e-5, :2246-2276) is evaluated and counted in flags[2] so that any instance
- * that would have taken it is visible to the caller. */
+ * (0 ok, 2 max iter, 3 min step, 1 NaN).  The Householder-LQ fall-back of lq_fact = 1 (trigger: linear-system residual
+ * > 1e-5, :2246-2276, evaluated by the forward sweep itself) is ipm_factor_lq(); the events are counted in flags[2]. */
 RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, int *iters, double *tq)
 {
     const int N = D.N, lane = rd_lane();
@@ -2162,33 +2358,31 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
         double lin[2];
         ipm_forward<0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);
         TQ(1);
-        if ((lin[0] == 0.0 && lin[1] > 0.5) || lin[0] > 1e-5)
+        bool lq = lin[1] > 0.5 || lin[0] > 1e-5;
+        if (I.pe && !lq)
+        { /* with a terminal row the recursion can be ill-conditioned enough for the rows that vanish by construction of the
+           * forward sweep (dynamics, bounds, complementarity) to leave rounding residue above HPIPM's threshold: evaluate
+           * all four norms of OCP_QP_RES_COMPUTE_LIN like the reference does */
+            double pn[6];
+            ipm_res<1, 0>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), nullptr,
+                          nullptr, nullptr, nullptr, pn);
+            lq = pn[0] > 1e-5 || pn[1] > 1e-5 || pn[2] > 1e-5 || pn[3] > 1e-5 || pn[5] > 0.5;
+        }
+#ifdef RMPC_EMU_FORCE_LQ
+        lq = true;
+#endif
+        if (lq)
         {
-            /* Inaccurate factorisation (x_ocp_qp_ipm.c:2246-2276).  HPIPM re-factorises this iteration with Householder
-             * LQ; here the SAME linear system is brought to the same accuracy by iterative refinement of the predictor
-             * step with the factors at hand (residual of the linear system -> correction solve -> add), at most twice.
-             * The event is counted in flags[2]. */
+            /* Inaccurate factorisation (x_ocp_qp_ipm.c:2246-2276: linear-system residual above 1e-5, or NaN): this
+             * iteration is re-factorised with Householder LQ and the affine step re-solved with the stored factors
+             * (OCP_QP_FACT_LQ_SOLVE_KKT_STEP).  The corrector solves below then run on the LQ factors.  Counted in flags[2]. */
             if (lane == 0) I.flags[2] += 1;
-            for (int it = 0; it < 2; it++)
-            {
-                double pn[6], a2, s2[2], l2[2];
-                ipm_res<1, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), AR(slam), AR(st), AR(ig),
-                              AR(ib), AR(id), AR(im), pn);
-                if (pn[0] < 1e-5 && pn[1] < 1e-5 && pn[2] < 1e-5 && pn[3] < 1e-5 && !(pn[5] > 0.5)) break;
-                ipm_backward<0, 0>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux));
-                ipm_forward<1>(D, I, sm, AR(ig), AR(ib), AR(id), AR(im), 0.0, AR(iux), AR(ipi), AR(ilam), AR(it), &a2, s2, l2);
-                for (int k = lane; k < (N + 1) * NV; k += GL) AR(dux)[k] += AR(iux)[k];
-                for (int k = lane; k < N * NX; k += GL) AR(dpi)[k] += AR(ipi)[k];
-                for (int k = lane; k < N * NB; k += GL) { AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k]; }
-                if (I.pe && lane < 2)
-                {
-                    const int k = lane ? TERM_UP(N) : TERM_LO(N);
-                    AR(dlam)[k] += AR(ilam)[k]; AR(dt_)[k] += AR(it)[k];
-                }
-                rd_sync();
-            }
-            alpha = ipm_alpha(D, I, AR(dlam), AR(dt_));
-            ipm_mu_sums(D, I, AR(dlam), AR(dt_), sums);
+            ipm_factor_lq(D, I, sm);
+            TQ(0);
+            ipm_backward<0, 1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux));
+            TQ(2);
+            ipm_forward<1>(D, I, sm, AR(res_g), AR(res_b), AR(res_d), AR(res_m), tau_min, AR(dux), AR(dpi), AR(dlam), AR(dt_), &alpha, sums, lin);
+            TQ(1);
         }
         double mu_aff = ipm_mu_aff(sum_lt, sums, alpha, nc_inv);
         const double tmp = mu_aff / mu, sigma = tmp * tmp * tmp;

@@ -54,7 +54,7 @@ def test_emulated_kernels_terminal_row_against_reference_golden(built, case):
     assert np.abs(r["z"][0] - g["z"][:ns + 1]).max() < tol * np.abs(g["z"]).max()
     assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"][:ns])
     assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"][:ns])
-    assert np.abs(r["slog"][0, :, 2] - g["qp_iter"][:ns]).max() <= 1
+    assert np.array_equal(r["slog"][0, :, 2].astype(int), g["qp_iter"][:ns])  # incl. the iterations that take the LQ route
     assert np.abs(r["slog"][0, :, 3] - g["cost"][:ns]).max() < tol * np.abs(g["cost"]).max()
 
 

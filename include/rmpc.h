@@ -77,7 +77,17 @@ int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
  *                    solver.set(N-1,'x',solver.get(N,'x'))` an acados MPC runs between two solves.  Default 0: the reference's
  *                    loop keeps the unshifted iterate (R/simulator.py:199-241).
  *   "graph"  0 | 1   rmpc_step_host replays a captured CUDA graph (default 1) or enqueues copy, kernel, copy one by one
- *   "statistics" 0 | 1  keep the per-iteration statistics table of the last full-SQP solve (rmpc_get "sqp_stat"). */
+ *   "statistics" 0 | 1  keep the per-iteration statistics table of the last full-SQP solve (rmpc_get "sqp_stat").
+ *   "as_rti_level" 0..4  SQP_RTI only: advanced-step RTI, acados' as_rti_level (0 = A, 1 = B, 2 = C, 3 = D, 4 = standard RTI,
+ *                    the default; AC/ocp_nlp/ocp_nlp_sqp_rti.c:654-1100, T/acados_ocp_options.py:1189-1208).  A PREPARATION
+ *                    phase (rmpc_solve_rti_phase(h, 1)) then first works on the ADVANCED problem -- stage-0 state fixed at
+ *                    the prediction phi(x_0, u_0) of the current iterate -- with one QP on the last linearisation (A),
+ *                    as_rti_iter zero-order (B) / exact-gradient (C) / full SQP (D) iterations, and re-linearises;
+ *                    rmpc_solve_rti_phase(h, 2) is the usual feedback.  Like acados, the combined rmpc_solve is refused
+ *                    while a level is set; rmpc_closed_loop runs preparation + feedback per step.  Level C has no
+ *                    counterpart to check against: the reference aborts in it for a NONLINEAR_LS cost
+ *                    ("ocp_nlp_cost_nls_compute_gradient not implemented").
+ *   "as_rti_iter" n >= 0  iterations of the levels B, C, D (default 1) */
 int rmpc_set_option(rmpc_handle *h, const char *name, double value);
 
 /* Replaces <name>_acados_free + _free_capsule. */

@@ -263,6 +263,20 @@ class RefSolver:
         st = self.lib.rmpc_ref_step(self.h, _dp(x), _dp(u), C.byref(sqp), C.byref(qp), _dp(res), C.byref(cost), C.byref(tt))
         return dict(u=u, status=int(st), sqp_iter=sqp.value, qp_iter=qp.value, res=res, cost=cost.value, time_tot=tt.value)
 
+    def prepare(self):
+        """options_set('rti_phase', 1); solve(): the preparation phase (advanced-step preparation when the problem carries an
+        as_rti_level), stage-0 bounds untouched."""
+        self.lib.rmpc_ref_prepare.argtypes = [C.c_void_p]
+        return int(self.lib.rmpc_ref_prepare(self.h))
+
+    def feedback(self, x):
+        """options_set('rti_phase', 2); set(0, 'lbx' / 'ubx', x); solve(); get(0, 'u')."""
+        self.lib.rmpc_ref_set_rti_phase.argtypes = [C.c_void_p, C.c_int]
+        self.lib.rmpc_ref_set_rti_phase(self.h, 2)
+        r = self.step(x)
+        self.lib.rmpc_ref_set_rti_phase(self.h, 0)
+        return r
+
     def statistics(self):
         """AcadosOcpSolver.get_stats('statistics') of the last solve: [(stat_n + 1), rows]."""
         buf, sn = np.zeros(16 * 256), C.c_int(0)

@@ -141,6 +141,7 @@ struct rmpc_handle
     double *pe_dev; /* [B][RE_COUNT] terminal-set blocks, allocated by the first "P_e" / "alpha_e" / "lh_e" / "term" set */
     double *stg_dev; /* [B][N][RT_COUNT] per-stage references and bounds, allocated by the first per-stage (stage >= 0) set */
     double *sqpstat_dev; /* [B][max_iter + 2][RQ_COUNT], allocated by rmpc_set_option("statistics", 1) */
+    double *asrti_dev = nullptr; /* [B][RMPC_ASRTI_STRIDE], allocated by rmpc_set_option("as_rti_level", 0) */
     /* rmpc_step_host: pinned staging of x0 / u0 / step record, the stream used when the caller passes NULL (a captured
      * sequence cannot live on the legacy stream), and the instantiated graph with the launch arguments it was captured with */
     double *pin_z = nullptr, *pin_u = nullptr, *pin_st = nullptr;
@@ -278,6 +279,7 @@ extern "C" int rmpc_create(const rmpc_dims *dims, int device, int nlog, rmpc_han
     h->W.par = h->par_dev;
     h->W.nlog = nlog;
     h->W.step0 = 0;
+    h->W.as_rti_iter = 1;
     *out = h;
     return 0;
 }
@@ -313,6 +315,35 @@ extern "C" int rmpc_set_option(rmpc_handle *h, const char *name, double value)
             h->sqpstat_dev = (double *) p;
         }
         h->W.sqpstat = value == 1.0 ? h->sqpstat_dev : nullptr;
+        return 0;
+    }
+    if (f == "as_rti_level")
+    { /* acados' as_rti_level: 0 = A, 1 = B, 2 = C, 3 = D, 4 (or -1) = standard RTI */
+        if (h->D.solver_type != RMPC_SOLVER_SQP_RTI) return fail(h, RMPC_EINVAL, "rmpc_set_option: as_rti_level needs an SQP_RTI handle");
+        const int lv = (int) value;
+        if ((double) lv != value || lv < -1 || lv > 4) return fail(h, RMPC_EINVAL, "rmpc_set_option: as_rti_level must be in [0, 1, 2, 3, 4]");
+        const int mode = (lv < 0 || lv == 4) ? 0 : lv + 1;
+        if (mode == 1 && !h->asrti_dev)
+        { /* level A keeps a copy of the iterate (acados: work->tmp_nlp_out) */
+            ON_DEVICE(h);
+            const size_t bytes = sizeof(double) * (size_t) h->D.B * (size_t) RMPC_ASRTI_STRIDE(h->W.Sp);
+            void *p = nullptr;
+            if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return fail(h, RMPC_ENOMEM, "rmpc_set_option: device allocation failed"); }
+            if (cudaMemset(p, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) return fail(h, RMPC_ECUDA, "rmpc_set_option: cudaMemset failed");
+            h->owned.push_back(p);
+            h->bytes += (long long) bytes;
+            h->asrti_dev = (double *) p;
+        }
+        h->W.as_rti = mode;
+        h->W.asrti = mode == 1 ? h->asrti_dev : nullptr;
+        if (h->W.as_rti_iter < 1) h->W.as_rti_iter = 1;
+        return 0;
+    }
+    if (f == "as_rti_iter")
+    {
+        const int it = (int) value;
+        if ((double) it != value || it < 0) return fail(h, RMPC_EINVAL, "rmpc_set_option: as_rti_iter must be a nonnegative integer");
+        h->W.as_rti_iter = it;
         return 0;
     }
     return fail(h, RMPC_EINVAL, "rmpc_set_option: unknown option " + f);
@@ -609,6 +640,8 @@ static int launch_loop(rmpc_handle *h, int nsteps, int advance, cudaStream_t s)
 extern "C" int rmpc_solve(rmpc_handle *h, void *stream)
 {
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve: null handle");
+    if (h->W.as_rti) /* AC/ocp_nlp/ocp_nlp_sqp_rti.c:1150-1154 */
+        return fail(h, RMPC_EINVAL, "rmpc_solve: rti_phase PREPARATION_AND_FEEDBACK is not supported with AS-RTI (as_rti_level != 4)");
     ON_DEVICE(h);
     h->W.rti_phase = 0;
     return launch_loop(h, 1, 0, (cudaStream_t) stream);
@@ -619,6 +652,8 @@ extern "C" int rmpc_solve_rti_phase(rmpc_handle *h, int phase, void *stream)
     if (!h) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: null handle");
     if (h->D.solver_type != RMPC_SOLVER_SQP_RTI) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: rti_phase is only supported for SQP_RTI");
     if (phase < 0 || phase > 2) return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: phase must be 0, 1 or 2");
+    if (phase == 0 && h->W.as_rti)
+        return fail(h, RMPC_EINVAL, "rmpc_solve_rti_phase: rti_phase PREPARATION_AND_FEEDBACK is not supported with AS-RTI (as_rti_level != 4)");
     ON_DEVICE(h);
     h->W.rti_phase = phase;
     int rc = launch_loop(h, 1, 0, (cudaStream_t) stream);

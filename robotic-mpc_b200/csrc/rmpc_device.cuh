@@ -692,7 +692,12 @@ RDN double nlp_linearise(const RmpcChain &ch, const RmpcDims &D, const Inst &I_,
         if (i == 0)
         {
             RD_UNROLL
-            for (int k = 0; k < NX; k++) (I.head + H_DX0)[k] = x0[k] - v[6 + k];
+            for (int k = 0; k < NX; k++)
+            {
+                (I.head + H_DX0)[k] = x0[k] - v[6 + k];
+                (I.head + H_B0)[k] = b[k];
+                (I.head + H_XLIN0)[k] = v[6 + k];
+            }
         }
     }
     for (int k = lane; k < NV; k += GL) AR(rqz)[NV * N + k] = 0.0; /* stage N: no cost (ny_e = 0) */
@@ -2481,8 +2486,12 @@ RD void qp_restore(const RmpcDims &D, const Inst &I)
  * AC/ocp_nlp/ocp_nlp_globalization_merit_backtracking.c:705-755), ocp_nlp_line_search (:290-408, alpha = 1, 0.7, ...
  * while alpha*0.7 > 0.05; the last alpha is taken untested), ocp_nlp_update_variables_sqp
  * (AC/ocp_nlp/ocp_nlp_common.c:3259-3318, full_step_dual = 0).  Returns 1 on a NaN/inf merit value. */
+/* trial: workspace of the trial iterates, null = the slab's tux.  acados uses work->tmp_nlp_out for them -- the SAME buffer
+ * AS-RTI level A keeps its iterate backup in (AC/ocp_nlp/ocp_nlp_sqp_rti.c:792,822,1104 vs
+ * ocp_nlp_globalization_merit_backtracking.c:308-374), so with level A the 'restored' primal iterate is the last trial point
+ * of the last line search; passing the backup's ux block here reproduces that. */
 RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, int nlp_iter, double *alpha_out,
-                               double *cost_new, int *cost_valid)
+                               double *cost_new, int *cost_valid, const double *x0, int lin_valid, double *trial = nullptr)
 {
     *cost_valid = 0; /* set when the accepted trial point's cost is known from its merit evaluation */
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
@@ -2511,14 +2520,17 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
         else { const double t1 = 0.5 * (t0 + AR(wlam)[k]); AR(wlam)[k] = t0 > t1 ? t0 : t1; }
     }
     rd_sync();
-    const double m0 = nlp_merit_lin(D, I, I.z);
+    /* merit value at the current iterate: from the linearisation of this iterate where there is one (lin_valid), else by a
+     * kinematics pass (AS-RTI levels B, C move the iterate without re-linearising) */
+    const double m0 = lin_valid ? nlp_merit_lin(D, I, x0) : nlp_merit(ch, D, I, AR(ux), x0, nullptr);
+    if (!trial) trial = AR(tux);
     double alpha = 1.0, m1 = 0.0, c1 = 0.0;
     int accepted = 0;
     while (alpha * 0.7 > 0.05)
     {
-        grp_xpay_to(AR(tux), AR(ux), AR(sux), alpha, (N + 1) * NV);
+        grp_xpay_to(trial, AR(ux), AR(sux), alpha, (N + 1) * NV);
         rd_sync();
-        m1 = nlp_merit(ch, D, I, AR(tux), I.z, &c1);
+        m1 = nlp_merit(ch, D, I, trial, x0, &c1);
         const bool bad = (m1 != m1) || (m1 - m1 != 0.0);
         if (m1 < m0 && !bad) { accepted = 1; *cost_new = c1; *cost_valid = 1; break; }
         alpha *= 0.7;
@@ -2545,12 +2557,14 @@ RDN int nlp_line_search_update(const RmpcChain &ch, const RmpcDims &D, const Ins
 
 /* ocp_qp_xcond_solve (AC/ocp_qp/ocp_qp_xcond_solver.c:518-576): reduce -> IPM -> restore.  warm start bookkeeping:
  * flags[1] != 0 until the first QP of the instance's lifetime has been solved (reference quirk, see ipm_init). */
-RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp, int *iters, double *tq)
+RD int qp_solve(const RmpcDims &D, const Inst &I, GrpSmem &sm, int init_from_nlp, int *iters, double *tq, int keep_warm = 0)
 {
     const int N = D.N, lane = rd_lane();
     const int warm = I.flags[1] ? 2 : 0;
     rd_sync();
-    if (lane == 0) I.flags[1] = 0;
+    /* keep_warm: QPs of an AS-RTI preparation -- the option is only put back to its default by a FEEDBACK phase
+     * (AC/ocp_nlp/ocp_nlp_sqp_rti.c:590-593), so the level-D iterations of a first call all run with warm_start 2 */
+    if (lane == 0 && !keep_warm) I.flags[1] = 0;
     const double tx0 = rd_time();
     qp_reduce(D, I);
     if (init_from_nlp && warm == 2)
@@ -2592,48 +2606,274 @@ RD void step_timers_clear(StepOut &o)
     o.tq[0] = o.tq[1] = o.tq[2] = o.tq[3] = o.tq[4] = 0.0;
 }
 
+/* ---------------------------------------------------------------------------------------------- AS-RTI
+ * Advanced-step real-time iterations, ocp_nlp_sqp_rti_preparation_advanced_step (AC/ocp_nlp/ocp_nlp_sqp_rti.c:773-1100): the
+ * PREPARATION phase first solves an ADVANCED problem -- stage-0 state fixed at the prediction phi(x_0, u_0) of the current
+ * iterate (as_rti_advance_problem, SIMULATE_ADVANCE, :697-727) -- by
+ *   level A  one QP with the matrices AND vectors of the last linearisation (iterate restored to that point);
+ *   level B  as_rti_iter zero-order iterations: gaps and bound residuals re-evaluated, gradient corrected by H * last step
+ *            (ocp_nlp_zero_order_qp_update, AC/ocp_nlp/ocp_nlp_common.c:3109-3160);
+ *   level C  as_rti_iter iterations with exact gaps, bound residuals and cost gradient, matrices kept
+ *            (ocp_nlp_level_c_update, :3163-3232; its adjoint correction (BAbt_new - BAbt_old) pi vanishes: linear dynamics);
+ *   level D  as_rti_iter full SQP iterations;
+ * each followed by the merit line search / iterate update, and then re-linearises (the normal preparation).  The FEEDBACK
+ * phase is the standard one.  The very first call only linearises.  iter counts like nlp_mem->iter does: it decides between
+ * initialising and updating the merit weights (ocp_nlp_globalization_merit_backtracking.c:321-328). */
+RD void asrti_backup(const RmpcDims &D, const Inst &I, double *bk, int restore)
+{
+    const int lane = rd_lane(), Sp = I.Sp;
+    double *bux = bk, *bpi = bk + (long) Sp * NV, *blam = bpi + (long) Sp * NX, *bl0 = blam + (long) Sp * NB;
+    const int N = D.N;
+    if (restore)
+    {
+        for (int k = lane; k < (N + 1) * NV; k += GL) AR(ux)[k] = bux[k];
+        for (int k = lane; k < N * NX; k += GL) AR(pi)[k] = bpi[k];
+        for (int k = lane; k < (N + 1) * NB; k += GL) AR(lam)[k] = blam[k];
+        for (int k = lane; k < NB; k += GL) (I.head + H_LAMX0)[k] = bl0[k];
+    }
+    else
+    {
+        for (int k = lane; k < (N + 1) * NV; k += GL) bux[k] = AR(ux)[k];
+        for (int k = lane; k < N * NX; k += GL) bpi[k] = AR(pi)[k];
+        for (int k = lane; k < (N + 1) * NB; k += GL) blam[k] = AR(lam)[k];
+        for (int k = lane; k < NB; k += GL) bl0[k] = (I.head + H_LAMX0)[k];
+    }
+    rd_sync();
+}
+
+/* the vectors of the QP as ocp_nlp_approximate_qp_vectors_sqp leaves them: the x0 elimination of the last QP solve is undone
+ * (qp_reduce works in place: r_0 and b_0 come back from their copies) */
+RD void asrti_unreduce(const Inst &I, int redo_b0)
+{
+    const int lane = rd_lane();
+    if (lane < 6) AR(rqz)[lane] = (I.head + H_G0U)[lane];
+    if (redo_b0 && lane < NX) AR(b)[lane] = (I.head + H_B0)[lane];
+    rd_sync();
+}
+
+struct GradEmit
+{ /* cost gradient only: the Gauss-Newton data Jc of the last linearisation stays */
+    double *g;
+    const double *par, *yr;
+    double dt, wr[5], gqd0[6];
+    RDM void begin(const double *y5)
+    {
+        RD_UNROLL
+        for (int m = 0; m < 5; m++) wr[m] = dt * par[RP_WTASK + m] * (y5[m] - yr[m]);
+    }
+    RDM void operator()(int k, const double *Jq, double Jd) const
+    {
+        double gq = 0.0, gqd = gqd0[k];
+        RD_UNROLL
+        for (int m = 0; m < 5; m++) gq += Jq[m] * wr[m];
+        gqd += Jd * wr[4];
+        g[6 + k] = gq;
+        g[12 + k] = gqd;
+    }
+};
+
+/* Vectors of the QP at the CURRENT iterate with the matrices of the last linearisation.  MODE 1 (level B): dynamics gaps,
+ * bound residuals, r += H * (last step); MODE 2 (level C): gaps, bound residuals, r = exact cost gradient. */
+template <int MODE>
+RDN void asrti_update_vectors(const RmpcChain &ch, const RmpcDims &D, const Inst &I_, const double *x0)
+{
+    const Inst I = I_;
+    const int N = D.N, lane = rd_lane();
+    const double dt = D.dt;
+    const double *par = I.par;
+    for (int i = lane; i < N; i += GL)
+    {
+        double v[NV];
+        load18(AR(ux) + NV * i, v);
+        double *g = AR(rqz) + NV * i;
+        const double *sp = I.stg ? I.stg + (long) RT_COUNT * i : nullptr, *yr = yref_of(par, I.stg, i);
+        if (MODE == 1)
+        { /* r += RSQ * step (dsymv_l on the Gauss-Newton Hessian of the last linearisation) */
+            double s[NV], hv[NV];
+            load18(AR(sux) + NV * i, s);
+            RD_UNROLL
+            for (int k = 0; k < NV; k++) hv[k] = 0.0;
+            task_hess_mv(AR(Jc) + NJ * i, s + 6, hv + 6);
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                const StageConst c = stage_const(par, dt, k);
+                hv[k] += c.hu * s[k] + c.hs * s[12 + k];
+                hv[12 + k] += c.hs * s[k] + c.hq * s[12 + k];
+            }
+            RD_UNROLL
+            for (int k = 0; k < NV; k++) g[k] += hv[k];
+        }
+        else
+        {
+            double y5[5];
+            GradEmit em;
+            em.g = g;
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                const double wq = par[RP_WQDD + k], wu = 2.0 * par[RP_WU + k];
+                const double cu = par[RP_B2 + k] / dt, cq = (par[RP_A22 + k] - 1.0) / dt;
+                const double a = (cu * v[k] + cq * v[12 + k]) - yr[11 + k];
+                g[k] = dt * (wu * (v[k] - yr[5 + k]) + wq * cu * a);
+                em.gqd0[k] = dt * (wq * cq * a);
+            }
+            em.par = par;
+            em.yr = yr;
+            em.dt = dt;
+            ur10_task<true>(ch, par, v + 6, v + 12, y5, em);
+        }
+        const double *xn = AR(ux) + NV * (i + 1) + 6;
+        double *b = AR(b) + NX * i, *d = AR(d) + NB * i;
+        RD_UNROLL
+        for (int k = 0; k < 6; k++)
+        {
+            b[k] = (v[6 + k] + par[RP_A12 + k] * v[12 + k]) + par[RP_B1 + k] * v[k] - xn[k];
+            b[6 + k] = par[RP_A22 + k] * v[12 + k] + par[RP_B2 + k] * v[k] - xn[6 + k];
+        }
+        RD_UNROLL
+        for (int j = 0; j < 12; j++)
+        {
+            if (i == 0 && j >= 6) { d[j] = 0.0; d[12 + j] = 0.0; }
+            else { d[j] = lb_of(par, sp, j) - v[j]; d[12 + j] = v[j] - ub_of(par, sp, j); }
+        }
+        if (i == 0)
+        {
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) (I.head + H_DX0)[k] = x0[k] - v[6 + k];
+        }
+    }
+    if (I.pe)
+    { /* terminal row: function value at the new x_N, gradient row of the last linearisation */
+        const double h = term_eval(I.pe, AR(ux) + NV * N + 6, nullptr);
+        if (lane == 0)
+        {
+            AR(d)[TERM_LO(N)] = I.pe[RE_LH] - h;
+            AR(d)[TERM_UP(N)] = h - I.pe[RE_UH];
+        }
+    }
+    rd_sync();
+}
+
 /* ocp_nlp_sqp_rti, PREPARATION_AND_FEEDBACK (AC/ocp_nlp/ocp_nlp_sqp_rti.c:455-646,1123-1175) */
 /* phase (opts->rti_phase, :1140-1170): 0 = both, 1 = PREPARATION only -- everything that does not depend on x0: model
  * functions, Gauss-Newton data, dynamics gaps, bound residuals (ocp_nlp_approximate_qp_matrices) --, 2 = FEEDBACK only:
  * the x0-dependent right-hand side (here: dx0 of the stage-0 equality), QP solve, globalisation and iterate update.
  * Preparation followed by feedback gives bit-identical results to the combined call for the same x0. */
-RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o, int phase)
+/* as_level / as_iter / bk: AS-RTI level (-1: standard RTI), iterations and level-A backup of this instance (RmpcWs) */
+RD void solve_rti(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem &sm, StepOut &o, int phase, int as_level = -1,
+                  int as_iter = 0, double *bk = nullptr)
 {
     o.sqp_iter = 0; o.qp_iter = 0; o.qp_status = 0; o.alpha = 0.0; o.status = 0;
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0;
     step_timers_clear(o);
     double tt = rd_time();
+    const int lane = rd_lane();
     if (phase != 2)
     {
+        int iter = 0; /* nlp_mem->iter, reset by every preparation (reset_stats_and_sub_timers) */
+        const int first_call = I.flags[0];
+        if (as_level >= 0 && phase == 1 && (!first_call || as_level == 3))
+        { /* ocp_nlp_sqp_rti_preparation_advanced_step; the first call only linearises -- except level D, whose iterations are
+           * not guarded by is_first_call (:1018) and then run on the stage-0 bounds as they are */
+            double *x0a = I.head + H_X0ADV;
+            const double *par = I.par;
+            rd_sync();
+            if (first_call)
+            {
+                if (lane < NX) x0a[lane] = I.z[lane];
+            }
+            else if (lane < 6)
+            { /* as_rti_advance_problem: lbx = ubx = (phi(x_0, u_0) - x_1) + x_1 of the current iterate */
+                const double *v = AR(ux), *xn = AR(ux) + NV + 6;
+                const double g0 = (v[6 + lane] + par[RP_A12 + lane] * v[12 + lane]) + par[RP_B1 + lane] * v[lane] - xn[lane];
+                const double g1 = par[RP_A22 + lane] * v[12 + lane] + par[RP_B2 + lane] * v[lane] - xn[6 + lane];
+                x0a[lane] = g0 + xn[lane];
+                x0a[6 + lane] = g1 + xn[6 + lane];
+            }
+            rd_sync();
+            int qi = 0, failed = 0;
+            if (as_level == 0)
+            { /* level A: the iterate goes back to the last linearisation point; only the stage-0 equality changes */
+                asrti_backup(D, I, bk, 1);
+                asrti_unreduce(I, 1);
+                /* bound residuals are re-formed from the constraint values kept at the linearisation (update_qp_vectors,
+                 * AC/ocp_nlp/ocp_nlp_constraints_bgh.c:1564-1586): only the moved stage-0 bounds change anything */
+                if (lane < NX) (I.head + H_DX0)[lane] = x0a[lane] - (I.head + H_XLIN0)[lane];
+                rd_sync();
+                { const double t = rd_time(); o.t_lin += t - tt; tt = t; }
+                iter += 1;
+                o.qp_status = qp_solve(D, I, sm, 0, &qi, o.tq, 1);
+                o.qp_iter += qi;
+                { const double t = rd_time(); o.t_qp += t - tt; tt = t; }
+                /* no status test here in the reference (:838-866): the iterate is updated whatever the QP returned */
+                int cv;
+                double cn;
+                if (nlp_line_search_update(ch, D, I, iter, &o.alpha, &cn, &cv, x0a, 0, bk)) { o.status = 1; failed = 1; }
+                { const double t = rd_time(); o.t_glob += t - tt; tt = t; }
+            }
+            else
+            {
+                for (; iter < as_iter && !failed; iter++)
+                {
+                    if (as_level == 1) { asrti_unreduce(I, 0); asrti_update_vectors<1>(ch, D, I, x0a); }
+                    else if (as_level == 2) asrti_update_vectors<2>(ch, D, I, x0a);
+                    else nlp_linearise(ch, D, I, x0a);
+                    { const double t = rd_time(); o.t_lin += t - tt; tt = t; }
+                    o.qp_status = qp_solve(D, I, sm, 0, &qi, o.tq, 1);
+                    o.qp_iter += qi;
+                    { const double t = rd_time(); o.t_qp += t - tt; tt = t; }
+                    if (o.qp_status != 0 && o.qp_status != 2) { o.status = 4; failed = 1; break; }
+                    int cv;
+                    double cn;
+                    if (nlp_line_search_update(ch, D, I, iter, &o.alpha, &cn, &cv, x0a, as_level == 3)) { o.status = 1; failed = 1; }
+                    { const double t = rd_time(); o.t_glob += t - tt; tt = t; }
+                }
+            }
+            if (failed)
+            { /* the reference returns from the preparation without re-linearising (:851-866,930-945) */
+                if (lane == 0) I.flags[3] = iter;
+                rd_sync();
+                o.sqp_iter = iter;
+                o.cost_valid = 0;
+                return;
+            }
+        }
         o.cost = nlp_linearise(ch, D, I, I.z);
-        if (rd_lane() == 0) (I.head + H_LINCOST)[0] = o.cost;
+        if (lane == 0) { (I.head + H_LINCOST)[0] = o.cost; I.flags[3] = iter; }
+        if (as_level == 0 && phase == 1) asrti_backup(D, I, bk, 0); /* level A: tmp_nlp_out <- nlp_out (:1080-1085) */
+        o.sqp_iter = iter;
     }
     else
     {
         /* ocp_nlp_approximate_qp_vectors_sqp: only the stage-0 state equality depends on x0 */
-        const int l = rd_lane();
-        if (l < NX) (I.head + H_DX0)[l] = I.z[l] - AR(ux)[6 + l];
+        if (lane < NX) (I.head + H_DX0)[lane] = I.z[lane] - AR(ux)[6 + lane];
         rd_sync();
         o.cost = (I.head + H_LINCOST)[0];
     }
     o.cost_valid = 1; /* cost at the iterate the step starts from; replaced below once the iterate moves */
-    { const double t = rd_time(); o.t_lin = t - tt; tt = t; }
+    { const double t = rd_time(); o.t_lin += t - tt; tt = t; }
     if (phase == 1) return;
     const int first = I.flags[0];
+    const int iter = (phase == 2 ? I.flags[3] : 0) + 1; /* nlp_mem->iter += 1 (:535) */
     rd_sync();
     int it = 0;
-    const int qs = qp_solve(D, I, sm, first, &it, o.tq);
-    { const double t = rd_time(); o.t_qp = t - tt; tt = t; }
+    /* ocp_nlp_initialize_qp_from_nlp on the first call reaches the interior-point start only through
+     * ocp_qp_xcond_solve (AC/ocp_qp/ocp_qp_xcond_solver.c:548-559); a FEEDBACK phase solves with
+     * ocp_qp_xcond_condense_rhs_and_solve (:614-660), which does not look at that request: the first QP of a split call
+     * then starts from the QP memory as it is (warm_start 2: zeros clipped at 0.1) */
+    const int qs = qp_solve(D, I, sm, first && phase != 2, &it, o.tq);
+    { const double t = rd_time(); o.t_qp += t - tt; tt = t; }
     PAIR_SYNC();
-    o.sqp_iter = 1; o.qp_iter = it; o.qp_status = qs;
+    o.sqp_iter = iter; o.qp_iter = it; o.qp_status = qs;
     o.res[0] = o.res[1] = o.res[2] = o.res[3] = 0.0; /* rti_log_residuals = 0: the reference reports zeros */
     o.alpha = 0.0;
     if (qs != 0 && qs != 2) { o.status = 4; return; } /* ACADOS_QP_FAILURE, iterate untouched (:609-622) */
     /* globalisation status ignored (:627-635); a NaN merit leaves the iterate where it was */
-    if (nlp_line_search_update(ch, D, I, 1, &o.alpha, &o.cost, &o.cost_valid)) o.cost_valid = 1;
-    if (rd_lane() == 0) I.flags[0] = 0;
+    if (nlp_line_search_update(ch, D, I, 1, &o.alpha, &o.cost, &o.cost_valid, I.z, 1, as_level == 0 ? bk : nullptr)) o.cost_valid = 1;
+    if (lane == 0) I.flags[0] = 0;
     rd_sync();
-    o.t_glob = rd_time() - tt;
+    o.t_glob += rd_time() - tt;
     o.status = 0;
 }
 
@@ -2676,7 +2916,7 @@ RD void solve_sqp(const RmpcChain &ch, const RmpcDims &D, const Inst &I, GrpSmem
             stat[RQ_COUNT * (it + 1) + RQ_QP_ITER] = qi;
         }
         if (qs != 0 && qs != 2) { o.sqp_iter = it + 1; o.status = 4; return; }
-        const int ls = nlp_line_search_update(ch, D, I, it, &o.alpha, &o.cost, &o.cost_valid);
+        const int ls = nlp_line_search_update(ch, D, I, it, &o.alpha, &o.cost, &o.cost_valid, I.z, 1);
         o.t_glob += rd_time() - tt;
         if (log) stat[RQ_COUNT * (it + 1) + RQ_ALPHA] = o.alpha;
         if (ls) { o.cost = cost; o.cost_valid = 1; o.status = 1; return; }
@@ -2735,7 +2975,20 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
         StepOut o;
         PAIR_SYNC();
         const double t_begin = rd_time();
-        if (D.solver_type == RMPC_SQP_RTI) solve_rti(ch, D, I, sm, o, advance ? 0 : W.rti_phase);
+        if (D.solver_type == RMPC_SQP_RTI)
+        {
+            double *bk = W.asrti ? W.asrti + inst * RMPC_ASRTI_STRIDE(W.Sp) : nullptr;
+            if (advance && W.as_rti)
+            { /* AS-RTI closed loop: advanced preparation on the prediction, then feedback on the measured state */
+                StepOut op;
+                solve_rti(ch, D, I, sm, op, 1, W.as_rti - 1, W.as_rti_iter, bk);
+                solve_rti(ch, D, I, sm, o, 2, W.as_rti - 1, W.as_rti_iter, bk);
+                o.qp_iter += op.qp_iter;
+                o.t_lin += op.t_lin; o.t_qp += op.t_qp; o.t_glob += op.t_glob;
+                for (int k = 0; k < 5; k++) o.tq[k] += op.tq[k];
+            }
+            else solve_rti(ch, D, I, sm, o, advance ? 0 : W.rti_phase, W.as_rti - 1, W.as_rti_iter, bk);
+        }
         else solve_sqp(ch, D, I, sm, o, W.sqpstat ? W.sqpstat + inst * (long) (D.max_iter + 2) * RQ_COUNT : nullptr);
         const double t_solve = rd_time() - t_begin; /* stands in for get_stats('time_tot') (R/simulator.py:220) */
         /* solver.get_cost(): cost at the returned iterate (T/acados_ocp_solver.py:1664-1679).  The solve usually knows it

@@ -107,7 +107,10 @@ enum
     H_G0U = 60,     /* 8 : stage-0 control gradient before the x0 elimination */
     H_QLAMX0 = 68,  /* 24: multipliers of the eliminated equalities recovered from the QP */
     H_LINCOST = 92, /* 1 : cost at the linearisation point, carried from an RTI preparation phase to its feedback phase */
-    RMPC_HEAD = 96
+    H_X0ADV = 96,   /* 12: AS-RTI: predicted initial state of the advanced problem (lbx = ubx of stage 0 during a preparation) */
+    H_B0 = 108,     /* 12: dynamics gap of stage 0 at the last linearisation, before the x0 elimination folds dx0 into it */
+    H_XLIN0 = 120,  /* 12: x_0 of the iterate the last linearisation was made at (acados: constr_eval_no_bounds of stage 0) */
+    RMPC_HEAD = 144
 };
 
 typedef struct
@@ -130,7 +133,12 @@ typedef struct
     int shift;         /* closed loop: shift the primal iterate by one stage after every step (0: like the reference) */
     const double *stg; /* [B][N][RT_COUNT] per-stage references and bounds, null: every stage uses "par" */
     double *sqpstat;   /* [B][max_iter + 2][RQ_COUNT] per-iteration statistics of the last SQP solve, null: not kept */
+    int as_rti;        /* SQP_RTI only: 0 standard RTI, else 1 + acados' as_rti_level (1 = A, 2 = B, 3 = C, 4 = D) */
+    int as_rti_iter;   /* iterations of the levels B, C, D inside a preparation (acados as_rti_iter) */
+    double *asrti;     /* [B][RMPC_ASRTI_STRIDE(Sp)] level A: backup of the iterate at the last linearisation point */
 } RmpcWs;
+/* backup of one iterate: ux [Sp][18] | pi [Sp][12] | lam [Sp][24] | lamx0 [24] */
+#define RMPC_ASRTI_STRIDE(Sp) ((long) (Sp) * (RMPC_NV + RMPC_NX + RMPC_NB) + 24)
 
 #ifdef __CUDACC__
 #define RMPC_HD __host__ __device__

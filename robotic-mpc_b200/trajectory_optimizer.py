@@ -51,6 +51,8 @@ class SolverOptions:
         self.nlp_solver_tol_eq = 1e-6
         self.nlp_solver_tol_ineq = 1e-6
         self.nlp_solver_tol_comp = 1e-6
+        self.as_rti_level = 4  # STANDARD_RTI (T/acados_ocp_options.py:137,1189-1208); 0..3 = AS-RTI level A..D
+        self.as_rti_iter = 1
 
     def validate(self):
         if self.nlp_solver_type not in ("SQP", "SQP_RTI"):
@@ -59,6 +61,12 @@ class SolverOptions:
             if getattr(self, key) not in allowed:
                 raise NotImplementedError(f"solver option {key}={getattr(self, key)!r} is not implemented "
                                           f"(supported: {allowed}); see DESIGN.md 'out of scope'")
+        if self.as_rti_level not in (0, 1, 2, 3, 4):
+            raise ValueError('Invalid as_rti_level value must be in [0, 1, 2, 3, 4].')
+        if not (isinstance(self.as_rti_iter, int) and self.as_rti_iter >= 0):
+            raise ValueError('Invalid as_rti_iter value. as_rti_iter must be a nonnegative int.')
+        if self.as_rti_level != 4 and self.nlp_solver_type != "SQP_RTI":
+            raise ValueError("as_rti_level != 4 needs nlp_solver_type 'SQP_RTI'")
         if self.qp_solver_cond_N not in (None, self.N_horizon):
             raise NotImplementedError("partial condensing with qp_solver_cond_N < N is not implemented (SURVEY.md 8(f))")
 
@@ -66,7 +74,7 @@ class SolverOptions:
         """What must be equal for two instances to share one batched launch."""
         return (self.nlp_solver_type, int(self.nlp_solver_max_iter), int(self.qp_solver_iter_max), float(self.qp_tol),
                 float(self.nlp_solver_tol_stat), float(self.nlp_solver_tol_eq), float(self.nlp_solver_tol_ineq),
-                float(self.nlp_solver_tol_comp))
+                float(self.nlp_solver_tol_comp), int(self.as_rti_level), int(self.as_rti_iter))
 
 
 class _Namespace:
@@ -165,11 +173,15 @@ class MPC:
 
 
 def bind_chain(engine, mpcs):
-    """Hand the batch-wide settings that are part of the static key to the engine: kinematic chain, shift option."""
+    """Hand the batch-wide settings that are part of the static key to the engine: kinematic chain, shift option, AS-RTI."""
     chain = getattr(mpcs[0].model, "chain", None)
     if chain is not None:
         engine.set_chain(*chain)
     engine.set_option("shift", 1 if mpcs[0].shift_initial_guess else 0)
+    o = mpcs[0].ocp.solver_options
+    if o.nlp_solver_type == "SQP_RTI" and o.as_rti_level != 4:
+        engine.set_option("as_rti_iter", o.as_rti_iter)
+        engine.set_option("as_rti_level", o.as_rti_level)
 
 
 def bind_terminal(engine, mpcs):
@@ -217,10 +229,16 @@ class BatchedSolver:
             self.engine.set_option("statistics", 1)  # get_stats('statistics') of the last solve, like acados keeps it
 
     def options_set(self, field, value):
-        """``AcadosOcpSolver.options_set`` (T/acados_ocp_solver.py:2220-2340) for the one runtime option the hot path has:
-        ``rti_phase`` (0 preparation + feedback, 1 preparation, 2 feedback; SQP_RTI only, like acados)."""
+        """``AcadosOcpSolver.options_set`` (T/acados_ocp_solver.py:2220-2340) for the runtime options the hot path has:
+        ``rti_phase`` (0 preparation + feedback, 1 preparation, 2 feedback; SQP_RTI only, like acados), ``as_rti_level``
+        (0..3 = A..D, 4 = standard RTI) and ``as_rti_iter``."""
+        if field in ("as_rti_level", "as_rti_iter"):  # T/acados_ocp_solver.py:2294-2300: int options forwarded to the solver
+            if self.mpcs[0].ocp.solver_options.nlp_solver_type != "SQP_RTI":
+                raise ValueError(f"AcadosOcpSolver.options_set(): {field!r} needs an SQP_RTI solver")
+            self.engine.set_option(field, int(value))
+            return
         if field != "rti_phase":
-            raise NotImplementedError(f"options_set({field!r}): only 'rti_phase' can be changed after creation")
+            raise NotImplementedError(f"options_set({field!r}): 'rti_phase', 'as_rti_level' and 'as_rti_iter' can be changed after creation")
         if value not in (0, 1, 2):
             raise ValueError("AcadosOcpSolver.options_set(): argument 'rti_phase' can take only values 0, 1, 2")
         if value and self.mpcs[0].ocp.solver_options.nlp_solver_type != "SQP_RTI":

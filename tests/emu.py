@@ -61,3 +61,8 @@ def plant_record(par, z):
 def set_shift(on):
     """Process-global 'shift' option of the emulated closed loop (rmpc_set_option(h, "shift", .))."""
     C.CDLL(str(SO)).rmpc_emu_set_shift(int(bool(on)))
+
+
+def set_as_rti(level, iters=1):
+    """Process-global AS-RTI level of the emulated closed loop (None / -1: standard RTI, 0..3 = A..D) and its iterations."""
+    C.CDLL(str(SO)).rmpc_emu_set_as_rti(-1 if level is None else int(level), int(iters))

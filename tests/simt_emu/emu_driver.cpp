@@ -26,6 +26,7 @@ void body(void *p, int)
     closed_loop_group(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
 }
 int g_shift = 0;
+int g_as_rti = 0, g_as_rti_iter = 1;
 bool g_custom_chain = false;
 RmpcChain g_chain;
 void current_chain(RmpcChain *ch)
@@ -45,6 +46,8 @@ extern "C" int rmpc_emu_set_chain(const double *xyzR, const int *axis)
 }
 
 extern "C" int rmpc_emu_set_shift(int on) { g_shift = on ? 1 : 0; return 0; }
+/* level: -1 standard RTI, 0..3 = A..D (acados as_rti_level); the emulated closed loop then runs preparation + feedback per step */
+extern "C" int rmpc_emu_set_as_rti(int level, int iter) { g_as_rti = level < 0 ? 0 : level + 1; g_as_rti_iter = iter; return 0; }
 
 /* the per-sample plant record (RK_*, 28 doubles) and the task outputs y5 of one state, with the current chain */
 extern "C" int rmpc_emu_plant_record(const double *par, const double *z, double *rec, double *y5)
@@ -94,6 +97,13 @@ extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, c
     W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
     W.nlog = nsteps; W.step0 = 0;
     W.shift = g_shift;
+    W.as_rti = g_as_rti;
+    W.as_rti_iter = g_as_rti_iter;
+    if (g_as_rti)
+    {
+        W.asrti = (double *) calloc((size_t) B * (size_t) RMPC_ASRTI_STRIDE(W.Sp), sizeof(double));
+        owned.push_back(W.asrti);
+    }
     for (long i = 0; i < B; i++)
     {
         memcpy(W.z + i * NX, z0 + i * NX, NX * sizeof(double));

@@ -87,7 +87,12 @@ int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
  *                    while a level is set; rmpc_closed_loop runs preparation + feedback per step.  Level C has no
  *                    counterpart to check against: the reference aborts in it for a NONLINEAR_LS cost
  *                    ("ocp_nlp_cost_nls_compute_gradient not implemented").
- *   "as_rti_iter" n >= 0  iterations of the levels B, C, D (default 1) */
+ *   "as_rti_iter" n >= 0  iterations of the levels B, C, D (default 1)
+ *   "qp_cond_N" N2 in [1, N]  qp_solver_cond_N of PARTIAL_CONDENSING_HPIPM (AC/ocp_qp/ocp_qp_partial_condensing.c:523-559,
+ *                    H/cond/x_part_cond.c:36-60,486-558): the interior point works on the N2-stage QP whose stages hold the
+ *                    controls of a block of stages and the block's first state.  Default N: no condensing (the reference's
+ *                    setting).  The device reproduces the condensed problem's interior-point iterates -- same QP iteration
+ *                    counts and solution as acados with that cond_N -- without forming the dense blocks. */
 int rmpc_set_option(rmpc_handle *h, const char *name, double value);
 
 /* Replaces <name>_acados_free + _free_capsule. */

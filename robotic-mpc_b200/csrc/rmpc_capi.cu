@@ -339,6 +339,13 @@ extern "C" int rmpc_set_option(rmpc_handle *h, const char *name, double value)
         if (h->W.as_rti_iter < 1) h->W.as_rti_iter = 1;
         return 0;
     }
+    if (f == "qp_cond_N")
+    { /* qp_solver_cond_N (T/acados_ocp_options.py:72-84): horizon of the partially condensed QP; N (or 0) = no condensing */
+        const int n2 = (int) value;
+        if ((double) n2 != value || n2 < 0 || n2 > h->D.N) return fail(h, RMPC_EINVAL, "rmpc_set_option: qp_cond_N must be an integer in [1, N]");
+        h->W.cond_N = (n2 == h->D.N) ? 0 : n2;
+        return 0;
+    }
     if (f == "as_rti_iter")
     {
         const int it = (int) value;

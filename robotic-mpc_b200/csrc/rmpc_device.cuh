@@ -258,6 +258,7 @@ struct Inst
     double *head, *arr0, *z;
     int *flags;
     int Sp;
+    int N2; /* horizon of the partially condensed QP (qp_solver_cond_N), 0: no condensing */
     unsigned pair; /* lane mask of all groups of this warp that run an instance (re-convergence points) */
 };
 /* Re-convergence point for the groups that share a warp.  They run independent instances and may drift apart inside
@@ -272,6 +273,7 @@ RD Inst inst_view(const RmpcWs &w, int N, long i)
     v.head = w.slab + i * w.slab_stride;
     v.arr0 = v.head + RMPC_HEAD;
     v.Sp = w.Sp;
+    v.N2 = (w.cond_N > 0 && w.cond_N < N) ? w.cond_N : 0;
     v.par = w.par + i * RP_COUNT;
     v.pe = w.pe ? w.pe + i * RE_COUNT : nullptr;
     v.stg = w.stg ? w.stg + i * (long) N * RT_COUNT : nullptr;
@@ -921,6 +923,98 @@ RD void qp_reduce(const RmpcDims &D, const Inst &I)
  * warm = 0 (every QP but the first, see oracle/rmpc_oracle.c:solve_qp for the reference quirk): ux = 0, pi = 0,
  * t = slack pushed to >= 0.1 by moving ux, lam = mu0 / t with mu0 = 1 (t0_init 2, var_init_scheme 1, :1837-1978).
  * The primal iterate is zeroed first in both cases (AC/ocp_qp/ocp_qp_hpipm.c:309-316). */
+/* Partial condensing, qp_solver_cond_N = N2 < N (AC/ocp_qp/ocp_qp_partial_condensing.c:523-559,664-689; H/cond/x_part_cond.c:
+ * 486-558, block sizes :36-60): acados hands HPIPM an N2-stage QP whose stage k holds the controls of the stages of block k
+ * and the state at its first stage; the states inside a block are eliminated through the dynamics and their bounds become
+ * general constraints.  The interior-point iterates of that QP are reproduced here WITHOUT forming its dense blocks.  Newton
+ * steps on the condensed KKT system are the Newton steps of the stage-wise system restricted to iterates that (i) satisfy the
+ * dynamics inside every block and (ii) carry, inside every block, the multipliers pi given by the adjoint recursion
+ * (stationarity of the eliminated states) -- both properties are linear, so every damped Newton step preserves them, the
+ * eliminated rows contribute nothing to the residual norms, and the set of inequality multipliers / slacks is the same.  What
+ * differs is the START: OCP_QP_INIT_VAR on the condensed QP (H/ocp_qp/x_ocp_qp_ipm.c:1724-1817) zeroes u and the block-start
+ * states only and treats the bounds of the eliminated states as GENERAL rows (slack = max(0.1, +-(C x + D u) - d), no move
+ * of the variables).  ipm_init_pcond() builds exactly that starting point; the stage-wise Riccati sweeps then walk the
+ * condensed problem's iterates (to rounding) and the final iterate is the expanded solution (d_part_cond_qp_expand_sol).
+ * Forming the dense blocks would not shorten the dependent chain on this machine: the factorisation of a block of k stages
+ * has the same 6 k sequential pivots as k stage-wise steps, at (6 k + 12)^3 / 3 instead of k 18^3 / 3 flops. */
+RD void task_hess_mv(const double *Jc, const double *x, double *y);
+RD void pc_block(int N, int N2, int k, int *s, int *bs)
+{
+    const int b0 = N / N2, r = N - N2 * b0;
+    *bs = b0 + (k < r ? 1 : 0);
+    *s = k < r ? k * (b0 + 1) : r * (b0 + 1) + (k - r) * b0;
+}
+RD bool pc_is_start(int N, int N2, int i)
+{
+    const int b0 = N / N2, r = N - N2 * b0, big = r * (b0 + 1);
+    return i < big ? (i % (b0 + 1)) == 0 : ((i - big) % b0) == 0;
+}
+
+RDN void ipm_init_pcond(const RmpcDims &D, const Inst &I_, const GrpSmem &sm, int warm)
+{
+    const Inst I = I_;
+    const int N = D.N, N2 = I.N2, lane = rd_lane();
+    for (int kb = lane; kb < N2; kb += GL)
+    {
+        int s, bs;
+        pc_block(N, N2, kb, &s, &bs);
+        if (bs < 2) continue;
+        /* (i) states inside the block from the dynamics, bounds of those states as general rows */
+        double x[NX];
+        RD_UNROLL
+        for (int k = 0; k < NX; k++) x[k] = AR(sux)[NV * s + 6 + k];
+        for (int i = s; i < s + bs - 1; i++)
+        {
+            const double *u = AR(sux) + NV * i, *b = AR(b) + NX * i;
+            double xn[NX];
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                xn[k] = (x[k] + C_A12(k) * x[6 + k]) + C_B1(k) * u[k] + b[k];
+                xn[6 + k] = C_A22(k) * x[6 + k] + C_B2(k) * u[k] + b[6 + k];
+            }
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) { x[k] = xn[k]; AR(sux)[NV * (i + 1) + 6 + k] = xn[k]; }
+            if (warm != 2)
+            {
+                const double *d = AR(d) + NB * (i + 1);
+                RD_UNROLL
+                for (int j = 0; j < 6; j++)
+                {
+                    double tl = xn[j] - d[6 + j], tu = -xn[j] - d[18 + j];
+                    tl = 1e-1 > tl ? 1e-1 : tl;
+                    tu = 1e-1 > tu ? 1e-1 : tu;
+                    AR(st)[NB * (i + 1) + 6 + j] = tl;
+                    AR(st)[NB * (i + 1) + 18 + j] = tu;
+                    AR(slam)[NB * (i + 1) + 6 + j] = 1.0 / tl;
+                    AR(slam)[NB * (i + 1) + 18 + j] = 1.0 / tu;
+                }
+            }
+        }
+        /* (ii) multipliers of the dynamics inside the block: stationarity of the eliminated states, backwards from the
+         *      multiplier of the block's last stage */
+        for (int i = s + bs - 1; i > s; i--)
+        {
+            double v[NV], g[NX];
+            load18(AR(sux) + NV * i, v);
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) g[k] = AR(rqz)[NV * i + 6 + k];
+            task_hess_mv(AR(Jc) + NJ * i, v + 6, g);
+            const double *pin = AR(spi) + NX * i, *l = AR(slam) + NB * i;
+            RD_UNROLL
+            for (int k = 0; k < 6; k++)
+            {
+                g[k] += pin[k];
+                g[6 + k] += sm.hc[6 + k] * v[k] + sm.hc[12 + k] * v[12 + k] + C_A12(k) * pin[k] + C_A22(k) * pin[6 + k];
+                g[k] += l[18 + k] - l[6 + k];
+            }
+            RD_UNROLL
+            for (int k = 0; k < NX; k++) AR(spi)[NX * (i - 1) + k] = g[k];
+        }
+    }
+    rd_sync();
+}
+
 RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
 {
     const Inst I = I_; /* by value: registers, not re-read from the caller's frame after every store */
@@ -941,6 +1035,7 @@ RDN void ipm_init(const RmpcDims &D, const Inst &I_, int warm)
         for (int h = 0; h < 12; h += 6)
         {
             if (i == 0 && h >= 6) continue;
+            if (h >= 6 && warm != 2 && I.N2 && !pc_is_start(N, I.N2, i)) continue; /* general rows of the condensed QP: ipm_init_pcond */
             double la[6], lb[6], ta[6], tb[6];
             double *pl = AR(slam) + NB * i + h, *pt = AR(st) + NB * i + h;
             if (warm == 2)
@@ -2350,6 +2445,7 @@ RDN int ipm_solve_qp(const RmpcDims &D, const Inst &I, GrpSmem &sm, int warm, in
     double t0 = rd_time(), t1;
 #define TQ(k) do { t1 = rd_time(); tq[k] += t1 - t0; t0 = t1; } while (0)
     ipm_init(D, I, warm);
+    if (I.N2) ipm_init_pcond(D, I, sm, warm);
     double nrm[6], inrm[6], alpha = 1.0, sums[2];
     double sum_lt = ipm_res_sweep<0>(D, I, sm, 0.0, nrm);
     double mu = nc_inv * sum_lt;

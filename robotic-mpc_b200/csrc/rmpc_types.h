@@ -136,6 +136,7 @@ typedef struct
     int as_rti;        /* SQP_RTI only: 0 standard RTI, else 1 + acados' as_rti_level (1 = A, 2 = B, 3 = C, 4 = D) */
     int as_rti_iter;   /* iterations of the levels B, C, D inside a preparation (acados as_rti_iter) */
     double *asrti;     /* [B][RMPC_ASRTI_STRIDE(Sp)] level A: backup of the iterate at the last linearisation point */
+    int cond_N;        /* qp_solver_cond_N: horizon N2 of the partially condensed QP the interior point works on; 0 or N: none */
 } RmpcWs;
 /* backup of one iterate: ux [Sp][18] | pi [Sp][12] | lam [Sp][24] | lamx0 [24] */
 #define RMPC_ASRTI_STRIDE(Sp) ((long) (Sp) * (RMPC_NV + RMPC_NX + RMPC_NB) + 24)

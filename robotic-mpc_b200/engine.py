@@ -198,7 +198,8 @@ class Engine:
         """Runtime option of the handle: 'shift' (0 | 1) = shift the primal iterate by one stage after every closed-loop step;
         'statistics' (0 | 1) = keep the per-iteration table of the last full-SQP solve (``get('sqp_stat')``); 'graph' (0 | 1) =
         ``step_host`` replays a captured CUDA graph (default) or enqueues its copies and kernel one by one; 'as_rti_level'
-        (0..3 = A..D, 4 = standard RTI) and 'as_rti_iter' = acados' advanced-step RTI options (SQP_RTI handles)."""
+        (0..3 = A..D, 4 = standard RTI) and 'as_rti_iter' = acados' advanced-step RTI options (SQP_RTI handles); 'qp_cond_N' =
+        qp_solver_cond_N, the horizon of the partially condensed QP (N = none)."""
         self._check(self.lib.rmpc_set_option(self.h, str(name).encode(), float(value)), f"rmpc_set_option({name})")
 
     def set_chain(self, xyzR=None, axis=None):

@@ -67,14 +67,15 @@ class SolverOptions:
             raise ValueError('Invalid as_rti_iter value. as_rti_iter must be a nonnegative int.')
         if self.as_rti_level != 4 and self.nlp_solver_type != "SQP_RTI":
             raise ValueError("as_rti_level != 4 needs nlp_solver_type 'SQP_RTI'")
-        if self.qp_solver_cond_N not in (None, self.N_horizon):
-            raise NotImplementedError("partial condensing with qp_solver_cond_N < N is not implemented (SURVEY.md 8(f))")
+        if self.qp_solver_cond_N is not None and not (isinstance(self.qp_solver_cond_N, int) and 1 <= self.qp_solver_cond_N <= self.N_horizon):
+            raise ValueError('Invalid qp_solver_cond_N value. qp_solver_cond_N must be a positive int not larger than N_horizon.')
 
     def static_key(self):
         """What must be equal for two instances to share one batched launch."""
         return (self.nlp_solver_type, int(self.nlp_solver_max_iter), int(self.qp_solver_iter_max), float(self.qp_tol),
                 float(self.nlp_solver_tol_stat), float(self.nlp_solver_tol_eq), float(self.nlp_solver_tol_ineq),
-                float(self.nlp_solver_tol_comp), int(self.as_rti_level), int(self.as_rti_iter))
+                float(self.nlp_solver_tol_comp), int(self.as_rti_level), int(self.as_rti_iter),
+                int(self.qp_solver_cond_N or self.N_horizon or 0))
 
 
 class _Namespace:
@@ -173,12 +174,14 @@ class MPC:
 
 
 def bind_chain(engine, mpcs):
-    """Hand the batch-wide settings that are part of the static key to the engine: kinematic chain, shift option, AS-RTI."""
+    """Hand the batch-wide settings that are part of the static key to the engine: kinematic chain, shift option, AS-RTI, partial condensing."""
     chain = getattr(mpcs[0].model, "chain", None)
     if chain is not None:
         engine.set_chain(*chain)
     engine.set_option("shift", 1 if mpcs[0].shift_initial_guess else 0)
     o = mpcs[0].ocp.solver_options
+    if o.qp_solver_cond_N is not None:
+        engine.set_option("qp_cond_N", int(o.qp_solver_cond_N))
     if o.nlp_solver_type == "SQP_RTI" and o.as_rti_level != 4:
         engine.set_option("as_rti_iter", o.as_rti_iter)
         engine.set_option("as_rti_level", o.as_rti_level)

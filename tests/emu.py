@@ -66,3 +66,8 @@ def set_shift(on):
 def set_as_rti(level, iters=1):
     """Process-global AS-RTI level of the emulated closed loop (None / -1: standard RTI, 0..3 = A..D) and its iterations."""
     C.CDLL(str(SO)).rmpc_emu_set_as_rti(-1 if level is None else int(level), int(iters))
+
+
+def set_cond_N(n2):
+    """Process-global qp_solver_cond_N of the emulated solver (None / 0: no condensing)."""
+    C.CDLL(str(SO)).rmpc_emu_set_cond_N(0 if n2 is None else int(n2))

@@ -26,7 +26,7 @@ void body(void *p, int)
     closed_loop_group(*j->ch, *j->D, *j->W, j->inst, *j->sm, j->nsteps);
 }
 int g_shift = 0;
-int g_as_rti = 0, g_as_rti_iter = 1;
+int g_as_rti = 0, g_as_rti_iter = 1, g_cond_N = 0;
 bool g_custom_chain = false;
 RmpcChain g_chain;
 void current_chain(RmpcChain *ch)
@@ -46,6 +46,7 @@ extern "C" int rmpc_emu_set_chain(const double *xyzR, const int *axis)
 }
 
 extern "C" int rmpc_emu_set_shift(int on) { g_shift = on ? 1 : 0; return 0; }
+extern "C" int rmpc_emu_set_cond_N(int n2) { g_cond_N = n2; return 0; }
 /* level: -1 standard RTI, 0..3 = A..D (acados as_rti_level); the emulated closed loop then runs preparation + feedback per step */
 extern "C" int rmpc_emu_set_as_rti(int level, int iter) { g_as_rti = level < 0 ? 0 : level + 1; g_as_rti_iter = iter; return 0; }
 
@@ -97,6 +98,7 @@ extern "C" int rmpc_emu_closed_loop_term(const RmpcDims *D, const double *par, c
     W.zlog = zlog; W.ulog = ulog; W.slog = slog; W.summary = summary;
     W.nlog = nsteps; W.step0 = 0;
     W.shift = g_shift;
+    W.cond_N = g_cond_N;
     W.as_rti = g_as_rti;
     W.as_rti_iter = g_as_rti_iter;
     if (g_as_rti)

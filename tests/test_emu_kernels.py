@@ -188,3 +188,58 @@ def test_emulated_as_rti_level_c_runs(built):
     dB, dD = np.abs(out[2]["u"] - out[1]["u"]).max(), np.abs(out[2]["u"] - out[3]["u"]).max()
     assert 0 < dB < 5e-2 and 0 < dD < 5e-2
     assert np.abs(out[2]["summary"][0, :5] - out[3]["summary"][0, :5]).max() < 0.05 * np.abs(out[3]["summary"][0, :5]).max()
+
+
+@pytest.mark.parametrize("N,N2,solver,seed", [(20, 2, 0, 1), (20, 10, 1, 2), (20, 7, 0, 3), (20, 3, 1, 4), (20, 5, 0, 5), (30, 4, 1, 6)])
+def test_emulated_partial_condensing_matches_reference(built, N, N2, solver, seed):
+    """qp_solver_cond_N = N2 < N: acados condenses the horizon into N2 blocks before HPIPM sees the QP.
+    With tight joint bounds the REFERENCE ITSELF gives different interior-point iteration sequences (and solutions that differ
+    at the QP tolerance) for different cond_N; the device must follow the one asked for.  Compared with the compiled acados
+    at that cond_N: controls at 1e-10, status / SQP / QP iteration sequences equal."""
+    import oracle.pyoracle as o
+    import robotic_mpc_b200 as rm
+
+    if not o.REF_SO.exists():
+        pytest.skip("oracle/_ref not built on this machine (needs /root/reference)")
+    rng = np.random.default_rng(100 + seed)
+    ns = 6
+    surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal(6)
+    q0 = o.README_Q0 + rng.uniform(-0.05, 0.05, 6)
+    z0 = np.concatenate([q0, o.README_QD0 + rng.uniform(-0.1, 0.1, 6)])
+    w = rng.uniform(0.06, 0.14)  # joint-angle box around the initial posture: active along the horizon
+    kw = dict(N=N, solver_type=solver, surf=surf, q_min=q0 - w, q_max=q0 + w)
+    g = o.RefLeg().closed_loop(o.make_problem(cond_N=N2, **kw), z0, ns)
+    par = rm.pack_params(1, 0.01, surf=surf[None], q_min=(q0 - w)[None], q_max=(q0 + w)[None])
+    try:
+        emu.set_cond_N(N2)
+        r = emu.closed_loop(par, z0[None], N, solver, ns, seed=3)
+    finally:
+        emu.set_cond_N(None)
+    assert np.abs(r["u"][0] - g["u"]).max() < 1e-10 * np.abs(g["u"]).max() and np.abs(r["z"][0] - g["z"]).max() < 1e-10
+    assert np.array_equal(r["slog"][0, :, 0].astype(int), g["status"])
+    assert np.array_equal(r["slog"][0, :, 1].astype(int), g["sqp_iter"])
+    assert np.array_equal(r["slog"][0, :, 2].astype(int), g["qp_iter"])
+
+
+def test_partial_condensing_changes_the_reference_iterates(built):
+    """The discriminating power of the test above: over its cases the compiled acados with cond_N = N2 and with cond_N = N
+    disagree in their QP iteration sequences at least once, and the un-condensed device run follows the cond_N = N one."""
+    import oracle.pyoracle as o
+    import robotic_mpc_b200 as rm
+
+    if not o.REF_SO.exists():
+        pytest.skip("oracle/_ref not built on this machine (needs /root/reference)")
+    differ = 0
+    for N, N2, solver, seed in [(20, 2, 0, 1), (20, 7, 0, 3), (20, 5, 0, 5)]:
+        rng = np.random.default_rng(100 + seed)
+        surf = np.array([-0.1, 0.1, -0.01, 0.01, 0.01, 0.0]) + 0.01 * rng.standard_normal(6)
+        q0 = o.README_Q0 + rng.uniform(-0.05, 0.05, 6)
+        z0 = np.concatenate([q0, o.README_QD0 + rng.uniform(-0.1, 0.1, 6)])
+        w = rng.uniform(0.06, 0.14)
+        kw = dict(N=N, solver_type=solver, surf=surf, q_min=q0 - w, q_max=q0 + w)
+        a = o.RefLeg().closed_loop(o.make_problem(cond_N=N2, **kw), z0, 6)
+        b = o.RefLeg().closed_loop(o.make_problem(**kw), z0, 6)
+        differ += int(not np.array_equal(a["qp_iter"], b["qp_iter"]))
+        r = emu.closed_loop(rm.pack_params(1, 0.01, surf=surf[None], q_min=(q0 - w)[None], q_max=(q0 + w)[None]), z0[None], N, solver, 6, seed=3)
+        assert np.array_equal(r["slog"][0, :, 2].astype(int), b["qp_iter"])
+    assert differ >= 1

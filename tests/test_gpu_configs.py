@@ -156,3 +156,40 @@ def test_qp_iteration_counts_equal_to_reference(oracle):
             n_tot += ns
     print(f"qp_iter: {n_exc} exceptions in {n_tot} solves")
     assert n_exc == 0
+
+
+@pytest.mark.parametrize("N,N2,solver", [(40, 20, "SQP_RTI"), (40, 8, "SQP"), (40, 4, "SQP_RTI"), (100, 10, "SQP_RTI"), (100, 50, "SQP")])
+def test_partial_condensing_cond_n(oracle, N, N2, solver):
+    """qp_solver_cond_N in {N/2, N/5, N/10} through the C ABI option 'qp_cond_N': 16 instances with a
+    tight joint-angle box (so that the condensed problem's interior-point path differs from the un-condensed one), closed
+    loop against the compiled acados at the same cond_N: controls / states at 1e-6, status, SQP and QP iteration sequences
+    equal; the number of instances where acados' own cond_N = N run takes a different QP iteration sequence is printed."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    if not o.REF_SO.exists():
+        pytest.skip("oracle/_ref did not travel (the port has no condensing)")
+    B, ns = 16, 5 if solver == "SQP" else 10
+    surf, z0 = _inputs(o, B, 900 + N + N2)
+    rng = np.random.default_rng(N2)
+    w = rng.uniform(0.06, 0.14, (B, 1))
+    qmin, qmax = z0[:, :6] - w, z0[:, :6] + w
+    eng = rm.Engine(B, N, solver, dt=0.01, nlog=ns)
+    eng.set_params(rm.pack_params(B, 0.01, surf=surf, q_min=qmin, q_max=qmax))
+    eng.set_option("qp_cond_N", N2)
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    ulog, zlog, slog = (eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog"))
+    eng.close()
+    st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
+    ref = _pool_closed_loops(o, [(dict(N=N, solver_type=st, surf=surf[i], q_min=qmin[i], q_max=qmax[i], cond_N=N2), z0[i], ns) for i in range(B)])
+    ref0 = _pool_closed_loops(o, [(dict(N=N, solver_type=st, surf=surf[i], q_min=qmin[i], q_max=qmax[i]), z0[i], ns) for i in range(B)])
+    n_other = 0
+    for i, g in enumerate(ref):
+        assert relerr(ulog[i], g["u"]) < RTOL and relerr(zlog[i], g["z"]) < RTOL, i
+        assert np.array_equal(slog[i, :, 0].astype(int), g["status"])
+        assert np.array_equal(slog[i, :, 1].astype(int), g["sqp_iter"])
+        assert np.array_equal(slog[i, :, 2].astype(int), g["qp_iter"]), (i, slog[i, :, 2], g["qp_iter"])
+        n_other += int(not np.array_equal(ref0[i]["qp_iter"], g["qp_iter"]))
+    print(f"cond_N {N2} of {N}: acados' cond_N = N run differs in its QP iteration sequence for {n_other} of {B} instances")

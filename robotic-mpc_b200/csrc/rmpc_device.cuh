@@ -58,6 +58,12 @@ RD void rd_cp_async16(double *dst_smem, const double *src) { dst_smem[0] = src[0
 RD void rd_cp_commit() {}
 RD void rd_cp_wait1() {}
 RD void rd_cp_wait0() {}
+RD void rd_bar_init(unsigned long long *) {}
+RD void rd_bar_inval(unsigned long long *) {}
+RD void rd_bar_expect(unsigned long long *, unsigned) {}
+RD void rd_bulk_cp(double *dst_smem, const double *src, unsigned bytes, unsigned long long *) { memcpy(dst_smem, src, bytes); }
+RD void rd_bar_wait(unsigned long long *, unsigned) {}
+RD void rd_fence_bar_init() {}
 #define RD_UNROLL
 struct rd_double2 { double x, y; };
 #else
@@ -91,6 +97,31 @@ RD void rd_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" 
 RD void rd_cp_async16(double *dst_smem, const double *src)
 {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned) __cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+/* TMA 1-D bulk copy global -> shared (UBLKCP): ONE instruction per contiguous chunk, issued by one lane of the group; the copy
+ * engine generates the addresses and writes shared memory itself -- nothing goes through the LSU address / data pipes that the
+ * sweeps' own shared-memory loads saturate.  Completion is counted in bytes on an mbarrier in shared memory.
+ * src, dst 16-byte aligned, bytes a multiple of 16. */
+RD unsigned rd_smem_u32(const void *p) { return (unsigned) __cvta_generic_to_shared(p); }
+RD void rd_bar_init(unsigned long long *bar) { asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(rd_smem_u32(bar)) : "memory"); }
+RD void rd_bar_inval(unsigned long long *bar) { asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(rd_smem_u32(bar)) : "memory"); }
+RD void rd_fence_bar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+RD void rd_bar_expect(unsigned long long *bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rd_smem_u32(bar)), "r"(bytes) : "memory");
+}
+RD void rd_bulk_cp(double *dst_smem, const double *src, unsigned bytes, unsigned long long *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(rd_smem_u32(dst_smem)), "l"(src),
+                 "r"(bytes), "r"(rd_smem_u32(bar))
+                 : "memory");
+}
+RD void rd_bar_wait(unsigned long long *bar, unsigned parity)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tRD_WAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra RD_DONE_%=;\n\tbra RD_WAIT_%=;\n\tRD_DONE_%=:\n\t}" ::"r"(
+                     rd_smem_u32(bar)),
+                 "r"(parity)
+                 : "memory");
 }
 RD void rd_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 RD void rd_cp_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
@@ -150,6 +181,7 @@ struct GrpSmem
     double pv[12];        /* cost-to-go vector p of stage ss+1 */
     double dp[12];        /* multiplier step of the current stage (forward sweep, residual check) */
     double wv[6];         /* Jc dx of the current stage (forward sweep, residual check) */
+    unsigned long long bar[2]; /* mbarriers of the two staging buffers (bulk-copy staging) */
     double buf[SM_BUF];
 };
 #define C_A12(c) sm.cst[(c)]
@@ -1306,6 +1338,23 @@ RD void fac_stage_in(const Inst &I, double *dst, int ss)
     if (ss > 0) stage_cp(dst + FG_JC, AR(Jc) + NJ * ss, NJ);
 }
 
+/* the same staging with TMA bulk copies: lane 0 of the group arms the buffer's mbarrier with the byte count and issues one
+ * copy per array */
+RD void fac_stage_in_bulk(const Inst &I, double *dst, int ss, unsigned long long *bar)
+{
+    if (rd_lane() == 0)
+    {
+        rd_bar_expect(bar, (unsigned) sizeof(double) * (4 * NB + NV + NX + (ss > 0 ? NJ : 0)));
+        rd_bulk_cp(dst + FG_LAM, AR(slam) + NB * ss, sizeof(double) * NB, bar);
+        rd_bulk_cp(dst + FG_T, AR(st) + NB * ss, sizeof(double) * NB, bar);
+        rd_bulk_cp(dst + FG_RD, AR(res_d) + NB * ss, sizeof(double) * NB, bar);
+        rd_bulk_cp(dst + FG_RM, AR(res_m) + NB * ss, sizeof(double) * NB, bar);
+        rd_bulk_cp(dst + FG_RG, AR(res_g) + NV * ss, sizeof(double) * NV, bar);
+        rd_bulk_cp(dst + FG_RB, AR(res_b) + NX * ss, sizeof(double) * NX, bar);
+        if (ss > 0) rd_bulk_cp(dst + FG_JC, AR(Jc) + NJ * ss, sizeof(double) * NJ, bar);
+    }
+}
+
 /* Shape of the stage body: every section LOADS its operands into registers first, computes, and STORES last, and the lanes
  * run one straight-line instruction stream (roles differ by coefficients, ca / cb / jcol, not by branches) -- shared-memory
  * stores in the middle of a section and divergent blocks both stop the compiler from batching the loads, and a stage then
@@ -1325,8 +1374,16 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
     const double reg = 1e-15, tau_min = 1e-16;
     double *P = FS_P(sm), *Lxu = FS_LXU(sm), *Min = FS_MIN(sm);
     const int slot = lane < 12 ? lane : lane - 12; /* bound slot of the lane (lanes 12.. mirror lanes 0.., results unused) */
+#ifdef RMPC_BULK_STAGING
+    rd_sync();
+    if (lane == 0) { rd_bar_init(&sm.bar[0]); rd_bar_init(&sm.bar[1]); rd_fence_bar_init(); }
+    rd_sync();
+    unsigned phase = 0; /* bit b: parity of the next completion of buffer b's barrier */
+    fac_stage_in_bulk(I, FS_STG(sm, (N - 1) & 1), N - 1, &sm.bar[(N - 1) & 1]);
+#else
     fac_stage_in(I, FS_STG(sm, (N - 1) & 1), N - 1);
     rd_cp_commit();
+#endif
     /* stage N: zero Hessian + reg => P_N = reg I, p_N = res_g_N  (POTRF_L_MN of :871-879) */
     if (R.x)
     {
@@ -1362,10 +1419,17 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
         const bool s0 = (ss == 0);
         double *F = AR(F) + (long) FS * ss;
         const double *G = FS_STG(sm, ss & 1);
+#ifdef RMPC_BULK_STAGING
+        if (ss > 0) fac_stage_in_bulk(I, FS_STG(sm, (ss - 1) & 1), ss - 1, &sm.bar[(ss - 1) & 1]);
+        SEC(0);
+        rd_bar_wait(&sm.bar[ss & 1], (phase >> (ss & 1)) & 1u);
+        phase ^= 1u << (ss & 1);
+#else
         if (ss > 0) fac_stage_in(I, FS_STG(sm, (ss - 1) & 1), ss - 1);
         rd_cp_commit();
         SEC(0);
         rd_cp_wait1();
+#endif
         rd_sync();
         SEC(1);
         /* ------------------------------------------------------------------------------------------------ S1 */
@@ -1596,7 +1660,11 @@ RDN void ipm_factor(const RmpcDims &D, const Inst &I_, GrpSmem &sm)
         }
         SEC(7);
     }
+#ifdef RMPC_BULK_STAGING
+    if (lane == 0) { rd_bar_inval(&sm.bar[0]); rd_bar_inval(&sm.bar[1]); }
+#else
     rd_cp_wait0();
+#endif
     rd_sync(); /* the factor blocks written by single lanes (stage 0: lane 12) are read by every lane of the next sweep */
     SECPROF_END(0);
 }

@@ -78,6 +78,17 @@ def test_solver_options_handling(capsys):
         rm.Simulator(**{**BASE, "robot_name": "ur3"})  # no built-in chain table
     s5 = rm.Simulator(**{**BASE, "robot_name": "ur5"})
     assert s5.static_key() != s.static_key()  # another chain = another batched launch
+    # round 2: partial condensing and AS-RTI are solver options like in acados (T/acados_ocp_options.py:72-84,1129-1208)
+    sc = rm.Simulator(**{**BASE, "solver_options": {"nlp_solver_type": "SQP_RTI", "qp_solver_cond_N": 5}})
+    assert sc.mpc.ocp.solver_options.qp_solver_cond_N == 5 and sc.static_key() != s.static_key()
+    sc.mpc.ocp.solver_options.validate()
+    sa = rm.Simulator(**{**BASE, "solver_options": {"nlp_solver_type": "SQP_RTI", "as_rti_level": 1, "as_rti_iter": 2}})
+    sa.mpc.ocp.solver_options.validate()
+    assert sa.static_key() != s.static_key()
+    for bad in ({"qp_solver_cond_N": 0}, {"qp_solver_cond_N": 10 ** 6}, {"nlp_solver_type": "SQP_RTI", "as_rti_level": 7},
+                {"nlp_solver_type": "SQP", "as_rti_level": 1}, {"nlp_solver_type": "SQP_RTI", "as_rti_iter": -1}):
+        with pytest.raises(ValueError):
+            rm.Simulator(**{**BASE, "solver_options": bad})  # validated at construction (R/simulator.py:129-135 sets them)
     ssh = rm.Simulator(**{**BASE, "shift_initial_guess": True})
     assert ssh.mpc.shift_initial_guess and ssh.static_key() != rm.Simulator(**BASE).static_key()
 

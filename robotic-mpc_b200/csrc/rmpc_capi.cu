@@ -561,7 +561,7 @@ extern "C" int rmpc_reset(rmpc_handle *h, void *stream)
  * memory, plant state, flags, accumulated summaries, step counter).  Blob = [magic, B, N, steps_done | slab | z | summary | flags]. */
 static const double RMPC_STATE_MAGIC = 20261104.0;
 #define RMPC_STATE_HDR 8
-/* header = [magic, B, N, steps_done, solver_type, terminal row on/off, shift option, checksum of the chain table]: a blob
+/* header = [magic, B, N, steps_done, solver_type, terminal row on/off, shift + AS-RTI + cond_N options, checksum of the chain table]: a blob
  * only loads into a handle whose solver semantics match (flags[] and the merit weights mean different things for SQP and
  * SQP_RTI; the iterate of another arm or another shift setting continues a different closed loop).  NOT in the blob: the
  * parameters ("par", terminal set, chain) -- set them again on the new handle -- and the per-step logs, whose rows below
@@ -576,7 +576,7 @@ static double chain_checksum(const RmpcChain &ch)
 static void state_header(const rmpc_handle *h, double *hdr)
 {
     hdr[0] = RMPC_STATE_MAGIC; hdr[1] = h->D.B; hdr[2] = h->D.N; hdr[3] = h->steps_done;
-    hdr[4] = h->D.solver_type; hdr[5] = h->pe_dev ? 1.0 : 0.0; hdr[6] = h->W.shift; hdr[7] = chain_checksum(h->ch);
+    hdr[4] = h->D.solver_type; hdr[5] = h->pe_dev ? 1.0 : 0.0; hdr[6] = h->W.shift + 10.0 * h->W.as_rti + 1e3 * (h->W.as_rti ? h->W.as_rti_iter : 0) + 1e6 * h->W.cond_N; hdr[7] = chain_checksum(h->ch);
 }
 extern "C" long long rmpc_state_size(const rmpc_handle *h)
 {
@@ -588,6 +588,8 @@ extern "C" long long rmpc_state_size(const rmpc_handle *h)
 extern "C" int rmpc_store_state(rmpc_handle *h, double *dev, void *stream)
 {
     if (!h || !dev) return fail(h, RMPC_EINVAL, "rmpc_store_state: null argument");
+    if (h->W.as_rti == 1) /* the level-A backup of the iterate (acados: work->tmp_nlp_out) is not part of the blob */
+        return fail(h, RMPC_EINVAL, "rmpc_store_state: not supported with AS-RTI level A");
     ON_DEVICE(h);
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B;
@@ -619,7 +621,7 @@ extern "C" int rmpc_load_state(rmpc_handle *h, const double *dev, void *stream)
         return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob was not stored by a handle with this B and N");
     if (hdr[4] != want[4]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another solver type");
     if (hdr[5] != want[5]) return fail(h, RMPC_EINVAL, "rmpc_load_state: terminal row on in one handle and off in the other (set it before loading)");
-    if (hdr[6] != want[6]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another shift option");
+    if (hdr[6] != want[6]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another shift / AS-RTI / partial-condensing option");
     if (hdr[7] != want[7]) return fail(h, RMPC_EINVAL, "rmpc_load_state: the blob comes from a handle with another kinematic chain");
     const double *p = dev + RMPC_STATE_HDR;
     CU(cudaMemcpyAsync(h->W.slab, p, sizeof(double) * B * (size_t) h->W.slab_stride, cudaMemcpyDeviceToDevice, s));

@@ -34,7 +34,8 @@ def _worker(job):
         leg.set_chain(*chain)
     out = []
     for i in idx:
-        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i], **term, **wkw), _G["z0"][i], ns)
+        box = dict(q_min=_G["qbox"][0][i], q_max=_G["qbox"][1][i]) if "qbox" in _G else {}
+        r = leg.closed_loop(o.make_problem(N=N, solver_type=st, surf=_G["surf"][i], **term, **wkw, **box), _G["z0"][i], ns)
         out.append((i, r["u"], r["z"], r["status"], r["sqp_iter"], r["qp_iter"]))
     return out
 
@@ -55,6 +56,8 @@ def main():
     ap.add_argument("--w-u", type=float, default=0.01)
     ap.add_argument("--w-qddot", type=float, default=0.02)
     ap.add_argument("--term-rho", type=float, default=0.0, help="> 0: terminal ellipsoid of the LQR with R = rho I (BASELINE configs[3])")
+    ap.add_argument("--cond-N", type=int, default=0, help="qp_solver_cond_N < N: partial condensing on both sides")
+    ap.add_argument("--q-box", type=float, default=0.0, help="> 0: joint-angle bounds q0 -+ U(0.06, 0.14) instead of -+2 pi (bounds active along the horizon)")
     a = ap.parse_args()
     B, N, K = a.batch, a.horizon, a.steps
     surf, z0 = workload(B, a.seed)
@@ -71,7 +74,15 @@ def main():
         term = dict(term_P=P, term_alpha=alpha, term_lh=-alpha)
         eng.set_terminal(P, alpha)
     wkw = dict(w_u=a.w_u, w_qddot=a.w_qddot)
-    eng.set_params(rm.pack_params(B, 0.01, surf=surf, **wkw))
+    pkw = {}
+    if a.q_box > 0:
+        w = np.random.default_rng(a.seed + 1).uniform(0.06, 0.14, (B, 1)) * (a.q_box / 0.1)
+        pkw = dict(q_min=z0[:, :6] - w, q_max=z0[:, :6] + w)
+        _G["qbox"] = (pkw["q_min"], pkw["q_max"])
+    eng.set_params(rm.pack_params(B, 0.01, surf=surf, **wkw, **pkw))
+    if a.cond_N:
+        eng.set_option("qp_cond_N", a.cond_N)
+        wkw = dict(wkw, cond_N=a.cond_N)
     eng.set_state(z0)
     eng.reset()
     torch.cuda.synchronize()
@@ -106,7 +117,7 @@ def main():
         qp_pm1 += int(d.max() <= 1)
     print(json.dumps({
         "what": "CUDA path vs compiled reference, closed loop, every instance", "oracle": "reference" if o.REF_SO.exists() else "port",
-        "robot": a.robot, "terminal_rho": a.term_rho, "w_u": a.w_u, "w_qddot": a.w_qddot, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
+        "robot": a.robot, "terminal_rho": a.term_rho, "w_u": a.w_u, "w_qddot": a.w_qddot, "cond_N": a.cond_N, "q_box": a.q_box, "instances": B, "N": N, "solver": a.solver, "closed_loop_steps": K, "seed": a.seed,
         "u_relerr": {"max": float(eu.max()), "p99": float(np.percentile(eu, 99)), "median": float(np.median(eu))},
         "z_relerr": {"max": float(ez.max()), "p99": float(np.percentile(ez, 99)), "median": float(np.median(ez))},
         "instances_over_1e-6": int((np.maximum(eu, ez) > 1e-6).sum()),

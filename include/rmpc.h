@@ -210,6 +210,48 @@ int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host,
  * once into a CUDA graph and replayed (rmpc_set_option "graph" 0 turns that off); stream NULL = a stream owned by the handle. */
 int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_host, double *stats_host, void *stream);
 
+/* One cold-started solve WITHOUT any device allocation.  No counterpart in the reference: acados allocates each capsule's
+ * memory when the capsule is created and has no allocation-free mode; this entry point exists for hosts of this library
+ * that are not free to allocate GPU memory themselves --
+ *   - a controller thread with a hard per-cycle deadline (the 1 kHz robot loop the MPC feeds): cudaMalloc and cudaFree take
+ *     driver-wide locks, may wait for the whole device to go idle and have no bounded run time, so they cannot sit inside
+ *     or next to the cycle;
+ *   - a process whose device memory is already committed to somebody else's pool (a framework's caching allocator, a
+ *     fixed per-client budget on a shared GPU): a cudaMalloc from a plug-in either fails or takes memory the owner counted on.
+ * Every other path of this library creates a handle first, and rmpc_create allocates the solver's work set; here the work
+ * set lives in a fixed array inside librmpc.so's device image instead.  The price: each GPU that loads the library sets
+ * aside RMPC_STATIC_SCRATCH_BYTES for that array until the process exits, whether this function is ever called or not.
+ *
+ * What it computes: exactly what  rmpc_create(dims, device, 1) ; rmpc_set "par" ; rmpc_set "z" = x0 ; rmpc_reset ; rmpc_solve ;
+ * rmpc_get "u" of stage 0 (and rmpc_get "stats")  computes, for the built-in UR10 chain and default options -- a NEW solver
+ * per call (iterate x_k = x0, u_k = 0, multipliers, merit weights and QP memory zero), one SQP / SQP_RTI solve, no plant step.
+ *   dims      batch and solver settings, as for rmpc_create
+ *   device    CUDA device ordinal (below 64); the caller's current device is put back before returning
+ *   par_dev   in   [B][RP_COUNT]  parameter blocks (device pointer, read only)
+ *   x0_dev    in   [B][12]        initial states (device pointer, read only)
+ *   u0_dev    out  [B][6]         control of stage 0
+ *   stats_dev out  [B][RL_COUNT]  step record (status, iteration counts, cost, KKT residuals, timers); may be NULL
+ * All four buffers are the caller's; the work is enqueued on `stream` and is asynchronous like rmpc_solve.
+ *
+ * Limit: B * (8 * S(N) + 16) <= RMPC_STATIC_SCRATCH_BYTES, where S(N) = 144 + 832 * (N + 1 rounded up to even), rounded up to
+ * a multiple of 16, is the number of doubles one instance's solver data takes -- 98 instances at N = 100, 454 at N = 20,
+ * 49 at N = 200.  A larger request returns RMPC_EINVAL with the numbers in rmpc_last_error(NULL); nothing is launched.
+ *
+ * Things a caller must know:
+ *   - the FIRST call on each device does a one-time set-up (looks up the device address of the array, raises the kernel's
+ *     shared-memory limit), which makes the CUDA runtime load the module on that device.  Make that first call during
+ *     start-up -- ahead of the time-critical loop and before any stream capture is begun -- e.g. with B = 1.
+ *   - it calls no cudaMalloc / cudaFree / cudaHostAlloc and no library routine that allocates device memory, on the first
+ *     call or any later one.
+ *   - there is ONE array per device and every call uses it from the start.  It still holds the previous call's data, so
+ *     each call first zeroes the part it is going to use; nothing is carried from call to call (no warm start -- callers
+ *     that want one need a handle).  Two calls whose GPU work can overlap (different streams, different threads) write the
+ *     same memory and corrupt each other: order them on one stream or with events.  Handles are not affected.
+ */
+#define RMPC_STATIC_SCRATCH_BYTES (64u << 20)
+int rmpc_solve_static(const rmpc_dims *dims, int device, const double *par_dev, const double *x0_dev, double *u0_dev,
+                      double *stats_dev, void *stream);
+
 /* Kernels launched by this handle so far (for bench accounting). */
 long long rmpc_launch_count(const rmpc_handle *h);
 

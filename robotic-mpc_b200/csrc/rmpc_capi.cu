@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -854,6 +855,105 @@ extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_
     CU(cudaStreamSynchronize(s));
     std::memcpy(u0_host, h->pin_u, sizeof(double) * B * 6);
     if (stats_host) std::memcpy(stats_host, h->pin_st, sizeof(double) * B * RL_COUNT);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------ rmpc_solve_static
+ * One cold-started solve for callers that must not allocate device memory (include/rmpc.h has the contract).  The solver's
+ * work set -- the per-instance slabs and the flag words, which rmpc_create would cudaMalloc -- lives in the file-scope array
+ * below: it is part of the loaded module, so every GPU that loads librmpc.so carries RMPC_STATIC_SCRATCH_BYTES for it until
+ * the process exits, used or not.
+ * In HOST code the name rmpc_static_scratch is only a stand-in for the symbol; it is not a device address, and a kernel
+ * handed &rmpc_static_scratch[0] from the host would touch the wrong memory.  The device address is looked up once per
+ * device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels receive. */
+static __device__ __align__(256) unsigned char rmpc_static_scratch[RMPC_STATIC_SCRATCH_BYTES];
+
+/* rmpc_closed_loop_kernel restricted to one solve without a plant step, with the stage-0 control written straight to the
+ * caller's output (the handle path gathers it from the slab with a second launch) */
+__global__ void RMPC_KERNEL_BOUNDS
+rmpc_solve_static_kernel(const __grid_constant__ RmpcChain ch, const __grid_constant__ RmpcDims D, const __grid_constant__ RmpcWs W, double *u0)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    GrpSmem *smem = reinterpret_cast<GrpSmem *>(smem_raw);
+    const int grp = threadIdx.x / RMPC_G;
+    const long inst = (long) blockIdx.x * RMPC_GROUPS_PER_CTA + grp;
+    if (inst >= D.B) return;
+    const long first = inst - (grp % (32 / RMPC_G));
+    unsigned pair = 0;
+    for (int g = 0; g < 32 / RMPC_G; g++)
+        if (first + g < D.B) pair |= (RMPC_G == 32 ? 0xffffffffu : ((1u << (RMPC_G & 31)) - 1u)) << (g * RMPC_G);
+    closed_loop_group(ch, D, W, inst, smem[grp], 1, 0, pair); /* ends with a group barrier: the iterate is visible to all lanes */
+    const int lane = threadIdx.x % RMPC_G;
+    if (lane < NU) u0[inst * NU + lane] = W.slab[inst * W.slab_stride + rmpc_slab_off(D.N, RC_ux, NV, 0) + lane];
+}
+
+#define RMPC_STATIC_MAX_DEVICES 64
+static std::mutex g_static_mutex;
+static unsigned char *g_static_base[RMPC_STATIC_MAX_DEVICES]; /* device address of rmpc_static_scratch on each device, null: not set up */
+
+extern "C" int rmpc_solve_static(const rmpc_dims *dims, int device, const double *par_dev, const double *x0_dev, double *u0_dev,
+                                 double *stats_dev, void *stream)
+{
+    rmpc_handle *h = nullptr; /* no handle: errors go to rmpc_last_error(NULL) */
+    if (!dims || !par_dev || !x0_dev || !u0_dev) return fail(h, RMPC_EINVAL, "rmpc_solve_static: null argument");
+    if (dims->B < 1 || dims->N < 2 || dims->N > 4096) return fail(h, RMPC_EINVAL, "rmpc_solve_static: need B >= 1, 2 <= N <= 4096");
+    if (dims->solver_type != RMPC_SOLVER_SQP && dims->solver_type != RMPC_SOLVER_SQP_RTI)
+        return fail(h, RMPC_EINVAL, "rmpc_solve_static: solver_type must be RMPC_SOLVER_SQP or RMPC_SOLVER_SQP_RTI");
+    /* scratch = [B slabs | B x 4 flag words]; refuse what the fixed array cannot hold */
+    const size_t B = (size_t) dims->B, stride = (size_t) rmpc_slab_stride(dims->N);
+    const size_t per_inst = stride * sizeof(double) + 4 * sizeof(int);
+    if (B > (size_t) RMPC_STATIC_SCRATCH_BYTES / per_inst)
+        return fail(h, RMPC_EINVAL, "rmpc_solve_static: B = " + std::to_string(B) + " instances at N = " + std::to_string(dims->N) + " need " +
+                                        std::to_string(B * per_inst) + " bytes of scratch, the static array holds " +
+                                        std::to_string((size_t) RMPC_STATIC_SCRATCH_BYTES) + " (at most " +
+                                        std::to_string((size_t) RMPC_STATIC_SCRATCH_BYTES / per_inst) + " instances at this N); use rmpc_create for larger batches");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1 || device < 0 || device >= ndev || device >= RMPC_STATIC_MAX_DEVICES)
+        return fail(h, RMPC_ENODEV, "rmpc_solve_static: no usable CUDA device (this library has no host fallback)");
+    DeviceGuard dev_guard_(device);
+    if (!dev_guard_.ok) return fail(h, RMPC_ENODEV, "rmpc_solve_static: cudaSetDevice failed");
+    unsigned char *base = nullptr;
+    {
+        /* set-up, once per device and with that device current: resolve the array's device address and opt the kernel in
+         * to its shared-memory size.  This is the part of the first call that loads the module. */
+        std::lock_guard<std::mutex> lock(g_static_mutex);
+        if (!g_static_base[device])
+        {
+            void *p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, rmpc_static_scratch);
+            if (e != cudaSuccess || !p)
+                return fail(h, RMPC_ECUDA, std::string("rmpc_solve_static: cudaGetSymbolAddress(rmpc_static_scratch): ") + cudaGetErrorString(e));
+            e = cudaFuncSetAttribute(rmpc_solve_static_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) (sizeof(GrpSmem) * RMPC_GROUPS_PER_CTA));
+            if (e != cudaSuccess)
+                return fail(h, RMPC_ECUDA, std::string("rmpc_solve_static: cannot reserve the shared memory the kernel needs: ") + cudaGetErrorString(e));
+            g_static_base[device] = (unsigned char *) p;
+        }
+        base = g_static_base[device];
+    }
+    cudaStream_t s = (cudaStream_t) stream;
+    RmpcDims D;
+    memcpy(&D, dims, sizeof(RmpcDims));
+    RmpcChain ch;
+    rmpc_chain_init(&ch);
+    RmpcWs W;
+    memset(&W, 0, sizeof(W));
+    W.par = par_dev;
+    W.slab = (double *) base;
+    W.slab_stride = (long) stride;
+    W.Sp = rmpc_slab_sp(dims->N);
+    W.z = const_cast<double *>(x0_dev); /* read only here: without a plant step no kernel of this path writes z */
+    W.flags = (int *) (base + B * stride * sizeof(double));
+    W.slog = stats_dev; /* log capacity of one step: the record of this solve lands in the caller's buffer */
+    W.nlog = stats_dev ? 1 : 0;
+    W.as_rti_iter = 1;
+    /* the array still holds the previous call's iterate, multipliers, merit weights and QP memory: a new solver starts
+     * from zeros (rmpc_reset), then x_k = x0, u_k = 0 and the first-call flags */
+    CU(cudaMemsetAsync(base, 0, B * stride * sizeof(double), s));
+    rmpc_init_iterate_kernel<<<grid_for((long) B * (dims->N + 1) * NV), 256, 0, s>>>(D, W);
+    CU(cudaGetLastError());
+    const int grid = (dims->B + RMPC_GROUPS_PER_CTA - 1) / RMPC_GROUPS_PER_CTA;
+    rmpc_solve_static_kernel<<<grid, 32 * RMPC_WARPS_PER_CTA, sizeof(GrpSmem) * RMPC_GROUPS_PER_CTA, s>>>(ch, D, W, u0_dev);
+    CU(cudaGetLastError());
     return 0;
 }
 

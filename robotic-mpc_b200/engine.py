@@ -62,6 +62,7 @@ def load_library() -> C.CDLL:
     lib.rmpc_step_host.argtypes = [vp, dp, dp, dp, vp]
     lib.rmpc_launch_count.argtypes = [vp]
     lib.rmpc_launch_count.restype = C.c_longlong
+    lib.rmpc_solve_static.argtypes = [C.POINTER(RmpcDims), ip, dp, dp, dp, dp, vp]
     _lib = lib
     return lib
 
@@ -69,7 +70,7 @@ def load_library() -> C.CDLL:
 EXPORTED_SYMBOLS = ["rmpc_create", "rmpc_destroy", "rmpc_last_error", "rmpc_device_bytes", "rmpc_set", "rmpc_reset",
                     "rmpc_solve", "rmpc_solve_rti_phase", "rmpc_closed_loop", "rmpc_get", "rmpc_steps_done", "rmpc_run_host",
                     "rmpc_launch_count", "rmpc_set_chain", "rmpc_set_option", "rmpc_state_size",
-                    "rmpc_store_state", "rmpc_load_state", "rmpc_step_host"]
+                    "rmpc_store_state", "rmpc_load_state", "rmpc_step_host", "rmpc_solve_static"]
 
 
 class RmpcError(RuntimeError):

@@ -198,7 +198,8 @@ int rmpc_steps_done(const rmpc_handle *h);
 
 /* Host-buffer convenience used for end-to-end measurements: upload par [B][RP_COUNT] and z0 [B][12] from host memory,
  * reset, run nsteps closed-loop steps, download the summary [B][20] and the last applied control [B][6] to host
- * memory; synchronises the stream before returning.  Any output pointer may be NULL. */
+ * memory; synchronises the stream before returning.  Any output pointer may be NULL.  Uploading the parameter block
+ * discards every per-stage override made before, like rmpc_set "par". */
 int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host, int nsteps, double *summary_host,
                   double *u_last_host, void *stream);
 
@@ -207,7 +208,9 @@ int rmpc_run_host(rmpc_handle *h, const double *par_host, const double *z0_host,
  * for the whole batch in one call: copy x0 [B][12] from host memory, solve, copy u0 [B][6] (and, when stats_host is not
  * NULL and the handle has nlog > 0, the step record [B][RL_COUNT]) back to host memory; synchronises the stream before
  * returning.  The plant is the caller's (the on-device plant does not advance).  The copy-solve-copy sequence is captured
- * once into a CUDA graph and replayed (rmpc_set_option "graph" 0 turns that off); stream NULL = a stream owned by the handle. */
+ * once into a CUDA graph and replayed (rmpc_set_option "graph" 0 turns that off; a change of the options, the kinematic chain
+ * or the stream re-captures it); stream NULL = a stream owned by the handle.  Refused (RMPC_EINVAL) while an AS-RTI level is
+ * set, like rmpc_solve: it is one combined preparation + feedback solve. */
 int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_host, double *stats_host, void *stream);
 
 /* One cold-started solve WITHOUT any device allocation.  No counterpart in the reference: acados allocates each capsule's

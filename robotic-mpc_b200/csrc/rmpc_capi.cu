@@ -101,9 +101,9 @@ __global__ void rmpc_plant_logs_kernel(const RmpcChain ch, const double *par, co
     }
 }
 
-/* per-stage table [B][N][RT_COUNT] <- the per-instance values of the parameter block, for every stage (cols: 0 all, 1 yref,
- * 2 lower bounds, 3 upper bounds) */
-__global__ void rmpc_stage_table_fill_kernel(double *stg, const double *par, long B, int N, int cols)
+/* per-stage table [B][N][RT_COUNT] <- the per-instance values of the parameter block, for every stage, columns
+ * c0 .. c0 + nc - 1 of the table only */
+__global__ void rmpc_stage_table_fill_kernel(double *stg, const double *par, long B, int N, int c0, int nc)
 {
     const long tot = B * N * RT_COUNT;
     for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < tot; k += (long) gridDim.x * blockDim.x)
@@ -111,8 +111,7 @@ __global__ void rmpc_stage_table_fill_kernel(double *stg, const double *par, lon
         const long i = k / ((long) N * RT_COUNT);
         const int c = (int) (k % RT_COUNT);
         const double *p = par + i * RP_COUNT;
-        const int grp = c < RT_LB ? 1 : (c < RT_UB ? 2 : 3);
-        if (cols && cols != grp) continue;
+        if (c < c0 || c >= c0 + nc) continue;
         double v;
         if (c < RT_LB) v = p[RP_YREF + c];
         else if (c < RT_UB) v = (c - RT_LB) < 6 ? p[RP_UMIN + c - RT_LB] : p[RP_QMIN + c - RT_LB - 6];
@@ -151,6 +150,7 @@ struct rmpc_handle
     cudaStream_t gstream = nullptr;
     RmpcWs gW;
     RmpcDims gD;
+    RmpcChain gch;
     int use_graph = 1;
     std::string err;
 };
@@ -394,9 +394,9 @@ static int strided2(rmpc_handle *h, const double *src, long sstride, long soff, 
     CU(cudaGetLastError());
     return 0;
 }
-static int stage_table_fill(rmpc_handle *h, int cols, cudaStream_t s)
+static int stage_table_fill(rmpc_handle *h, int c0, int nc, cudaStream_t s)
 {
-    rmpc_stage_table_fill_kernel<<<grid_for((long) h->D.B * h->D.N * RT_COUNT), 256, 0, s>>>(h->stg_dev, h->par_dev, h->D.B, h->D.N, cols);
+    rmpc_stage_table_fill_kernel<<<grid_for((long) h->D.B * h->D.N * RT_COUNT), 256, 0, s>>>(h->stg_dev, h->par_dev, h->D.B, h->D.N, c0, nc);
     h->launches++;
     CU(cudaGetLastError());
     return 0;
@@ -412,7 +412,7 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
     if (f == "par")
     {
         CU(cudaMemcpyAsync(h->par_dev, dev, sizeof(double) * h->D.B * RP_COUNT, cudaMemcpyDeviceToDevice, s));
-        if (h->stg_dev) return stage_table_fill(h, 0, s); /* a new parameter block resets every per-stage override */
+        if (h->stg_dev) return stage_table_fill(h, 0, RT_COUNT, s); /* a new parameter block resets every per-stage override */
         return 0;
     }
     /* ---- named fields of the cost / constraint modules (AcadosOcpSolver.cost_set / constraints_set,
@@ -435,7 +435,8 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
             const long off = is_y ? RP_YREF : (is_u ? (lower ? RP_UMIN : RP_UMAX) : (lower ? RP_QMIN : RP_QMAX));
             int rc = strided(h, (double *) dev, h->par_dev, RP_COUNT, off, n, 0, s);
             if (rc) return rc;
-            if (h->stg_dev) return stage_table_fill(h, is_y ? 1 : (lower ? 2 : 3), s);
+            /* only this field's columns: per-stage overrides of the other fields stay (lbu next to lbx in the lower group) */
+            if (h->stg_dev) return stage_table_fill(h, is_y ? RT_YREF : ((lower ? RT_LB : RT_UB) + (is_u ? 0 : 6)), n, s);
             return 0;
         }
         if (!h->stg_dev)
@@ -446,7 +447,7 @@ extern "C" int rmpc_set(rmpc_handle *h, const char *field, int stage, const doub
             h->owned.push_back(p);
             h->bytes += (long long) bytes;
             h->stg_dev = (double *) p;
-            int rc = stage_table_fill(h, 0, s);
+            int rc = stage_table_fill(h, 0, RT_COUNT, s);
             if (rc) return rc;
             h->W.stg = h->stg_dev;
         }
@@ -768,6 +769,11 @@ extern "C" int rmpc_run_host(rmpc_handle *h, const double *par_host, const doubl
     cudaStream_t s = (cudaStream_t) stream;
     const size_t B = (size_t) h->D.B;
     CU(cudaMemcpyAsync(h->par_dev, par_host, sizeof(double) * B * RP_COUNT, cudaMemcpyHostToDevice, s));
+    if (h->stg_dev)
+    { /* like rmpc_set "par": a new parameter block discards every per-stage override */
+        int rc_fill = stage_table_fill(h, 0, RT_COUNT, s);
+        if (rc_fill) return rc_fill;
+    }
     CU(cudaMemcpyAsync(h->W.z, z0_host, sizeof(double) * B * NX, cudaMemcpyHostToDevice, s));
     int rc = rmpc_reset(h, stream);
     if (rc) return rc;
@@ -810,6 +816,9 @@ extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_
     if (!h || !x0_host || !u0_host) return fail(h, RMPC_EINVAL, "rmpc_step_host: null argument");
     if (stats_host && !(h->nlog > 0 && h->steps_done < h->nlog))
         return fail(h, RMPC_EINVAL, "rmpc_step_host: the step record needs a handle created with nlog > 0");
+    if (h->W.as_rti) /* one combined solve per call, which acados refuses with a level set (AC/ocp_nlp/ocp_nlp_sqp_rti.c:1150-1154) */
+        return fail(h, RMPC_EINVAL, "rmpc_step_host: rti_phase PREPARATION_AND_FEEDBACK is not supported with AS-RTI (as_rti_level != 4); "
+                                    "drive the two phases with rmpc_solve_rti_phase");
     ON_DEVICE(h);
     const size_t B = (size_t) h->D.B;
     if (!h->pin_z)
@@ -826,7 +835,8 @@ extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_
     if (h->use_graph)
     {
         /* the captured sequence is valid as long as the launch arguments are the ones it was captured with */
-        if (h->gexec && (h->gstream != s || std::memcmp(&h->gW, &h->W, sizeof(RmpcWs)) != 0 || std::memcmp(&h->gD, &h->D, sizeof(RmpcDims)) != 0))
+        if (h->gexec && (h->gstream != s || std::memcmp(&h->gW, &h->W, sizeof(RmpcWs)) != 0 || std::memcmp(&h->gD, &h->D, sizeof(RmpcDims)) != 0 ||
+                         std::memcmp(&h->gch, &h->ch, sizeof(RmpcChain)) != 0)) /* the chain is a by-value kernel argument too */
             step_graph_drop(h);
         if (!h->gexec)
         {
@@ -841,6 +851,7 @@ extern "C" int rmpc_step_host(rmpc_handle *h, const double *x0_host, double *u0_
             if (e != cudaSuccess) { h->gexec = nullptr; return fail(h, RMPC_ECUDA, std::string("rmpc_step_host: cudaGraphInstantiate: ") + cudaGetErrorString(e)); }
             std::memcpy(&h->gW, &h->W, sizeof(RmpcWs));
             std::memcpy(&h->gD, &h->D, sizeof(RmpcDims));
+            std::memcpy(&h->gch, &h->ch, sizeof(RmpcChain));
             h->gstream = s;
         }
         else

@@ -3148,6 +3148,7 @@ RD void closed_loop_group(const RmpcChain &ch, const RmpcDims &D, const RmpcWs &
                 solve_rti(ch, D, I, sm, op, 1, W.as_rti - 1, W.as_rti_iter, bk);
                 solve_rti(ch, D, I, sm, o, 2, W.as_rti - 1, W.as_rti_iter, bk);
                 o.qp_iter += op.qp_iter;
+                if (o.status == 0 && op.status != 0) o.status = op.status; /* a failed advanced step (1 NaN merit, 4 QP failure) reaches slog / RS_NFAIL */
                 o.t_lin += op.t_lin; o.t_qp += op.t_qp; o.t_glob += op.t_glob;
                 for (int k = 0; k < 5; k++) o.tq[k] += op.tq[k];
             }

@@ -142,11 +142,15 @@ class Engine:
             pass
 
     # ------------------------------------------------------------------ setters
-    def set(self, field, value, stage=0):
+    def set(self, field, value, stage=None):
         """``rmpc_set``: copy a ``[B, n]`` array into the engine.  Per-instance blocks ("par", "z", the terminal set), the
         iterate ("x", "u", "pi" of ``stage``) and the named cost / constraint fields: "yref" [B, 18], "lbu" / "ubu" [B, 6],
         "lbx" / "ubx" [B, 6] (on q; stage 0: [B, 12] = the initial state) with ``stage = -1`` for every stage or a stage
-        index for that stage only; "W_diag" [B, 18], "surf_coeffs" [B, 6], "wcv" [B, 6] per instance (``stage = -1``)."""
+        index for that stage only; "W_diag" [B, 18], "surf_coeffs" [B, 6], "wcv" [B, 6] per instance (``stage = -1``).
+        ``stage=None`` means -1 (every stage) for the named cost / constraint fields and 0 for the iterate fields, so that
+        ``set('lbu', v)`` bounds every stage and ``set('lbx', v)`` never lands on the initial-state slot by accident."""
+        if stage is None:
+            stage = -1 if field in ("yref", "lbu", "ubu", "lbx", "ubx", "W_diag", "surf_coeffs", "wcv") else 0
         n = {"par": RP["COUNT"], "z": 12, "x": 12, "u": 6, "pi": 12, "P_e": 144, "alpha_e": 1, "lh_e": 1, "term": 146,
              "yref": 18, "lbu": 6, "ubu": 6, "lbx": 6, "ubx": 6, "W_diag": 18, "surf_coeffs": 6, "wcv": 6}[field]
         if field in ("lbx", "ubx") and stage == 0:
@@ -243,11 +247,14 @@ class Engine:
                     "rmpc_run_host")
         return summ, u
 
-    def step_host(self, x0, u0=None, stats=None, stream=False):
+    def step_host(self, x0, u0=None, stats=None, stream=True):
         """One step of an externally driven loop with host buffers: x0 [B, 12] in, u0 [B, 6] (and, with ``stats`` [B, RL_COUNT]
         and nlog > 0, the step record) out -- ``solver.set(0,'lbx',x); solver.set(0,'ubx',x); solver.solve();
         solver.get(0,'u')`` of R/simulator.py:209-217 for the batch in one call.  ``u0`` / ``stats`` are filled in place when
-        given (float64, C-contiguous); returns u0.  ``stream=True`` uses torch's current stream instead of the handle's own."""
+        given (float64, C-contiguous); returns u0.  The step runs on torch's current stream, like every other Engine call, so it
+        is ordered after a pending ``set`` / ``reset`` (when that stream is the legacy default stream, which a CUDA graph cannot
+        be captured on, the library uses the handle's own blocking stream, which the default stream orders implicitly);
+        ``stream=False`` forces the handle's own stream whatever torch's current stream is."""
         x0 = np.ascontiguousarray(x0, dtype=np.float64)
         if x0.shape != (self.B, 12):
             raise ValueError(f"expected shape {(self.B, 12)}, got {x0.shape}")

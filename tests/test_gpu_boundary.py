@@ -242,3 +242,105 @@ def test_step_host_equals_set_solve_get(oracle, graph):
         c.step_host(z, u, st)  # the step record needs nlog > 0
     for e in (a, b, c):
         e.close()
+
+
+def test_step_host_graph_follows_a_chain_change(oracle):
+    """The captured step of rmpc_step_host bakes in the kinematic chain (a by-value kernel argument): after rmpc_set_chain
+    the graph must be re-captured, so graph = 1 and graph = 0 keep giving the same controls."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N = 4, 12
+    surf, z0 = _inputs(o, B, 91)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    res = {}
+    for graph in (0, 1):
+        e = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=1)
+        e.set_option("graph", graph)
+        e.set_params(par)
+        e.set_state(z0)
+        e.reset()
+        u10 = e.step_host(z0).copy()
+        e.set_chain("ur5")
+        e.set_state(z0)
+        e.reset()
+        u5 = e.step_host(z0).copy()
+        e.set_chain(None)  # back to the built-in UR10
+        e.set_state(z0)
+        e.reset()
+        res[graph] = (u10, u5, e.step_host(z0).copy())
+        e.close()
+    assert not np.array_equal(res[0][0], res[0][1])  # the two arms really give different controls
+    for a, b in zip(res[0], res[1]):
+        assert np.array_equal(a, b, equal_nan=True)
+    assert np.array_equal(res[1][0], res[1][2], equal_nan=True)
+
+
+def test_run_host_discards_per_stage_overrides(oracle):
+    """rmpc_run_host uploads a new parameter block: like rmpc_set "par" it drops every per-stage override made before."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 4, 12, 5
+    surf, z0 = _inputs(o, B, 92)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    fresh = rm.Engine(B, N, "SQP_RTI", dt=0.01)
+    want, u_want = fresh.run_host(par, z0, ns)
+    e = rm.Engine(B, N, "SQP_RTI", dt=0.01)
+    e.set_params(par)
+    e.set("ubu", np.full((B, 6), 0.05), stage=1)
+    e.set("yref", np.ones((B, 18)), stage=3)
+    got, u_got = e.run_host(par, z0, ns)
+    assert np.array_equal(e.get("ubu", stage=1).cpu().numpy(), par[:, rm.RP["UMAX"]:rm.RP["UMAX"] + 6])
+    assert np.array_equal(got, want) and np.array_equal(u_got, u_want)
+    for x in (fresh, e):
+        x.close()
+
+
+def test_step_host_refuses_as_rti(oracle):
+    """One combined solve per call is what acados refuses while an AS-RTI level is set; so do rmpc_solve and rmpc_step_host."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N = 3, 10
+    surf, z0 = _inputs(o, B, 93)
+    e = rm.Engine(B, N, "SQP_RTI", dt=0.01)
+    e.set_params(rm.pack_params(B, 0.01, surf=surf))
+    e.set_state(z0)
+    e.reset()
+    e.set_option("as_rti_level", 1)
+    with pytest.raises(rm.RmpcError) as ei:
+        e.step_host(z0)
+    assert ei.value.code == -1 and "AS-RTI" in str(ei.value)
+    e.set_option("as_rti_level", 4)
+    assert np.isfinite(e.step_host(z0)).all()
+    e.close()
+
+
+def test_every_stage_setter_keeps_the_other_fields_overrides(oracle):
+    """stage = -1 for one field drops that field's per-stage overrides only: lbu and lbx share the lower-bound group of the
+    per-stage table.  Engine.set without a stage means every stage for these fields and never touches the plant state."""
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N = 3, 10
+    surf, z0 = _inputs(o, B, 94)
+    par = rm.pack_params(B, 0.01, surf=surf)
+    e = rm.Engine(B, N, "SQP_RTI", dt=0.01)
+    e.set_params(par)
+    e.set_state(z0)
+    lbx3, ubx4, lbu2 = np.full((B, 6), -0.3), np.full((B, 6), 0.4), np.full((B, 6), -0.7)
+    e.set("lbx", lbx3, stage=3)
+    e.set("ubx", ubx4, stage=4)
+    e.set("lbu", lbu2, stage=2)
+    e.set("lbu", np.full((B, 6), -1.1))  # every stage
+    e.set("ubu", np.full((B, 6), 1.3), stage=-1)
+    g = lambda f, s: e.get(f, stage=s).cpu().numpy()
+    assert np.array_equal(g("lbx", 3), lbx3) and np.array_equal(g("ubx", 4), ubx4)
+    assert np.array_equal(g("lbu", 2), np.full((B, 6), -1.1)) and np.array_equal(g("lbu", 7), np.full((B, 6), -1.1))
+    assert np.array_equal(g("ubu", 5), np.full((B, 6), 1.3))
+    e.set("lbx", np.full((B, 6), -2.0))  # every stage: the override of stage 3 goes, the control bounds stay
+    assert np.array_equal(g("lbx", 3), np.full((B, 6), -2.0)) and np.array_equal(g("lbu", 3), np.full((B, 6), -1.1))
+    assert np.array_equal(e.get("z").cpu().numpy(), z0)
+    assert np.array_equal(g("yref", 3), par[:, rm.RP["YREF"]:rm.RP["YREF"] + 18])
+    e.close()

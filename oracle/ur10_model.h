@@ -12,8 +12,9 @@
  *     *_cost_y_fun, *_cost_y_fun_jac_ut_xt, *_dyn_disc_phi_fun[_jac]
  *     (T/casadi_function_generation.py:244-255,555-575).
  * PARITY OF THESE FUNCTIONS IS UNPINNED by the reference (it has no tests / golden data); they are
- * pinned here by finite differences, an independent PyTorch-autograd restatement and UR10 DH
- * known answers (tests/test_oracle_model.py).
+ * pinned here by finite differences, UR10 DH known answers and the exact-ZOH matrix exponential
+ * (tests/test_oracle_model.py) and by an independent PyTorch FP64 restatement differentiated with
+ * autograd, agreeing to 1e-12 (tests/test_oracle_model_torch.py).
  *
  * Conventions: x = [q(6); qdot(6)], u = qdot_cmd(6), stage variable order [u; x] (AC/ocp_nlp/ocp_nlp_common.h:281).
  */

@@ -175,6 +175,12 @@ class PortLeg(_Leg):
     so = PORT_SO
 
 
+def checker_leg() -> _Leg:
+    """The leg parity tests compare the device with: the reference's own compiled code wherever oracle/_ref was built (it
+    travels to the GPU box with the repo), the plain-C port only where it was not."""
+    return RefLeg() if REF_SO.exists() else PortLeg()
+
+
 # ------------------------------------------------------------------ model functions (libur10 inside either .so)
 class Model:
     def __init__(self, lib: C.CDLL):

@@ -79,7 +79,7 @@ def test_run_all_grid_matches_oracle_per_instance(oracle):
                   name_template=lambda p, k: f"s{k}_H{p['prediction_horizon']}_wu{p['w_u']}_{p['solver_options']['nlp_solver_type']}")
     res = m.run_all()
     assert len(res) == 24 and m.last_run_info["launches"] == 4  # (H=8|12) x (SQP|SQP_RTI)
-    port = o.PortLeg()
+    port = o.checker_leg()  # the compiled reference where it was built
     z0 = np.concatenate([o.README_Q0, o.README_QD0])
     for r, spec in zip(res, m.simulations):
         c = spec["config"]
@@ -119,7 +119,7 @@ def test_trajectory_optimizer_solver_interface(oracle):
     status = mpc.solver.solve()
     u = mpc.solver.get(0, "u")
     p = o.make_problem(N=15, solver_type=o.SQP, surf=surf.coeff_vector(), qdot_min=-3 * np.ones(6), qdot_max=3 * np.ones(6))
-    gld = o.PortLeg().closed_loop(p, x, 1, full_traj=True)
+    gld = o.checker_leg().closed_loop(p, x, 1, full_traj=True)
     assert status == gld["status"][0] and mpc.solver.get_stats("sqp_iter") == gld["sqp_iter"][0]
     assert relerr(u, gld["u"][0]) < RTOL
     assert relerr(mpc.solver.get(7, "x"), gld["xtraj"][0][7]) < RTOL

@@ -51,7 +51,7 @@ def test_closed_loop_matches_oracle(oracle, solver, N, ns):
     surf, z0 = _inputs(o, B, 100 + N)
     par = rm.pack_params(B, 0.01, surf=surf, w_u=0.01, w_qddot=0.02)
     r = _run(rm, B, N, solver, par, z0, ns)
-    port = o.PortLeg()
+    port = o.checker_leg()  # the compiled reference where it was built
     st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
     for i in range(B):
         g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i], ns, full_traj=True)
@@ -105,7 +105,7 @@ def test_solver_interface_single_solve(oracle):
     st = eng.get("stats").cpu().numpy()
     u0 = eng.get("u", 0).cpu().numpy()
     assert np.array_equal(eng.get("z").cpu().numpy(), z0)  # plant untouched
-    port = o.PortLeg()
+    port = o.checker_leg()  # the compiled reference where it was built
     for i in range(B):
         g = port.closed_loop(o.make_problem(N=N, solver_type=o.SQP, surf=surf[i]), z0[i], 1)
         assert relerr(u0[i], g["u"][0]) < RTOL
@@ -140,7 +140,7 @@ def test_full_size_properties(built):
     c = _run(rm, len(sub), N, "SQP_RTI", par[sub], z0[sub], ns)
     assert np.array_equal(c["ulog"], a["ulog"][sub])
     # oracle spot check on 3 instances of the big batch
-    port = o.PortLeg()
+    port = o.checker_leg()  # the compiled reference where it was built
     for i in (0, 1234, 4095):
         g = port.closed_loop(o.make_problem(N=N, solver_type=o.SQP_RTI, surf=surf[i]), z0[i], ns)
         assert relerr(a["ulog"][i], g["u"]) < RTOL
@@ -207,7 +207,7 @@ def test_long_horizons_match_oracle(oracle, solver, N, ns):
     B = 5
     surf, z0 = _inputs(o, B, 700 + N)
     r = _run(rm, B, N, solver, rm.pack_params(B, 0.01, surf=surf), z0, ns)
-    port = o.PortLeg()
+    port = o.checker_leg()  # the compiled reference where it was built
     st = o.SQP_RTI if solver == "SQP_RTI" else o.SQP
     for i in range(B):
         g = port.closed_loop(o.make_problem(N=N, solver_type=st, surf=surf[i]), z0[i], ns, full_traj=True)

@@ -158,6 +158,39 @@ def test_qp_iteration_counts_equal_to_reference(oracle):
     assert n_exc == 0
 
 
+def test_bench_window_full_batch_sample_against_reference(oracle):
+    """The window the driver's bench times -- bench.py's own workload (make_workload(4096, 44 + rank), rank 0), 4096 instances x
+    N = 100 x SQP_RTI, the first 20 closed-loop steps from the initial state -- run as ONE batch through rmpc_run_host-sized
+    geometry, with every 16th instance (256 of them, every CTA position and both halves of a warp) checked step by step
+    against the compiled reference on the host cores: controls and states at 1e-6, status / SQP / QP iteration sequences equal."""
+    import bench
+    import robotic_mpc_b200 as rm
+
+    o = oracle
+    B, N, ns = 4096, 100, 20
+    surf, z0 = bench.make_workload(B, 44)
+    eng = rm.Engine(B, N, "SQP_RTI", dt=0.01, nlog=ns)
+    eng.set_params(rm.pack_params(B, 0.01, surf=surf))
+    eng.set_state(z0)
+    eng.reset()
+    eng.closed_loop(ns)
+    ulog, zlog, slog = (eng.get(k).cpu().numpy() for k in ("ulog", "zlog", "slog"))
+    summ = eng.get("summary").cpu().numpy()
+    eng.close()
+    assert int(summ[:, rm.RS["NFAIL"]].sum()) == 0
+    pick = list(range(5, B, 16))
+    ref = _pool_closed_loops(o, [(dict(N=N, solver_type=o.SQP_RTI, surf=surf[i]), z0[i], ns) for i in pick])
+    worst = 0.0
+    for i, g in zip(pick, ref):
+        worst = max(worst, relerr(ulog[i], g["u"]), relerr(zlog[i], g["z"]))
+        assert relerr(ulog[i], g["u"]) < RTOL and relerr(zlog[i], g["z"]) < RTOL, i
+        assert np.array_equal(slog[i, :, 0].astype(int), g["status"]), i
+        assert np.array_equal(slog[i, :, 1].astype(int), g["sqp_iter"]), i
+        assert np.array_equal(slog[i, :, 2].astype(int), g["qp_iter"]), (i, slog[i, :, 2].astype(int) - g["qp_iter"])
+        assert relerr(slog[i, :, 3], g["cost"]) < RTOL, i
+    print(f"bench window, {len(pick)} of {B} instances x {ns} steps: worst relative deviation {worst:.2e}")
+
+
 @pytest.mark.parametrize("N,N2,solver", [(40, 20, "SQP_RTI"), (40, 8, "SQP"), (40, 4, "SQP_RTI"), (100, 10, "SQP_RTI"), (100, 50, "SQP")])
 def test_partial_condensing_cond_n(oracle, N, N2, solver):
     """qp_solver_cond_N in {N/2, N/5, N/10} through the C ABI option 'qp_cond_N': 16 instances with a

@@ -71,3 +71,28 @@ def test_field_layouts_match_public_header():
         for key, v in table.items():
             assert vals[f"{prefix}_{key}"] == v, (prefix, key)
     assert pm.pack_params(3, 0.01).shape == (3, vals["RP_COUNT"])
+
+
+def test_solve_static_argument_checks_need_no_gpu(built):
+    """rmpc_solve_static validates before it touches the device: null buffers and batches beyond the fixed scratch array are
+    RMPC_EINVAL with the numbers in the message; a valid request without a CUDA device is RMPC_ENODEV (no host fallback)."""
+    import torch
+
+    import robotic_mpc_b200.engine as eng
+
+    lib = eng.load_library()
+    d = eng.RmpcDims()
+    d.B, d.N, d.solver_type, d.max_iter, d.qp_iter_max = 4, 10, 1, 100, 50
+    one = C.c_void_p(8)  # never dereferenced on these paths
+    assert lib.rmpc_solve_static(C.byref(d), 0, None, one, one, None, None) == eng.RMPC_EINVAL
+    assert lib.rmpc_solve_static(None, 0, one, one, one, None, None) == eng.RMPC_EINVAL
+    d.B, d.N = 99, 100  # 98 instances fit at N = 100
+    assert lib.rmpc_solve_static(C.byref(d), 0, one, one, one, None, None) == eng.RMPC_EINVAL
+    msg = lib.rmpc_last_error(None).decode()
+    assert "at most 98 instances" in msg and str(64 << 20) in msg, msg
+    d.B, d.N, d.solver_type = 4, 10, 5
+    assert lib.rmpc_solve_static(C.byref(d), 0, one, one, one, None, None) == eng.RMPC_EINVAL
+    if not torch.cuda.is_available():
+        d.solver_type = 1
+        assert lib.rmpc_solve_static(C.byref(d), 0, one, one, one, None, None) == eng.RMPC_ENODEV
+        assert b"no usable CUDA device" in lib.rmpc_last_error(None)

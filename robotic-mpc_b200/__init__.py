@@ -4,7 +4,7 @@ The directory name contains a hyphen (it is the repository's package name); impo
 ``robotic_mpc_b200`` symlink at the repository root or with ``importlib.import_module("robotic-mpc_b200")``.
 """
 from .params import RK, RL, RP, RS, pack_params  # noqa: F401
-from .engine import SQP, SQP_RTI, Engine, RmpcError, load_library  # noqa: F401
+from .engine import SQP, SQP_RTI, Engine, RmpcError, load_library, solve_static  # noqa: F401
 from .surface import Surface  # noqa: F401,E402
 from .prediction_model import SixDofRobot, UrdfLoader  # noqa: F401,E402
 from .simulation_model import Robot  # noqa: F401,E402

@@ -84,6 +84,43 @@ class RmpcError(RuntimeError):
 RMPC_EINVAL, RMPC_ENODEV, RMPC_ENOMEM, RMPC_ECUDA = -1, -2, -3, -4
 
 
+def solve_static(par, x0, N, solver_type="SQP_RTI", dt=0.01, u0=None, stats=None, max_iter=100, qp_iter_max=50, tol=1e-6,
+                 qp_tol=1e-8):
+    """``rmpc_solve_static``: one cold-started solve of every instance with NO device allocation inside the library -- for
+    hosts that must not call cudaMalloc where the solver runs (a hard-deadline control thread; a process whose device memory
+    belongs to another pool).  ``par`` [B, RP_COUNT] and ``x0`` [B, 12] are CUDA float64 tensors the caller already holds;
+    ``u0`` [B, 6] and ``stats`` [B, RL_COUNT] are filled in place when given (pass them to keep this wrapper allocation-free
+    too: without them torch allocates the outputs from its own pool).  Runs on torch's current stream of ``par``'s device and
+    returns ``(u0, stats)`` without synchronising.  B is limited by the library's fixed scratch array (98 instances at
+    N = 100, 454 at N = 20; ``RmpcError`` with code RMPC_EINVAL beyond); calls share that array and must not overlap on the
+    GPU.  The first call on a device does the one-time set-up: make it during start-up."""
+    import torch
+
+    lib = load_library()
+    for t, n in ((par, RP["COUNT"]), (x0, 12)):
+        if not (torch.is_tensor(t) and t.is_cuda and t.dtype == torch.float64 and t.is_contiguous() and t.dim() == 2
+                and t.shape[1] == n and t.shape[0] == par.shape[0]):
+            raise ValueError(f"solve_static needs contiguous CUDA float64 tensors par [B, {RP['COUNT']}] and x0 [B, 12]")
+    B, dev = int(par.shape[0]), par.device
+    if u0 is None:
+        u0 = torch.empty(B, 6, dtype=torch.float64, device=dev)
+    if stats is None:
+        stats = torch.empty(B, RL["COUNT"], dtype=torch.float64, device=dev)
+    for t, n in ((u0, 6), (stats, RL["COUNT"])):
+        if not (t.is_cuda and t.device == dev and t.dtype == torch.float64 and t.is_contiguous() and tuple(t.shape) == (B, n)):
+            raise ValueError(f"output buffers must be contiguous CUDA float64 tensors [B, {n}] on {dev}")
+    d = RmpcDims()
+    d.B, d.N, d.solver_type, d.max_iter, d.qp_iter_max = B, int(N), _SOLVER_TYPES[solver_type], int(max_iter), int(qp_iter_max)
+    d.tol[:] = [float(tol)] * 4
+    d.qp_tol, d.dt, d.plant_dt = float(qp_tol), float(dt), float(dt)
+    rc = lib.rmpc_solve_static(C.byref(d), dev.index or 0, C.c_void_p(par.data_ptr()), C.c_void_p(x0.data_ptr()),
+                               C.c_void_p(u0.data_ptr()), C.c_void_p(stats.data_ptr()),
+                               C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    if rc != 0:
+        raise RmpcError(f"rmpc_solve_static failed ({rc}): {lib.rmpc_last_error(None).decode()}", rc)
+    return u0, stats
+
+
 class Engine:
     """A batch of B independent UR10 surface-tracking MPC instances resident on one GPU.
 

@@ -119,3 +119,38 @@ def test_solve_static_without_step_record_and_over_the_limit(built, oracle):
     assert lib.rmpc_solve_static(C.byref(d), 0, par.data_ptr(), x0.data_ptr(), u.data_ptr(), None, None) == 0
     torch.cuda.synchronize()
     assert torch.cuda.mem_get_info()[0] >= free_before  # the calls took no device memory
+
+
+def test_python_wrapper_solve_static(built, oracle):
+    """robotic_mpc_b200.solve_static, the Python face of the same entry point: caller-owned output tensors, torch's current
+    stream, the same numbers as an Engine driven the usual way; the size limit surfaces as RmpcError."""
+    import torch
+
+    import robotic_mpc_b200 as rm
+
+    B, N = 7, 16
+    surf, z0 = _inputs(oracle, B, 404)
+    par = torch.as_tensor(rm.pack_params(B, 0.01, surf=surf), dtype=torch.float64).cuda().contiguous()
+    x0 = torch.as_tensor(z0, dtype=torch.float64).cuda().contiguous()
+    u0 = torch.empty(B, 6, dtype=torch.float64, device="cuda")
+    st = torch.empty(B, rm.RL["COUNT"], dtype=torch.float64, device="cuda")
+    e = rm.Engine(B, N, "SQP", dt=0.01, nlog=1)
+    e.set_params(par)
+    e.set_state(x0)
+    e.reset()
+    e.solve()
+    want_u, want_st = e.get("u", 0).cpu().numpy(), e.get("stats").cpu().numpy()
+    e.close()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        got_u, got_st = rm.solve_static(par, x0, N, "SQP", u0=u0, stats=st)
+    side.synchronize()
+    assert got_u is u0 and got_st is st
+    assert np.abs(u0.cpu().numpy() - want_u).max() <= RTOL * np.abs(want_u).max()
+    assert np.array_equal(st.cpu().numpy()[:, :3], want_st[:, :3])  # status, SQP and QP iteration counts
+    with pytest.raises(rm.RmpcError) as ei:
+        rm.solve_static(par.repeat(100, 1), x0.repeat(100, 1), 100)  # 700 instances at N = 100
+    assert ei.value.code == -1
+    with pytest.raises(ValueError):
+        rm.solve_static(par.cpu(), x0, N)

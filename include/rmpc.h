@@ -84,7 +84,9 @@ int rmpc_set_chain(rmpc_handle *h, const double *xyzR, const int *axis);
  *                    the prediction phi(x_0, u_0) of the current iterate -- with one QP on the last linearisation (A),
  *                    as_rti_iter zero-order (B) / exact-gradient (C) / full SQP (D) iterations, and re-linearises;
  *                    rmpc_solve_rti_phase(h, 2) is the usual feedback.  Like acados, the combined rmpc_solve is refused
- *                    while a level is set; rmpc_closed_loop runs preparation + feedback per step.  Level C has no
+ *                    while a level is set; rmpc_closed_loop runs preparation + feedback per step and, when the feedback
+ *                    succeeds but the advanced step failed (1 NaN merit, 4 QP failure), reports that status in the step
+ *                    record and counts it in RS_NFAIL.  Level C has no
  *                    counterpart to check against: the reference aborts in it for a NONLINEAR_LS cost
  *                    ("ocp_nlp_cost_nls_compute_gradient not implemented").
  *   "as_rti_iter" n >= 0  iterations of the levels B, C, D (default 1)
